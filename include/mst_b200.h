@@ -1,0 +1,187 @@
+/*
+ * mst_b200.h — C ABI of the B200-native hot path of marcinp7/music-style-transfer.
+ *
+ * Plain C: fixed-width scalars, raw pointers and sizes only.  No torch / C++ types cross
+ * this boundary.  The reference is pure Python and has no FFI of its own,
+ * so each entry point names the reference function(s) it replaces (file:line relative to the
+ * reference tree) and INTEGRATION.md shows the ctypes binding a maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative MST_E_* code on an API error
+ *     (mst_last_error() gives the text); per-song problems never fail the call: they are
+ *     reported in MstSongInfo.status (mirrors the reference raising MidiFormatError per file,
+ *     style/data.py:47);
+ *   - "d_" pointers are device pointers, "h_" pointers are host pointers;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); device entry points
+ *     are asynchronous on that stream, host ("_host") entry points return after completion;
+ *   - the caller owns every buffer; scratch sizes come from the *_workspace_bytes calls.
+ */
+#ifndef MST_B200_H
+#define MST_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MST_ABI_VERSION 1
+
+/* ---------------------------------------------------------------- errors */
+#define MST_OK                0
+#define MST_E_INVALID        -1   /* bad argument */
+#define MST_E_CUDA           -2   /* CUDA runtime error (text in mst_last_error) */
+#define MST_E_CAPACITY       -3   /* a caller-provided buffer is too small */
+#define MST_E_NO_DEVICE      -4   /* no CUDA device: the product path has no CPU fallback */
+
+/* per-song status (MstSongInfo.status) */
+#define MST_SONG_OK                   0
+#define MST_SONG_TIME_SIG_CHANGED     1  /* "Time signature changed"  midi_conversion.py:153 */
+#define MST_SONG_KEY_SIG_CHANGED      2  /* "Key signature changed"   midi_conversion.py:157 */
+#define MST_SONG_UNKNOWN_MESSAGE      3  /* "Unknown message type"    midi_conversion.py:165,191 */
+#define MST_SONG_NO_NOTES             4  /* no note_on with velocity>0: min() of empty list, :125 */
+#define MST_SONG_NO_PITCHED           5  /* filtered song has no pitched channel, data.py:57 */
+#define MST_SONG_BAD_TIMING           6  /* ticks_per_beat<=0 or numerator==0 (reference crashes) */
+#define MST_SONG_TOO_MANY_INSTRUMENTS 7  /* >MST_MAX_LISTS_PER_CHANNEL programs with notes on one channel */
+#define MST_SONG_ARENA_FULL           8  /* grids did not fit the caller's arena; info is valid */
+#define MST_SONG_LOAD_FAILED          9  /* SMF parse error: load_midi_from_file returns None, midi.py:104-108 */
+
+/* ---------------------------------------------------------------- events */
+/* One MIDI event, 16 bytes.  Replaces mido message objects as consumed by merge_tracks /
+ * split_channels (style/midi_conversion.py:37-66).  A song's events are laid out track after
+ * track, each track in file order, `tick` already accumulated per track (absolute ticks);
+ * events beyond MST_MAX_TICK are dropped by the encoder exactly like :52,59. */
+typedef struct MstEvent {
+    uint32_t tick;     /* absolute tick inside its track */
+    uint32_t aux;      /* set_tempo: microseconds per beat; key_signature: (sf+7)*2+minor */
+    uint8_t  kind;     /* MST_EV_* */
+    uint8_t  channel;  /* channel voice messages: 0..15; channel_prefix: its data byte */
+    uint8_t  d1;       /* note | control | program | time_signature numerator */
+    uint8_t  d2;       /* velocity | value | time_signature log2(denominator) */
+    uint16_t track;    /* informative */
+    uint16_t reserved;
+} MstEvent;
+
+#define MST_MAX_TICK 10000000u
+
+#define MST_EV_NOTE_OFF        0   /* 0x8n */
+#define MST_EV_NOTE_ON         1   /* 0x9n */
+#define MST_EV_POLYTOUCH       2   /* 0xAn */
+#define MST_EV_CONTROL_CHANGE  3   /* 0xBn */
+#define MST_EV_PROGRAM_CHANGE  4   /* 0xCn */
+#define MST_EV_AFTERTOUCH      5   /* 0xDn */
+#define MST_EV_PITCHWHEEL      6   /* 0xEn */
+#define MST_EV_SET_TEMPO      16
+#define MST_EV_TIME_SIGNATURE 17
+#define MST_EV_KEY_SIGNATURE  18
+#define MST_EV_CHANNEL_PREFIX 19   /* meta 0x20: carries a .channel attribute in mido, so the
+                                      reference routes it into the channel lists (:61) */
+#define MST_EV_META_IGNORED   20   /* any type in messages_to_ignore (:80-98) without channel */
+#define MST_EV_UNKNOWN        21   /* type outside known_messages (:109): rejects the song */
+
+/* One song inside a batch. */
+typedef struct MstSongIn {
+    uint64_t event_offset;   /* index of the song's first event in the batch event array */
+    uint32_t n_events;
+    int32_t  ticks_per_beat; /* SMF header division (mid.ticks_per_beat) */
+} MstSongIn;
+
+/* Channel filter of iter_inputs (style/data.py:53-58) / get_model_input
+ * (style/style_transfer.py:62). */
+typedef struct MstFilter {
+    int32_t apply;              /* 0: keep every (channel, instrument) list */
+    int32_t min_n_messages;     /* keep lists with at least this many note messages */
+    uint8_t included[128];      /* included[p] != 0: program p passes; percussion (-1) always */
+    int32_t crop_channel_bars;  /* >0: write only the first crop_channel_bars // C bars
+                                   (prepare_input, data.py:133-137 with train-model.py:101) */
+    int32_t reserved;
+} MstFilter;
+
+#define MST_MAX_PITCHED   120   /* programs 0..119 are pitched (midi.py:96-101) */
+#define MST_MAX_UNPITCHED 12    /* -1 (channel 9) and sound effects 120..127 */
+#define MST_MAX_LISTS_PER_CHANNEL 16
+
+#define MST_N_FRACTIONS       10  /* sorted {i/8} U {i/3}, midi_conversion.py:358-362 */
+#define MST_N_PITCHED_ROWS    56  /* 8 octaves x 7 degrees, :366 */
+#define MST_N_PITCHED_FEATS   5   /* duration, velocity, flat, natural, sharp (:502-510) */
+#define MST_N_UNPITCHED_ROWS  47  /* percussion keys 35..81, :367 */
+#define MST_N_UNPITCHED_FEATS 2
+#define MST_PITCHED_BEAT_FLOATS   (MST_N_FRACTIONS * MST_N_PITCHED_ROWS * MST_N_PITCHED_FEATS)     /* 2800 */
+#define MST_UNPITCHED_BEAT_FLOATS (MST_N_FRACTIONS * MST_N_UNPITCHED_ROWS * MST_N_UNPITCHED_FEATS) /* 940 */
+
+/* Song-level result: the reference's `info` dict (get_midi_info, :117-179) + info['scale']
+ * (style/scales.py:160-221) + the shapes/instrument lists get_input returns (data.py:66-100). */
+typedef struct MstSongInfo {
+    int32_t status;            /* MST_SONG_* */
+    int32_t ticks_per_beat;
+    int32_t numerator;         /* info['time_signature'] */
+    int32_t denominator_log2;
+    int32_t key_signature;     /* -1 = None, else (sf+7)*2+minor */
+    int32_t duration;          /* max tick over channel messages */
+    int32_t ticks_per_bar;
+    int32_t n_bars;            /* ceil(duration / ticks_per_bar); grids hold n_bars+1 bars */
+    int32_t n_beats;
+    int32_t tempo;
+    int32_t bpm;
+    int32_t tonic;             /* 0..11 = C..B */
+    int32_t mode;              /* 0 major (Ionian), 1 minor (Aeolian) */
+    int32_t n_pitched;         /* C */
+    int32_t n_unpitched;       /* U */
+    int32_t n_bars_out;        /* bars actually written per channel (n_bars+1, or the crop) */
+    double  scale_coverage;
+    double  scale_loose_coverage;
+    double  scale_cross_entropy;
+    double  scale_loss;
+    double  scale_margin;      /* runner-up loss - best loss (near-tie audit) */
+    double  keys_dist[12];
+    uint64_t pitched_offset;   /* float offset of (C, n_bars_out, n_beats, 10, 56, 5) in the arena */
+    uint64_t unpitched_offset; /* float offset of (U, n_bars_out, n_beats, 10, 47, 2) */
+    int32_t n_notes;           /* notes scattered (after dropping out-of-range rows) */
+    int32_t n_lists;           /* (channel, instrument) lists before filtering (read_midi channels) */
+    int16_t pitched_instruments[MST_MAX_PITCHED];
+    int16_t unpitched_instruments[MST_MAX_UNPITCHED];
+} MstSongInfo;
+
+/* ---------------------------------------------------------------- library */
+int         mst_abi_version(void);
+const char *mst_last_error(void);
+int         mst_device_count(void);   /* 0 when no GPU is visible */
+
+/* ---------------------------------------------------------------- SMF I/O (host, C++) */
+/* Replaces mido.MidiFile(path) as used by load_midi_from_file (style/midi.py:104-108):
+ * parses Standard MIDI File bytes into MstEvent records (absolute ticks, track-major order).
+ * Returns the number of events (>=0) or MST_E_CAPACITY (needed count in *n_needed) or
+ * -(100+reason) for the load failures on which the reference returns None. */
+int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent *h_events, size_t capacity,
+                      int32_t *ticks_per_beat, int32_t *n_tracks, size_t *n_needed);
+
+/* ---------------------------------------------------------------- encode (MIDI -> grids) */
+/* Replaces read_midi (midi_conversion.py:216-232), iter_inputs' filter (data.py:53-58),
+ * get_input (data.py:66-100) incl. ChannelConverter.channel2nchannel / nchannel2vchannel
+ * (:371-456,490-516), get_keys_dist (:340) + get_scale (scales.py:214), and prepare_input's
+ * crop + f32 cast (data.py:130-143) for a whole batch of songs. */
+size_t mst_encode_workspace_bytes(uint64_t n_events_total, uint32_t n_songs);
+
+int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_events_total,
+                            const MstSongIn *d_songs, uint32_t n_songs,
+                            const MstFilter *h_filter,
+                            MstSongInfo *d_info,
+                            float *d_arena, uint64_t arena_floats,
+                            void *d_workspace, size_t workspace_bytes,
+                            void *stream);
+
+/* Same through host buffers: H2D of events/songs, kernels, D2H of the song infos (and of the
+ * grids when h_arena != NULL; otherwise they stay in d_arena for the device consumer). */
+int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events_total,
+                          const MstSongIn *h_songs, uint32_t n_songs,
+                          const MstFilter *h_filter,
+                          MstSongInfo *h_info,
+                          float *d_arena, uint64_t arena_floats, float *h_arena,
+                          void *d_workspace, size_t workspace_bytes,
+                          void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MST_B200_H */
