@@ -161,7 +161,7 @@ int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent *h_events, 
  * get_input (data.py:66-100) incl. ChannelConverter.channel2nchannel / nchannel2vchannel
  * (:371-456,490-516), get_keys_dist (:340) + get_scale (scales.py:214), and prepare_input's
  * crop + f32 cast (data.py:130-143) for a whole batch of songs. */
-size_t mst_encode_workspace_bytes(uint64_t n_events_total, uint32_t n_songs);
+size_t mst_encode_workspace_bytes(uint64_t n_events_total, uint32_t n_songs, uint64_t arena_floats);
 
 int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_events_total,
                             const MstSongIn *d_songs, uint32_t n_songs,
@@ -172,7 +172,10 @@ int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_events_total,
                             void *stream);
 
 /* Same through host buffers: H2D of events/songs, kernels, D2H of the song infos (and of the
- * grids when h_arena != NULL; otherwise they stay in d_arena for the device consumer). */
+ * grids when h_arena != NULL; otherwise they stay in d_arena for the device consumer).
+ * The workspace additionally stages the events/songs/infos: size it with the _host_ query. */
+size_t mst_encode_host_workspace_bytes(uint64_t n_events_total, uint32_t n_songs, uint64_t arena_floats);
+
 int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events_total,
                           const MstSongIn *h_songs, uint32_t n_songs,
                           const MstFilter *h_filter,

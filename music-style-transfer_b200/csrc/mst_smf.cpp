@@ -1,0 +1,193 @@
+// mst_smf.cpp — Standard MIDI File bytes <-> MstEvent records (host side of libmst_b200.so).
+//
+// Replaces mido.MidiFile(path) as used by load_midi_from_file (style/midi.py:104-108) and, for the
+// decode side, create_midi's track serialisation + mid.save (style/midi.py:125-168,
+// style/style_transfer.py:98).  mido is an un-vendored, un-pinned dependency of the reference
+// (requirements.txt:2), so this follows mido >= 1.3's published parsing rules:
+//   - running status; meta events do not touch it; every other status byte (sysex included) sets it
+//   - data bytes > 127, undefined status bytes, a missing MThd/MTrk tag, a truncated file and an
+//     undecodable key signature all make the load fail (the reference then gets None)
+//   - events keep their delta times per track; here they are accumulated to absolute ticks
+// Only what the encoder consumes is emitted: channel voice messages, set_tempo, time_signature,
+// key_signature, channel_prefix (it carries a `.channel`, midi_conversion.py:61) and one
+// MST_EV_UNKNOWN per message whose type the reference does not know (:109,164).
+#include <stdint.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../../include/mst_b200.h"
+
+namespace {
+
+enum LoadFail {
+    kFailEof = 1,         // EOFError
+    kFailNoHeader = 2,    // IOError: MThd not found
+    kFailNoTrack = 3,     // IOError: no MTrk header at start of track
+    kFailRunning = 4,     // IOError: running status without last_status
+    kFailDataByte = 5,    // IOError: data byte must be in range 0..127
+    kFailStatus = 6,      // IOError: undefined status byte
+    kFailKeySig = 7,      // KeySignatureError
+    kFailMeta = 8,        // truncated meta payload (mido raises IndexError; treated as a load failure)
+    kFailSysex = 9,       // ValueError: sysex data byte out of range
+};
+
+struct Reader {
+    const uint8_t *p;
+    size_t n, pos;
+    bool eof;
+    int byte() {
+        if (pos >= n) { eof = true; return 0; }
+        return p[pos++];
+    }
+    uint64_t varint() {
+        uint64_t v = 0;
+        while (true) {
+            int b = byte();
+            if (eof) return 0;
+            v = (v << 7) | (uint64_t)(b & 0x7F);
+            if (b < 0x80) return v;
+        }
+    }
+    bool skip(size_t k) {
+        if (pos + k > n) { eof = true; pos = n; return false; }
+        pos += k;
+        return true;
+    }
+};
+
+inline uint32_t be32(const uint8_t *b) { return ((uint32_t)b[0] << 24) | ((uint32_t)b[1] << 16) | ((uint32_t)b[2] << 8) | b[3]; }
+
+}  // namespace
+
+extern "C" int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent *out, size_t capacity,
+                                 int32_t *ticks_per_beat, int32_t *n_tracks_out, size_t *n_needed) {
+    Reader r{bytes, n_bytes, 0, false};
+    if (n_needed) *n_needed = 0;
+    if (n_bytes < 8) return -(100 + kFailEof);
+    if (memcmp(bytes, "MThd", 4) != 0) return -(100 + kFailNoHeader);
+    const uint32_t hsize = be32(bytes + 4);
+    r.pos = 8;
+    const size_t avail = n_bytes - 8 < hsize ? n_bytes - 8 : hsize;
+    if (avail < 6) return -(100 + kFailEof);
+    const int16_t n_tracks = (int16_t)((bytes[10] << 8) | bytes[11]);
+    const int16_t division = (int16_t)((bytes[12] << 8) | bytes[13]);
+    r.pos = 8 + avail;
+    if (ticks_per_beat) *ticks_per_beat = division;
+    if (n_tracks_out) *n_tracks_out = n_tracks;
+
+    size_t count = 0;
+    auto emit = [&](uint64_t tick, uint8_t kind, uint8_t ch, uint8_t d1, uint8_t d2, uint32_t aux, int track) {
+        if (tick > MST_MAX_TICK) return;   // split_channels drops these (midi_conversion.py:52,59)
+        if (out && count < capacity) {
+            MstEvent e;
+            e.tick = (uint32_t)tick; e.aux = aux; e.kind = kind; e.channel = ch; e.d1 = d1; e.d2 = d2;
+            e.track = (uint16_t)(track > 65535 ? 65535 : track); e.reserved = 0;
+            out[count] = e;
+        }
+        count++;
+    };
+
+    for (int t = 0; t < n_tracks; t++) {
+        if (r.pos + 8 > r.n) return -(100 + kFailEof);
+        if (memcmp(r.p + r.pos, "MTrk", 4) != 0) return -(100 + kFailNoTrack);
+        const uint32_t size = be32(r.p + r.pos + 4);
+        r.pos += 8;
+        const size_t start = r.pos;
+        int last_status = -1;
+        uint64_t tick = 0;
+        while (r.pos - start != size) {
+            const uint64_t delta = r.varint();
+            if (r.eof) return -(100 + kFailEof);
+            tick += delta;
+            int status = r.byte();
+            if (r.eof) return -(100 + kFailEof);
+            int peek = -1;
+            if (status < 0x80) {
+                if (last_status < 0) return -(100 + kFailRunning);
+                peek = status;
+                status = last_status;
+            } else if (status != 0xFF) {
+                last_status = status;
+            }
+            if (status == 0xFF) {
+                const int type = r.byte();
+                const uint64_t len = r.varint();
+                if (r.eof) return -(100 + kFailEof);
+                const size_t dpos = r.pos;
+                if (!r.skip((size_t)len)) return -(100 + kFailEof);
+                const uint8_t *d = r.p + dpos;
+                switch (type) {
+                    case 0x51:
+                        if (len < 3) return -(100 + kFailMeta);
+                        emit(tick, MST_EV_SET_TEMPO, 0, 0, 0, ((uint32_t)d[0] << 16) | ((uint32_t)d[1] << 8) | d[2], t);
+                        break;
+                    case 0x58:
+                        if (len < 4) return -(100 + kFailMeta);
+                        emit(tick, MST_EV_TIME_SIGNATURE, 0, d[0], d[1], 0, t);
+                        break;
+                    case 0x59: {
+                        if (len < 2) return -(100 + kFailMeta);
+                        const int sf = (int8_t)d[0], mi = d[1];
+                        if (sf < -7 || sf > 7 || mi > 1) return -(100 + kFailKeySig);
+                        emit(tick, MST_EV_KEY_SIGNATURE, 0, 0, 0, (uint32_t)((sf + 7) * 2 + mi), t);
+                        break;
+                    }
+                    case 0x20:
+                        if (len < 1) return -(100 + kFailMeta);
+                        emit(tick, MST_EV_CHANNEL_PREFIX, d[0], 0, 0, 0, t);
+                        break;
+                    case 0x09:   // device_name: a meta type outside known_messages
+                        emit(tick, MST_EV_UNKNOWN, 0, 0, 0, 0x0900u, t);
+                        break;
+                    default:     // messages_to_ignore (midi_conversion.py:80-98), incl. unknown_meta
+                        break;
+                }
+            } else if (status == 0xF0 || status == 0xF7) {
+                const uint64_t len = r.varint();
+                if (r.eof) return -(100 + kFailEof);
+                const size_t dpos = r.pos;
+                if (!r.skip((size_t)len)) return -(100 + kFailEof);
+                size_t a = dpos, b = dpos + (size_t)len;
+                if (b > a && r.p[a] == 0xF0) a++;
+                if (b > a && r.p[b - 1] == 0xF7) b--;
+                for (size_t i = a; i < b; i++) if (r.p[i] > 127) return -(100 + kFailSysex);
+            } else if (status < 0xF0) {
+                const int hi = status & 0xF0;
+                const int need = (hi == 0xC0 || hi == 0xD0) ? 1 : 2;
+                int data[2] = {0, 0};
+                int have = 0;
+                if (peek >= 0) data[have++] = peek;
+                while (have < need) {
+                    data[have++] = r.byte();
+                    if (r.eof) return -(100 + kFailEof);
+                }
+                for (int i = 0; i < need; i++) if (data[i] > 127) return -(100 + kFailDataByte);
+                const uint8_t kind = (uint8_t)((hi >> 4) - 8);
+                // polytouch / aftertouch / pitchwheel only matter through their tick and channel
+                const bool payload = kind == MST_EV_NOTE_OFF || kind == MST_EV_NOTE_ON ||
+                                     kind == MST_EV_CONTROL_CHANGE || kind == MST_EV_PROGRAM_CHANGE;
+                emit(tick, kind, (uint8_t)(status & 0x0F), payload ? (uint8_t)data[0] : 0,
+                     payload ? (uint8_t)data[1] : 0, 0, t);
+            } else {
+                int ndata;
+                switch (status) {
+                    case 0xF1: case 0xF3: ndata = 1; break;
+                    case 0xF2: ndata = 2; break;
+                    case 0xF6: case 0xF8: case 0xFA: case 0xFB: case 0xFC: case 0xFE: ndata = 0; break;
+                    default: return -(100 + kFailStatus);
+                }
+                if (peek >= 0) return -(100 + kFailStatus);
+                for (int i = 0; i < ndata; i++) {
+                    const int b = r.byte();
+                    if (r.eof) return -(100 + kFailEof);
+                    if (b > 127) return -(100 + kFailDataByte);
+                }
+                emit(tick, MST_EV_UNKNOWN, 0, 0, 0, (uint32_t)status, t);
+            }
+        }
+    }
+    if (n_needed) *n_needed = count;
+    if (out && count > capacity) return MST_E_CAPACITY;
+    return (int64_t)count;
+}

@@ -1,0 +1,183 @@
+"""ctypes binding of libmst_b200.so (C ABI: include/mst_b200.h).
+
+torch is used only for device memory and streams.  There is no CPU fallback: every compute entry
+point raises when the library or a CUDA device is missing.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import abi
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG, 'libmst_b200.so')
+
+_lib = None
+
+# every symbol include/mst_b200.h declares (tests check that the library exports them all)
+EXPORTS = [
+    'mst_abi_version', 'mst_last_error', 'mst_device_count',
+    'mst_smf_parse',
+    'mst_encode_workspace_bytes', 'mst_encode_batch_device',
+    'mst_encode_host_workspace_bytes', 'mst_encode_batch_host',
+]
+
+
+class MstError(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MstError(f'{LIB_PATH} is missing: build it with `python music-style-transfer_b200/build.py` '
+                       '(there is no CPU fallback)')
+    L = ctypes.CDLL(LIB_PATH)
+    L.mst_abi_version.restype = ctypes.c_int
+    L.mst_last_error.restype = ctypes.c_char_p
+    L.mst_device_count.restype = ctypes.c_int
+    L.mst_smf_parse.restype = ctypes.c_int64
+    L.mst_smf_parse.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
+                                ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
+                                ctypes.POINTER(ctypes.c_size_t)]
+    for name in ('mst_encode_workspace_bytes', 'mst_encode_host_workspace_bytes'):
+        f = getattr(L, name)
+        f.restype = ctypes.c_size_t
+        f.argtypes = [ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint64]
+    L.mst_encode_batch_device.restype = ctypes.c_int
+    L.mst_encode_batch_device.argtypes = [
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    L.mst_encode_batch_host.restype = ctypes.c_int
+    L.mst_encode_batch_host.argtypes = [
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    if L.mst_abi_version() != abi.MST_ABI_VERSION:
+        raise MstError('libmst_b200.so ABI version mismatch: rebuild')
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise MstError(f'libmst_b200 error {rc}: {load().mst_last_error().decode()}')
+
+
+def require_gpu():
+    L = load()
+    if L.mst_device_count() == 0:
+        raise MstError('no CUDA device visible: the B200 path has no CPU fallback')
+    return L
+
+
+def _np_ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+# ---------------------------------------------------------------------------------- SMF parsing
+def smf_parse(data):
+    """bytes -> (events ndarray[EVENT_DTYPE], ticks_per_beat) or None when the load fails the way
+    mido.MidiFile would (style/midi.py:104-108)."""
+    L = load()
+    buf = np.frombuffer(data, dtype=np.uint8)
+    tpb, ntr, need = ctypes.c_int32(0), ctypes.c_int32(0), ctypes.c_size_t(0)
+    # an event needs at least 2 bytes (delta + running-status data byte): size once, no second pass
+    cap = max(1, len(buf) // 2)
+    out = np.empty(cap, dtype=abi.EVENT_DTYPE)
+    n = L.mst_smf_parse(_np_ptr(buf), len(buf), _np_ptr(out), cap, ctypes.byref(tpb), ctypes.byref(ntr),
+                        ctypes.byref(need))
+    if n < 0:
+        return None
+    return out[:n].copy(), int(tpb.value)
+
+
+# ---------------------------------------------------------------------------------- batches
+def make_songs(event_arrays, tpbs):
+    """Concatenate per-song event arrays into (events, songs[SONG_IN_DTYPE])."""
+    songs = np.zeros(len(event_arrays), dtype=abi.SONG_IN_DTYPE)
+    off = 0
+    for i, (e, t) in enumerate(zip(event_arrays, tpbs)):
+        songs[i]['event_offset'] = off
+        songs[i]['n_events'] = len(e)
+        songs[i]['ticks_per_beat'] = int(t)
+        off += len(e)
+    events = np.concatenate(event_arrays) if event_arrays else np.zeros(0, abi.EVENT_DTYPE)
+    return np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE), songs
+
+
+def grid_floats(info):
+    """Floats one encoded song occupies in the arena (pitched then unpitched)."""
+    per_bar = int(info['n_beats']) * (int(info['n_pitched']) * abi.PITCHED_BEAT_FLOATS
+                                       + int(info['n_unpitched']) * abi.UNPITCHED_BEAT_FLOATS)
+    return int(info['n_bars_out']) * per_bar
+
+
+class DeviceBatch:
+    """A batch of songs resident in HBM: events + song table (+ reusable workspace / info)."""
+
+    def __init__(self, events, songs, device=None):
+        import torch
+        require_gpu()
+        self.torch = torch
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        self.n_events = int(len(events))
+        self.n_songs = int(len(songs))
+        ev_bytes = torch.from_numpy(events.view(np.uint8).reshape(-1)) if self.n_events else torch.zeros(16, dtype=torch.uint8)
+        self.d_events = ev_bytes.to(self.device)
+        self.d_songs = torch.from_numpy(songs.view(np.uint8).reshape(-1)).to(self.device)
+        self.d_info = torch.empty(max(1, self.n_songs) * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8, device=self.device)
+        self._ws = None
+        self._ws_arena = -1
+
+    def workspace(self, arena_floats):
+        L = load()
+        need = L.mst_encode_workspace_bytes(self.n_events, self.n_songs, arena_floats)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = self.torch.empty(need, dtype=self.torch.uint8, device=self.device)
+        return self._ws
+
+    def encode(self, filt, arena, stream=None):
+        """Launch the encode pipeline (asynchronous).  arena: float32 CUDA tensor or None (plan only)."""
+        L = load()
+        torch = self.torch
+        arena_floats = 0 if arena is None else arena.numel()
+        ws = self.workspace(arena_floats)
+        s = torch.cuda.current_stream(self.device) if stream is None else stream
+        check(L.mst_encode_batch_device(
+            self.d_events.data_ptr(), self.n_events, self.d_songs.data_ptr(), self.n_songs,
+            _np_ptr(filt.reshape(1)) if filt is not None else None, self.d_info.data_ptr(),
+            arena.data_ptr() if arena is not None else None, arena_floats,
+            ws.data_ptr(), ws.numel(), s.cuda_stream))
+
+    def infos(self):
+        """Synchronising D2H read of the MstSongInfo records."""
+        raw = self.d_info.cpu().numpy()
+        return raw[:self.n_songs * abi.SONG_INFO_DTYPE.itemsize].view(abi.SONG_INFO_DTYPE).copy()
+
+
+def encode_songs(event_arrays, tpbs, filt=None, device=None):
+    """Plan + fill: returns (infos, arena float32 CUDA tensor).  Grids of song i live at
+    infos[i]['pitched_offset'] / ['unpitched_offset'] (float offsets into the arena)."""
+    import torch
+    events, songs = make_songs(event_arrays, tpbs)
+    batch = DeviceBatch(events, songs, device)
+    batch.encode(filt, None)
+    plan = batch.infos()
+    total = sum(grid_floats(r) for r in plan if r['status'] in (abi.SONG_OK, abi.SONG_ARENA_FULL))
+    arena = torch.empty(max(total, 1), dtype=torch.float32, device=batch.device)
+    batch.encode(filt, arena)
+    return batch.infos(), arena
+
+
+def song_grids(info, arena):
+    """Views (no copy) of one song's grids inside the arena: (pitched, unpitched or None)."""
+    C, U, B, nb = (int(info[k]) for k in ('n_pitched', 'n_unpitched', 'n_bars_out', 'n_beats'))
+    po, uo = int(info['pitched_offset']), int(info['unpitched_offset'])
+    pitched = arena[po:po + C * B * nb * abi.PITCHED_BEAT_FLOATS].view(C, B, nb, 10, 56, 5)
+    unpitched = None
+    if U:
+        unpitched = arena[uo:uo + U * B * nb * abi.UNPITCHED_BEAT_FLOATS].view(U, B, nb, 10, 47, 2)
+    return pitched, unpitched
