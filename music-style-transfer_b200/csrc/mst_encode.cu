@@ -374,7 +374,8 @@ k_info(const MstSongIn *__restrict__ songs, uint32_t n_songs, Workspace ws, MstF
 
         int first_on = INT_MAX, last_on = -1, duration = -1, too_many = 0;
         if (lane < 16) { first_on = chans[lane].first_on; last_on = chans[lane].last_on; too_many = chans[lane].error; }
-        if (lane < kClassEnd && seg[lane + 1] > seg[lane]) duration = (int)(keys[seg[lane + 1] - 1] & 0xFFFFFFu);
+        // duration = max tick over messages that carry a channel (:126): classes 0..15 and 17, not the globals
+        if (lane < kClassEnd && lane != kClassGlobal && seg[lane + 1] > seg[lane]) duration = (int)(keys[seg[lane + 1] - 1] & 0xFFFFFFu);
         first_on = warp_reduce_min(first_on);
         last_on = warp_reduce_max(last_on);
         duration = warp_reduce_max(duration);
@@ -860,6 +861,7 @@ k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
             } else {
                 if (nt.note_id < 35 || nt.note_id > 81) continue;       // :605-609
                 row = nt.note_id - 35;
+                acc = 7;                                                // no accidental features
             }
             int qtime, bar, beat;
             const int col = quantise(nt.time, tpb, tpbar, &qtime, &bar, &beat);
