@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native music-style-transfer hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[2]): bulk encode of a synthetic MIDI
+corpus — 16 tracks (15 pitched + drums), 128 bars, tpb 480, ~33 k events per file.  One "step" =
+one pass of the whole encode pipeline (libmst_b200.so, mst_encode_batch_device) over one batch of
+`--batch` songs whose events are already resident in HBM; batches cycle through a pool of distinct
+songs that is larger than L2, and every step rewrites a grid arena that is far larger than L2.
+
+Prints ONE JSON line (see the task contract): value = song-bars/s over all ranks, `roofline` for
+the dominant kernel (k_grid, HBM-bound), `e2e` through the host-buffer C-ABI entry point, and
+`cpu_baseline` (the C oracle port on the host cores, rank 0, N=1 only).
+`--impl reference` times the CPU implementation (oracle port, all host threads) on the same config.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, 'music-style-transfer_b200'))
+
+import numpy as np  # noqa: E402
+
+METRIC = 'piano-roll bars/sec encoded'
+UNIT = 'song-bars/s'
+KERNELS_PER_STEP = 9   # k_sort, k_walk<0>, k_info, k_offsets, k_walk<1>, k_pair, k_scale, k_cells, k_grid
+
+
+def workload_config(args):
+    return {
+        'workload': 'configs[2]: synthetic MIDI corpus bulk encode (16 tracks = 15 pitched + drums, 128 bars, '
+                    'tpb 480, 1/16 + triplet onsets, ~33k events/file)',
+        'songs_per_step': args.batch,
+        'distinct_songs_in_pool': args.pool,
+        'corpus_files_equivalent': args.batch * args.steps,
+        'l2_policy': 'inputs larger than L2: >=270 MB of events and a multi-GB grid arena per step',
+        'filter': 'iter_inputs filter: popular_instruments, min_n_messages=100',
+    }
+
+
+def measured_peak_hbm():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the GPU is under load."""
+    FIELDS = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+              'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+              'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.samples = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', f'--query-gpu={self.FIELDS}', '--format=csv,noheader,nounits', '-lms', '100',
+                 '-i', str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], [], set()
+        for t, line in self.samples:
+            if not (t0 <= t <= t1 + 0.2):
+                continue
+            parts = [p.strip() for p in line.split(',')]
+            try:
+                sm.append(float(parts[0]))
+                smax.append(float(parts[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'),
+                                 parts[3:7]):
+                if val == 'Active':
+                    reasons.add(name)
+        return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(smax) if smax else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def run_reference(args):
+    """CPU arm: the oracle port (oracle/mst_oracle.c, pthreads over all host cores).  The reference
+    itself is pure Python and cannot travel to the GPU box (its dependencies are not in the image);
+    the C port is a strictly faster restatement of the same algorithm."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import oracle_lib
+    from mst_native import abi, synth
+    cores = os.cpu_count() or 1
+    sample = max(cores * 2, 32)
+    events, songs = synth.synth_corpus(sample, seed=1234)
+    filt = abi.make_filter(synth.POPULAR, 100)
+    for _ in range(args.warmup):
+        oracle_lib.encode_batch(events, songs, filt, cores)
+    t0 = time.perf_counter()
+    bars = 0
+    for _ in range(args.steps):
+        infos, _ = oracle_lib.encode_batch(events, songs, filt, cores)
+        bars += int(infos['n_bars_out'][infos['status'] == 0].sum())
+    dt = time.perf_counter() - t0
+    value = bars / dt
+    cfg = workload_config(args)
+    print(json.dumps({
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64 quantise -> f32 grid',
+        'data': 'synthetic', 'config': cfg,
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': f'{sample} songs of the corpus per step, {args.steps} steps'},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--batch', type=int, default=512, help='songs per step per GPU')
+    ap.add_argument('--pool', type=int, default=1024, help='distinct songs generated per GPU')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
+    args.pool = max(args.pool, args.batch)
+    if args.impl == 'reference':
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from mst_native import abi, lib, synth
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: the B200 path has no CPU fallback')
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+    L = lib.require_gpu()
+
+    # ---- synthetic corpus shard of this rank, resident in HBM (events are NOT part of the timed copies)
+    n_batches = max(1, args.pool // args.batch)
+    filt = abi.make_filter(synth.POPULAR, 100)
+    batches, host_batches = [], []
+    for b in range(n_batches):
+        events, songs = synth.synth_corpus(args.batch, seed=1234 + 1000 * rank + b)
+        batches.append(lib.DeviceBatch(events, songs))
+        host_batches.append((events, songs))
+    plans = []
+    for batch in batches:
+        batch.encode(filt, None)
+        plans.append(batch.infos())
+    floats = [sum(lib.grid_floats(r) for r in p if r['status'] in (0, 8)) for p in plans]
+    bars = [int(sum(int(r['n_bars_out']) for r in p if r['status'] in (0, 8))) for p in plans]
+    chan_bars = [int(sum(int(r['n_bars_out']) * (int(r['n_pitched']) + int(r['n_unpitched'])) for r in p
+                         if r['status'] in (0, 8))) for p in plans]
+    arena = torch.empty(max(floats), dtype=torch.float32, device='cuda')
+
+    def step(i):
+        batches[i % n_batches].encode(filt, arena)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    for i in range(args.warmup):
+        step(i)
+    # sanity: the run really produced grids
+    torch.cuda.synchronize()
+    check = batches[(args.warmup - 1) % n_batches].infos()
+    assert all(int(r['status']) == 0 for r in check), 'warm-up step reported non-OK songs'
+
+    # ---- timed region: K steps, device timed, max over ranks
+    barrier()
+    t_load0 = time.time()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        step(i)
+    ev1.record()
+    barrier()
+    elapsed_ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device='cuda')
+    total_bars = torch.tensor([sum(bars[i % n_batches] for i in range(args.steps))], dtype=torch.float64, device='cuda')
+    total_chan_bars = torch.tensor([sum(chan_bars[i % n_batches] for i in range(args.steps))], dtype=torch.float64,
+                                   device='cuda')
+    if world > 1:
+        dist.all_reduce(elapsed_ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(total_bars, op=dist.ReduceOp.SUM)
+        dist.all_reduce(total_chan_bars, op=dist.ReduceOp.SUM)
+    elapsed_s = float(elapsed_ms.item()) / 1e3
+    value = float(total_bars.item()) / elapsed_s
+
+    # ---- roofline of the dominant kernel (k_grid), CUDA events recorded by the library on the same stream
+    lib.check(L.mst_profile_enable(1))
+    grid_ms, front_ms, grid_bytes = [], [], []
+    for i in range(args.steps):
+        step(i)
+        torch.cuda.synchronize()
+        grid_ms.append(L.mst_profile_encode_ms(1))
+        front_ms.append(L.mst_profile_encode_ms(0))
+        p = plans[i % n_batches]
+        n_cells = int(sum(int(r['n_notes']) for r in batches[i % n_batches].infos())) if i < n_batches else None
+        grid_bytes.append(floats[i % n_batches] * 4)
+    lib.check(L.mst_profile_enable(0))
+    peak, peak_src = measured_peak_hbm()
+    g_ms = statistics.mean(grid_ms)
+    g_bytes = statistics.mean(grid_bytes)
+    achieved = g_bytes / (g_ms * 1e-3) / 1e9
+    ev_bytes = statistics.mean(len(h[0]) * 16 for h in host_batches)
+    roofline = {
+        'kernel': 'k_grid', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+        'frac': achieved / peak, 'traffic': None, 'peak_source': peak_src,
+        'algorithmic_bytes_per_launch': g_bytes, 'ms_per_launch': g_ms,
+        'share_of_step': g_ms / (g_ms + statistics.mean(front_ms)),
+        'pipeline': {'front_end_ms': statistics.mean(front_ms),
+                     'whole_step_achieved_GBps': (g_bytes + ev_bytes) / (elapsed_s / args.steps) / 1e9},
+    }
+
+    # ---- e2e: host buffers through the C ABI (H2D of events + song table, kernels, D2H of the infos)
+    h_events = [torch.from_numpy(h[0].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
+    h_songs = [torch.from_numpy(h[1].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
+    h_info = torch.empty(args.batch * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    n_ev = [len(h[0]) for h in host_batches]
+    wsb = max(L.mst_encode_host_workspace_bytes(n, args.batch, arena.numel()) for n in n_ev)
+    for b in batches:
+        b._ws = None   # release the device-path workspaces before allocating the host-path one
+    ws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def e2e_step(i):
+        j = i % n_batches
+        lib.check(L.mst_encode_batch_host(
+            h_events[j].data_ptr(), n_ev[j], h_songs[j].data_ptr(), args.batch, filt.reshape(1).ctypes.data,
+            h_info.data_ptr(), arena.data_ptr(), arena.numel(), None, ws.data_ptr(), wsb, stream))
+
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+    barrier()
+    t_load1 = time.time()
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = float(total_bars.item()) / float(e2e_s.item())
+    e2e = {'value': e2e_value, 'unit': UNIT,
+           'h2d_bytes_per_step': int(statistics.mean(n_ev) * 16 + args.batch * 16),
+           'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
+           'note': 'grids stay in HBM for the training consumer (device tensors, SURVEY.md 8(b)); '
+                   'infos are read back every step'}
+    clocks = sampler.stop(t_load0, t_load1) if sampler else None
+
+    # ---- CPU baseline (rank 0, N=1): the oracle port, one thread, bounded sample
+    cpu_baseline = None
+    if rank == 0 and world == 1:
+        sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+        import oracle_lib
+        sample = 256
+        ev_s, sg_s = host_batches[0][0], host_batches[0][1][:sample]
+        t0 = time.perf_counter()
+        infos, _ = oracle_lib.encode_batch(ev_s, sg_s, filt, 1)
+        dt = time.perf_counter() - t0
+        cpu_baseline = {'value': float(infos['n_bars_out'][infos['status'] == 0].sum()) / dt, 'unit': UNIT,
+                        'cores': 1, 'kind': 'port',
+                        'sample': f'first {sample} songs of batch 0 (same generator, same filter), one pass'}
+
+    if rank == 0:
+        print(json.dumps({
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': elapsed_s / args.steps * 1e3, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64 quantise -> f32 grid', 'data': 'synthetic',
+            'config': workload_config(args),
+            'channel_bars_per_s': float(total_chan_bars.item()) / elapsed_s,
+            'roofline': roofline, 'e2e': e2e, 'cpu_baseline': cpu_baseline, 'clocks': clocks,
+            'gpu_launches': KERNELS_PER_STEP * args.steps,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -1055,6 +1055,22 @@ extern "C" size_t mst_encode_workspace_bytes(uint64_t n_events_total, uint32_t n
     return carve(&ws, nullptr, n_events_total, n_songs ? n_songs : 1, max_bins_for(arena_floats));
 }
 
+// optional device-side timing of the two halves of the pipeline (bench.py's roofline numbers)
+static bool g_profile = false;
+static cudaEvent_t g_ev[3] = {nullptr, nullptr, nullptr};
+extern "C" int mst_profile_enable(int on) {
+    if (on && !g_ev[0]) for (int i = 0; i < 3; i++) MST_CUDA_CHECK(cudaEventCreate(&g_ev[i]));
+    g_profile = on != 0;
+    return MST_OK;
+}
+// which: 0 = front end (k_sort .. k_cells), 1 = k_grid; valid after the stream has been synchronised
+extern "C" float mst_profile_encode_ms(int which) {
+    if (!g_ev[0]) return -1.f;
+    float ms = -1.f;
+    if (cudaEventElapsedTime(&ms, g_ev[which ? 1 : 0], g_ev[which ? 2 : 1]) != cudaSuccess) { cudaGetLastError(); return -1.f; }
+    return ms;
+}
+
 static int g_num_sms = 0;
 static int num_sms() {
     if (!g_num_sms) {
@@ -1091,6 +1107,7 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
     if (h_filter) filter = *h_filter; else { memset(&filter, 0, sizeof(filter)); }
     const int sms = num_sms();
 
+    if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[0], stream));
     k_sort<<<n_songs, kSortThreads, 0, stream>>>(d_events, d_songs, ws);
     MST_LAUNCH_CHECK("k_sort");
     const uint32_t walk_blocks = (uint32_t)std::min<uint64_t>(((uint64_t)n_songs * 16u + 3) / 4, (uint64_t)sms * 16);
@@ -1115,7 +1132,9 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
         MST_CUDA_CHECK(cudaFuncSetAttribute(k_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)grid_smem));
         attr_set = true;
     }
+    if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
     k_grid<<<sms, kGridThreads, grid_smem, stream>>>(n_songs, ws, d_info, d_arena);
     MST_LAUNCH_CHECK("k_grid");
+    if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
     return MST_OK;
 }

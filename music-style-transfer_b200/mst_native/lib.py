@@ -18,6 +18,7 @@ _lib = None
 # every symbol include/mst_b200.h declares (tests check that the library exports them all)
 EXPORTS = [
     'mst_abi_version', 'mst_last_error', 'mst_device_count',
+    'mst_profile_enable', 'mst_profile_encode_ms',
     'mst_smf_parse',
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
     'mst_encode_host_workspace_bytes', 'mst_encode_batch_host',
@@ -39,6 +40,10 @@ def load():
     L.mst_abi_version.restype = ctypes.c_int
     L.mst_last_error.restype = ctypes.c_char_p
     L.mst_device_count.restype = ctypes.c_int
+    L.mst_profile_enable.restype = ctypes.c_int
+    L.mst_profile_enable.argtypes = [ctypes.c_int]
+    L.mst_profile_encode_ms.restype = ctypes.c_float
+    L.mst_profile_encode_ms.argtypes = [ctypes.c_int]
     L.mst_smf_parse.restype = ctypes.c_int64
     L.mst_smf_parse.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
                                 ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),

@@ -14,6 +14,7 @@
  * Plain sequential C on purpose: it is the checker, not the thing measured.
  */
 #include <math.h>
+#include <pthread.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -393,9 +394,12 @@ static int quantise(int32_t time, int32_t tpb, int32_t tpbar, int32_t *qtime, in
  * followed by prepare_input's crop and f32 cast (data.py:133-143).
  * Pass pitched/unpitched == NULL to only plan (info is filled, sizes known).
  */
+typedef struct MstoScratch { float *p; uint64_t cap_p; float *u; uint64_t cap_u; } MstoScratch;
+
 int msto_get_input(const MstoList *lists, int n_lists, const uint8_t *keep, const MstoNoteMsg *msgs,
                    MstSongInfo *info, int crop_channel_bars,
-                   float *pitched, uint64_t pitched_cap, float *unpitched, uint64_t unpitched_cap) {
+                   float *pitched, uint64_t pitched_cap, float *unpitched, uint64_t unpitched_cap,
+                   MstoScratch *grow) {
     int32_t tpb = info->ticks_per_beat, tpbar = info->ticks_per_bar, nb = info->n_beats;
     /* group_by instrument_id in first-seen order (data.py:69) */
     int instr[MST_MAX_PITCHED + MST_MAX_UNPITCHED]; int n_instr = 0;
@@ -460,6 +464,11 @@ int msto_get_input(const MstoList *lists, int n_lists, const uint8_t *keep, cons
     uint64_t u_floats = (uint64_t)U * n_out * nb * MST_UNPITCHED_BEAT_FLOATS;
     info->pitched_offset = 0; info->unpitched_offset = p_floats;
     int n_scattered = 0;
+    if (grow) {   /* output allocated here, like the reference's np.zeros (midi_conversion.py:590-595) */
+        if (grow->cap_p < p_floats) { free(grow->p); grow->p = (float *)malloc(p_floats * sizeof(float)); grow->cap_p = p_floats; }
+        if (grow->cap_u < u_floats) { free(grow->u); grow->u = (float *)malloc(u_floats * sizeof(float)); grow->cap_u = u_floats; }
+        pitched = grow->p; pitched_cap = grow->cap_p; unpitched = grow->u; unpitched_cap = grow->cap_u;
+    }
     int write = (pitched != NULL);
     if (write) {
         if (p_floats > pitched_cap || (U && (unpitched == NULL || u_floats > unpitched_cap))) {
@@ -531,9 +540,9 @@ static void apply_filter(const MstoList *lists, int n_lists, const MstFilter *f,
  * Whole encode of one song: events -> info + f32 grids (what iter_inputs + prepare_input yield).
  * pitched == NULL: plan only.  Returns 0; per-song problems are in info->status.
  */
-int msto_encode_song(const MstEvent *ev, uint32_t n_events, int32_t tpb, const MstFilter *filter,
+static int encode_song_impl(const MstEvent *ev, uint32_t n_events, int32_t tpb, const MstFilter *filter,
                      MstSongInfo *info, float *pitched, uint64_t pitched_cap,
-                     float *unpitched, uint64_t unpitched_cap) {
+                     float *unpitched, uint64_t unpitched_cap, MstoScratch *grow) {
     MstoList lists[16 * MST_MAX_LISTS_PER_CHANNEL];
     MstoNoteMsg *msgs = (MstoNoteMsg *)malloc(sizeof(MstoNoteMsg) * (n_events ? n_events : 1));
     uint32_t n_msgs = 0;
@@ -542,10 +551,60 @@ int msto_encode_song(const MstEvent *ev, uint32_t n_events, int32_t tpb, const M
         uint8_t keep[16 * MST_MAX_LISTS_PER_CHANNEL];
         apply_filter(lists, n_lists, filter, keep);
         msto_get_input(lists, n_lists, keep, msgs, info, filter ? filter->crop_channel_bars : 0,
-                       pitched, pitched_cap, unpitched, unpitched_cap);
+                       pitched, pitched_cap, unpitched, unpitched_cap, grow);
     }
     free(msgs);
     return 0;
+}
+
+int msto_encode_song(const MstEvent *ev, uint32_t n_events, int32_t tpb, const MstFilter *filter,
+                     MstSongInfo *info, float *pitched, uint64_t pitched_cap,
+                     float *unpitched, uint64_t unpitched_cap) {
+    return encode_song_impl(ev, n_events, tpb, filter, info, pitched, pitched_cap, unpitched, unpitched_cap, NULL);
+}
+
+/* Timed CPU baseline (bench.py cpu_baseline / --impl reference): a batch of songs on n_threads host
+ * threads (pthreads, dynamic work queue), each writing its grids into a thread-private buffer.
+ * Returns a checksum of a strided sample of all grids. */
+typedef struct {
+    const MstEvent *ev; const MstSongIn *songs; uint32_t n_songs; const MstFilter *filter; MstSongInfo *infos;
+    volatile uint32_t *next; double checksum;
+} BatchJob;
+
+static void *batch_worker(void *arg) {
+    BatchJob *job = (BatchJob *)arg;
+    MstoScratch sc = {NULL, 0, NULL, 0};
+    double checksum = 0.0;
+    for (;;) {
+        uint32_t s = __atomic_fetch_add(job->next, 1u, __ATOMIC_RELAXED);
+        if (s >= job->n_songs) break;
+        encode_song_impl(job->ev + job->songs[s].event_offset, job->songs[s].n_events, job->songs[s].ticks_per_beat,
+                         job->filter, &job->infos[s], NULL, 0, NULL, 0, &sc);
+        if (job->infos[s].status == MST_SONG_OK) {
+            uint64_t n = job->infos[s].unpitched_offset;
+            for (uint64_t i = 0; i < n; i += 4099) checksum += sc.p[i];
+        }
+    }
+    free(sc.p); free(sc.u);
+    job->checksum = checksum;
+    return NULL;
+}
+
+double msto_encode_batch(const MstEvent *ev, const MstSongIn *songs, uint32_t n_songs, const MstFilter *filter,
+                         MstSongInfo *infos, int n_threads) {
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 256) n_threads = 256;
+    pthread_t th[256]; BatchJob jobs[256];
+    volatile uint32_t next = 0;
+    for (int t = 0; t < n_threads; t++) {
+        jobs[t].ev = ev; jobs[t].songs = songs; jobs[t].n_songs = n_songs; jobs[t].filter = filter;
+        jobs[t].infos = infos; jobs[t].next = &next; jobs[t].checksum = 0.0;
+        if (t > 0) pthread_create(&th[t], NULL, batch_worker, &jobs[t]);
+    }
+    batch_worker(&jobs[0]);
+    double checksum = jobs[0].checksum;
+    for (int t = 1; t < n_threads; t++) { pthread_join(th[t], NULL); checksum += jobs[t].checksum; }
+    return checksum;
 }
 
 /* Export of the stage-R result for tests of read_midi parity (lists + message counts). */

@@ -70,3 +70,17 @@ def read_midi_lists(events, tpb):
     n = L.msto_read_midi_lists(_p(events), ctypes.c_uint32(len(events)), ctypes.c_int32(int(tpb)), _p(info),
                                _p(ch), _p(ins), _p(cnt), ctypes.c_int(cap))
     return info[0].copy(), np.stack([ch[:n], ins[:n], cnt[:n]], 1)
+
+
+def encode_batch(events, songs, filt=None, n_threads=1):
+    """Timed CPU baseline: encode every song of the batch on n_threads host threads (OpenMP).
+    Returns (infos, checksum)."""
+    L = lib()
+    L.msto_encode_batch.restype = ctypes.c_double
+    events = np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE)
+    songs = np.ascontiguousarray(songs, dtype=abi.SONG_IN_DTYPE)
+    infos = np.zeros(len(songs), dtype=abi.SONG_INFO_DTYPE)
+    fptr = _p(filt.reshape(1)) if filt is not None else None
+    chk = L.msto_encode_batch(_p(events), _p(songs), ctypes.c_uint32(len(songs)), fptr, _p(infos),
+                              ctypes.c_int(int(n_threads)))
+    return infos, float(chk)
