@@ -88,6 +88,15 @@ struct ChanRec {
     uint32_t slot_ons[MST_MAX_LISTS_PER_CHANNEL];
 };
 
+struct __align__(16) TileDesc {   // one k_grid work item: up to kTileBeats beats of one (slot, bar)
+    uint64_t dst;            // float offset in the arena
+    uint32_t floats;
+    uint32_t cell_lo, cell_hi;     // range in cells_sorted (absolute)
+    uint32_t beat_lo_off;          // float offset of the tile's first beat inside the bar slab
+    uint32_t pad[2];
+};
+static_assert(sizeof(TileDesc) == 32, "TileDesc layout");
+
 struct SongPlan {
     uint64_t out_floats;   // requested grid floats (pitched + unpitched)
     uint32_t n_bins;       // (C+U) * n_bars_out
@@ -112,6 +121,7 @@ struct Workspace {
     uint32_t *tile_prefix;    // [S+1]
     uint32_t *bin_count, *bin_start, *bin_fill;  // [max_bins + 1]
     uint32_t *totals;         // [4]: total tiles, total bins
+    TileDesc *tiles;          // [max_bins + 1] (a tile never covers more than one bin)
     uint64_t max_bins;
 };
 
@@ -671,12 +681,23 @@ __constant__ int8_t c_accidental[2][12] = {{1, 0, 1, 0, 1, 1, 2, 1, 2, 1, 0, 1},
 __constant__ int8_t c_col8[8] = {0, 1, 2, 4, 5, 6, 8, 9};
 __constant__ int8_t c_col3[3] = {0, 3, 7};
 
-__global__ void __launch_bounds__(128)
+struct __align__(16) ScaleTerm {   // duration * velocity of one note, placed at its merged-order rank
+    double prod;
+    int32_t key;
+    int32_t pad;
+};
+static_assert(sizeof(ScaleTerm) == sizeof(Cell), "ScaleTerm aliases the cell scratch");
+
+constexpr int kScaleThreads = 256;
+
+__global__ void __launch_bounds__(kScaleThreads)
 k_scale(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out) {
     __shared__ double sec[MST_MAX_PITCHED * 12];
     __shared__ uint8_t started[MST_MAX_PITCHED * 12];
     __shared__ double hist[12];
     __shared__ double losses[24], covs[24], looses[24], ces[24];
+    __shared__ uint32_t inst_base[MST_MAX_PITCHED + 1];
+    __shared__ uint16_t inst_lists[MST_MAX_PITCHED];
     const uint32_t song = blockIdx.x;
     MstSongInfo *info = info_out + song;
     if (!song_active(info->status)) return;
@@ -685,49 +706,76 @@ k_scale(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
     const int n_lists = (int)ws.plans[song].n_lists;
     const int C = info->n_pitched;
     const Note *notes = ws.notes + base;
+    ScaleTerm *terms = reinterpret_cast<ScaleTerm *>(ws.cells + base);   // free until k_cells runs
+    const unsigned lane = lane_id(), warp = threadIdx.x >> 5, nwarps = kScaleThreads / 32;
 
-    for (int chain = threadIdx.x; chain < C * 12; chain += blockDim.x) {
-        const int p = chain / 12, key = chain % 12;
-        // lists of this instrument, in channel-entry order (merge_nchannels concatenation order)
-        int L = 0, l_first = -1;
-        for (int l = 0; l < n_lists; l++) if (lists[l].pitched && lists[l].out_slot == p) { if (!L) l_first = l; L++; }
-        PySum ps; ps.started = false; ps.s = 0; ps.c = 0;
-        if (L == 1) {
-            const Note *nt = notes + lists[l_first].note_offset;
-            const uint32_t n = lists[l_first].n_notes;
-            for (uint32_t j = 0; j < n; j++) {
-                if (nt[j].note_id % 12 != key) continue;
-                ps.add(__dmul_rn((double)(nt[j].end_time - nt[j].time), nt[j].velocity));
-            }
-        } else {
-            // stable merge by time of several lists (sorted(notes, key=time), data.py:107-108), stateless:
-            // after (t, l, j) comes the smallest (time, list, pos) that is lexicographically larger
-            int cur_t = -1, cur_l = -1; uint32_t cur_j = 0;
-            while (true) {
-                int best_t = INT_MAX, best_l = -1; uint32_t best_j = 0;
-                for (int l = 0; l < n_lists; l++) {
-                    if (!(lists[l].pitched && lists[l].out_slot == p)) continue;
-                    const Note *nt = notes + lists[l].note_offset;
-                    const uint32_t n = lists[l].n_notes;
-                    uint32_t j;
-                    if (l == cur_l) j = cur_j + 1;
-                    else {
-                        // first position with time >= cur_t (lists after cur_l) or > cur_t (lists before)
-                        const int thr = (l > cur_l) ? cur_t : cur_t + 1;
-                        uint32_t lo = 0, hi = n;
-                        while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (nt[mid].time < thr) lo = mid + 1; else hi = mid; }
-                        j = lo;
-                    }
-                    if (j < n && nt[j].time < best_t) { best_t = nt[j].time; best_l = l; best_j = j; }
+    // notes per pitched instrument (merge_nchannels, data.py:103-114) and their term ranges
+    for (int p = threadIdx.x; p < C; p += kScaleThreads) {
+        uint32_t cnt = 0; int nl = 0;
+        for (int l = 0; l < n_lists; l++) if (lists[l].pitched && lists[l].out_slot == p) { cnt += lists[l].n_notes; nl++; }
+        inst_base[p + 1] = cnt;
+        inst_lists[p] = (uint16_t)nl;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        inst_base[0] = 0;
+        for (int p = 0; p < C; p++) inst_base[p + 1] += inst_base[p];
+    }
+    __syncthreads();
+    // each note goes to its rank in sorted(notes, key=time) of the concatenated lists (stable):
+    // own position + notes of earlier lists with time <= t + notes of later lists with time < t
+    for (int l = 0; l < n_lists; l++) {
+        const ListRec L = lists[l];
+        if (!L.pitched || L.out_slot < 0) continue;
+        const int p = L.out_slot;
+        const Note *nt = notes + L.note_offset;
+        const bool multi = inst_lists[p] > 1;
+        for (uint32_t j = threadIdx.x; j < L.n_notes; j += kScaleThreads) {
+            const Note x = nt[j];
+            uint32_t rank = j;
+            if (multi) {
+                for (int l2 = 0; l2 < n_lists; l2++) {
+                    if (l2 == l || !lists[l2].pitched || lists[l2].out_slot != p) continue;
+                    const Note *o = notes + lists[l2].note_offset;
+                    const int thr = (l2 < l) ? x.time + 1 : x.time;   // count notes with time < thr
+                    uint32_t lo = 0, hi = lists[l2].n_notes;
+                    while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (o[mid].time < thr) lo = mid + 1; else hi = mid; }
+                    rank += lo;
                 }
-                if (best_l < 0) break;
-                const Note &x = notes[lists[best_l].note_offset + best_j];
-                if (x.note_id % 12 == key) ps.add(__dmul_rn((double)(x.end_time - x.time), x.velocity));
-                cur_t = best_t; cur_l = best_l; cur_j = best_j;
+            }
+            ScaleTerm t;
+            t.prod = __dmul_rn((double)(x.end_time - x.time), x.velocity);   // duration * velocity (:342)
+            t.key = x.note_id % 12;
+            t.pad = 0;
+            terms[inst_base[p] + rank] = t;
+        }
+    }
+    __syncthreads();
+    // Python sum() per (instrument, pitch class) in merged order: lane k owns class k.  Inside a strip of 32
+    // terms every lane walks the set bits of its own class mask, so the adds of different classes overlap.
+    for (int p = warp; p < C; p += nwarps) {
+        PySum acc; acc.started = false; acc.s = 0; acc.c = 0;
+        const uint32_t t0 = inst_base[p], t1 = inst_base[p + 1];
+        for (uint32_t b = t0; b < t1; b += 32) {
+            const uint32_t i = b + lane;
+            const bool valid = i < t1;
+            double prod = 0.0; int key = -1;
+            if (valid) { ScaleTerm t = terms[i]; prod = t.prod; key = t.key; }
+            unsigned mine = 0;
+#pragma unroll
+            for (int k = 0; k < 12; k++) {
+                const unsigned mk = __ballot_sync(0xffffffffu, key == k);
+                if (lane == (unsigned)k) mine = mk;
+            }
+            int iters = __popc(mine);
+            iters = warp_reduce_max(iters);
+            for (int it = 0; it < iters; it++) {
+                const int src = mine ? __ffs(mine) - 1 : 0;
+                const double x = __shfl_sync(0xffffffffu, prod, src);
+                if (mine) { acc.add(x); mine &= mine - 1; }
             }
         }
-        sec[chain] = ps.result();
-        started[chain] = ps.started ? 1 : 0;
+        if (lane < 12) { sec[p * 12 + lane] = acc.result(); started[p * 12 + lane] = acc.started ? 1 : 0; }
     }
     __syncthreads();
     if (threadIdx.x < 12) {
@@ -905,33 +953,63 @@ k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
         const uint32_t pos = bin_start[b] + atomicAdd(&bin_fill[b], 1u);
         sorted[pos] = c;
     }
+    // tile descriptors for k_grid: (slot, bar, beat chunk) -> destination + cell range
+    const uint32_t C = (uint32_t)info->n_pitched;
+    const uint32_t chunks = ((uint32_t)nb + kTileBeats - 1) / kTileBeats;
+    TileDesc *tiles = ws.tiles + plan.tile_base;
+    for (uint32_t local = threadIdx.x; local < plan.n_tiles; local += blockDim.x) {
+        const uint32_t bin = local / chunks, chunk = local % chunks;
+        const uint32_t slot = bin / (uint32_t)n_out, bar = bin % (uint32_t)n_out;
+        const bool pitched = slot < C;
+        const uint32_t beat_floats = pitched ? MST_PITCHED_BEAT_FLOATS : MST_UNPITCHED_BEAT_FLOATS;
+        const uint32_t beat_lo = chunk * kTileBeats, beats = min((uint32_t)kTileBeats, (uint32_t)nb - beat_lo);
+        const uint64_t slab = pitched
+            ? info->pitched_offset + ((uint64_t)slot * n_out + bar) * nb * beat_floats
+            : info->unpitched_offset + ((uint64_t)(slot - C) * n_out + bar) * nb * beat_floats;
+        TileDesc t;
+        t.dst = slab + (uint64_t)beat_lo * beat_floats;
+        t.floats = beats * beat_floats;
+        t.beat_lo_off = beat_lo * beat_floats;
+        const uint32_t cnt = bin_count[bin];
+        t.cell_lo = cnt ? bin_start[bin] : 0u;
+        t.cell_hi = t.cell_lo + cnt;
+        t.pad[0] = 0; t.pad[1] = 0;
+        tiles[local] = t;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
 // k_grid: qchannel2vchannel's scatter-max (:490-516) + np.stack (data.py:91-95) + f32 cast.
-// Persistent CTAs.  A tile = up to kTileBeats beats of one (slot, bar).  Tile buffers in shared memory
-// are kept all-zero between uses: notes are scattered with atomicMax on the (non-negative) f32 bit
-// patterns, the tile leaves with one TMA bulk store, and once the store has read the buffer only the
+// Persistent CTAs over the tile descriptors k_cells wrote.  A tile = up to kTileBeats beats of one
+// (slot, bar) = 44.8 KB (pitched, 4/4).  Tile buffers in shared memory are kept all-zero between uses:
+// notes are scattered with atomicMax on the (non-negative) f32 bit patterns, the tile leaves with one
+// TMA bulk store (cp.async.bulk shared -> global), and once that store has read the buffer only the
 // touched cells are reset.  Empty tiles are stored straight from a read-only zero buffer.
 // ------------------------------------------------------------------------------------------------
 constexpr int kGridThreads = 256;
-constexpr int kGridBufs = 3;
+constexpr int kGridBufs = 4;
 constexpr uint32_t kTileFloatsMax = kTileBeats * MST_PITCHED_BEAT_FLOATS;   // 11200 floats = 44800 B
 
-struct TileDesc {
-    float *dst;
-    uint32_t bytes;
-    uint32_t cell_lo, cell_hi;     // range in cells_sorted (absolute)
-    uint32_t beat_lo_off;          // float offset of the tile's first beat inside the bar slab
-    uint32_t floats;
-};
+__device__ __forceinline__ TileDesc load_tile(const TileDesc *tiles, uint32_t tile, uint32_t n_tiles) {
+    TileDesc t;
+    if (tile < n_tiles) {
+        const uint4 *p = reinterpret_cast<const uint4 *>(tiles + tile);
+        const uint4 a = __ldg(p), b = __ldg(p + 1);
+        t.dst = ((uint64_t)a.y << 32) | a.x; t.floats = a.z; t.cell_lo = a.w;
+        t.cell_hi = b.x; t.beat_lo_off = b.y; t.pad[0] = 0; t.pad[1] = 0;
+    } else {
+        t.dst = 0; t.floats = 0; t.cell_lo = 0; t.cell_hi = 0; t.beat_lo_off = 0; t.pad[0] = 0; t.pad[1] = 0;
+    }
+    return t;
+}
 
-__device__ __forceinline__ void scatter_cells(float *buf, const Cell *cells, const TileDesc &t, bool reset) {
-    for (uint32_t i = t.cell_lo + threadIdx.x; i < t.cell_hi; i += kGridThreads) {
+__device__ __forceinline__ void scatter_cells(float *buf, const Cell *cells, uint32_t cell_lo, uint32_t cell_hi,
+                                              uint32_t beat_lo_off, uint32_t floats, bool reset) {
+    for (uint32_t i = cell_lo + threadIdx.x; i < cell_hi; i += kGridThreads) {
         const Cell c = cells[i];
         const uint32_t off = c.off_acc & 0x0FFFFFFFu;
-        if (off < t.beat_lo_off || off >= t.beat_lo_off + t.floats) continue;   // other beat chunk of the bar
-        float *cell = buf + (off - t.beat_lo_off);
+        if (off < beat_lo_off || off >= beat_lo_off + floats) continue;   // other beat chunk of the bar
+        float *cell = buf + (off - beat_lo_off);
         const uint32_t acc = c.off_acc >> 28;
         if (reset) {
             cell[0] = 0.f; cell[1] = 0.f;
@@ -945,53 +1023,24 @@ __device__ __forceinline__ void scatter_cells(float *buf, const Cell *cells, con
 }
 
 __global__ void __launch_bounds__(kGridThreads, 1)
-k_grid(uint32_t n_songs, Workspace ws, const MstSongInfo *__restrict__ info,
-       float *__restrict__ arena) {
+k_grid(Workspace ws, float *__restrict__ arena) {
     extern __shared__ __align__(128) float smem[];
     float *zero_buf = smem;                                  // never written after init
     float *bufs = smem + kTileFloatsMax;                     // kGridBufs tile buffers
-    __shared__ TileDesc desc[kGridBufs];
-    __shared__ TileDesc cur;
+    __shared__ uint32_t used_lo[kGridBufs], used_hi[kGridBufs], used_beat[kGridBufs], used_floats[kGridBufs];
     const uint32_t n_tiles = ws.totals[0];
+    const TileDesc *tiles = ws.tiles;
     for (uint32_t i = threadIdx.x; i < (1 + kGridBufs) * kTileFloatsMax; i += kGridThreads) smem[i] = 0.f;
     fence_proxy_async_smem();
     __syncthreads();
     uint32_t used = 0;   // tiles that went through a scatter buffer
+    TileDesc next = load_tile(tiles, blockIdx.x, n_tiles);
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        if (threadIdx.x == 0) {
-            // tile -> song (binary search in the tile prefix), slot, bar, beat chunk
-            uint32_t lo = 0, hi = n_songs;
-            while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (ws.tile_prefix[mid] <= tile) lo = mid; else hi = mid; }
-            const uint32_t song = lo;
-            const SongPlan p = ws.plans[song];
-            const MstSongInfo *si = info + song;
-            const uint32_t nb = (uint32_t)si->n_beats, n_out = (uint32_t)si->n_bars_out, C = (uint32_t)si->n_pitched;
-            const uint32_t chunks = (nb + kTileBeats - 1) / kTileBeats;
-            const uint32_t local = tile - p.tile_base;
-            const uint32_t bin = local / chunks, chunk = local % chunks;
-            const uint32_t slot = bin / n_out, bar = bin % n_out;
-            const bool pitched = slot < C;
-            const uint32_t beat_floats = pitched ? MST_PITCHED_BEAT_FLOATS : MST_UNPITCHED_BEAT_FLOATS;
-            const uint32_t beat_lo = chunk * kTileBeats, beats = min((uint32_t)kTileBeats, nb - beat_lo);
-            const uint64_t slab = pitched
-                ? si->pitched_offset + ((uint64_t)slot * n_out + bar) * nb * beat_floats
-                : si->unpitched_offset + ((uint64_t)(slot - C) * n_out + bar) * nb * beat_floats;
-            TileDesc t;
-            t.dst = arena + slab + (uint64_t)beat_lo * beat_floats;
-            t.floats = beats * beat_floats;
-            t.bytes = t.floats * 4u;
-            t.beat_lo_off = beat_lo * beat_floats;
-            t.cell_lo = 0; t.cell_hi = 0;
-            const uint32_t gb = p.bin_base + bin;
-            const uint32_t cnt = ws.bin_count[gb];
-            if (cnt) { t.cell_lo = ws.bin_start[gb]; t.cell_hi = t.cell_lo + cnt; }
-            cur = t;
-        }
-        __syncthreads();
-        const TileDesc t = cur;
+        const TileDesc t = next;
+        next = load_tile(tiles, tile + gridDim.x, n_tiles);   // prefetch the next descriptor
+        float *dst = arena + t.dst;
         if (t.cell_hi == t.cell_lo) {
-            if (threadIdx.x == 0) { bulk_store_s2g(t.dst, zero_buf, t.bytes); bulk_commit(); }
-            __syncthreads();
+            if (threadIdx.x == 0) { bulk_store_s2g(dst, zero_buf, t.floats * 4u); bulk_commit(); }
             continue;
         }
         const uint32_t b = used % kGridBufs;
@@ -1001,14 +1050,14 @@ k_grid(uint32_t n_songs, Workspace ws, const MstSongInfo *__restrict__ info,
             // committed in tile order by thread 0; zero-buffer stores in between only make this stricter.
             if (threadIdx.x == 0) bulk_wait_read<kGridBufs - 1>();
             __syncthreads();
-            scatter_cells(buf, ws.cells_sorted, desc[b], true);
+            scatter_cells(buf, ws.cells_sorted, used_lo[b], used_hi[b], used_beat[b], used_floats[b], true);
             __syncthreads();
         }
-        scatter_cells(buf, ws.cells_sorted, t, false);
-        if (threadIdx.x == 0) desc[b] = t;
+        scatter_cells(buf, ws.cells_sorted, t.cell_lo, t.cell_hi, t.beat_lo_off, t.floats, false);
+        if (threadIdx.x == 0) { used_lo[b] = t.cell_lo; used_hi[b] = t.cell_hi; used_beat[b] = t.beat_lo_off; used_floats[b] = t.floats; }
         fence_proxy_async_smem();
         __syncthreads();
-        if (threadIdx.x == 0) { bulk_store_s2g(t.dst, buf, t.bytes); bulk_commit(); }
+        if (threadIdx.x == 0) { bulk_store_s2g(dst, buf, t.floats * 4u); bulk_commit(); }
         used++;
     }
     if (threadIdx.x == 0) bulk_wait<0>();
@@ -1041,6 +1090,7 @@ static size_t carve(Workspace *ws, void *base, uint64_t E, uint32_t S, uint64_t 
     ws->bin_start = (uint32_t *)take((max_bins + 1) * 4);
     ws->bin_fill = (uint32_t *)take((max_bins + 1) * 4);
     ws->totals = (uint32_t *)take(16);
+    ws->tiles = (TileDesc *)take((max_bins + 1) * sizeof(TileDesc));
     ws->max_bins = max_bins;
     return off;
 }
@@ -1122,7 +1172,7 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
     MST_LAUNCH_CHECK("k_walk<1>");
     k_pair<<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info);
     MST_LAUNCH_CHECK("k_pair");
-    k_scale<<<n_songs, 128, 0, stream>>>(d_songs, ws, d_info);
+    k_scale<<<n_songs, kScaleThreads, 0, stream>>>(d_songs, ws, d_info);
     MST_LAUNCH_CHECK("k_scale");
     k_cells<<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info);
     MST_LAUNCH_CHECK("k_cells");
@@ -1133,7 +1183,7 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
         attr_set = true;
     }
     if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
-    k_grid<<<sms, kGridThreads, grid_smem, stream>>>(n_songs, ws, d_info, d_arena);
+    k_grid<<<sms, kGridThreads, grid_smem, stream>>>(ws, d_arena);
     MST_LAUNCH_CHECK("k_grid");
     if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
     return MST_OK;
