@@ -1003,23 +1003,26 @@ __device__ __forceinline__ TileDesc load_tile(const TileDesc *tiles, uint32_t ti
     return t;
 }
 
-__device__ __forceinline__ void scatter_cells(float *buf, const Cell *cells, uint32_t cell_lo, uint32_t cell_hi,
-                                              uint32_t beat_lo_off, uint32_t floats, bool reset) {
-    for (uint32_t i = cell_lo + threadIdx.x; i < cell_hi; i += kGridThreads) {
-        const Cell c = cells[i];
-        const uint32_t off = c.off_acc & 0x0FFFFFFFu;
-        if (off < beat_lo_off || off >= beat_lo_off + floats) continue;   // other beat chunk of the bar
-        float *cell = buf + (off - beat_lo_off);
-        const uint32_t acc = c.off_acc >> 28;
-        if (reset) {
-            cell[0] = 0.f; cell[1] = 0.f;
-            if (acc < 3) cell[2 + acc] = 0.f;
-        } else {
-            if (c.dur > 0.f) atomicMax((int *)cell, __float_as_int(c.dur));       // np.maximum with 0 (:514)
-            atomicMax((int *)cell + 1, __float_as_int(c.vel));
-            if (acc < 3) cell[2 + acc] = 1.0f;
-        }
-    }
+constexpr uint32_t kNoCell = 0xFFFFFFFFu;
+
+// scatter (or reset) one cell into a tile buffer; returns the tile-relative offset|acc word, kNoCell when
+// the cell belongs to another beat chunk of the bar
+__device__ __forceinline__ uint32_t apply_cell(float *buf, const Cell &c, uint32_t beat_lo_off, uint32_t floats) {
+    const uint32_t off = c.off_acc & 0x0FFFFFFFu;
+    if (off < beat_lo_off || off >= beat_lo_off + floats) return kNoCell;
+    float *cell = buf + (off - beat_lo_off);
+    const uint32_t acc = c.off_acc >> 28;
+    if (c.dur > 0.f) atomicMax((int *)cell, __float_as_int(c.dur));       // np.maximum with 0 (:514)
+    atomicMax((int *)cell + 1, __float_as_int(c.vel));
+    if (acc < 3) cell[2 + acc] = 1.0f;
+    return (off - beat_lo_off) | (acc << 28);
+}
+__device__ __forceinline__ void reset_cell(float *buf, uint32_t word) {
+    if (word == kNoCell) return;
+    float *cell = buf + (word & 0x0FFFFFFFu);
+    const uint32_t acc = word >> 28;
+    cell[0] = 0.f; cell[1] = 0.f;
+    if (acc < 3) cell[2 + acc] = 0.f;
 }
 
 __global__ void __launch_bounds__(kGridThreads, 1)
@@ -1027,17 +1030,30 @@ k_grid(Workspace ws, float *__restrict__ arena) {
     extern __shared__ __align__(128) float smem[];
     float *zero_buf = smem;                                  // never written after init
     float *bufs = smem + kTileFloatsMax;                     // kGridBufs tile buffers
-    __shared__ uint32_t used_lo[kGridBufs], used_hi[kGridBufs], used_beat[kGridBufs], used_floats[kGridBufs];
+    __shared__ uint32_t touched[kGridBufs][kGridThreads];    // cells each buffer's last tile wrote
+    __shared__ uint32_t over_lo[kGridBufs], over_hi[kGridBufs], over_beat[kGridBufs], over_floats[kGridBufs];
     const uint32_t n_tiles = ws.totals[0];
     const TileDesc *tiles = ws.tiles;
+    const Cell *cells = ws.cells_sorted;
     for (uint32_t i = threadIdx.x; i < (1 + kGridBufs) * kTileFloatsMax; i += kGridThreads) smem[i] = 0.f;
+    for (int b = 0; b < kGridBufs; b++) touched[b][threadIdx.x] = kNoCell;
+    if (threadIdx.x < kGridBufs) { over_lo[threadIdx.x] = 0; over_hi[threadIdx.x] = 0; }
     fence_proxy_async_smem();
     __syncthreads();
     uint32_t used = 0;   // tiles that went through a scatter buffer
-    TileDesc next = load_tile(tiles, blockIdx.x, n_tiles);
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const TileDesc t = next;
-        next = load_tile(tiles, tile + gridDim.x, n_tiles);   // prefetch the next descriptor
+    // software pipeline: descriptors two tiles ahead, this thread's cell one tile ahead
+    const uint32_t stride = gridDim.x;
+    TileDesc d0 = load_tile(tiles, blockIdx.x, n_tiles);
+    TileDesc d1 = load_tile(tiles, blockIdx.x + stride, n_tiles);
+    Cell c0;
+    c0.bin = 0; c0.off_acc = 0; c0.dur = 0.f; c0.vel = 0.f;
+    if (d0.cell_lo + threadIdx.x < d0.cell_hi) c0 = cells[d0.cell_lo + threadIdx.x];
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += stride) {
+        const TileDesc t = d0;
+        const Cell mine = c0;
+        const TileDesc d2 = load_tile(tiles, tile + 2 * stride, n_tiles);
+        if (d1.cell_lo + threadIdx.x < d1.cell_hi) c0 = cells[d1.cell_lo + threadIdx.x];
+        d0 = d1; d1 = d2;
         float *dst = arena + t.dst;
         if (t.cell_hi == t.cell_lo) {
             if (threadIdx.x == 0) { bulk_store_s2g(dst, zero_buf, t.floats * 4u); bulk_commit(); }
@@ -1050,11 +1066,21 @@ k_grid(Workspace ws, float *__restrict__ arena) {
             // committed in tile order by thread 0; zero-buffer stores in between only make this stricter.
             if (threadIdx.x == 0) bulk_wait_read<kGridBufs - 1>();
             __syncthreads();
-            scatter_cells(buf, ws.cells_sorted, used_lo[b], used_hi[b], used_beat[b], used_floats[b], true);
+            reset_cell(buf, touched[b][threadIdx.x]);
+            for (uint32_t i = over_lo[b] + threadIdx.x; i < over_hi[b]; i += kGridThreads) {   // rare: > 256 cells
+                const Cell c = cells[i];
+                const uint32_t off = c.off_acc & 0x0FFFFFFFu;
+                if (off >= over_beat[b] && off < over_beat[b] + over_floats[b])
+                    reset_cell(buf, (off - over_beat[b]) | (c.off_acc & 0xF0000000u));
+            }
             __syncthreads();
         }
-        scatter_cells(buf, ws.cells_sorted, t.cell_lo, t.cell_hi, t.beat_lo_off, t.floats, false);
-        if (threadIdx.x == 0) { used_lo[b] = t.cell_lo; used_hi[b] = t.cell_hi; used_beat[b] = t.beat_lo_off; used_floats[b] = t.floats; }
+        uint32_t word = kNoCell;
+        if (t.cell_lo + threadIdx.x < t.cell_hi) word = apply_cell(buf, mine, t.beat_lo_off, t.floats);
+        touched[b][threadIdx.x] = word;
+        const uint32_t olo = min(t.cell_lo + (uint32_t)kGridThreads, t.cell_hi);
+        for (uint32_t i = olo + threadIdx.x; i < t.cell_hi; i += kGridThreads) apply_cell(buf, cells[i], t.beat_lo_off, t.floats);
+        if (threadIdx.x == 0) { over_lo[b] = olo; over_hi[b] = t.cell_hi; over_beat[b] = t.beat_lo_off; over_floats[b] = t.floats; }
         fence_proxy_async_smem();
         __syncthreads();
         if (threadIdx.x == 0) { bulk_store_s2g(dst, buf, t.floats * 4u); bulk_commit(); }
