@@ -190,6 +190,73 @@ int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events_total,
                           void *d_workspace, size_t workspace_bytes,
                           void *stream);
 
+
+/* ---------------------------------------------------------------- decode (grids -> MIDI events) */
+/* Replaces hard_output (style/model.py:818-832), ChannelConverter.vchannel2channel
+ * (midi_conversion.py:518-573 = vchannel2qchannel + qchannel2channel), decode_midi
+ * (style/style_transfer.py:145-158) and create_midi's ordering / delta / 1-second clip
+ * (style/midi.py:120-168) for a batch of songs. */
+#define MST_MAX_DECODE_CHANNELS 32
+
+#define MST_DECODE_OK             0
+#define MST_DECODE_NO_MESSAGES    1   /* nothing above the velocity gate: messages[-1] raises (midi.py:158) */
+#define MST_DECODE_BAD_VALUE      2   /* non-finite duration / time out of range (int() raises) */
+#define MST_DECODE_VELOCITY       3   /* int(velocity*127) > 127: the assert at midi.py:148 */
+#define MST_DECODE_CAPACITY       4   /* message buffer too small; n_messages is the needed count */
+
+typedef struct MstDecodeSong {
+    uint64_t pitched_offset;     /* float offset of (C, n_bars, n_beats, 10, 56, 5) in the grid buffer */
+    uint64_t unpitched_offset;   /* float offset of (1, n_bars, n_beats, 10, 47, 2) */
+    int32_t  n_pitched;          /* channels to decode (len(channels_info) zipped with the grid) */
+    int32_t  has_unpitched;
+    int32_t  n_bars;
+    int32_t  n_beats;
+    int32_t  ticks_per_beat;
+    int32_t  ticks_per_bar;
+    int32_t  tempo;
+    int32_t  tonic;              /* info['scale']['key'] as 0..11 */
+    int32_t  mode;               /* 0 major, 1 minor */
+    int32_t  duration;           /* info.get('duration'); < 0 = absent (last time + ticks_per_bar) */
+    int32_t  numerator;
+    int32_t  denominator_log2;
+    uint8_t  channel_id[MST_MAX_DECODE_CHANNELS];      /* MIDI channel of each pitched grid channel */
+    int16_t  instrument_id[MST_MAX_DECODE_CHANNELS];   /* program written by create_midi */
+    int32_t  unpitched_channel_id;                     /* 9 */
+    int32_t  write_back;         /* != 0: zero gated velocities in the input like hard_output's in-place `*=` */
+} MstDecodeSong;
+
+typedef struct MstOutMsg {       /* one note message of the output track, in final order */
+    int32_t time;                /* absolute tick */
+    int32_t delta;               /* max(0, min(time - previous, second2tick(1 s)))  (midi.py:161-167) */
+    uint8_t is_on;               /* 1: 0x9n, 0: 0x8n */
+    uint8_t channel;
+    uint8_t note;
+    uint8_t velocity;            /* int(velocity * 127), 0 for note_off */
+} MstOutMsg;
+
+typedef struct MstDecodeResult {
+    int32_t  status;             /* MST_DECODE_* */
+    uint32_t n_messages;
+    uint64_t msg_offset;         /* index of the song's first message in the output array */
+    int32_t  eot_delta;          /* delta time of end_of_track */
+    int32_t  max_delta;          /* second2tick(1, ticks_per_beat, tempo) */
+} MstDecodeResult;
+
+size_t mst_decode_workspace_bytes(uint32_t n_songs, uint64_t grid_floats, uint64_t msg_capacity);
+
+int mst_decode_batch_device(float *d_grids, uint64_t grid_floats,
+                            const MstDecodeSong *d_songs, uint32_t n_songs,
+                            MstOutMsg *d_msgs, uint64_t msg_capacity,
+                            MstDecodeResult *d_results,
+                            void *d_workspace, size_t workspace_bytes, void *stream);
+
+/* SMF serialisation of one decoded song (create_midi's track + mid.save, style/midi.py:125-168 and
+ * style_transfer.py:98): type-1 file, one track, time_signature + set_tempo + one program_change per
+ * non-9 channel + the messages with running status + end_of_track.  Returns bytes written or
+ * MST_E_CAPACITY (needed size in *n_needed). */
+int64_t mst_smf_write(const MstDecodeSong *song, const MstOutMsg *h_msgs, uint32_t n_messages,
+                      int32_t eot_delta, uint8_t *out, size_t capacity, size_t *n_needed);
+
 #ifdef __cplusplus
 }
 #endif

@@ -68,6 +68,54 @@ SONG_INFO_DTYPE = np.dtype([
 assert SONG_INFO_DTYPE.itemsize == 488
 
 
+MAX_DECODE_CHANNELS = 32
+DECODE_OK, DECODE_NO_MESSAGES, DECODE_BAD_VALUE, DECODE_VELOCITY, DECODE_CAPACITY = 0, 1, 2, 3, 4
+
+DECODE_SONG_DTYPE = np.dtype([
+    ('pitched_offset', '<u8'), ('unpitched_offset', '<u8'),
+    ('n_pitched', '<i4'), ('has_unpitched', '<i4'), ('n_bars', '<i4'), ('n_beats', '<i4'),
+    ('ticks_per_beat', '<i4'), ('ticks_per_bar', '<i4'), ('tempo', '<i4'), ('tonic', '<i4'), ('mode', '<i4'),
+    ('duration', '<i4'), ('numerator', '<i4'), ('denominator_log2', '<i4'),
+    ('channel_id', 'u1', (MAX_DECODE_CHANNELS,)), ('instrument_id', '<i2', (MAX_DECODE_CHANNELS,)),
+    ('unpitched_channel_id', '<i4'), ('write_back', '<i4'),
+])
+assert DECODE_SONG_DTYPE.itemsize == 168
+
+OUT_MSG_DTYPE = np.dtype([('time', '<i4'), ('delta', '<i4'), ('is_on', 'u1'), ('channel', 'u1'),
+                          ('note', 'u1'), ('velocity', 'u1')])
+assert OUT_MSG_DTYPE.itemsize == 12
+
+DECODE_RESULT_DTYPE = np.dtype([('status', '<i4'), ('n_messages', '<u4'), ('msg_offset', '<u8'),
+                                ('eot_delta', '<i4'), ('max_delta', '<i4')])
+assert DECODE_RESULT_DTYPE.itemsize == 24
+
+
+def make_decode_song(info, n_pitched, has_unpitched, n_bars, channel_ids=None, instrument_ids=None,
+                     duration=None, write_back=True, pitched_offset=0, unpitched_offset=0):
+    """MstDecodeSong from an info record/dict with ticks_per_beat, ticks_per_bar, tempo, tonic, mode,
+    numerator, denominator_log2 (+ n_beats).  channel ids default to 0..15 without 9
+    (style/style_transfer.py:78-80)."""
+    d = np.zeros((), dtype=DECODE_SONG_DTYPE)
+    d['pitched_offset'], d['unpitched_offset'] = pitched_offset, unpitched_offset
+    d['n_pitched'], d['has_unpitched'], d['n_bars'] = n_pitched, int(bool(has_unpitched)), n_bars
+    for k in ('n_beats', 'ticks_per_beat', 'ticks_per_bar', 'tempo', 'tonic', 'mode', 'numerator',
+              'denominator_log2'):
+        d[k] = int(info[k])
+    d['duration'] = -1 if duration is None else int(duration)
+    if channel_ids is None:
+        channel_ids = [i for i in range(16) if i != 9][:n_pitched]
+    ch = np.zeros(MAX_DECODE_CHANNELS, np.uint8)
+    ch[:len(channel_ids)] = channel_ids
+    d['channel_id'] = ch
+    ins = np.zeros(MAX_DECODE_CHANNELS, np.int16)
+    if instrument_ids is not None:
+        ins[:len(instrument_ids)] = instrument_ids
+    d['instrument_id'] = ins
+    d['unpitched_channel_id'] = 9
+    d['write_back'] = int(bool(write_back))
+    return d
+
+
 def make_filter(included=None, min_n_messages=100, crop_channel_bars=0):
     """MstFilter for iter_inputs (style/data.py:53-56); included=None disables the filter."""
     f = np.zeros((), dtype=FILTER_DTYPE)

@@ -624,3 +624,118 @@ int msto_read_midi_lists(const MstEvent *ev, uint32_t n_events, int32_t tpb, Mst
 
 size_t msto_sizeof_song_info(void) { return sizeof(MstSongInfo); }
 size_t msto_sizeof_event(void) { return sizeof(MstEvent); }
+
+/* ================================================================== decode (grids -> messages) */
+
+typedef struct { int32_t time; uint32_t seq; uint8_t is_on, channel, note, velocity; } DecMsg;
+static int cmp_decmsg(const void *a, const void *b) {   /* (time, seq): stable sort by time */
+    const DecMsg *x = (const DecMsg *)a, *y = (const DecMsg *)b;
+    if (x->time != y->time) return x->time < y->time ? -1 : 1;
+    return x->seq < y->seq ? -1 : (x->seq > y->seq);
+}
+
+/*
+ * decode_midi (style/style_transfer.py:145-158): hard_output (style/model.py:818-832) ->
+ * vchannel2qchannel (midi_conversion.py:518-562) -> qchannel2channel (:458-488, scale_loc2key_octave
+ * :269-283) -> create_midi (style/midi.py:120-168).  `grids` is the float buffer the song's offsets
+ * point into; with song->write_back the gated velocities are zeroed in place like `velocity *= mask`.
+ * Environment pin: numpy >= 2 keeps np.float32 * int in f32.
+ */
+int msto_decode_song(float *grids, const MstDecodeSong *d, MstOutMsg *out, uint32_t capacity,
+                     MstDecodeResult *res) {
+    const float thr_v = 0.01f, thr_a = 0.1f;   /* torch compares f32 with the scalar cast to f32 */
+    const int nb = d->n_beats, tpb = d->ticks_per_beat, tpbar = d->ticks_per_bar;
+    memset(res, 0, sizeof(*res));
+    /* mido.second2tick(1, tpb, tempo) = int(round(1 / (tempo * 1e-6 / tpb))), then int() (midi.py:121-123) */
+    {
+        double scale = (double)d->tempo * 1e-6 / (double)tpb;
+        res->max_delta = (int32_t)nearbyint(1.0 / scale);
+    }
+    uint64_t cells = (uint64_t)d->n_bars * nb * MST_N_FRACTIONS;
+    uint64_t cap_msgs = 2 * ((uint64_t)d->n_pitched * cells * MST_N_PITCHED_ROWS +
+                             (d->has_unpitched ? cells * MST_N_UNPITCHED_ROWS : 0));
+    if (cap_msgs > (1u << 26)) cap_msgs = 1u << 26;
+    DecMsg *m = (DecMsg *)malloc(sizeof(DecMsg) * (cap_msgs ? cap_msgs : 1));
+    uint32_t n = 0; int status = MST_DECODE_OK;
+    int n_ch = d->n_pitched + (d->has_unpitched ? 1 : 0);
+    for (int c = 0; c < n_ch && status == MST_DECODE_OK; c++) {
+        const int pitched = c < d->n_pitched;
+        const int rows = pitched ? MST_N_PITCHED_ROWS : MST_N_UNPITCHED_ROWS;
+        const int feats = pitched ? MST_N_PITCHED_FEATS : MST_N_UNPITCHED_FEATS;
+        float *g = pitched ? grids + d->pitched_offset + (uint64_t)c * cells * rows * feats
+                           : grids + d->unpitched_offset;
+        const int channel = pitched ? d->channel_id[c] : d->unpitched_channel_id;
+        for (uint64_t cell = 0; cell < cells && status == MST_DECODE_OK; cell++) {
+            const int frac = (int)(cell % MST_N_FRACTIONS);
+            const int beat = (int)((cell / MST_N_FRACTIONS) % nb);
+            const int64_t bar = (int64_t)(cell / MST_N_FRACTIONS / nb);
+            for (int row = 0; row < rows; row++) {
+                float *v = g + (cell * rows + row) * feats;
+                float vel = v[1];
+                float gated = vel * ((vel > thr_v) ? 1.0f : 0.0f);       /* velocity *= (velocity > .01).float() */
+                if (d->write_back) v[1] = gated;
+                if (gated == 0.0f) continue;                            /* np.nonzero (:526); NaN counts as non-zero */
+                int note;
+                if (pitched) {
+                    float a0 = v[2], a1 = v[3], a2 = v[4];
+                    float mx = a0; if (a1 > mx) mx = a1; if (a2 > mx) mx = a2;
+                    if (a0 != a0 || a1 != a1 || a2 != a2) mx = NAN;      /* torch.max propagates NaN */
+                    int f0 = (a0 == mx) && (a0 > thr_a), f1 = (a1 == mx) && (a1 > thr_a), f2 = (a2 == mx) && (a2 > thr_a);
+                    int acc = f0 ? 0 : (f1 ? 1 : (f2 ? 2 : 1));          /* flat > natural > sharp, else none (:532-539) */
+                    int degree = row % 7 + 1, octave = row / 7;
+                    int interval = k_abs_intervals[d->mode][degree - 1] + d->tonic;   /* :270-271 */
+                    if (acc == 2) interval += 1; else if (acc == 0) interval -= 1;
+                    if (interval < 0) { octave -= 1; interval += 12; }
+                    else if (interval >= 12) { octave += 1; interval -= 12; }
+                    note = 12 * (octave + 1) + interval;                 /* note2note_id (:320-324) */
+                } else {
+                    note = row + 35;                                     /* :549 */
+                }
+                float dur = v[0];
+                float prod = dur * (float)tpb;                           /* np.float32 * int -> f32 (:558) */
+                if (!(prod == prod) || prod > 1.0e9f || prod < -1.0e9f) { status = MST_DECODE_BAD_VALUE; break; }
+                int32_t qdur = (int32_t)prod;                            /* int(): truncation */
+                int64_t t = bar * tpbar + (int64_t)beat * tpb + ((int64_t)k_frac_num[frac] * tpb) / k_frac_den[frac];
+                if (t > (1 << 30)) { status = MST_DECODE_BAD_VALUE; break; }
+                float vf = gated * 127.0f;                               /* int(msg.velocity * max_velocity) (midi.py:147) */
+                if (!(vf == vf)) { status = MST_DECODE_BAD_VALUE; break; }
+                int vi = (int)vf;
+                if (vi > 127) { status = MST_DECODE_VELOCITY; break; }
+                if (n + 2 > cap_msgs) { status = MST_DECODE_BAD_VALUE; break; }
+                m[n].time = (int32_t)t; m[n].seq = n; m[n].is_on = 1; m[n].channel = (uint8_t)channel;
+                m[n].note = (uint8_t)note; m[n].velocity = (uint8_t)vi; n++;
+                m[n].time = (int32_t)(t + qdur); m[n].seq = n; m[n].is_on = 0; m[n].channel = (uint8_t)channel;
+                m[n].note = (uint8_t)note; m[n].velocity = 0; n++;
+            }
+        }
+    }
+    if (status == MST_DECODE_OK && n == 0) status = MST_DECODE_NO_MESSAGES;
+    res->status = status;
+    res->n_messages = n;
+    if (status != MST_DECODE_OK) { free(m); return 0; }
+    /* per-channel stable sort by time (:487) followed by the global stable sort (midi.py:157) == one
+     * stable sort of the channel-major emission order */
+    qsort(m, n, sizeof(DecMsg), cmp_decmsg);
+    if (n > capacity) { res->status = MST_DECODE_CAPACITY; free(m); return 0; }
+    int32_t prev = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        int32_t delta = m[i].time - prev; if (delta > res->max_delta) delta = res->max_delta;
+        prev = m[i].time;
+        if (delta < 0) delta = 0;
+        out[i].time = m[i].time; out[i].delta = delta; out[i].is_on = m[i].is_on; out[i].channel = m[i].channel;
+        out[i].note = m[i].note; out[i].velocity = m[i].velocity;
+    }
+    {
+        int32_t last = m[n - 1].time;
+        int32_t end = d->duration >= 0 ? d->duration : last + tpbar;    /* midi.py:158 */
+        int32_t delta = end - last; if (delta > res->max_delta) delta = res->max_delta;
+        if (delta < 0) delta = 0;
+        res->eot_delta = delta;
+    }
+    free(m);
+    return 0;
+}
+
+size_t msto_sizeof_decode_song(void) { return sizeof(MstDecodeSong); }
+size_t msto_sizeof_out_msg(void) { return sizeof(MstOutMsg); }
+size_t msto_sizeof_decode_result(void) { return sizeof(MstDecodeResult); }

@@ -84,3 +84,26 @@ def encode_batch(events, songs, filt=None, n_threads=1):
     chk = L.msto_encode_batch(_p(events), _p(songs), ctypes.c_uint32(len(songs)), fptr, _p(infos),
                               ctypes.c_int(int(n_threads)))
     return infos, float(chk)
+
+
+def decode_song(grids, dsong):
+    """grids: contiguous float32 array the song's offsets index into (mutated when write_back).
+    Returns (result record, messages[OUT_MSG_DTYPE])."""
+    L = lib()
+    for f, dt in (('msto_sizeof_decode_song', abi.DECODE_SONG_DTYPE), ('msto_sizeof_out_msg', abi.OUT_MSG_DTYPE),
+                  ('msto_sizeof_decode_result', abi.DECODE_RESULT_DTYPE)):
+        getattr(L, f).restype = ctypes.c_size_t
+        assert getattr(L, f)() == dt.itemsize, f
+    assert grids.dtype == np.float32 and grids.flags['C_CONTIGUOUS']
+    res = np.zeros(1, dtype=abi.DECODE_RESULT_DTYPE)
+    d = np.ascontiguousarray(dsong.reshape(1))
+    cap = 1 << 16
+    while True:
+        out = np.zeros(cap, dtype=abi.OUT_MSG_DTYPE)
+        L.msto_decode_song(_p(grids), _p(d), _p(out), ctypes.c_uint32(cap), _p(res))
+        if res[0]['status'] == abi.DECODE_CAPACITY:
+            cap = int(res[0]['n_messages'])
+            continue
+        break
+    n = int(res[0]['n_messages']) if res[0]['status'] == abi.DECODE_OK else 0
+    return res[0].copy(), out[:n].copy()

@@ -36,3 +36,21 @@ def dense(shape, idx, val):
     a = np.zeros(int(np.prod(shape)), dtype=np.float32)
     a[idx] = val
     return a.reshape([int(x) for x in shape])
+
+
+def decode_inputs(s):
+    """(grid buffer, MstDecodeSong) for a golden song: what style_transfer.save feeds decode_midi."""
+    from mst_native import abi
+    p = dense(s['pitched_shape'], s['pitched_idx'], s['pitched_val'])
+    C, B = int(s['pitched_shape'][0]), int(s['pitched_shape'][1])
+    parts = [p.ravel()]
+    has_u = 'unpitched_shape' in s
+    if has_u:
+        parts.append(dense(s['unpitched_shape'], s['unpitched_idx'], s['unpitched_val']).ravel())
+    grids = np.ascontiguousarray(np.concatenate(parts))
+    g = s['info']
+    info = dict(ticks_per_beat=g[0], numerator=g[1], denominator_log2=g[2], ticks_per_bar=g[4], n_beats=g[6],
+                tempo=g[7], tonic=s['scale'][0], mode=s['scale'][1])
+    d = abi.make_decode_song(info, C, has_u, B, instrument_ids=list(s['instruments']), duration=int(g[3]),
+                             pitched_offset=0, unpitched_offset=p.size)
+    return grids, d
