@@ -242,10 +242,12 @@ typedef struct MstDecodeResult {
     int32_t  max_delta;          /* second2tick(1, ticks_per_beat, tempo) */
 } MstDecodeResult;
 
-size_t mst_decode_workspace_bytes(uint32_t n_songs, uint64_t grid_floats, uint64_t msg_capacity);
+/* n_chunks = sum over songs of (n_pitched + has_unpitched) * n_bars (the caller built the song table).
+ * d_grids is written only when a song asks for write_back. */
+size_t mst_decode_workspace_bytes(uint32_t n_songs, uint64_t n_chunks, uint64_t msg_capacity);
 
-int mst_decode_batch_device(float *d_grids, uint64_t grid_floats,
-                            const MstDecodeSong *d_songs, uint32_t n_songs,
+int mst_decode_batch_device(float *d_grids,
+                            const MstDecodeSong *d_songs, uint32_t n_songs, uint64_t n_chunks,
                             MstOutMsg *d_msgs, uint64_t msg_capacity,
                             MstDecodeResult *d_results,
                             void *d_workspace, size_t workspace_bytes, void *stream);

@@ -23,6 +23,7 @@ COMMON = ['-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC', '-Xcompiler',
 UNITS = [
     ('mst_lib.cu', []),
     ('mst_encode.cu', ['-fmad=false']),
+    ('mst_decode.cu', ['-fmad=false']),
     ('mst_smf.cpp', []),
 ]
 

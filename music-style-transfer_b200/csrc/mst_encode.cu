@@ -27,11 +27,10 @@
 #include <algorithm>
 
 #include "mst_device.cuh"
+#include "mst_sort.cuh"
 
 namespace {
 
-constexpr int kSortThreads = 1024;
-constexpr int kSortWarps = kSortThreads / 32;
 constexpr uint32_t kClassGlobal = 16;     // messages without a channel attribute that matter
 constexpr uint32_t kClassPrefixHi = 17;   // channel_prefix with channel > 15 (only counts for `duration`)
 constexpr uint32_t kClassEnd = 18;        // first class that is not walked
@@ -141,64 +140,6 @@ __device__ __forceinline__ uint32_t event_class(const MstEvent &e) {
 // in one stable LSD radix sort on key = class << 24 | tick.  Stability keeps (track, in-track index)
 // order for equal ticks because the input is track-major.
 // ------------------------------------------------------------------------------------------------
-__device__ void radix_pass(const uint32_t *kin, const uint32_t *vin, uint32_t *kout, uint32_t *vout, uint32_t n,
-                           int shift, uint32_t (*whist)[256], uint32_t *scan_tmp, int *skip_flag) {
-    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (unsigned i = tid; i < kSortWarps * 256; i += kSortThreads) (&whist[0][0])[i] = 0;
-    if (tid == 0) *skip_flag = 0;
-    __syncthreads();
-    const uint32_t per = ((n + kSortThreads - 1) / kSortThreads) * 32;
-    const uint32_t lo = min(n, warp * per), hi = min(n, lo + per);
-    for (uint32_t b = lo; b < hi; b += 32) {
-        uint32_t i = b + lane;
-        bool valid = i < hi;
-        unsigned act = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            uint32_t d = (kin[i] >> shift) & 255u;
-            unsigned peers = __match_any_sync(act, d);
-            if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
-        }
-        __syncwarp();
-    }
-    __syncthreads();
-    uint32_t total = 0;
-    if (tid < 256) {
-        for (int w = 0; w < kSortWarps; w++) {
-            uint32_t t = whist[w][tid];
-            whist[w][tid] = total;
-            total += t;
-        }
-        if (total == n) *skip_flag = 1;
-    }
-    uint32_t grand;
-    uint32_t base = block_exclusive_scan(tid < 256 ? total : 0u, scan_tmp, &grand);
-    if (tid < 256)
-        for (int w = 0; w < kSortWarps; w++) whist[w][tid] += base;
-    __syncthreads();
-    if (*skip_flag) {   // every key has the same digit: the pass is the identity
-        for (uint32_t i = tid; i < n; i += kSortThreads) { kout[i] = kin[i]; vout[i] = vin[i]; }
-        __syncthreads();
-        return;
-    }
-    for (uint32_t b = lo; b < hi; b += 32) {
-        uint32_t i = b + lane;
-        bool valid = i < hi;
-        unsigned act = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            uint32_t k = kin[i], v = vin[i];
-            uint32_t d = (k >> shift) & 255u;
-            unsigned peers = __match_any_sync(act, d);
-            uint32_t dst = whist[warp][d] + __popc(peers & lanemask_lt());
-            kout[dst] = k;
-            vout[dst] = v;
-            __syncwarp(act);
-            if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
-        }
-        __syncwarp();
-    }
-    __syncthreads();
-}
-
 __global__ void __launch_bounds__(kSortThreads, 1)
 k_sort(const MstEvent *__restrict__ ev, const MstSongIn *__restrict__ songs, Workspace ws) {
     __shared__ uint32_t whist[kSortWarps][256];

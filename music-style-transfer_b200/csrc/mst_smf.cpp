@@ -191,3 +191,71 @@ extern "C" int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent 
     if (out && count > capacity) return MST_E_CAPACITY;
     return (int64_t)count;
 }
+
+// ------------------------------------------------------------------------------------------------
+// SMF writer: create_midi's track layout (style/midi.py:125-168) serialised the way mido's
+// MidiFile.save does (running status for channel messages, meta events reset it).
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct Writer {
+    uint8_t *out;
+    size_t cap, n;
+    void put(uint8_t b) { if (out && n < cap) out[n] = b; n++; }
+    void varint(uint32_t v) {
+        uint8_t tmp[5]; int k = 0;
+        tmp[k++] = v & 0x7F; v >>= 7;
+        while (v) { tmp[k++] = (v & 0x7F) | 0x80; v >>= 7; }
+        while (k) put(tmp[--k]);
+    }
+};
+}  // namespace
+
+extern "C" int64_t mst_smf_write(const MstDecodeSong *song, const MstOutMsg *msgs, uint32_t n_messages,
+                                 int32_t eot_delta, uint8_t *out, size_t capacity, size_t *n_needed) {
+    Writer w{out, capacity, 0};
+    const char hdr[8] = {'M', 'T', 'h', 'd', 0, 0, 0, 6};
+    for (int i = 0; i < 8; i++) w.put((uint8_t)hdr[i]);
+    w.put(0); w.put(1);                       // type 1 (MidiFile() default)
+    w.put(0); w.put(1);                       // one track
+    w.put((uint8_t)((song->ticks_per_beat >> 8) & 0xFF)); w.put((uint8_t)(song->ticks_per_beat & 0xFF));
+    const char trk[4] = {'M', 'T', 'r', 'k'};
+    for (int i = 0; i < 4; i++) w.put((uint8_t)trk[i]);
+    const size_t len_pos = w.n;
+    for (int i = 0; i < 4; i++) w.put(0);
+    const size_t start = w.n;
+    // MetaMessage('time_signature', numerator, denominator): clocks_per_click 24, notated_32nd 8 (mido defaults)
+    w.put(0); w.put(0xFF); w.put(0x58); w.put(4);
+    w.put((uint8_t)song->numerator); w.put((uint8_t)song->denominator_log2); w.put(24); w.put(8);
+    w.put(0); w.put(0xFF); w.put(0x51); w.put(3);
+    w.put((uint8_t)((song->tempo >> 16) & 0xFF)); w.put((uint8_t)((song->tempo >> 8) & 0xFF)); w.put((uint8_t)(song->tempo & 0xFF));
+    int running = -1;
+    for (int c = 0; c < song->n_pitched; c++) {           // one program_change per non-9 channel (:139-145)
+        const int ch = song->channel_id[c];
+        if (ch == 9) continue;
+        const int prog = song->instrument_id[c];
+        if (prog < 0 || prog > 127 || ch > 15) return MST_E_INVALID;   // mido rejects the Message
+        const int status = 0xC0 | ch;
+        w.put(0);
+        if (status != running) w.put((uint8_t)status);
+        w.put((uint8_t)prog);
+        running = status;
+    }
+    for (uint32_t i = 0; i < n_messages; i++) {
+        const MstOutMsg &m = msgs[i];
+        const int status = (m.is_on ? 0x90 : 0x80) | (m.channel & 0x0F);
+        w.varint((uint32_t)m.delta);
+        if (status != running) w.put((uint8_t)status);
+        w.put(m.note); w.put(m.velocity);
+        running = status;
+    }
+    w.varint((uint32_t)eot_delta);
+    w.put(0xFF); w.put(0x2F); w.put(0);
+    const size_t len = w.n - start;
+    if (out && w.n <= capacity) {
+        out[len_pos] = (uint8_t)(len >> 24); out[len_pos + 1] = (uint8_t)(len >> 16);
+        out[len_pos + 2] = (uint8_t)(len >> 8); out[len_pos + 3] = (uint8_t)len;
+    }
+    if (n_needed) *n_needed = w.n;
+    if (!out || w.n > capacity) return MST_E_CAPACITY;
+    return (int64_t)w.n;
+}

@@ -1,0 +1,69 @@
+// mst_sort.cuh — stable LSD radix sort of (key, value) pairs by one 1024-thread CTA, in global memory.
+// Used for merge_tracks' stable sort by tick (encode) and for create_midi's stable sort by time (decode).
+#pragma once
+#include "mst_device.cuh"
+
+constexpr int kSortThreads = 1024;
+constexpr int kSortWarps = kSortThreads / 32;
+
+// One 8-bit pass.  Every warp owns a contiguous segment of the input, so the relative order of equal
+// digits is preserved: warp-private digit offsets come from a per-digit scan over the warps, ranks
+// inside a 32-element strip from match_any.  whist: [kSortWarps][256] words of shared memory.
+__device__ inline void radix_pass(const uint32_t *kin, const uint32_t *vin, uint32_t *kout, uint32_t *vout, uint32_t n,
+                           int shift, uint32_t (*whist)[256], uint32_t *scan_tmp, int *skip_flag) {
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (unsigned i = tid; i < kSortWarps * 256; i += kSortThreads) (&whist[0][0])[i] = 0;
+    if (tid == 0) *skip_flag = 0;
+    __syncthreads();
+    const uint32_t per = ((n + kSortThreads - 1) / kSortThreads) * 32;
+    const uint32_t lo = min(n, warp * per), hi = min(n, lo + per);
+    for (uint32_t b = lo; b < hi; b += 32) {
+        uint32_t i = b + lane;
+        bool valid = i < hi;
+        unsigned act = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            uint32_t d = (kin[i] >> shift) & 255u;
+            unsigned peers = __match_any_sync(act, d);
+            if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    uint32_t total = 0;
+    if (tid < 256) {
+        for (int w = 0; w < kSortWarps; w++) {
+            uint32_t t = whist[w][tid];
+            whist[w][tid] = total;
+            total += t;
+        }
+        if (total == n) *skip_flag = 1;
+    }
+    uint32_t grand;
+    uint32_t base = block_exclusive_scan(tid < 256 ? total : 0u, scan_tmp, &grand);
+    if (tid < 256)
+        for (int w = 0; w < kSortWarps; w++) whist[w][tid] += base;
+    __syncthreads();
+    if (*skip_flag) {   // every key has the same digit: the pass is the identity
+        for (uint32_t i = tid; i < n; i += kSortThreads) { kout[i] = kin[i]; vout[i] = vin[i]; }
+        __syncthreads();
+        return;
+    }
+    for (uint32_t b = lo; b < hi; b += 32) {
+        uint32_t i = b + lane;
+        bool valid = i < hi;
+        unsigned act = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            uint32_t k = kin[i], v = vin[i];
+            uint32_t d = (k >> shift) & 255u;
+            unsigned peers = __match_any_sync(act, d);
+            uint32_t dst = whist[warp][d] + __popc(peers & lanemask_lt());
+            kout[dst] = k;
+            vout[dst] = v;
+            __syncwarp(act);
+            if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+}
+

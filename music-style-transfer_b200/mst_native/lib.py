@@ -22,6 +22,7 @@ EXPORTS = [
     'mst_smf_parse',
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
     'mst_encode_host_workspace_bytes', 'mst_encode_batch_host',
+    'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write',
 ]
 
 
@@ -60,6 +61,15 @@ def load():
     L.mst_encode_batch_host.argtypes = [
         ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
         ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    L.mst_decode_workspace_bytes.restype = ctypes.c_size_t
+    L.mst_decode_workspace_bytes.argtypes = [ctypes.c_uint32, ctypes.c_uint64, ctypes.c_uint64]
+    L.mst_decode_batch_device.restype = ctypes.c_int
+    L.mst_decode_batch_device.argtypes = [
+        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64,
+        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    L.mst_smf_write.restype = ctypes.c_int64
+    L.mst_smf_write.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int32, ctypes.c_void_p,
+                                ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
     if L.mst_abi_version() != abi.MST_ABI_VERSION:
         raise MstError('libmst_b200.so ABI version mismatch: rebuild')
     _lib = L
@@ -186,3 +196,52 @@ def song_grids(info, arena):
     if U:
         unpitched = arena[uo:uo + U * B * nb * abi.UNPITCHED_BEAT_FLOATS].view(U, B, nb, 10, 47, 2)
     return pitched, unpitched
+
+
+# ---------------------------------------------------------------------------------- decode
+def decode_chunks(dsongs):
+    """Number of (channel, bar) chunks of a MstDecodeSong table."""
+    return int(((dsongs['n_pitched'].astype(np.int64) + (dsongs['has_unpitched'] != 0)) * dsongs['n_bars']).sum())
+
+
+def decode_batch(grids, dsongs, msg_capacity=None, stream=None):
+    """grids: float32 CUDA tensor the songs' offsets index into; dsongs: ndarray[DECODE_SONG_DTYPE].
+    Returns (results ndarray[DECODE_RESULT_DTYPE], messages ndarray[OUT_MSG_DTYPE]); song i's messages are
+    messages[msg_offset : msg_offset + n_messages].  Grows the message buffer once if it was too small."""
+    import torch
+    L = require_gpu()
+    dsongs = np.ascontiguousarray(dsongs, dtype=abi.DECODE_SONG_DTYPE).reshape(-1)
+    S = len(dsongs)
+    n_chunks = decode_chunks(dsongs)
+    dev = grids.device
+    d_songs = torch.from_numpy(dsongs.view(np.uint8).reshape(-1)).to(dev)
+    d_res = torch.empty(S * abi.DECODE_RESULT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    cap = int(msg_capacity) if msg_capacity else max(1024, n_chunks * 16)
+    s = torch.cuda.current_stream(dev) if stream is None else stream
+    while True:
+        d_msgs = torch.empty(cap * abi.OUT_MSG_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        wsb = L.mst_decode_workspace_bytes(S, n_chunks, cap)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+        check(L.mst_decode_batch_device(grids.data_ptr(), d_songs.data_ptr(), S, n_chunks, d_msgs.data_ptr(), cap,
+                                        d_res.data_ptr(), ws.data_ptr(), wsb, s.cuda_stream))
+        res = d_res.cpu().numpy().view(abi.DECODE_RESULT_DTYPE).copy()
+        if (res['status'] == abi.DECODE_CAPACITY).any():
+            cap = int(res['n_messages'].astype(np.int64).sum())
+            continue
+        break
+    msgs = d_msgs.cpu().numpy().view(abi.OUT_MSG_DTYPE)
+    return res, msgs
+
+
+def smf_write(dsong, msgs, eot_delta):
+    """Serialise one decoded song to Standard MIDI File bytes (mid.save, style_transfer.py:98)."""
+    L = load()
+    d = np.ascontiguousarray(dsong.reshape(1))
+    msgs = np.ascontiguousarray(msgs, dtype=abi.OUT_MSG_DTYPE)
+    cap = 64 + 8 * abi.MAX_DECODE_CHANNELS + 8 * len(msgs)
+    out = np.empty(cap, dtype=np.uint8)
+    need = ctypes.c_size_t(0)
+    n = L.mst_smf_write(_np_ptr(d), _np_ptr(msgs), len(msgs), int(eot_delta), _np_ptr(out), cap, ctypes.byref(need))
+    if n < 0:
+        raise MstError(f'mst_smf_write failed ({n})')
+    return out[:n].tobytes()

@@ -133,3 +133,18 @@ def test_smf_parse_edge_cases(L):
     big = bytes([0x85, 0x80, 0x80, 0x00])   # delta 10485760 > 1e7
     events, _ = lib.smf_parse(_smf([bytes([0, 0x90, 60, 100]) + big + bytes([0x80, 60, 0]) + eot]))
     assert len(events) == 1
+
+
+def test_smf_write_matches_reference_saved_bytes(L):
+    """mst_smf_write of the oracle-decoded messages == the bytes the reference's mid.save() produced."""
+    import oracle_lib
+    n = 0
+    for name in ('codec_bundled', 'codec_synth'):
+        for s in gu.load_songs(name):
+            if 'decoded_smf' not in s:
+                continue
+            grids, d = gu.decode_inputs(s)
+            res, msgs = oracle_lib.decode_song(grids, d)
+            assert lib.smf_write(d, msgs, int(res['eot_delta'])) == bytes(s['decoded_smf']), s['name']
+            n += 1
+    assert n >= 40
