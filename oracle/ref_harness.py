@@ -90,15 +90,14 @@ def build_model(seed=108):
     torch.manual_seed(seed)
     beat_size, bar_size, n_rhythm_features = 64, 128, 8
     style_size, melody_size, rhythm_size = 256, 8, 32
-    model = m.StyleTransferModel(
-        m.PitchedChannelsEncoder(beat_size, bar_size, d.instrument_size),
-        m.UnpitchedChannelsEncoder(beat_size, bar_size),
-        m.StyleEncoder(style_size, bar_size, d.instrument_size),
-        m.MelodyEncoder(melody_size, beat_size, bar_size, d.instrument_size),
-        m.PitchedRhythmEncoder(rhythm_size, beat_size, bar_size, d.instrument_size),
-        m.UnpitchedRhythmEncoder(rhythm_size, beat_size, bar_size),
-        m.SongInfoModel(n_rhythm_features, style_size, rhythm_size, d.n_instruments),
-        m.PitchedStyleApplier(style_size, melody_size, rhythm_size, d.instrument_size),
-        m.UnpitchedStyleApplier(style_size, rhythm_size),
-    )
-    return model
+    # construction order of train-model.py:62-76 (it fixes the RNG stream, hence the weights)
+    pce = m.PitchedChannelsEncoder(beat_size, bar_size, d.instrument_size)
+    uce = m.UnpitchedChannelsEncoder(beat_size, bar_size)
+    pre = m.PitchedRhythmEncoder(rhythm_size, beat_size, bar_size, d.instrument_size)
+    ure = m.UnpitchedRhythmEncoder(rhythm_size, beat_size, bar_size)
+    se = m.StyleEncoder(style_size, bar_size, d.instrument_size)
+    me = m.MelodyEncoder(melody_size, beat_size, bar_size, d.instrument_size)
+    sim = m.SongInfoModel(n_rhythm_features, style_size, rhythm_size, d.n_instruments)
+    psa = m.PitchedStyleApplier(style_size, melody_size, rhythm_size, d.instrument_size)
+    usa = m.UnpitchedStyleApplier(style_size, rhythm_size)
+    return m.StyleTransferModel(pce, uce, se, me, pre, ure, sim, psa, usa)
