@@ -259,6 +259,44 @@ int mst_decode_batch_device(float *d_grids,
 int64_t mst_smf_write(const MstDecodeSong *song, const MstOutMsg *h_msgs, uint32_t n_messages,
                       int32_t eot_delta, uint8_t *out, size_t capacity, size_t *n_needed);
 
+/* ---------------------------------------------------------------- model (style/model.py) */
+/* Replaces StyleTransferModel.forward / extract_style / predict_song_info / apply_style
+ * (style/model.py:751-793) with its nine sub-modules, get_total_loss (:935-997), loss.backward() and
+ * torch.optim.Adam.step (train-model.py:113-154) for a batch of N independent batch-1 samples of one shape.
+ * Parameters live in ONE flat fp32 buffer; mst_model_param_* describe its layout by state-dict name. */
+typedef struct MstModelShape {
+    int32_t n_samples;      /* N independent samples (the reference runs N = 1) */
+    int32_t n_channels;     /* C pitched channels */
+    int32_t n_bars;         /* B */
+    int32_t n_beats;        /* beats per bar (time-signature numerator) */
+    int32_t has_unpitched;  /* drums grid present */
+} MstModelShape;
+
+typedef struct MstModelOutputs {   /* device pointers into the workspace, valid until it is reused */
+    float *instruments;  /* (N, 41) logits */
+    float *mode;         /* (N, 2) logits */
+    float *bpm;          /* (N) */
+    float *pitched;      /* (N, C, B, nb, 10, 56, 5) */
+    float *unpitched;    /* (N, B, nb, 10, 47, 2) or NULL */
+    float *style;        /* (N, 256) */
+    float *melody;       /* (N, B, nb, 10, 56, 8) */
+    float *rhythm;       /* (N, B, nb, 10, 32) */
+} MstModelOutputs;
+
+int         mst_model_param_count(void);
+const char *mst_model_param_name(int i);
+long long   mst_model_param_numel(int i);
+long long   mst_model_param_offset(int i);   /* i == count: total number of parameters */
+
+size_t mst_model_workspace_bytes(const MstModelShape *shape, int training);
+
+/* d_pitched (N,C,B,nb,10,56,5), d_unpitched (N,B,nb,10,47,2) or NULL, d_features (N,C,51), d_mode (N,2), d_bpm (N).
+ * training != 0 keeps what the backward pass needs (workspace sized with training = 1). */
+int mst_model_forward(const float *d_params, const MstModelShape *shape, const float *d_pitched,
+                      const float *d_unpitched, const float *d_features, const float *d_mode, const float *d_bpm,
+                      MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes, int training,
+                      void *stream, int *n_launches);
+
 #ifdef __cplusplus
 }
 #endif

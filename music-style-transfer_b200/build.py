@@ -24,6 +24,7 @@ UNITS = [
     ('mst_lib.cu', []),
     ('mst_encode.cu', ['-fmad=false']),
     ('mst_decode.cu', ['-fmad=false']),
+    ('mst_model.cu', []),
     ('mst_smf.cpp', []),
 ]
 

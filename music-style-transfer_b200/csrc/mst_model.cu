@@ -1,0 +1,682 @@
+// mst_model.cu — training step of the style-transfer network (style/model.py) on sm_100a: host-side runtime.
+//
+// One flat fp32 parameter buffer (980 325 values, table below) + one flat gradient buffer; activations live in
+// a caller-provided arena.  A batch is N *independent* batch-1 samples of identical shape (C, B, T, drums):
+// every reduction of the reference that spans the batch dimension (combine, the loss sums) is segmented per
+// sample, and gradients are summed over samples — exactly train-model.py's iter_size accumulation.
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "mst_model_tails.cuh"
+
+using namespace mstm;
+
+// ------------------------------------------------------------------------------------------------ parameters
+// X(id, state-dict name, numel).  Names are the reference's (style/model.py); Python maps by name.
+// octave_linear / scale_degree_linear weights (and biases) are adjacent on purpose: they act as one matrix.
+#define MST_PARAMS(X) \
+    X(pce_conv_w, "pitched_channels_encoder.beats_conv.module.weight", 57 * 50 * 14) \
+    X(pce_conv_b, "pitched_channels_encoder.beats_conv.module.bias", 57) \
+    X(pce_il_w, "pitched_channels_encoder.instruments_linear.weight", 58 * 51) \
+    X(pce_il_b, "pitched_channels_encoder.instruments_linear.bias", 58) \
+    X(pce_lin_w, "pitched_channels_encoder.linear.weight", 64 * 514) \
+    X(pce_lin_b, "pitched_channels_encoder.linear.bias", 64) \
+    X(pce_bl_wih, "pitched_channels_encoder.beats_lstm.module.weight_ih_l0", 256 * 64) \
+    X(pce_bl_whh, "pitched_channels_encoder.beats_lstm.module.weight_hh_l0", 256 * 64) \
+    X(pce_bl_bih, "pitched_channels_encoder.beats_lstm.module.bias_ih_l0", 256) \
+    X(pce_bl_bhh, "pitched_channels_encoder.beats_lstm.module.bias_hh_l0", 256) \
+    X(pce_br_wih, "pitched_channels_encoder.bars_lstm.weight_ih_l0", 256 * 64) \
+    X(pce_br_whh, "pitched_channels_encoder.bars_lstm.weight_hh_l0", 256 * 64) \
+    X(pce_br_bih, "pitched_channels_encoder.bars_lstm.bias_ih_l0", 256) \
+    X(pce_br_bhh, "pitched_channels_encoder.bars_lstm.bias_hh_l0", 256) \
+    X(pce_br_wih_r, "pitched_channels_encoder.bars_lstm.weight_ih_l0_reverse", 256 * 64) \
+    X(pce_br_whh_r, "pitched_channels_encoder.bars_lstm.weight_hh_l0_reverse", 256 * 64) \
+    X(pce_br_bih_r, "pitched_channels_encoder.bars_lstm.bias_ih_l0_reverse", 256) \
+    X(pce_br_bhh_r, "pitched_channels_encoder.bars_lstm.bias_hh_l0_reverse", 256) \
+    X(uce_lin_w, "unpitched_channels_encoder.linear.weight", 64 * 940) \
+    X(uce_lin_b, "unpitched_channels_encoder.linear.bias", 64) \
+    X(uce_bl_wih, "unpitched_channels_encoder.beats_lstm.module.weight_ih_l0", 256 * 64) \
+    X(uce_bl_whh, "unpitched_channels_encoder.beats_lstm.module.weight_hh_l0", 256 * 64) \
+    X(uce_bl_bih, "unpitched_channels_encoder.beats_lstm.module.bias_ih_l0", 256) \
+    X(uce_bl_bhh, "unpitched_channels_encoder.beats_lstm.module.bias_hh_l0", 256) \
+    X(uce_br_wih, "unpitched_channels_encoder.bars_lstm.weight_ih_l0", 256 * 64) \
+    X(uce_br_whh, "unpitched_channels_encoder.bars_lstm.weight_hh_l0", 256 * 64) \
+    X(uce_br_bih, "unpitched_channels_encoder.bars_lstm.bias_ih_l0", 256) \
+    X(uce_br_bhh, "unpitched_channels_encoder.bars_lstm.bias_hh_l0", 256) \
+    X(uce_br_wih_r, "unpitched_channels_encoder.bars_lstm.weight_ih_l0_reverse", 256 * 64) \
+    X(uce_br_whh_r, "unpitched_channels_encoder.bars_lstm.weight_hh_l0_reverse", 256 * 64) \
+    X(uce_br_bih_r, "unpitched_channels_encoder.bars_lstm.bias_ih_l0_reverse", 256) \
+    X(uce_br_bhh_r, "unpitched_channels_encoder.bars_lstm.bias_hh_l0_reverse", 256) \
+    X(se_lstm_wih, "style_encoder.bars_lstm.weight_ih_l0", 768 * 128) \
+    X(se_lstm_whh, "style_encoder.bars_lstm.weight_hh_l0", 768 * 192) \
+    X(se_lstm_bih, "style_encoder.bars_lstm.bias_ih_l0", 768) \
+    X(se_lstm_bhh, "style_encoder.bars_lstm.bias_hh_l0", 768) \
+    X(se_il_w, "style_encoder.instruments_linear.weight", 39 * 51) \
+    X(se_il_b, "style_encoder.instruments_linear.bias", 39) \
+    X(se_ml_w, "style_encoder.mode_linear.weight", 13 * 2) \
+    X(se_ml_b, "style_encoder.mode_linear.bias", 13) \
+    X(se_bp_w, "style_encoder.bpm_linear.weight", 7) \
+    X(se_bp_b, "style_encoder.bpm_linear.bias", 7) \
+    X(se_lin_w, "style_encoder.linear.weight", 256 * 251) \
+    X(se_lin_b, "style_encoder.linear.bias", 256) \
+    X(me_bl_w, "melody_encoder.beats_linear.weight", 36 * 64) \
+    X(me_bl_b, "melody_encoder.beats_linear.bias", 36) \
+    X(me_br_w, "melody_encoder.bars_linear.weight", 68 * 128) \
+    X(me_br_b, "melody_encoder.bars_linear.bias", 68) \
+    X(me_il_w, "melody_encoder.instruments_linear.weight", 8 * 51) \
+    X(me_il_b, "melody_encoder.instruments_linear.bias", 8) \
+    X(me_oct_w, "melody_encoder.octave_linear.weight", 64 * 112) \
+    X(me_deg_w, "melody_encoder.scale_degree_linear.weight", 56 * 112) \
+    X(me_oct_b, "melody_encoder.octave_linear.bias", 64) \
+    X(me_deg_b, "melody_encoder.scale_degree_linear.bias", 56) \
+    X(me_ch_w, "melody_encoder.channels_linear.weight", 7 * 5) \
+    X(me_ch_b, "melody_encoder.channels_linear.bias", 7) \
+    X(me_lin_w, "melody_encoder.linear.weight", 8 * 15) \
+    X(me_lin_b, "melody_encoder.linear.bias", 8) \
+    X(pre_bl_w, "pitched_rhythm_encoder.beats_linear.weight", 48 * 64) \
+    X(pre_bl_b, "pitched_rhythm_encoder.beats_linear.bias", 48) \
+    X(pre_br_w, "pitched_rhythm_encoder.bars_linear.weight", 40 * 128) \
+    X(pre_br_b, "pitched_rhythm_encoder.bars_linear.bias", 40) \
+    X(pre_ch_w, "pitched_rhythm_encoder.channels_linear.weight", 16 * 280) \
+    X(pre_ch_b, "pitched_rhythm_encoder.channels_linear.bias", 16) \
+    X(pre_il_w, "pitched_rhythm_encoder.instruments_linear.weight", 21 * 51) \
+    X(pre_il_b, "pitched_rhythm_encoder.instruments_linear.bias", 21) \
+    X(pre_ml_w, "pitched_rhythm_encoder.mode_linear.weight", 5 * 2) \
+    X(pre_ml_b, "pitched_rhythm_encoder.mode_linear.bias", 5) \
+    X(pre_bp_w, "pitched_rhythm_encoder.bpm_linear.weight", 5) \
+    X(pre_bp_b, "pitched_rhythm_encoder.bpm_linear.bias", 5) \
+    X(pre_lin_w, "pitched_rhythm_encoder.linear.weight", 32 * 135) \
+    X(pre_lin_b, "pitched_rhythm_encoder.linear.bias", 32) \
+    X(ure_bl_w, "unpitched_rhythm_encoder.beats_linear.weight", 48 * 64) \
+    X(ure_bl_b, "unpitched_rhythm_encoder.beats_linear.bias", 48) \
+    X(ure_br_w, "unpitched_rhythm_encoder.bars_linear.weight", 40 * 128) \
+    X(ure_br_b, "unpitched_rhythm_encoder.bars_linear.bias", 40) \
+    X(ure_ch_w, "unpitched_rhythm_encoder.channels_linear.weight", 16 * 94) \
+    X(ure_ch_b, "unpitched_rhythm_encoder.channels_linear.bias", 16) \
+    X(ure_bp_w, "unpitched_rhythm_encoder.bpm_linear.weight", 5) \
+    X(ure_bp_b, "unpitched_rhythm_encoder.bpm_linear.bias", 5) \
+    X(ure_lin_w, "unpitched_rhythm_encoder.linear.weight", 32 * 109) \
+    X(ure_lin_b, "unpitched_rhythm_encoder.linear.bias", 32) \
+    X(sim_bl_wih, "song_info_model.beats_lstm.module.weight_ih_l0", 36 * 320) \
+    X(sim_bl_whh, "song_info_model.beats_lstm.module.weight_hh_l0", 36 * 9) \
+    X(sim_bl_bih, "song_info_model.beats_lstm.module.bias_ih_l0", 36) \
+    X(sim_bl_bhh, "song_info_model.beats_lstm.module.bias_hh_l0", 36) \
+    X(sim_br_wih, "song_info_model.bars_lstm.weight_ih_l0", 32 * 9) \
+    X(sim_br_whh, "song_info_model.bars_lstm.weight_hh_l0", 32 * 8) \
+    X(sim_br_bih, "song_info_model.bars_lstm.bias_ih_l0", 32) \
+    X(sim_br_bhh, "song_info_model.bars_lstm.bias_hh_l0", 32) \
+    X(sim_si_w, "song_info_model.style_instruments_linear.weight", 8 * 256) \
+    X(sim_si_b, "song_info_model.style_instruments_linear.bias", 8) \
+    X(sim_ri_w, "song_info_model.rhythm_instruments_linear.weight", 10 * 8) \
+    X(sim_ri_b, "song_info_model.rhythm_instruments_linear.bias", 10) \
+    X(sim_i_w, "song_info_model.instruments_linear.weight", 41 * 18) \
+    X(sim_i_b, "song_info_model.instruments_linear.bias", 41) \
+    X(sim_sm_w, "song_info_model.style_mode_linear.weight", 2 * 256) \
+    X(sim_sm_b, "song_info_model.style_mode_linear.bias", 2) \
+    X(sim_rm_w, "song_info_model.rhythm_mode_linear.weight", 2 * 8) \
+    X(sim_rm_b, "song_info_model.rhythm_mode_linear.bias", 2) \
+    X(sim_m_w, "song_info_model.mode_linear.weight", 2 * 4) \
+    X(sim_m_b, "song_info_model.mode_linear.bias", 2) \
+    X(sim_sb_w, "song_info_model.style_bpm_linear.weight", 2 * 256) \
+    X(sim_sb_b, "song_info_model.style_bpm_linear.bias", 2) \
+    X(sim_rb_w, "song_info_model.rhythm_bpm_linear.weight", 2 * 8) \
+    X(sim_rb_b, "song_info_model.rhythm_bpm_linear.bias", 2) \
+    X(sim_b_w, "song_info_model.bpm_linear.weight", 4) \
+    X(sim_b_b, "song_info_model.bpm_linear.bias", 1) \
+    X(psa_sl_w, "pitched_style_applier.style_linear.weight", 66 * 256) \
+    X(psa_sl_b, "pitched_style_applier.style_linear.bias", 66) \
+    X(psa_rl_w, "pitched_style_applier.rhythm_linear.weight", 10 * 32) \
+    X(psa_rl_b, "pitched_style_applier.rhythm_linear.bias", 10) \
+    X(psa_il_w, "pitched_style_applier.instruments_linear.weight", 12 * 51) \
+    X(psa_il_b, "pitched_style_applier.instruments_linear.bias", 12) \
+    X(psa_oct_w, "pitched_style_applier.octave_linear.weight", 240 * 88) \
+    X(psa_deg_w, "pitched_style_applier.scale_degree_linear.weight", 210 * 88) \
+    X(psa_oct_b, "pitched_style_applier.octave_linear.bias", 240) \
+    X(psa_deg_b, "pitched_style_applier.scale_degree_linear.bias", 210) \
+    X(psa_ml_w, "pitched_style_applier.melody_linear.weight", 20 * 8) \
+    X(psa_ml_b, "pitched_style_applier.melody_linear.bias", 20) \
+    X(psa_lin_w, "pitched_style_applier.linear.weight", 5 * 50) \
+    X(psa_lin_b, "pitched_style_applier.linear.bias", 5) \
+    X(usa_sl_w, "unpitched_style_applier.style_linear.weight", 650 * 256) \
+    X(usa_sl_b, "unpitched_style_applier.style_linear.bias", 650) \
+    X(usa_rl_w, "unpitched_style_applier.rhythm_linear.weight", 17 * 32) \
+    X(usa_rl_b, "unpitched_style_applier.rhythm_linear.bias", 17) \
+    X(usa_nl_w, "unpitched_style_applier.notes_linear.weight", 376 * 82) \
+    X(usa_nl_b, "unpitched_style_applier.notes_linear.bias", 376) \
+    X(usa_lin_w, "unpitched_style_applier.linear.weight", 2 * 8) \
+    X(usa_lin_b, "unpitched_style_applier.linear.bias", 2)
+
+enum ParamId {
+#define X(id, name, n) id,
+    MST_PARAMS(X)
+#undef X
+    kNumParams
+};
+static const char *const kParamNames[kNumParams] = {
+#define X(id, name, n) name,
+    MST_PARAMS(X)
+#undef X
+};
+static const int kParamNumel[kNumParams] = {
+#define X(id, name, n) n,
+    MST_PARAMS(X)
+#undef X
+};
+static long long g_param_off[kNumParams + 1];
+static bool g_param_off_ready = false;
+static void init_param_offsets() {
+    if (g_param_off_ready) return;
+    long long off = 0;
+    for (int i = 0; i < kNumParams; i++) { g_param_off[i] = off; off += kParamNumel[i]; }
+    g_param_off[kNumParams] = off;
+    g_param_off_ready = true;
+}
+
+extern "C" int mst_model_param_count(void) { return kNumParams; }
+extern "C" const char *mst_model_param_name(int i) { return (i >= 0 && i < kNumParams) ? kParamNames[i] : nullptr; }
+extern "C" long long mst_model_param_numel(int i) { return (i >= 0 && i < kNumParams) ? kParamNumel[i] : -1; }
+extern "C" long long mst_model_param_offset(int i) { init_param_offsets(); return (i >= 0 && i <= kNumParams) ? g_param_off[i] : -1; }
+
+// ------------------------------------------------------------------------------------------------ small glue kernels
+namespace {
+
+// out[s, k] = in[((s * T) + T - 1) * H + k]  (x[:, -1] of an LSTM output); backward adds into the same place
+__global__ void __launch_bounds__(256) k_take_last(const float *__restrict__ in, float *__restrict__ out, long long S, int T, int H) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < S * H; i += (long long)gridDim.x * blockDim.x) {
+        const long long s = i / H; const int k = (int)(i - s * H);
+        out[i] = in[(s * T + T - 1) * H + k];
+    }
+}
+__global__ void __launch_bounds__(256) k_put_last(const float *__restrict__ src, float *__restrict__ dst, long long S, int T, int H) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < S * H; i += (long long)gridDim.x * blockDim.x) {
+        const long long s = i / H; const int k = (int)(i - s * H);
+        dst[(s * T + T - 1) * H + k] += src[i];
+    }
+}
+__global__ void __launch_bounds__(256) k_add2(const float *a, const float *b, float *out, int n) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = a[i] + b[i];
+}
+// pair buffer [N, 2, M] <- a[N, M], b[N, M]   (and back, adding into da / db)
+__global__ void __launch_bounds__(256) k_pair_pack(const float *a, const float *b, float *pair, int N, long long M) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)N * M; i += (long long)gridDim.x * blockDim.x) {
+        const long long n = i / M, m = i - n * M;
+        pair[(n * 2) * M + m] = a[i];
+        pair[(n * 2 + 1) * M + m] = b[i];
+    }
+}
+__global__ void __launch_bounds__(256) k_pair_unpack_add(const float *dpair, float *da, float *db, int N, long long M) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)N * M; i += (long long)gridDim.x * blockDim.x) {
+        const long long n = i / M, m = i - n * M;
+        da[i] += dpair[(n * 2) * M + m];
+        db[i] += dpair[(n * 2 + 1) * M + m];
+    }
+}
+// bpm head (model.py:552-554): out = sigmoid(x) * 150 + 50
+__global__ void k_bpm_head(const float *x, float *out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = sigmoidf(x[i]) * 150.f + 50.f;
+}
+
+struct Arena {
+    char *base; size_t off; bool dry;
+    float *take(long long n_floats) {
+        const size_t o = off;
+        off = mst_align_up(off + (size_t)(n_floats > 0 ? n_floats : 1) * sizeof(float), 256);
+        return dry ? nullptr : (float *)(base + o);
+    }
+};
+
+inline int grid_for(long long n, int threads = 256, int cap = 148 * 16) {
+    long long b = (n + threads - 1) / threads;
+    return (int)std::max<long long>(1, std::min<long long>(b, cap));
+}
+
+struct Launcher {
+    cudaStream_t st;
+    int launches = 0;
+    cudaError_t err = cudaSuccess;
+    void check() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && err == cudaSuccess) err = e; launches++; }
+
+    // C[M,N] (op)= act(A·B + bias) with explicit strides
+    void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
+              int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int amode = 0) {
+        if (M <= 0 || N <= 0 || K <= 0) return;
+        GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
+        if (split_k > 1) g.accumulate = 2;
+        dim3 grid((N + kGemmTile - 1) / kGemmTile, (M + kGemmTile - 1) / kGemmTile, split_k);
+        if (amode == 0) k_gemm<0><<<grid, kGemmThreads, 0, st>>>(g); else k_gemm<1><<<grid, kGemmThreads, 0, st>>>(g);
+        check();
+    }
+    // Y[M,N] = act(X[M,K]·W[N,K]^T + bias)      (nn.Linear); W row stride ldw (column block of a wider weight)
+    void linear(const float *X, long long ldx, const float *W, long long ldw, const float *bias, float *Y, long long ldy,
+                int M, int N, int K, int act, int accumulate = 0) {
+        gemm(X, ldx, 1, W, 1, ldw, Y, ldy, M, N, K, bias, act, accumulate);
+    }
+    // dX[M,K] (+)= dY[M,N]·W[N,K]
+    void linear_dx(const float *dY, long long ldy, const float *W, long long ldw, float *dX, long long ldx, int M, int N, int K, int accumulate) {
+        gemm(dY, ldy, 1, W, ldw, 1, dX, ldx, M, K, N, nullptr, 0, accumulate);
+    }
+    // dW[N,K] += dY[M,N]^T·X[M,K]   (atomic accumulate, K-dimension of the GEMM = M rows, split over CTAs)
+    void linear_dw(const float *dY, long long ldy, const float *X, long long ldx, float *dW, long long ldw, int M, int N, int K) {
+        const int split = (int)std::max(1, std::min(64, M / 2048));
+        gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
+    }
+    void colsum(const float *in, float *out, long long rows, int cols) {
+        if (rows <= 0) return;
+        dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((rows + 63) / 64, 256)), (cols + 31) / 32);
+        k_colsum<<<grid, 256, 0, st>>>(in, out, rows, cols); check();
+    }
+    void fill(float *p, long long n, float v) { if (n > 0) { k_fill<<<grid_for(n), 256, 0, st>>>(p, n, v); check(); } }
+    void axpy(float *y, const float *x, long long n) { if (n > 0) { k_axpy<<<grid_for(n), 256, 0, st>>>(y, x, n); check(); } }
+    void act_grad(const float *dY, const float *Y, float *dPre, long long n) { k_act_grad<<<grid_for(n), 256, 0, st>>>(dY, Y, dPre, n); check(); }
+    void reduce_mid(const float *in, float *out, long long A, int L, long long inner, int accumulate) {
+        k_reduce_mid<<<grid_for(A * inner), 256, 0, st>>>(in, out, A, L, inner, accumulate); check();
+    }
+    void bcast(BcastArgs &a) {
+        const long long total = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f * a.cols;
+        k_bcast_add<<<grid_for(total), 256, 0, st>>>(a); check();
+    }
+    void take_last(const float *in, float *out, long long S, int T, int H) { k_take_last<<<grid_for(S * H), 256, 0, st>>>(in, out, S, T, H); check(); }
+    void put_last(const float *src, float *dst, long long S, int T, int H) { k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }
+
+    static size_t lstm_smem(int H, int G, bool w_smem) { return sizeof(float) * ((size_t)2 * G * H + (size_t)G * 4 * H + (w_smem ? (size_t)H * 4 * H : 0)); }
+    void lstm(LstmArgs a, bool backward) {
+        a.G = a.S >= 148 * 2 ? kLstmG : 1;
+        a.w_smem = ((size_t)a.H * 4 * a.H * sizeof(float) <= 96 * 1024) ? 1 : 0;
+        const size_t smem = lstm_smem(a.H, a.G, a.w_smem);
+        const int threads = std::max(32, (4 * a.H + 31) / 32 * 32);
+        const int blocks = (a.S + a.G - 1) / a.G;
+        if (backward) {
+            cudaFuncSetAttribute(k_lstm_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+            k_lstm_bwd<<<blocks, threads, smem, st>>>(a);
+        } else {
+            cudaFuncSetAttribute(k_lstm_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+            k_lstm_fwd<<<blocks, threads, smem, st>>>(a);
+        }
+        check();
+    }
+    void combine_fwd(CombineArgs a) {
+        fill(a.ss, (long long)a.N * a.K, 0.f);
+        dim3 g1((unsigned)std::max<long long>(1, std::min<long long>((a.M + 2047) / 2048, 64)), a.N * a.K);
+        k_combine_sumsq<<<g1, 256, 0, st>>>(a); check();
+        dim3 g2((unsigned)std::max<long long>(1, std::min<long long>((a.M + 255) / 256, 256)), a.N);
+        k_combine_fwd<<<g2, 256, 0, st>>>(a); check();
+    }
+    void combine_bwd(CombineArgs a) {
+        fill(a.stats, (long long)a.N * (a.K + 1), 0.f);
+        dim3 g1((unsigned)std::max<long long>(1, std::min<long long>((a.M + 2047) / 2048, 64)), a.N);
+        k_combine_bwd_stats<<<g1, 256, 0, st>>>(a); check();
+        dim3 g2((unsigned)std::max<long long>(1, std::min<long long>((a.M + 255) / 256, 256)), a.N);
+        k_combine_bwd<<<g2, 256, 0, st>>>(a); check();
+    }
+};
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ context
+namespace {
+
+__global__ void __launch_bounds__(256) k_transpose(const float *__restrict__ in, float *__restrict__ out, int rows, int cols) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < rows * cols; i += gridDim.x * blockDim.x) {
+        const int r = i / cols, c = i - r * cols;
+        out[c * rows + r] = in[i];
+    }
+}
+
+struct LstmBuf {
+    float *xproj, *gates, *cells, *hprev, *dgates, *bias_sum, *wt;
+    int S, T, H, I;
+    void carve(Arena &ar, int S_, int T_, int H_, int I_) {
+        S = S_; T = T_; H = H_; I = I_;
+        const long long st = (long long)S * T;
+        xproj = ar.take(st * 4 * H); gates = ar.take(st * 4 * H); cells = ar.take(st * H); hprev = ar.take(st * H);
+        dgates = ar.take(st * 4 * H); bias_sum = ar.take(4 * H); wt = ar.take((long long)H * 4 * H);
+    }
+};
+
+struct Ctx {
+    int N, C, B, T, U;
+    long long Rb, Rf, Rbf, Nb;      // beat rows (n,c,b,t), fraction rows, (n,b,t,f) rows, bar rows (n,b)
+    const float *P, *Ug, *F, *mode, *bpm;   // inputs
+    const float *prm;               // flat parameters
+    float *grad;                    // flat gradients (may be null for inference)
+    // permuted weights
+    float *wconv_p, *wpcelin_p, *wucelin_p;
+    // PCE
+    float *pce_conv, *pce_il, *pce_zi, *pce_zc, *pce_x, *pce_beats, *pce_last, *pce_ss, *pce_bars_in, *pce_bars;
+    LstmBuf pce_bl, pce_brf, pce_brr;
+    // PRE
+    float *pre_a1, *pre_a2, *pre_a3, *pre_a4, *pre_a5, *pre_a6, *pre_z[6], *pre_x, *pre_ss, *pre_out;
+    // UCE / URE
+    float *uce_lin, *uce_beats, *uce_last, *uce_ss, *uce_bars_in, *uce_bars;
+    LstmBuf uce_bl, uce_brf, uce_brr;
+    float *ure_a1, *ure_a2, *ure_a3, *ure_a4, *ure_z[4], *ure_x, *ure_ss, *ure_out;
+    // pair combines
+    float *bars_pair, *bars_ss, *bars_c, *rh_pair, *rh_ss, *rh_c;
+    const float *bars, *rhythm;     // what the rest of the model consumes
+    // SE
+    LstmBuf se_l;
+    float *se_h, *se_last, *se_a2, *se_a3, *se_a4, *se_z[4], *se_x, *se_ss, *style;
+    // ME
+    float *me_a1, *me_a2, *me_a3, *me_z[3], *me_od, *me_ss, *melody;
+    // SIM
+    LstmBuf sim_l1, sim_l2;
+    float *sim_h1, *sim_last1, *sim_h2, *sim_rf, *sim_si, *sim_ri, *sim_instr, *sim_sm, *sim_rm, *sim_mode, *sim_sb, *sim_rb, *sim_bpm_pre, *sim_bpm;
+    // PSA / USA
+    float *psa_s66, *psa_r10, *psa_i12, *psa_zs, *psa_zr, *psa_zi, *psa_out;
+    float *usa_s650, *usa_r17, *usa_zs, *usa_zr, *usa_h, *usa_out;
+    // backward scratch (carved by plan_backward)
+    float *scratch[8]; long long scratch_floats[8];
+};
+
+const float *PRM(const Ctx &c, ParamId id) { return c.prm + g_param_off[id]; }
+float *GRD(const Ctx &c, ParamId id) { return c.grad + g_param_off[id]; }
+
+size_t plan_forward(Ctx &c, Arena &ar) {
+    const long long N = c.N, C = c.C, B = c.B, T = c.T;
+    c.Rb = N * C * B * T; c.Rf = c.Rb * 10; c.Rbf = N * B * T * 10; c.Nb = N * B;
+    const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb, NC = N * C;
+    c.wconv_p = ar.take(57 * 700); c.wpcelin_p = ar.take(64 * 514); c.wucelin_p = ar.take(64 * 940);
+    c.pce_conv = ar.take(Rb * 456); c.pce_il = ar.take(NC * 58); c.pce_zi = ar.take(NC * 64); c.pce_zc = ar.take(Rb * 64);
+    c.pce_x = ar.take(Rb * 64); c.pce_beats = ar.take(Rb * 64); c.pce_last = ar.take(NC * B * 64); c.pce_ss = ar.take(NC);
+    c.pce_bars_in = ar.take(Nb * 64); c.pce_bars = ar.take(Nb * 128);
+    c.pce_bl.carve(ar, (int)(NC * B), (int)T, 64, 64); c.pce_brf.carve(ar, (int)N, (int)B, 64, 64); c.pce_brr.carve(ar, (int)N, (int)B, 64, 64);
+    c.pre_a1 = ar.take(Rb * 48); c.pre_a2 = ar.take(Nb * 40); c.pre_a3 = ar.take(Rf * 16); c.pre_a4 = ar.take(NC * 21);
+    c.pre_a5 = ar.take(N * 5); c.pre_a6 = ar.take(N * 5);
+    const long long pre_rows[6] = {Rb, Nb, Rf, NC, N, N};
+    for (int i = 0; i < 6; i++) c.pre_z[i] = ar.take(pre_rows[i] * 32);
+    c.pre_x = ar.take(Rf * 32); c.pre_ss = ar.take(NC); c.pre_out = ar.take(Rbf * 32);
+    if (c.U) {
+        c.uce_lin = ar.take(Nb * T * 64); c.uce_beats = ar.take(Nb * T * 64); c.uce_last = ar.take(Nb * 64); c.uce_ss = ar.take(N);
+        c.uce_bars_in = ar.take(Nb * 64); c.uce_bars = ar.take(Nb * 128);
+        c.uce_bl.carve(ar, (int)Nb, (int)T, 64, 64); c.uce_brf.carve(ar, (int)N, (int)B, 64, 64); c.uce_brr.carve(ar, (int)N, (int)B, 64, 64);
+        c.ure_a1 = ar.take(Nb * T * 48); c.ure_a2 = ar.take(Nb * 40); c.ure_a3 = ar.take(Rbf * 16); c.ure_a4 = ar.take(N * 5);
+        const long long ure_rows[4] = {Nb * T, Nb, Rbf, N};
+        for (int i = 0; i < 4; i++) c.ure_z[i] = ar.take(ure_rows[i] * 32);
+        c.ure_x = ar.take(Rbf * 32); c.ure_ss = ar.take(N); c.ure_out = ar.take(Rbf * 32);
+        c.bars_pair = ar.take(N * 2 * B * 128); c.bars_ss = ar.take(N * 2); c.bars_c = ar.take(Nb * 128);
+        c.rh_pair = ar.take(2 * Rbf * 32); c.rh_ss = ar.take(N * 2); c.rh_c = ar.take(Rbf * 32);
+    }
+    c.se_l.carve(ar, (int)N, (int)B, 192, 128);
+    c.se_h = ar.take(Nb * 192); c.se_last = ar.take(N * 192); c.se_a2 = ar.take(NC * 39); c.se_a3 = ar.take(N * 13); c.se_a4 = ar.take(N * 7);
+    const long long se_rows[4] = {N, NC, N, N};
+    for (int i = 0; i < 4; i++) c.se_z[i] = ar.take(se_rows[i] * 256);
+    c.se_x = ar.take(NC * 256); c.se_ss = ar.take(NC); c.style = ar.take(N * 256);
+    c.me_a1 = ar.take(Rb * 36); c.me_a2 = ar.take(Nb * 68); c.me_a3 = ar.take(NC * 8);
+    const long long me_rows[3] = {Rb, Nb, NC};
+    for (int i = 0; i < 3; i++) c.me_z[i] = ar.take(me_rows[i] * 120);
+    c.me_od = ar.take(Rb * 120); c.me_ss = ar.take(NC); c.melody = ar.take(Rbf * 56 * 8);
+    c.sim_l1.carve(ar, (int)Nb, (int)T, 9, 320); c.sim_l2.carve(ar, (int)N, (int)B, 8, 9);
+    c.sim_h1 = ar.take(Nb * T * 9); c.sim_last1 = ar.take(Nb * 9); c.sim_h2 = ar.take(Nb * 8); c.sim_rf = ar.take(N * 8);
+    c.sim_si = ar.take(N * 8); c.sim_ri = ar.take(N * 10); c.sim_instr = ar.take(N * 41);
+    c.sim_sm = ar.take(N * 2); c.sim_rm = ar.take(N * 2); c.sim_mode = ar.take(N * 2);
+    c.sim_sb = ar.take(N * 2); c.sim_rb = ar.take(N * 2); c.sim_bpm_pre = ar.take(N); c.sim_bpm = ar.take(N);
+    c.psa_s66 = ar.take(N * 66); c.psa_r10 = ar.take(Rbf * 10); c.psa_i12 = ar.take(NC * 12);
+    c.psa_zs = ar.take(N * 450); c.psa_zr = ar.take(Rbf * 450); c.psa_zi = ar.take(NC * 450); c.psa_out = ar.take(Rf * 56 * 5);
+    if (c.U) {
+        c.usa_s650 = ar.take(N * 650); c.usa_r17 = ar.take(Rbf * 17); c.usa_zs = ar.take(N * 10 * 376); c.usa_zr = ar.take(Rbf * 376);
+        c.usa_h = ar.take(Rbf * 376); c.usa_out = ar.take(Rbf * 47 * 2);
+    }
+    return ar.off;
+}
+
+// LSTM weights: bias_ih + bias_hh and W_hh^T, refreshed every step because the weights change
+void prep_lstm(Launcher &L, const Ctx &c, LstmBuf &lb, ParamId whh, ParamId bih, ParamId bhh) {
+    k_add2<<<grid_for(4 * lb.H), 256, 0, L.st>>>(PRM(c, bih), PRM(c, bhh), lb.bias_sum, 4 * lb.H); L.check();
+    k_transpose<<<grid_for(4 * lb.H * lb.H), 256, 0, L.st>>>(PRM(c, whh), lb.wt, 4 * lb.H, lb.H); L.check();
+}
+
+void prep_weights(Launcher &L, Ctx &c) {
+    k_permute_cols<<<grid_for(57 * 700), 256, 0, L.st>>>(PRM(c, pce_conv_w), c.wconv_p, 57, 700, 0, 0, 0); L.check();
+    k_permute_cols<<<grid_for(64 * 514), 256, 0, L.st>>>(PRM(c, pce_lin_w), c.wpcelin_p, 64, 514, 1, 0, 0); L.check();
+    prep_lstm(L, c, c.pce_bl, pce_bl_whh, pce_bl_bih, pce_bl_bhh);
+    prep_lstm(L, c, c.pce_brf, pce_br_whh, pce_br_bih, pce_br_bhh);
+    prep_lstm(L, c, c.pce_brr, pce_br_whh_r, pce_br_bih_r, pce_br_bhh_r);
+    if (c.U) {
+        k_permute_cols<<<grid_for(64 * 940), 256, 0, L.st>>>(PRM(c, uce_lin_w), c.wucelin_p, 64, 940, 2, 0, 0); L.check();
+        prep_lstm(L, c, c.uce_bl, uce_bl_whh, uce_bl_bih, uce_bl_bhh);
+        prep_lstm(L, c, c.uce_brf, uce_br_whh, uce_br_bih, uce_br_bhh);
+        prep_lstm(L, c, c.uce_brr, uce_br_whh_r, uce_br_bih_r, uce_br_bhh_r);
+    }
+    prep_lstm(L, c, c.se_l, se_lstm_whh, se_lstm_bih, se_lstm_bhh);
+    prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
+    prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
+}
+
+// run one LSTM direction: xproj = X·W_ih^T + (b_ih + b_hh), then the recurrence
+void lstm_forward(Launcher &L, const Ctx &c, LstmBuf &lb, const float *X, ParamId wih, float *out, long long out_ld, int out_off, int reverse) {
+    L.linear(X, lb.I, PRM(c, wih), lb.I, lb.bias_sum, lb.xproj, 4 * lb.H, lb.S * lb.T, 4 * lb.H, lb.I, 0);
+    LstmArgs a{};
+    a.xproj = lb.xproj; a.w = lb.wt; a.out = out; a.out_ld = out_ld; a.out_off = out_off;
+    a.gates = lb.gates; a.cells = lb.cells; a.hprev = lb.hprev; a.S = lb.S; a.T = lb.T; a.H = lb.H; a.reverse = reverse;
+    L.lstm(a, false);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ forward
+namespace {
+
+// masks over (n, c, b, t, f)
+constexpr int M_N = 16, M_C = 8, M_B = 4, M_T = 2, M_F = 1;
+
+void bcast_fwd(Launcher &L, Dims5 d, int cols, const float *bias, float *Y, int act, std::initializer_list<std::pair<const float *, int>> srcs) {
+    BcastArgs a{};
+    int i = 0;
+    for (auto &s : srcs) { a.src[i] = s.first; a.mask[i] = s.second; i++; }
+    a.n_src = i; a.bias = bias; a.Y = Y; a.d = d; a.cols = cols; a.act = act;
+    L.bcast(a);
+}
+
+void forward_extract(Launcher &L, Ctx &c) {
+    const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
+    const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb;
+    prep_weights(L, c);
+    // ---------------- PitchedChannelsEncoder (model.py:77-99)
+    L.gemm(c.P, 0, 0, c.wconv_p, 1, 700, c.pce_conv, 57, (int)(Rb * 8), 57, 700, PRM(c, pce_conv_b), 1, 0, 1, 1);   // beats_conv + leaky
+    L.linear(c.F, 51, PRM(c, pce_il_w), 51, PRM(c, pce_il_b), c.pce_il, 58, NC, 58, 51, 1);
+    L.linear(c.pce_il, 58, c.wpcelin_p + 456, 514, nullptr, c.pce_zi, 64, NC, 64, 58, 0);
+    L.linear(c.pce_conv, 456, c.wpcelin_p, 514, nullptr, c.pce_zc, 64, (int)Rb, 64, 456, 0);
+    bcast_fwd(L, Dims5{N, C, B, T, 1}, 64, PRM(c, pce_lin_b), c.pce_x, 1, {{c.pce_zc, M_N | M_C | M_B | M_T}, {c.pce_zi, M_N | M_C}});
+    lstm_forward(L, c, c.pce_bl, c.pce_x, pce_bl_wih, c.pce_beats, 64, 0, 0);
+    L.take_last(c.pce_beats, c.pce_last, (long long)NC * B, T, 64);
+    { CombineArgs a{}; a.x = c.pce_last; a.n_stride = (long long)C * B * 64; a.k_stride = (long long)B * 64; a.N = N; a.K = C; a.M = (long long)B * 64;
+      a.ss = c.pce_ss; a.out = c.pce_bars_in; L.combine_fwd(a); }
+    lstm_forward(L, c, c.pce_brf, c.pce_bars_in, pce_br_wih, c.pce_bars, 128, 0, 0);
+    lstm_forward(L, c, c.pce_brr, c.pce_bars_in, pce_br_wih_r, c.pce_bars, 128, 64, 1);
+    // ---------------- PitchedRhythmEncoder (model.py:346-381)
+    const float *plw = PRM(c, pre_lin_w);
+    L.linear(c.pce_beats, 64, PRM(c, pre_bl_w), 64, PRM(c, pre_bl_b), c.pre_a1, 48, (int)Rb, 48, 64, 1);
+    L.linear(c.pce_bars, 128, PRM(c, pre_br_w), 128, PRM(c, pre_br_b), c.pre_a2, 40, (int)Nb, 40, 128, 1);
+    L.linear(c.P, 280, PRM(c, pre_ch_w), 280, PRM(c, pre_ch_b), c.pre_a3, 16, (int)Rf, 16, 280, 1);
+    L.linear(c.F, 51, PRM(c, pre_il_w), 51, PRM(c, pre_il_b), c.pre_a4, 21, NC, 21, 51, 1);
+    L.linear(c.mode, 2, PRM(c, pre_ml_w), 2, PRM(c, pre_ml_b), c.pre_a5, 5, N, 5, 2, 1);
+    L.linear(c.bpm, 1, PRM(c, pre_bp_w), 1, PRM(c, pre_bp_b), c.pre_a6, 5, N, 5, 1, 1);
+    L.linear(c.pre_a1, 48, plw + 0, 135, nullptr, c.pre_z[0], 32, (int)Rb, 32, 48, 0);
+    L.linear(c.pre_a2, 40, plw + 48, 135, nullptr, c.pre_z[1], 32, (int)Nb, 32, 40, 0);
+    L.linear(c.pre_a3, 16, plw + 88, 135, nullptr, c.pre_z[2], 32, (int)Rf, 32, 16, 0);
+    L.linear(c.pre_a4, 21, plw + 104, 135, nullptr, c.pre_z[3], 32, NC, 32, 21, 0);
+    L.linear(c.pre_a5, 5, plw + 125, 135, nullptr, c.pre_z[4], 32, N, 32, 5, 0);
+    L.linear(c.pre_a6, 5, plw + 130, 135, nullptr, c.pre_z[5], 32, N, 32, 5, 0);
+    bcast_fwd(L, Dims5{N, C, B, T, 10}, 32, PRM(c, pre_lin_b), c.pre_x, 1,
+              {{c.pre_z[0], M_N | M_C | M_B | M_T}, {c.pre_z[1], M_N | M_B}, {c.pre_z[2], M_N | M_C | M_B | M_T | M_F},
+               {c.pre_z[3], M_N | M_C}, {c.pre_z[4], M_N}, {c.pre_z[5], M_N}});
+    { CombineArgs a{}; a.x = c.pre_x; a.M = (long long)B * T * 320; a.n_stride = C * a.M; a.k_stride = a.M; a.N = N; a.K = C;
+      a.ss = c.pre_ss; a.out = c.pre_out; L.combine_fwd(a); }
+    c.bars = c.pce_bars; c.rhythm = c.pre_out;
+    if (c.U) {
+        // ---------------- UnpitchedChannelsEncoder (model.py:128-141)
+        L.linear(c.Ug, 940, c.wucelin_p, 940, PRM(c, uce_lin_b), c.uce_lin, 64, (int)(Nb * T), 64, 940, 1);
+        lstm_forward(L, c, c.uce_bl, c.uce_lin, uce_bl_wih, c.uce_beats, 64, 0, 0);
+        L.take_last(c.uce_beats, c.uce_last, Nb, T, 64);
+        { CombineArgs a{}; a.x = c.uce_last; a.M = (long long)B * 64; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
+          a.ss = c.uce_ss; a.out = c.uce_bars_in; L.combine_fwd(a); }
+        lstm_forward(L, c, c.uce_brf, c.uce_bars_in, uce_br_wih, c.uce_bars, 128, 0, 0);
+        lstm_forward(L, c, c.uce_brr, c.uce_bars_in, uce_br_wih_r, c.uce_bars, 128, 64, 1);
+        // ---------------- UnpitchedRhythmEncoder (model.py:418-443)
+        const float *ulw = PRM(c, ure_lin_w);
+        L.linear(c.uce_beats, 64, PRM(c, ure_bl_w), 64, PRM(c, ure_bl_b), c.ure_a1, 48, (int)(Nb * T), 48, 64, 1);
+        L.linear(c.uce_bars, 128, PRM(c, ure_br_w), 128, PRM(c, ure_br_b), c.ure_a2, 40, (int)Nb, 40, 128, 1);
+        L.linear(c.Ug, 94, PRM(c, ure_ch_w), 94, PRM(c, ure_ch_b), c.ure_a3, 16, (int)Rbf, 16, 94, 1);
+        L.linear(c.bpm, 1, PRM(c, ure_bp_w), 1, PRM(c, ure_bp_b), c.ure_a4, 5, N, 5, 1, 1);
+        L.linear(c.ure_a1, 48, ulw + 0, 109, nullptr, c.ure_z[0], 32, (int)(Nb * T), 32, 48, 0);
+        L.linear(c.ure_a2, 40, ulw + 48, 109, nullptr, c.ure_z[1], 32, (int)Nb, 32, 40, 0);
+        L.linear(c.ure_a3, 16, ulw + 88, 109, nullptr, c.ure_z[2], 32, (int)Rbf, 32, 16, 0);
+        L.linear(c.ure_a4, 5, ulw + 104, 109, nullptr, c.ure_z[3], 32, N, 32, 5, 0);
+        bcast_fwd(L, Dims5{N, 1, B, T, 10}, 32, PRM(c, ure_lin_b), c.ure_x, 1,
+                  {{c.ure_z[0], M_N | M_B | M_T}, {c.ure_z[1], M_N | M_B}, {c.ure_z[2], M_N | M_B | M_T | M_F}, {c.ure_z[3], M_N}});
+        { CombineArgs a{}; a.x = c.ure_x; a.M = (long long)B * T * 320; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
+          a.ss = c.ure_ss; a.out = c.ure_out; L.combine_fwd(a); }
+        // ---------------- combine(pitched, unpitched) for bars and rhythm (model.py:766-767)
+        k_pair_pack<<<grid_for(Nb * 128), 256, 0, L.st>>>(c.pce_bars, c.uce_bars, c.bars_pair, N, (long long)B * 128); L.check();
+        { CombineArgs a{}; a.x = c.bars_pair; a.M = (long long)B * 128; a.n_stride = 2 * a.M; a.k_stride = a.M; a.N = N; a.K = 2;
+          a.ss = c.bars_ss; a.out = c.bars_c; L.combine_fwd(a); }
+        k_pair_pack<<<grid_for(Rbf * 32), 256, 0, L.st>>>(c.pre_out, c.ure_out, c.rh_pair, N, (long long)B * T * 320); L.check();
+        { CombineArgs a{}; a.x = c.rh_pair; a.M = (long long)B * T * 320; a.n_stride = 2 * a.M; a.k_stride = a.M; a.N = N; a.K = 2;
+          a.ss = c.rh_ss; a.out = c.rh_c; L.combine_fwd(a); }
+        c.bars = c.bars_c; c.rhythm = c.rh_c;
+    }
+    // ---------------- StyleEncoder (model.py:179-200)
+    lstm_forward(L, c, c.se_l, c.bars, se_lstm_wih, c.se_h, 192, 0, 0);
+    L.take_last(c.se_h, c.se_last, N, B, 192);
+    const float *slw = PRM(c, se_lin_w);
+    L.linear(c.F, 51, PRM(c, se_il_w), 51, PRM(c, se_il_b), c.se_a2, 39, NC, 39, 51, 1);
+    L.linear(c.mode, 2, PRM(c, se_ml_w), 2, PRM(c, se_ml_b), c.se_a3, 13, N, 13, 2, 1);
+    L.linear(c.bpm, 1, PRM(c, se_bp_w), 1, PRM(c, se_bp_b), c.se_a4, 7, N, 7, 1, 1);
+    L.linear(c.se_last, 192, slw + 0, 251, nullptr, c.se_z[0], 256, N, 256, 192, 0);
+    L.linear(c.se_a2, 39, slw + 192, 251, nullptr, c.se_z[1], 256, NC, 256, 39, 0);
+    L.linear(c.se_a3, 13, slw + 231, 251, nullptr, c.se_z[2], 256, N, 256, 13, 0);
+    L.linear(c.se_a4, 7, slw + 244, 251, nullptr, c.se_z[3], 256, N, 256, 7, 0);
+    bcast_fwd(L, Dims5{N, C, 1, 1, 1}, 256, PRM(c, se_lin_b), c.se_x, 1,
+              {{c.se_z[0], M_N}, {c.se_z[1], M_N | M_C}, {c.se_z[2], M_N}, {c.se_z[3], M_N}});
+    { CombineArgs a{}; a.x = c.se_x; a.M = 256; a.n_stride = (long long)C * 256; a.k_stride = 256; a.N = N; a.K = C;
+      a.ss = c.se_ss; a.out = c.style; L.combine_fwd(a); }
+    // ---------------- MelodyEncoder (model.py:252-297); octave+degree weights act as one (120, 112) matrix
+    const float *mow = PRM(c, me_oct_w);
+    L.linear(c.pce_beats, 64, PRM(c, me_bl_w), 64, PRM(c, me_bl_b), c.me_a1, 36, (int)Rb, 36, 64, 1);
+    L.linear(c.pce_bars, 128, PRM(c, me_br_w), 128, PRM(c, me_br_b), c.me_a2, 68, (int)Nb, 68, 128, 1);
+    L.linear(c.F, 51, PRM(c, me_il_w), 51, PRM(c, me_il_b), c.me_a3, 8, NC, 8, 51, 1);
+    L.linear(c.me_a1, 36, mow + 0, 112, nullptr, c.me_z[0], 120, (int)Rb, 120, 36, 0);
+    L.linear(c.me_a2, 68, mow + 36, 112, nullptr, c.me_z[1], 120, (int)Nb, 120, 68, 0);
+    L.linear(c.me_a3, 8, mow + 104, 112, nullptr, c.me_z[2], 120, NC, 120, 8, 0);
+    bcast_fwd(L, Dims5{N, C, B, T, 1}, 120, PRM(c, me_oct_b), c.me_od, 1,
+              {{c.me_z[0], M_N | M_C | M_B | M_T}, {c.me_z[1], M_N | M_B}, {c.me_z[2], M_N | M_C}});
+    {
+        MeArgs a{};
+        a.w = MeParams{PRM(c, me_ch_w), PRM(c, me_ch_b), PRM(c, me_lin_w), PRM(c, me_lin_b)};
+        a.od = c.me_od; a.P = c.P; a.ss = c.me_ss; a.melody = c.melody; a.N = N; a.C = C; a.B = B; a.T = T;
+        L.fill(c.me_ss, NC, 0.f);
+        k_me_sumsq<<<(int)std::min<long long>(Rb, 148 * 8), 256, 0, L.st>>>(a); L.check();
+        k_me_fwd<<<(int)std::min<long long>((long long)N * B * T, 148 * 8), 256, (size_t)C * 121 * sizeof(float), L.st>>>(a); L.check();
+    }
+}
+
+void forward_song_info(Launcher &L, Ctx &c) {   // SongInfoModel (model.py:513-562)
+    const int N = c.N, B = c.B, T = c.T;
+    lstm_forward(L, c, c.sim_l1, c.rhythm, sim_bl_wih, c.sim_h1, 9, 0, 0);
+    L.take_last(c.sim_h1, c.sim_last1, c.Nb, T, 9);
+    lstm_forward(L, c, c.sim_l2, c.sim_last1, sim_br_wih, c.sim_h2, 8, 0, 0);
+    L.take_last(c.sim_h2, c.sim_rf, N, B, 8);
+    auto head = [&](ParamId sw, ParamId sb, int ks, float *sa, ParamId rw, ParamId rb, int kr, float *ra, ParamId fw, ParamId fb, int nout, float *out) {
+        L.linear(c.style, 256, PRM(c, sw), 256, PRM(c, sb), sa, ks, N, ks, 256, 1);
+        L.linear(c.sim_rf, 8, PRM(c, rw), 8, PRM(c, rb), ra, kr, N, kr, 8, 1);
+        L.linear(sa, ks, PRM(c, fw), ks + kr, PRM(c, fb), out, nout, N, nout, ks, 0);
+        L.linear(ra, kr, PRM(c, fw) + ks, ks + kr, nullptr, out, nout, N, nout, kr, 0, 1);
+    };
+    head(sim_si_w, sim_si_b, 8, c.sim_si, sim_ri_w, sim_ri_b, 10, c.sim_ri, sim_i_w, sim_i_b, 41, c.sim_instr);
+    head(sim_sm_w, sim_sm_b, 2, c.sim_sm, sim_rm_w, sim_rm_b, 2, c.sim_rm, sim_m_w, sim_m_b, 2, c.sim_mode);
+    head(sim_sb_w, sim_sb_b, 2, c.sim_sb, sim_rb_w, sim_rb_b, 2, c.sim_rb, sim_b_w, sim_b_b, 1, c.sim_bpm_pre);
+    k_bpm_head<<<(N + 63) / 64, 64, 0, L.st>>>(c.sim_bpm_pre, c.sim_bpm, N); L.check();
+}
+
+void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
+    const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
+    const long long Rbf = c.Rbf;
+    // ---------------- PitchedStyleApplier (model.py:624-675); octave+degree weights = one (450, 88) matrix
+    const float *pow_ = PRM(c, psa_oct_w);
+    L.linear(c.style, 256, PRM(c, psa_sl_w), 256, PRM(c, psa_sl_b), c.psa_s66, 66, N, 66, 256, 1);
+    L.linear(c.rhythm, 32, PRM(c, psa_rl_w), 32, PRM(c, psa_rl_b), c.psa_r10, 10, (int)Rbf, 10, 32, 1);
+    L.linear(c.F, 51, PRM(c, psa_il_w), 51, PRM(c, psa_il_b), c.psa_i12, 12, NC, 12, 51, 1);
+    L.linear(c.psa_s66, 66, pow_ + 0, 88, nullptr, c.psa_zs, 450, N, 450, 66, 0);
+    L.linear(c.psa_r10, 10, pow_ + 66, 88, nullptr, c.psa_zr, 450, (int)Rbf, 450, 10, 0);
+    L.linear(c.psa_i12, 12, pow_ + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
+    {
+        PsaArgs a{};
+        a.w = PsaParams{PRM(c, psa_oct_b), PRM(c, psa_ml_w), PRM(c, psa_ml_b), PRM(c, psa_lin_w), PRM(c, psa_lin_b)};
+        a.Zr = c.psa_zr; a.Zi = c.psa_zi; a.Zs = c.psa_zs; a.melody = c.melody; a.out = c.psa_out; a.N = N; a.C = C; a.B = B; a.T = T;
+        k_psa_fwd<<<(int)std::min<long long>(Rbf, 148 * 8), 256, (size_t)C * 450 * sizeof(float), L.st>>>(a); L.check();
+    }
+    if (unpitched) {
+        // ---------------- UnpitchedStyleApplier (model.py:703-724)
+        const float *nw = PRM(c, usa_nl_w);
+        L.linear(c.style, 256, PRM(c, usa_sl_w), 256, PRM(c, usa_sl_b), c.usa_s650, 650, N, 650, 256, 1);
+        L.linear(c.rhythm, 32, PRM(c, usa_rl_w), 32, PRM(c, usa_rl_b), c.usa_r17, 17, (int)Rbf, 17, 32, 1);
+        L.linear(c.usa_s650, 65, nw + 0, 82, nullptr, c.usa_zs, 376, N * 10, 376, 65, 0);
+        L.linear(c.usa_r17, 17, nw + 65, 82, nullptr, c.usa_zr, 376, (int)Rbf, 376, 17, 0);
+        UsaArgs a{};
+        a.bias = PRM(c, usa_nl_b); a.Wl = PRM(c, usa_lin_w); a.bl = PRM(c, usa_lin_b); a.Zr = c.usa_zr; a.Zs = c.usa_zs;
+        a.H = c.usa_h; a.out = c.usa_out; a.N = N; a.B = B; a.T = T;
+        k_usa_fwd<<<(int)std::min<long long>(Rbf, 148 * 16), 64, 0, L.st>>>(a); L.check();
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ C ABI
+static size_t plan_backward(Ctx &c, Arena &ar);   // defined with the backward pass
+
+static int setup_ctx(Ctx &c, const MstModelShape *s, void *ws, size_t ws_bytes, bool training, bool dry) {
+    init_param_offsets();
+    memset(&c, 0, sizeof(c));
+    c.N = s->n_samples; c.C = s->n_channels; c.B = s->n_bars; c.T = s->n_beats; c.U = s->has_unpitched ? 1 : 0;
+    if (c.N < 1 || c.C < 1 || c.B < 1 || c.T < 1 || c.C > 64) { mst_set_error("mst_model: bad shape"); return MST_E_INVALID; }
+    Arena ar{(char *)ws, 0, dry};
+    plan_forward(c, ar);
+    if (training) plan_backward(c, ar);
+    if (!dry && ar.off > ws_bytes) { mst_set_error("mst_model: workspace too small (%zu < %zu)", ws_bytes, ar.off); return MST_E_CAPACITY; }
+    return (int)0;
+}
+
+extern "C" size_t mst_model_workspace_bytes(const MstModelShape *s, int training) {
+    Ctx c;
+    init_param_offsets();
+    memset(&c, 0, sizeof(c));
+    c.N = s->n_samples; c.C = s->n_channels; c.B = s->n_bars; c.T = s->n_beats; c.U = s->has_unpitched ? 1 : 0;
+    Arena ar{nullptr, 0, true};
+    plan_forward(c, ar);
+    if (training) plan_backward(c, ar);
+    return ar.off;
+}
+
+static void fill_outputs(const Ctx &c, MstModelOutputs *o) {
+    o->instruments = c.sim_instr; o->mode = c.sim_mode; o->bpm = c.sim_bpm;
+    o->pitched = c.psa_out; o->unpitched = c.U ? c.usa_out : nullptr;
+    o->style = c.style; o->melody = c.melody; o->rhythm = (float *)c.rhythm;
+}
+
+extern "C" int mst_model_forward(const float *d_params, const MstModelShape *shape, const float *d_pitched,
+                                 const float *d_unpitched, const float *d_features, const float *d_mode, const float *d_bpm,
+                                 MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes, int training,
+                                 void *stream, int *n_launches) {
+    if (!d_params || !shape || !d_pitched || !d_features || !d_mode || !d_bpm || !outputs || !d_workspace ||
+        (shape->has_unpitched && !d_unpitched)) {
+        mst_set_error("mst_model_forward: null pointer argument");
+        return MST_E_INVALID;
+    }
+    Ctx c;
+    int rc = setup_ctx(c, shape, d_workspace, workspace_bytes, training != 0, false);
+    if (rc) return rc;
+    c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params;
+    Launcher L; L.st = (cudaStream_t)stream;
+    forward_extract(L, c);
+    forward_song_info(L, c);
+    forward_apply(L, c, c.U != 0);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_forward: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    fill_outputs(c, outputs);
+    if (n_launches) *n_launches = L.launches;
+    return MST_OK;
+}
+
+static size_t plan_backward(Ctx &c, Arena &ar) { (void)c; return ar.off; }   // placeholder until the backward pass lands

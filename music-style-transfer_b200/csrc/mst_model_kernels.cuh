@@ -1,0 +1,239 @@
+// mst_model_kernels.cuh — device kernels of the style-transfer network's training step (fp32 path).
+//
+// The reference (style/model.py) is a stack of small nn.Linear / nn.LSTM / Conv1d layers glued by
+// cat_with_broadcast (style/utils/pytorch.py:54-65) and `combine` (model.py:796-815).  Here every
+// "Linear over a broadcast concat" is decomposed: W·cat(x1..xk) = sum_s W_s·x_s, each term computed at the
+// source's own (small) row space by one GEMM and summed by a broadcast-add kernel, so the concatenated
+// tensors (rows x 135, rows x 88, note-rows x 50 ...) never exist.  The backward pass mirrors it: the
+// pre-activation gradient is reduced over the broadcast axes and each source sees a plain GEMM.
+#pragma once
+#include "mst_device.cuh"
+
+namespace mstm {
+
+constexpr float kSlope = 0.01f;   // F.leaky_relu default negative_slope, used everywhere in the reference
+
+__device__ __forceinline__ float leaky(float x) { return x > 0.f ? x : kSlope * x; }
+// derivative from the OUTPUT (sign preserved by a positive slope; torch uses slope at x == 0)
+__device__ __forceinline__ float leaky_grad_from_out(float y) { return y > 0.f ? 1.f : kSlope; }
+__device__ __forceinline__ float sigmoidf(float x) { return 1.f / (1.f + expf(-x)); }
+
+// ------------------------------------------------------------------------------------------------
+// Strided SIMT GEMM:  C[i, j] (op)= act( sum_k A(i, k) * B(k, j) + bias[j] )
+//   A(i, k) = A[i * a_si + k * a_sk],  B(k, j) = B[k * b_sk + j * b_sj],  C[i * c_si + j]
+// 64 x 64 x 16 tiles, 256 threads, 4 x 4 outputs per thread.  gridDim.z splits K (atomic accumulate).
+// Covers X·W^T (forward), dY·W (input grad) and dY^T·X (weight grad, K = rows, split over z).
+// AMODE 1 = implicit im2col of the pitched grid for beats_conv (model.py:46-52): row m = (beat-row, octave),
+// k = (fraction, tap, feature); A(m, k) = P[row][f][(oct*7 + tap - 4)][feat] or 0 outside the 56 notes.
+// ------------------------------------------------------------------------------------------------
+struct GemmArgs {
+    const float *A, *B, *bias;
+    float *C;
+    int M, N, K;
+    long long a_si, a_sk, b_sk, b_sj, c_si;
+    int act;          // 0 none, 1 leaky
+    int accumulate;   // 0 store, 1 C += (plain), 2 atomicAdd (split-K or shared destination)
+};
+
+constexpr int kGemmTile = 64, kGemmK = 16, kGemmThreads = 256;
+
+template <int AMODE>
+__device__ __forceinline__ float gemm_load_a(const GemmArgs &g, int i, int k) {
+    if (AMODE == 0) return g.A[(long long)i * g.a_si + (long long)k * g.a_sk];
+    // conv gather: k = f * 70 + tap * 5 + feat over the (10, 56, 5) beat block
+    const int row = i >> 3, oct = i & 7;
+    const int f = k / 70, r = k - f * 70;
+    const int tap = r / 5, feat = r - tap * 5;
+    const int note = oct * 7 + tap - 4;
+    if (note < 0 || note >= 56) return 0.f;
+    return g.A[(long long)row * 2800 + f * 280 + note * 5 + feat];
+}
+
+template <int AMODE>
+__global__ void __launch_bounds__(kGemmThreads)
+k_gemm(GemmArgs g) {
+    __shared__ float As[kGemmK][kGemmTile + 4];
+    __shared__ float Bs[kGemmK][kGemmTile + 4];
+    const int tid = threadIdx.x;
+    const int i0 = blockIdx.y * kGemmTile, j0 = blockIdx.x * kGemmTile;
+    const int kz = gridDim.z;
+    const int k_per = ((g.K + kz - 1) / kz + kGemmK - 1) / kGemmK * kGemmK;
+    const int k_lo = blockIdx.z * k_per, k_hi = min(g.K, k_lo + k_per);
+    const int tx = tid & 15, ty = tid >> 4;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
+    // load mapping: pick the contiguous direction of each operand for coalescing
+    const bool a_k_contig = (AMODE == 1) || (g.a_sk == 1);
+    const bool b_j_contig = (g.b_sj == 1);
+    for (int k0 = k_lo; k0 < k_hi; k0 += kGemmK) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int idx = tid + e * kGemmThreads;   // 0..1023 = 64 x 16
+            int ii, kk;
+            if (a_k_contig) { kk = idx & 15; ii = idx >> 4; } else { ii = idx & 63; kk = idx >> 6; }
+            const int gi = i0 + ii, gk = k0 + kk;
+            As[kk][ii] = (gi < g.M && gk < k_hi) ? gemm_load_a<AMODE>(g, gi, gk) : 0.f;
+            int jj, kb;
+            if (b_j_contig) { jj = idx & 63; kb = idx >> 6; } else { kb = idx & 15; jj = idx >> 4; }
+            const int gj = j0 + jj, gkb = k0 + kb;
+            Bs[kb][jj] = (gj < g.N && gkb < k_hi) ? g.B[(long long)gkb * g.b_sk + (long long)gj * g.b_sj] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < kGemmK; kk++) {
+            float a[4], b[4];
+#pragma unroll
+            for (int x = 0; x < 4; x++) { a[x] = As[kk][ty * 4 + x]; b[x] = Bs[kk][tx * 4 + x]; }
+#pragma unroll
+            for (int x = 0; x < 4; x++)
+#pragma unroll
+                for (int y = 0; y < 4; y++) acc[x][y] = fmaf(a[x], b[y], acc[x][y]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int x = 0; x < 4; x++) {
+        const int gi = i0 + ty * 4 + x;
+        if (gi >= g.M) continue;
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            const int gj = j0 + tx * 4 + y;
+            if (gj >= g.N) continue;
+            float v = acc[x][y];
+            if (g.bias && blockIdx.z == 0) v += g.bias[gj];
+            if (g.act == 1) v = leaky(v);
+            float *dst = g.C + (long long)gi * g.c_si + gj;
+            if (g.accumulate == 0) *dst = v;
+            else if (g.accumulate == 1) *dst += v;
+            else atomicAdd(dst, v);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Broadcast add + activation over the row space (n, c, b, t, f):  Y[row, :] = act(bias + sum_s Z_s[map_s(row), :])
+// A source keeps a subset of the five coordinates (bit 4 = n, 3 = c, 2 = b, 1 = t, 0 = f); its rows are the
+// row-major linearisation of the kept coordinates.  This is cat_with_broadcast + Linear, decomposed.
+// ------------------------------------------------------------------------------------------------
+struct Dims5 { int n, c, b, t, f; };
+constexpr int kMaxSources = 6;
+struct BcastArgs {
+    const float *src[kMaxSources];
+    int mask[kMaxSources];
+    int n_src;
+    const float *bias;   // may be null
+    float *Y;
+    Dims5 d;
+    int cols;
+    int act;             // 0 none, 1 leaky
+};
+
+__device__ __forceinline__ long long src_row(const Dims5 &d, int mask, int n, int c, int b, int t, int f) {
+    long long r = 0;
+    if (mask & 16) r = n;
+    if (mask & 8) r = r * d.c + c;
+    if (mask & 4) r = r * d.b + b;
+    if (mask & 2) r = r * d.t + t;
+    if (mask & 1) r = r * d.f + f;
+    return r;
+}
+
+__global__ void __launch_bounds__(256)
+k_bcast_add(BcastArgs a) {
+    const long long rows = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f;
+    const long long total = rows * a.cols;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const long long row = idx / a.cols;
+        const int j = (int)(idx - row * a.cols);
+        long long r = row;
+        const int f = (int)(r % a.d.f); r /= a.d.f;
+        const int t = (int)(r % a.d.t); r /= a.d.t;
+        const int b = (int)(r % a.d.b); r /= a.d.b;
+        const int c = (int)(r % a.d.c); r /= a.d.c;
+        const int n = (int)r;
+        float v = a.bias ? a.bias[j] : 0.f;
+#pragma unroll
+        for (int s = 0; s < kMaxSources; s++)
+            if (s < a.n_src) v += a.src[s][src_row(a.d, a.mask[s], n, c, b, t, f) * a.cols + j];
+        a.Y[idx] = a.act ? leaky(v) : v;
+    }
+}
+
+// dPre = dY * act'(Y) elementwise (in place allowed)
+__global__ void __launch_bounds__(256)
+k_act_grad(const float *__restrict__ dY, const float *__restrict__ Y, float *__restrict__ dPre, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        dPre[i] = dY[i] * leaky_grad_from_out(Y[i]);
+}
+
+// out[a, i] (+)= sum_l in[a, l, i]   (sum over the middle axis; `inner` contiguous)
+__global__ void __launch_bounds__(256)
+k_reduce_mid(const float *__restrict__ in, float *__restrict__ out, long long A, int L, long long inner, int accumulate) {
+    const long long total = A * inner;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const long long a = idx / inner, i = idx - a * inner;
+        const float *p = in + a * L * inner + i;
+        float s = 0.f;
+        for (int l = 0; l < L; l++) s += p[(long long)l * inner];
+        if (accumulate) out[idx] += s; else out[idx] = s;
+    }
+}
+
+// column sums of a [rows, cols] matrix into out[cols] (atomic accumulate) — bias gradients
+__global__ void __launch_bounds__(256)
+k_colsum(const float *__restrict__ in, float *__restrict__ out, long long rows, int cols) {
+    // blockDim = 256 = 8 row-lanes x 32 col-lanes (cols handled in chunks of 32)
+    __shared__ float part[8][33];
+    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    for (int c0 = blockIdx.y * 32; c0 < cols; c0 += gridDim.y * 32) {
+        const int c = c0 + cl;
+        float s = 0.f;
+        if (c < cols)
+            for (long long r = (long long)blockIdx.x * 8 + rl; r < rows; r += (long long)gridDim.x * 8) s += in[r * cols + c];
+        part[rl][cl] = s;
+        __syncthreads();
+        if (rl == 0 && c < cols) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; k++) t += part[k][cl];
+            atomicAdd(out + c, t);
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_fill(float *p, long long n, float v) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
+}
+
+__global__ void __launch_bounds__(256)
+k_axpy(float *__restrict__ y, const float *__restrict__ x, long long n) {   // y += x
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) y[i] += x[i];
+}
+
+// dst[r, perm(j)] = src[r, j] style column permutations of weights (and the inverse for their gradients)
+//   mode 0: beats_conv  (57, 50, 14) [o][f*5+feat][tap]  <->  [o][f*70 + tap*5 + feat]
+//   mode 1: PCE.linear  (64, 514)    [j][o*8+oct | 456+i]  <->  [j][oct*57+o | 456+i]
+//   mode 2: UCE.linear  (64, 940)    [j][f*94 + feat*47 + note]  <->  [j][f*94 + note*2 + feat]
+__device__ __forceinline__ int perm_col(int mode, int j) {
+    if (mode == 0) { const int ch = j / 14, tap = j - ch * 14; const int f = ch / 5, feat = ch - f * 5; return f * 70 + tap * 5 + feat; }
+    if (mode == 1) { if (j >= 456) return j; const int o = j >> 3, oct = j & 7; return oct * 57 + o; }
+    const int f = j / 94, r = j - f * 94; const int feat = r / 47, note = r - feat * 47; return f * 94 + note * 2 + feat;
+}
+__global__ void __launch_bounds__(256)
+k_permute_cols(const float *__restrict__ src, float *__restrict__ dst, int rows, int cols, int mode, int inverse, int accumulate) {
+    const int total = rows * cols;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int r = idx / cols, j = idx - r * cols;
+        const int pj = perm_col(mode, j);
+        if (!inverse) dst[r * cols + pj] = src[idx];
+        else if (accumulate) dst[idx] += src[r * cols + pj];
+        else dst[idx] = src[r * cols + pj];
+    }
+}
+
+}  // namespace mstm

@@ -1,0 +1,218 @@
+// mst_model_kernels2.cuh — LSTM recurrences and `combine` (forward + backward), fp32.
+#pragma once
+#include "mst_model_kernels.cuh"
+
+namespace mstm {
+
+// ------------------------------------------------------------------------------------------------
+// LSTM (nn.LSTM, 1 layer, batch_first; style/model.py:62,69,113,120,156,462,468).  The input projection
+// x·W_ih^T + b_ih + b_hh for all time steps is one GEMM (xproj); only h·W_hh^T runs serially here.
+// One CTA carries up to kLstmG sequences through time; thread j owns gate row j (gate order i, f, g, o).
+// W_hh^T lives in shared memory when it fits (H = 64: 64 KB), else it streams from L2 (H = 192).
+// Saved for backward: post-activation gates, cell states, and h_{t-1} per step.
+// ------------------------------------------------------------------------------------------------
+constexpr int kLstmG = 8;
+
+struct LstmArgs {
+    const float *xproj;   // (S, T, 4H)
+    const float *w;       // forward: W_hh^T (H, 4H); backward: W_hh (4H, H)
+    float *out;           // forward: h written at out[(s*T + t) * out_ld + out_off + k]
+    const float *dout;    // backward: gradient w.r.t. out, same addressing
+    long long out_ld; int out_off;
+    float *gates;         // (S, T, 4H) post-activation
+    float *cells;         // (S, T, H)
+    float *hprev;         // (S, T, H)  h_{t-1} as seen by step t
+    float *dgates;        // backward out: (S, T, 4H) pre-activation gradients
+    int S, T, H, G;
+    int reverse;
+    int w_smem;
+};
+
+__global__ void k_lstm_fwd(LstmArgs a) {
+    extern __shared__ float sm[];
+    const int H = a.H, H4 = 4 * a.H, G = a.G;
+    float *h_s = sm;                 // [G][H]
+    float *c_s = h_s + G * H;        // [G][H]
+    float *g_s = c_s + G * H;        // [G][4H]
+    float *w_s = g_s + G * H4;       // [H][4H] if w_smem
+    const int j = threadIdx.x;
+    const int s0 = blockIdx.x * G;
+    const int ng = min(G, a.S - s0);
+    for (int i = j; i < G * H; i += blockDim.x) { h_s[i] = 0.f; c_s[i] = 0.f; }
+    if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
+    __syncthreads();
+    const float *w = a.w_smem ? w_s : a.w;
+    for (int step = 0; step < a.T; step++) {
+        const int t = a.reverse ? a.T - 1 - step : step;
+        if (j < H4) {
+            float acc[kLstmG];
+#pragma unroll
+            for (int g = 0; g < kLstmG; g++) acc[g] = (g < ng) ? a.xproj[((long long)(s0 + g) * a.T + t) * H4 + j] : 0.f;
+            for (int k = 0; k < H; k++) {
+                const float wv = w[k * H4 + j];
+#pragma unroll
+                for (int g = 0; g < kLstmG; g++) if (g < ng) acc[g] = fmaf(wv, h_s[g * H + k], acc[g]);
+            }
+            const bool is_tanh = (j >= 2 * H) && (j < 3 * H);
+#pragma unroll
+            for (int g = 0; g < kLstmG; g++) if (g < ng) {
+                const float v = is_tanh ? tanhf(acc[g]) : sigmoidf(acc[g]);
+                g_s[g * H4 + j] = v;
+                a.gates[((long long)(s0 + g) * a.T + t) * H4 + j] = v;
+            }
+        }
+        __syncthreads();
+        for (int i = j; i < ng * H; i += blockDim.x) {
+            const int g = i / H, k = i - g * H;
+            const float *gs = g_s + g * H4;
+            const long long row = (long long)(s0 + g) * a.T + t;
+            a.hprev[row * H + k] = h_s[i];
+            const float c = gs[H + k] * c_s[i] + gs[k] * gs[2 * H + k];
+            const float h = gs[3 * H + k] * tanhf(c);
+            c_s[i] = c;
+            h_s[i] = h;
+            a.cells[row * H + k] = c;
+            a.out[row * a.out_ld + a.out_off + k] = h;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void k_lstm_bwd(LstmArgs a) {
+    extern __shared__ float sm[];
+    const int H = a.H, H4 = 4 * a.H, G = a.G;
+    float *dh_s = sm;                 // [G][H]  dL/dh carried from the later step
+    float *dc_s = dh_s + G * H;       // [G][H]
+    float *dg_s = dc_s + G * H;       // [G][4H]
+    float *w_s = dg_s + G * H4;       // [4H][H] if w_smem
+    const int j = threadIdx.x;
+    const int s0 = blockIdx.x * G;
+    const int ng = min(G, a.S - s0);
+    for (int i = j; i < G * H; i += blockDim.x) { dh_s[i] = 0.f; dc_s[i] = 0.f; }
+    if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
+    __syncthreads();
+    const float *w = a.w_smem ? w_s : a.w;
+    for (int step = a.T - 1; step >= 0; step--) {
+        const int t = a.reverse ? a.T - 1 - step : step;          // time index of forward step `step`
+        const int t_prev = a.reverse ? t + 1 : t - 1;             // where c_{step-1} lives
+        for (int i = j; i < ng * H; i += blockDim.x) {
+            const int g = i / H, k = i - g * H;
+            const long long row = (long long)(s0 + g) * a.T + t;
+            const float *gs = a.gates + row * H4;
+            const float gi = gs[k], gf = gs[H + k], gg = gs[2 * H + k], go = gs[3 * H + k];
+            const float c = a.cells[row * H + k];
+            const float c_prev = step > 0 ? a.cells[((long long)(s0 + g) * a.T + t_prev) * H + k] : 0.f;
+            const float tc = tanhf(c);
+            const float dh = dh_s[i] + (a.dout ? a.dout[row * a.out_ld + a.out_off + k] : 0.f);
+            const float dc = dc_s[i] + dh * go * (1.f - tc * tc);
+            const float d_i = dc * gg * gi * (1.f - gi);
+            const float d_f = dc * c_prev * gf * (1.f - gf);
+            const float d_g = dc * gi * (1.f - gg * gg);
+            const float d_o = dh * tc * go * (1.f - go);
+            dc_s[i] = dc * gf;
+            float *dgo = a.dgates + row * H4;
+            dgo[k] = d_i; dgo[H + k] = d_f; dgo[2 * H + k] = d_g; dgo[3 * H + k] = d_o;
+            float *ds = dg_s + g * H4;
+            ds[k] = d_i; ds[H + k] = d_f; ds[2 * H + k] = d_g; ds[3 * H + k] = d_o;
+        }
+        __syncthreads();
+        for (int i = j; i < ng * H; i += blockDim.x) {            // dh_{step-1} = W_hh^T · dgates
+            const int g = i / H, k = i - g * H;
+            const float *ds = dg_s + g * H4;
+            float acc = 0.f;
+            for (int r = 0; r < H4; r++) acc = fmaf(w[r * H + k], ds[r], acc);
+            dh_s[i] = acc;
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// combine (style/model.py:796-815): out[n, m] = sum_k x[n,k,m] w[n,k] / sum_k w[n,k],  w = sqrt(1 + sum_m x^2).
+// x is addressed as x[n * n_stride + k * k_stride + m].
+// ------------------------------------------------------------------------------------------------
+struct CombineArgs {
+    const float *x; long long n_stride, k_stride;
+    int N, K; long long M;
+    float *ss;          // [N, K] sums of squares (zeroed by the caller before k_combine_sumsq)
+    float *out;         // [N, M]
+    const float *dout;  // [N, M]
+    float *stats;       // backward: [N, K + 1]: A_k = sum dout*x_k, then B = sum dout*out (zeroed by the caller)
+    float *dx;          // same addressing as x; accumulate flag below
+    int accumulate;
+};
+
+__device__ __forceinline__ float block_sum(float v, float *tmp) {
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) tmp[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = 0.f;
+    if (threadIdx.x < 32) {
+        r = threadIdx.x < (blockDim.x >> 5) ? tmp[threadIdx.x] : 0.f;
+        for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    }
+    __syncthreads();
+    return r;   // valid on thread 0
+}
+
+// grid: (chunks, N*K)
+__global__ void __launch_bounds__(256)
+k_combine_sumsq(CombineArgs a) {
+    __shared__ float tmp[8];
+    const int nk = blockIdx.y, n = nk / a.K, k = nk - n * a.K;
+    const float *p = a.x + n * a.n_stride + k * a.k_stride;
+    float s = 0.f;
+    for (long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x; m < a.M; m += (long long)gridDim.x * blockDim.x) s = fmaf(p[m], p[m], s);
+    s = block_sum(s, tmp);
+    if (threadIdx.x == 0) atomicAdd(a.ss + nk, s);
+}
+
+// grid: (chunks, N)
+__global__ void __launch_bounds__(256)
+k_combine_fwd(CombineArgs a) {
+    const int n = blockIdx.y;
+    float wsum = 0.f;
+    for (int k = 0; k < a.K; k++) wsum += sqrtf(1.f + a.ss[n * a.K + k]);
+    for (long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x; m < a.M; m += (long long)gridDim.x * blockDim.x) {
+        float v = 0.f;
+        for (int k = 0; k < a.K; k++) v = fmaf(a.x[n * a.n_stride + k * a.k_stride + m], sqrtf(1.f + a.ss[n * a.K + k]), v);
+        a.out[(long long)n * a.M + m] = v / wsum;
+    }
+}
+
+// grid: (chunks, N): stats[n, k] += sum_m dout*x_k ; stats[n, K] += sum_m dout*out
+__global__ void __launch_bounds__(256)
+k_combine_bwd_stats(CombineArgs a) {
+    __shared__ float tmp[8];
+    const int n = blockIdx.y;
+    for (int k = 0; k <= a.K; k++) {
+        float s = 0.f;
+        for (long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x; m < a.M; m += (long long)gridDim.x * blockDim.x) {
+            const float d = a.dout[(long long)n * a.M + m];
+            const float v = k < a.K ? a.x[n * a.n_stride + k * a.k_stride + m] : a.out[(long long)n * a.M + m];
+            s = fmaf(d, v, s);
+        }
+        s = block_sum(s, tmp);
+        if (threadIdx.x == 0) atomicAdd(a.stats + n * (a.K + 1) + k, s);
+    }
+}
+
+// dx[n,k,m] (+)= dout[n,m] * w_k / S + (A_k - B) / (S * w_k) * x[n,k,m]
+__global__ void __launch_bounds__(256)
+k_combine_bwd(CombineArgs a) {
+    const int n = blockIdx.y;
+    float wsum = 0.f;
+    for (int k = 0; k < a.K; k++) wsum += sqrtf(1.f + a.ss[n * a.K + k]);
+    const float Bs = a.stats[n * (a.K + 1) + a.K];
+    for (long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x; m < a.M; m += (long long)gridDim.x * blockDim.x) {
+        const float d = a.dout[(long long)n * a.M + m];
+        for (int k = 0; k < a.K; k++) {
+            const float w = sqrtf(1.f + a.ss[n * a.K + k]);
+            const long long idx = n * a.n_stride + k * a.k_stride + m;
+            const float g = d * w / wsum + (a.stats[n * (a.K + 1) + k] - Bs) / (wsum * w) * a.x[idx];
+            if (a.accumulate) a.dx[idx] += g; else a.dx[idx] = g;
+        }
+    }
+}
+
+}  // namespace mstm

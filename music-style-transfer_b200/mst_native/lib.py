@@ -23,6 +23,8 @@ EXPORTS = [
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
     'mst_encode_host_workspace_bytes', 'mst_encode_batch_host',
     'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write',
+    'mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
+    'mst_model_workspace_bytes', 'mst_model_forward',
 ]
 
 

@@ -1,0 +1,123 @@
+"""ctypes binding of the model entry points of libmst_b200.so (mst_model_*, include/mst_b200.h).
+
+Parameters live in one flat fp32 CUDA buffer whose layout the library describes by state-dict name
+(mst_model_param_*), so a reference `state_dict()` maps onto it by name."""
+import ctypes
+
+import numpy as np
+
+from . import lib as _lib
+
+
+class ModelShape(ctypes.Structure):
+    _fields_ = [('n_samples', ctypes.c_int32), ('n_channels', ctypes.c_int32), ('n_bars', ctypes.c_int32),
+                ('n_beats', ctypes.c_int32), ('has_unpitched', ctypes.c_int32)]
+
+
+class ModelOutputs(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_void_p) for k in ('instruments', 'mode', 'bpm', 'pitched', 'unpitched', 'style',
+                                               'melody', 'rhythm')]
+
+
+EXPORTS = ['mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
+           'mst_model_workspace_bytes', 'mst_model_forward']
+
+_ready = False
+
+
+def _L():
+    global _ready
+    L = _lib.load()
+    if not _ready:
+        L.mst_model_param_count.restype = ctypes.c_int
+        L.mst_model_param_name.restype = ctypes.c_char_p
+        L.mst_model_param_name.argtypes = [ctypes.c_int]
+        L.mst_model_param_numel.restype = ctypes.c_longlong
+        L.mst_model_param_numel.argtypes = [ctypes.c_int]
+        L.mst_model_param_offset.restype = ctypes.c_longlong
+        L.mst_model_param_offset.argtypes = [ctypes.c_int]
+        L.mst_model_workspace_bytes.restype = ctypes.c_size_t
+        L.mst_model_workspace_bytes.argtypes = [ctypes.POINTER(ModelShape), ctypes.c_int]
+        L.mst_model_forward.restype = ctypes.c_int
+        L.mst_model_forward.argtypes = [ctypes.c_void_p, ctypes.POINTER(ModelShape)] + [ctypes.c_void_p] * 5 + [
+            ctypes.POINTER(ModelOutputs), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_void_p,
+            ctypes.POINTER(ctypes.c_int)]
+        _ready = True
+    return L
+
+
+def param_table():
+    """[(name, offset, numel)] of the flat parameter buffer."""
+    L = _L()
+    n = L.mst_model_param_count()
+    return [(L.mst_model_param_name(i).decode(), int(L.mst_model_param_offset(i)), int(L.mst_model_param_numel(i)))
+            for i in range(n)]
+
+
+def total_params():
+    L = _L()
+    return int(L.mst_model_param_offset(L.mst_model_param_count()))
+
+
+def flatten_state_dict(sd, device='cuda'):
+    """state_dict (reference names) -> flat fp32 tensor in the library's layout."""
+    import torch
+    flat = torch.empty(total_params(), dtype=torch.float32, device=device)
+    for name, off, numel in param_table():
+        t = sd[name]
+        assert t.numel() == numel, (name, tuple(t.shape), numel)
+        flat[off:off + numel] = t.detach().reshape(-1).to(device=device, dtype=torch.float32)
+    return flat
+
+
+def unflatten(flat, like_sd):
+    """flat buffer -> {name: tensor view shaped like like_sd[name]}."""
+    return {name: flat[off:off + numel].view(like_sd[name].shape) for name, off, numel in param_table()}
+
+
+class Workspace:
+    """Activation arena for one batch shape (reused across steps)."""
+
+    def __init__(self, N, C, B, nb, has_unpitched, training=False, device=None):
+        import torch
+        _lib.require_gpu()
+        self.shape = ModelShape(int(N), int(C), int(B), int(nb), int(bool(has_unpitched)))
+        self.training = bool(training)
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        self.bytes = _L().mst_model_workspace_bytes(ctypes.byref(self.shape), int(self.training))
+        self.buf = torch.empty(self.bytes, dtype=torch.uint8, device=self.device)
+        self.launches = 0
+
+    def _view(self, ptr, shape):
+        import torch
+        if not ptr:
+            return None
+        off = ptr - self.buf.data_ptr()
+        n = int(np.prod(shape))
+        return self.buf[off:off + 4 * n].view(torch.float32).view(*shape)
+
+    def forward(self, flat_params, pitched, unpitched, feats, mode, bpm, stream=None):
+        """Inputs are contiguous float32 CUDA tensors with a leading sample dim N.  Returns a dict of views into
+        the workspace (valid until the next call)."""
+        import torch
+        s = self.shape
+        N, C, B, nb = s.n_samples, s.n_channels, s.n_bars, s.n_beats
+        assert tuple(pitched.shape) == (N, C, B, nb, 10, 56, 5) and pitched.is_contiguous()
+        assert tuple(feats.shape) == (N, C, 51) and tuple(mode.shape) == (N, 2) and tuple(bpm.shape) == (N,)
+        if s.has_unpitched:
+            assert unpitched is not None and unpitched.numel() == N * B * nb * 10 * 47 * 2 and unpitched.is_contiguous()
+        outs = ModelOutputs()
+        nl = ctypes.c_int(0)
+        st = torch.cuda.current_stream(self.device) if stream is None else stream
+        _lib.check(_L().mst_model_forward(
+            flat_params.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
+            unpitched.data_ptr() if s.has_unpitched else None, feats.contiguous().data_ptr(),
+            mode.contiguous().data_ptr(), bpm.contiguous().data_ptr(), ctypes.byref(outs), self.buf.data_ptr(),
+            self.bytes, int(self.training), st.cuda_stream, ctypes.byref(nl)))
+        self.launches = nl.value
+        return dict(
+            instruments=self._view(outs.instruments, (N, 41)), mode=self._view(outs.mode, (N, 2)),
+            bpm=self._view(outs.bpm, (N,)), pitched=self._view(outs.pitched, (N, C, B, nb, 10, 56, 5)),
+            unpitched=self._view(outs.unpitched, (N, 1, B, nb, 10, 47, 2)) if s.has_unpitched else None,
+            style=self._view(outs.style, (N, 256)), melody=self._view(outs.melody, (N, B, nb, 10, 56, 8)),
+            rhythm=self._view(outs.rhythm, (N, B, nb, 10, 32)))
