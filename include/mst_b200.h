@@ -297,6 +297,58 @@ int mst_model_forward(const float *d_params, const MstModelShape *shape, const f
                       MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes, int training,
                       void *stream, int *n_launches);
 
+/* One training iteration of train-model.py:111-126 for N independent samples: forward, get_total_loss
+ * (style/model.py:935-997, the positional quirk of train-model.py:115-122 resolved by the caller: "mode" is the
+ * cross-entropy pair (mode logits vs the one-hot input mode), "bpm" the squared-error pair (predicted bpm vs
+ * d_bpm_target)), and loss.backward().  Parameter gradients are ADDED into d_grads (flat, same layout as d_params):
+ * the sum over the N samples and over successive calls, i.e. the reference's iter_size accumulation (:151-154).
+ * d_losses (N, MST_N_LOSS_LEAVES) receives every leaf of the nested loss dict per sample (MST_LOSS_* indices).
+ * The workspace is sized by mst_model_workspace_bytes(shape, 1).  outputs may be NULL. */
+#define MST_N_LOSS_LEAVES 16
+#define MST_LOSS_TOTAL            0   /* ['total'] */
+#define MST_LOSS_CHANNELS         1   /* ['channels_loss']['total'] */
+#define MST_LOSS_P_TOTAL          2   /* ['channels_loss']['pitched']['total'] */
+#define MST_LOSS_P_NOTES          3
+#define MST_LOSS_P_VELOCITY       4
+#define MST_LOSS_P_DURATION       5
+#define MST_LOSS_P_ACCIDENTALS    6
+#define MST_LOSS_U_TOTAL          7   /* ['channels_loss']['unpitched'][...]; 0 when there is no unpitched grid */
+#define MST_LOSS_U_NOTES          8
+#define MST_LOSS_U_VELOCITY       9
+#define MST_LOSS_U_DURATION      10
+#define MST_LOSS_SONG_TOTAL      11   /* ['song_info_loss']['total'] */
+#define MST_LOSS_INSTRUMENTS     12
+#define MST_LOSS_MODE            13
+#define MST_LOSS_BPM             14
+
+int mst_model_train_step(const float *d_params, float *d_grads, const MstModelShape *shape, const float *d_pitched,
+                         const float *d_unpitched, const float *d_features, const float *d_mode, const float *d_bpm,
+                         const float *d_instruments_target /* (N,41) get_used_instruments, data.py:159 */,
+                         const float *d_bpm_target /* (N) info['bpm'] */, int normalize,
+                         float *d_losses, MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes,
+                         void *stream, int *n_launches);
+
+/* get_total_loss alone (style/model.py:935-997) on caller-provided predictions / targets, N samples segmented. */
+typedef struct MstLossIn {
+    const float *pitched_pred, *pitched_target;         /* (N,C,B,nb,10,56,5) */
+    const float *unpitched_pred, *unpitched_target;     /* (N,1,B,nb,10,47,2) or both NULL */
+    const float *instruments_logits, *instruments_target; /* (N,41) */
+    const float *mode_logits, *mode_target;             /* (N,2): cross-entropy against argmax(mode_target) */
+    const float *bpm_pred, *bpm_target;                 /* (N): ((pred - target) / 150)^2 */
+    int32_t normalize;
+    int32_t reserved;
+} MstLossIn;
+size_t mst_model_loss_workspace_bytes(const MstModelShape *shape);
+int mst_model_loss(const MstModelShape *shape, const MstLossIn *in, float *d_losses, void *d_workspace,
+                   size_t workspace_bytes, void *stream);
+
+/* torch.optim.Adam.step (train-model.py:89,152; defaults betas (.9,.999), eps 1e-8, no weight decay) on the flat
+ * buffers, `step` = 1-based optimizer step count (bias correction), lr already scheduled by the caller
+ * (StepLR(200, .9), :90,154).  grad_scale multiplies the gradient first (1 = the reference's summed gradients);
+ * zero_grad != 0 clears d_grads in the same pass (optimizer.zero_grad(), :153). */
+int mst_adam_step(float *d_params, float *d_grads, float *d_m, float *d_v, long long n, int step, float lr,
+                  float beta1, float beta2, float eps, float grad_scale, int zero_grad, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

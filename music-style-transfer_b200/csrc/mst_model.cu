@@ -4,12 +4,13 @@
 // a caller-provided arena.  A batch is N *independent* batch-1 samples of identical shape (C, B, T, drums):
 // every reduction of the reference that spans the batch dimension (combine, the loss sums) is segmented per
 // sample, and gradients are summed over samples — exactly train-model.py's iter_size accumulation.
+#include <math.h>
 #include <string.h>
 
 #include <algorithm>
 #include <vector>
 
-#include "mst_model_tails.cuh"
+#include "mst_model_tails_bwd.cuh"
 
 using namespace mstm;
 
@@ -236,17 +237,20 @@ inline int grid_for(long long n, int threads = 256, int cap = 148 * 16) {
 struct Launcher {
     cudaStream_t st;
     int launches = 0;
+    bool dry = false;             // planning pass: carve the arena, launch nothing
     cudaError_t err = cudaSuccess;
     void check() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && err == cudaSuccess) err = e; launches++; }
 
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
               int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int amode = 0) {
-        if (M <= 0 || N <= 0 || K <= 0) return;
+        if (dry || M <= 0 || N <= 0 || K <= 0) return;
         GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
         if (split_k > 1) g.accumulate = 2;
         dim3 grid((N + kGemmTile - 1) / kGemmTile, (M + kGemmTile - 1) / kGemmTile, split_k);
-        if (amode == 0) k_gemm<0><<<grid, kGemmThreads, 0, st>>>(g); else k_gemm<1><<<grid, kGemmThreads, 0, st>>>(g);
+        if (amode == 0) k_gemm<0><<<grid, kGemmThreads, 0, st>>>(g);
+        else if (amode == 1) k_gemm<1><<<grid, kGemmThreads, 0, st>>>(g);
+        else k_gemm<2><<<grid, kGemmThreads, 0, st>>>(g);
         check();
     }
     // Y[M,N] = act(X[M,K]·W[N,K]^T + bias)      (nn.Linear); W row stride ldw (column block of a wider weight)
@@ -264,25 +268,28 @@ struct Launcher {
         gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
     }
     void colsum(const float *in, float *out, long long rows, int cols) {
-        if (rows <= 0) return;
+        if (dry || rows <= 0) return;
         dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((rows + 63) / 64, 256)), (cols + 31) / 32);
         k_colsum<<<grid, 256, 0, st>>>(in, out, rows, cols); check();
     }
-    void fill(float *p, long long n, float v) { if (n > 0) { k_fill<<<grid_for(n), 256, 0, st>>>(p, n, v); check(); } }
-    void axpy(float *y, const float *x, long long n) { if (n > 0) { k_axpy<<<grid_for(n), 256, 0, st>>>(y, x, n); check(); } }
-    void act_grad(const float *dY, const float *Y, float *dPre, long long n) { k_act_grad<<<grid_for(n), 256, 0, st>>>(dY, Y, dPre, n); check(); }
+    void fill(float *p, long long n, float v) { if (!dry && n > 0) { k_fill<<<grid_for(n), 256, 0, st>>>(p, n, v); check(); } }
+    void axpy(float *y, const float *x, long long n) { if (!dry && n > 0) { k_axpy<<<grid_for(n), 256, 0, st>>>(y, x, n); check(); } }
+    void act_grad(const float *dY, const float *Y, float *dPre, long long n) { if (dry || n <= 0) return; k_act_grad<<<grid_for(n), 256, 0, st>>>(dY, Y, dPre, n); check(); }
     void reduce_mid(const float *in, float *out, long long A, int L, long long inner, int accumulate) {
+        if (dry) return;
         k_reduce_mid<<<grid_for(A * inner), 256, 0, st>>>(in, out, A, L, inner, accumulate); check();
     }
     void bcast(BcastArgs &a) {
+        if (dry) return;
         const long long total = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f * a.cols;
         k_bcast_add<<<grid_for(total), 256, 0, st>>>(a); check();
     }
-    void take_last(const float *in, float *out, long long S, int T, int H) { k_take_last<<<grid_for(S * H), 256, 0, st>>>(in, out, S, T, H); check(); }
-    void put_last(const float *src, float *dst, long long S, int T, int H) { k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }
+    void take_last(const float *in, float *out, long long S, int T, int H) { if (dry) return; k_take_last<<<grid_for(S * H), 256, 0, st>>>(in, out, S, T, H); check(); }
+    void put_last(const float *src, float *dst, long long S, int T, int H) { if (dry) return; k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }
 
     static size_t lstm_smem(int H, int G, bool w_smem) { return sizeof(float) * ((size_t)2 * G * H + (size_t)G * 4 * H + (w_smem ? (size_t)H * 4 * H : 0)); }
     void lstm(LstmArgs a, bool backward) {
+        if (dry) return;
         a.G = a.S >= 148 * 2 ? kLstmG : 1;
         a.w_smem = ((size_t)a.H * 4 * a.H * sizeof(float) <= 96 * 1024) ? 1 : 0;
         const size_t smem = lstm_smem(a.H, a.G, a.w_smem);
@@ -298,6 +305,7 @@ struct Launcher {
         check();
     }
     void combine_fwd(CombineArgs a) {
+        if (dry) return;
         fill(a.ss, (long long)a.N * a.K, 0.f);
         dim3 g1((unsigned)std::max<long long>(1, std::min<long long>((a.M + 2047) / 2048, 64)), a.N * a.K);
         k_combine_sumsq<<<g1, 256, 0, st>>>(a); check();
@@ -305,6 +313,7 @@ struct Launcher {
         k_combine_fwd<<<g2, 256, 0, st>>>(a); check();
     }
     void combine_bwd(CombineArgs a) {
+        if (dry) return;
         fill(a.stats, (long long)a.N * (a.K + 1), 0.f);
         dim3 g1((unsigned)std::max<long long>(1, std::min<long long>((a.M + 2047) / 2048, 64)), a.N);
         k_combine_bwd_stats<<<g1, 256, 0, st>>>(a); check();
@@ -624,8 +633,12 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
 
 }  // namespace
 
+// ------------------------------------------------------------------------------------------------ losses + backward
+namespace {
+#include "mst_model_bwd_host.inl"
+}  // namespace
+
 // ------------------------------------------------------------------------------------------------ C ABI
-static size_t plan_backward(Ctx &c, Arena &ar);   // defined with the backward pass
 
 static int setup_ctx(Ctx &c, const MstModelShape *s, void *ws, size_t ws_bytes, bool training, bool dry) {
     init_param_offsets();
@@ -679,4 +692,68 @@ extern "C" int mst_model_forward(const float *d_params, const MstModelShape *sha
     return MST_OK;
 }
 
-static size_t plan_backward(Ctx &c, Arena &ar) { (void)c; return ar.off; }   // placeholder until the backward pass lands
+extern "C" int mst_model_train_step(const float *d_params, float *d_grads, const MstModelShape *shape, const float *d_pitched,
+                                    const float *d_unpitched, const float *d_features, const float *d_mode, const float *d_bpm,
+                                    const float *d_instruments_target, const float *d_bpm_target, int normalize,
+                                    float *d_losses, MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes,
+                                    void *stream, int *n_launches) {
+    if (!d_params || !d_grads || !shape || !d_pitched || !d_features || !d_mode || !d_bpm || !d_instruments_target ||
+        !d_bpm_target || !d_losses || !d_workspace || (shape->has_unpitched && !d_unpitched)) {
+        mst_set_error("mst_model_train_step: null pointer argument");
+        return MST_E_INVALID;
+    }
+    init_param_offsets();
+    Ctx c;
+    memset(&c, 0, sizeof(c));
+    c.N = shape->n_samples; c.C = shape->n_channels; c.B = shape->n_bars; c.T = shape->n_beats; c.U = shape->has_unpitched ? 1 : 0;
+    if (c.N < 1 || c.C < 1 || c.B < 1 || c.T < 1 || c.C > 64) { mst_set_error("mst_model: bad shape"); return MST_E_INVALID; }
+    if (mst_model_workspace_bytes(shape, 1) > workspace_bytes) {
+        mst_set_error("mst_model_train_step: workspace too small (%zu < %zu)", workspace_bytes, mst_model_workspace_bytes(shape, 1));
+        return MST_E_CAPACITY;
+    }
+    Arena ar{(char *)d_workspace, 0, false};
+    plan_forward(c, ar);
+    c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
+    Launcher L; L.st = (cudaStream_t)stream;
+    forward_extract(L, c);
+    forward_song_info(L, c);
+    forward_apply(L, c, c.U != 0);
+    TrainIn ti{d_instruments_target, d_bpm_target, normalize, d_losses};
+    backward(L, c, ar, ti);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_train_step: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    if (outputs) fill_outputs(c, outputs);
+    if (n_launches) *n_launches = L.launches;
+    return MST_OK;
+}
+
+extern "C" size_t mst_model_loss_workspace_bytes(const MstModelShape *shape) {
+    return (size_t)(shape ? shape->n_samples : 1) * 1024 + 4096;
+}
+
+extern "C" int mst_model_loss(const MstModelShape *shape, const MstLossIn *in, float *d_losses, void *d_workspace,
+                              size_t workspace_bytes, void *stream) {
+    if (!shape || !in || !d_losses || !d_workspace || !in->pitched_pred || !in->pitched_target || !in->instruments_logits ||
+        !in->instruments_target || !in->mode_logits || !in->mode_target || !in->bpm_pred || !in->bpm_target) {
+        mst_set_error("mst_model_loss: null pointer argument");
+        return MST_E_INVALID;
+    }
+    if (workspace_bytes < mst_model_loss_workspace_bytes(shape)) { mst_set_error("mst_model_loss: workspace too small"); return MST_E_CAPACITY; }
+    const int N = shape->n_samples, U = (in->unpitched_pred && in->unpitched_target) ? 1 : 0;
+    Arena ar{(char *)d_workspace, 0, false};
+    Launcher L; L.st = (cudaStream_t)stream;
+    run_losses(L, ar, N, U, (long long)shape->n_channels * shape->n_bars * shape->n_beats * 560, (long long)shape->n_bars * shape->n_beats * 470,
+               in->pitched_pred, in->pitched_target, in->unpitched_pred, in->unpitched_target, in->instruments_logits,
+               in->instruments_target, in->mode_logits, in->mode_target, in->bpm_pred, in->bpm_target, in->normalize, d_losses, false);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_loss: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    return MST_OK;
+}
+
+extern "C" int mst_adam_step(float *d_params, float *d_grads, float *d_m, float *d_v, long long n, int step, float lr,
+                             float beta1, float beta2, float eps, float grad_scale, int zero_grad, void *stream) {
+    if (!d_params || !d_grads || !d_m || !d_v || n <= 0 || step < 1) { mst_set_error("mst_adam_step: bad argument"); return MST_E_INVALID; }
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    k_adam<<<grid_for(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(d_params, d_grads, d_m, d_v, n, beta1, beta2, eps,
+                                                                     (float)((double)lr / bc1), (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad);
+    MST_LAUNCH_CHECK("k_adam");
+    return MST_OK;
+}

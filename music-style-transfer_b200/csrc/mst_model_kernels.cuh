@@ -40,6 +40,8 @@ constexpr int kGemmTile = 64, kGemmK = 16, kGemmThreads = 256;
 template <int AMODE>
 __device__ __forceinline__ float gemm_load_a(const GemmArgs &g, int i, int k) {
     if (AMODE == 0) return g.A[(long long)i * g.a_si + (long long)k * g.a_sk];
+    // AMODE 2 is the transposed gather (i = im2col column, k = (beat-row, octave)): the weight-gradient GEMM
+    if (AMODE == 2) { const int t = i; i = k; k = t; }
     // conv gather: k = f * 70 + tap * 5 + feat over the (10, 56, 5) beat block
     const int row = i >> 3, oct = i & 7;
     const int f = k / 70, r = k - f * 70;
@@ -182,6 +184,39 @@ k_reduce_mid(const float *__restrict__ in, float *__restrict__ out, long long A,
     }
 }
 
+// out[a, i] += sum_l in[a, l, i] with the middle axis split over blockIdx.y (atomic accumulate into `out`)
+__global__ void __launch_bounds__(256)
+k_reduce_mid_split(const float *__restrict__ in, float *__restrict__ out, long long A, int L, long long inner, int l_per) {
+    const long long total = A * inner;
+    const int l0 = blockIdx.y * l_per, l1 = min(L, l0 + l_per);
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const long long a = idx / inner, i = idx - a * inner;
+        const float *p = in + a * L * inner + i;
+        float s = 0.f;
+        for (int l = l0; l < l1; l++) s += p[(long long)l * inner];
+        atomicAdd(out + idx, s);
+    }
+}
+
+// beats_conv weight gradient: G[o][ch][tap] (57, 50, 14) += gT[perm(ch, tap)][o] with gT (700, 57) in im2col column order
+__global__ void __launch_bounds__(256)
+k_conv_wgrad_unpack(const float *__restrict__ gT, float *__restrict__ G);
+
+// Adam (torch.optim.Adam defaults: no amsgrad, no weight decay) on the flat buffers + optional zero_grad.
+//   m = b1 m + (1 - b1) g ; v = b2 v + (1 - b2) g^2 ; p -= lr / (1 - b1^t) * m / (sqrt(v) / sqrt(1 - b2^t) + eps)
+__global__ void __launch_bounds__(256)
+k_adam(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m, float *__restrict__ v, long long n,
+       float b1, float b2, float eps, float step_size, float inv_sqrt_bc2, float grad_scale, int zero_grad) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float gi = g[i] * grad_scale;
+        const float mi = b1 * m[i] + (1.f - b1) * gi;
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        p[i] -= step_size * (mi / (sqrtf(vi) * inv_sqrt_bc2 + eps));
+        if (zero_grad) g[i] = 0.f;
+    }
+}
+
 // column sums of a [rows, cols] matrix into out[cols] (atomic accumulate) — bias gradients
 __global__ void __launch_bounds__(256)
 k_colsum(const float *__restrict__ in, float *__restrict__ out, long long rows, int cols) {
@@ -224,6 +259,14 @@ __device__ __forceinline__ int perm_col(int mode, int j) {
     if (mode == 1) { if (j >= 456) return j; const int o = j >> 3, oct = j & 7; return oct * 57 + o; }
     const int f = j / 94, r = j - f * 94; const int feat = r / 47, note = r - feat * 47; return f * 94 + note * 2 + feat;
 }
+__global__ void __launch_bounds__(256)
+k_conv_wgrad_unpack(const float *__restrict__ gT, float *__restrict__ G) {
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < 57 * 700; idx += gridDim.x * blockDim.x) {
+        const int o = idx / 700, j = idx - o * 700;
+        G[idx] += gT[perm_col(0, j) * 57 + o];
+    }
+}
+
 __global__ void __launch_bounds__(256)
 k_permute_cols(const float *__restrict__ src, float *__restrict__ dst, int rows, int cols, int mode, int inverse, int accumulate) {
     const int total = rows * cols;

@@ -19,8 +19,26 @@ class ModelOutputs(ctypes.Structure):
                                                'melody', 'rhythm')]
 
 
+class LossIn(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_void_p) for k in (
+        'pitched_pred', 'pitched_target', 'unpitched_pred', 'unpitched_target', 'instruments_logits',
+        'instruments_target', 'mode_logits', 'mode_target', 'bpm_pred', 'bpm_target')] + [
+        ('normalize', ctypes.c_int32), ('reserved', ctypes.c_int32)]
+
+
 EXPORTS = ['mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
-           'mst_model_workspace_bytes', 'mst_model_forward']
+           'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_loss_workspace_bytes',
+           'mst_model_loss', 'mst_adam_step']
+
+N_LOSS_LEAVES = 16
+# index of every leaf of get_total_loss's nested dict in the (N, 16) loss buffer (include/mst_b200.h MST_LOSS_*)
+LOSS_LEAVES = {
+    'total': 0, 'channels_loss/total': 1, 'channels_loss/pitched/total': 2, 'channels_loss/pitched/notes_loss': 3,
+    'channels_loss/pitched/velocity_loss': 4, 'channels_loss/pitched/duration_loss': 5,
+    'channels_loss/pitched/accidentals_loss': 6, 'channels_loss/unpitched/total': 7,
+    'channels_loss/unpitched/notes_loss': 8, 'channels_loss/unpitched/velocity_loss': 9,
+    'channels_loss/unpitched/duration_loss': 10, 'song_info_loss/total': 11, 'song_info_loss/instruments_loss': 12,
+    'song_info_loss/mode_loss': 13, 'song_info_loss/bpm_loss': 14}
 
 _ready = False
 
@@ -42,6 +60,18 @@ def _L():
         L.mst_model_forward.argtypes = [ctypes.c_void_p, ctypes.POINTER(ModelShape)] + [ctypes.c_void_p] * 5 + [
             ctypes.POINTER(ModelOutputs), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_void_p,
             ctypes.POINTER(ctypes.c_int)]
+        L.mst_model_train_step.restype = ctypes.c_int
+        L.mst_model_train_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ModelShape)] + \
+            [ctypes.c_void_p] * 7 + [ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ModelOutputs), ctypes.c_void_p,
+                                     ctypes.c_size_t, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        L.mst_model_loss_workspace_bytes.restype = ctypes.c_size_t
+        L.mst_model_loss_workspace_bytes.argtypes = [ctypes.POINTER(ModelShape)]
+        L.mst_model_loss.restype = ctypes.c_int
+        L.mst_model_loss.argtypes = [ctypes.POINTER(ModelShape), ctypes.POINTER(LossIn), ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_size_t, ctypes.c_void_p]
+        L.mst_adam_step.restype = ctypes.c_int
+        L.mst_adam_step.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_longlong, ctypes.c_int] + [ctypes.c_float] * 5 + [
+            ctypes.c_int, ctypes.c_void_p]
         _ready = True
     return L
 
@@ -121,3 +151,69 @@ class Workspace:
             unpitched=self._view(outs.unpitched, (N, 1, B, nb, 10, 47, 2)) if s.has_unpitched else None,
             style=self._view(outs.style, (N, 256)), melody=self._view(outs.melody, (N, B, nb, 10, 56, 8)),
             rhythm=self._view(outs.rhythm, (N, B, nb, 10, 32)))
+
+    def _outs(self, outs):
+        s = self.shape
+        N, C, B, nb = s.n_samples, s.n_channels, s.n_bars, s.n_beats
+        return dict(
+            instruments=self._view(outs.instruments, (N, 41)), mode=self._view(outs.mode, (N, 2)),
+            bpm=self._view(outs.bpm, (N,)), pitched=self._view(outs.pitched, (N, C, B, nb, 10, 56, 5)),
+            unpitched=self._view(outs.unpitched, (N, 1, B, nb, 10, 47, 2)) if s.has_unpitched else None,
+            style=self._view(outs.style, (N, 256)), melody=self._view(outs.melody, (N, B, nb, 10, 56, 8)),
+            rhythm=self._view(outs.rhythm, (N, B, nb, 10, 32)))
+
+    def train_step(self, flat_params, flat_grads, pitched, unpitched, feats, mode, bpm, instruments_target,
+                   bpm_target, losses=None, normalize=True, stream=None):
+        """forward + get_total_loss + backward for N independent samples; gradients are ADDED into flat_grads.
+        Returns (losses (N, 16) device tensor, outputs dict of workspace views)."""
+        import torch
+        assert self.training, 'Workspace(training=True) is required'
+        s = self.shape
+        N, C, B, nb = s.n_samples, s.n_channels, s.n_bars, s.n_beats
+        assert tuple(pitched.shape) == (N, C, B, nb, 10, 56, 5) and pitched.is_contiguous()
+        assert tuple(feats.shape) == (N, C, 51) and tuple(mode.shape) == (N, 2) and tuple(bpm.shape) == (N,)
+        assert tuple(instruments_target.shape) == (N, 41) and tuple(bpm_target.shape) == (N,)
+        if s.has_unpitched:
+            assert unpitched is not None and unpitched.numel() == N * B * nb * 10 * 47 * 2 and unpitched.is_contiguous()
+        if losses is None:
+            losses = torch.empty(N, N_LOSS_LEAVES, dtype=torch.float32, device=self.device)
+        outs = ModelOutputs()
+        nl = ctypes.c_int(0)
+        st = torch.cuda.current_stream(self.device) if stream is None else stream
+        _lib.check(_L().mst_model_train_step(
+            flat_params.data_ptr(), flat_grads.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
+            unpitched.data_ptr() if s.has_unpitched else None, feats.contiguous().data_ptr(),
+            mode.contiguous().data_ptr(), bpm.contiguous().data_ptr(), instruments_target.contiguous().data_ptr(),
+            bpm_target.contiguous().data_ptr(), int(bool(normalize)), losses.data_ptr(), ctypes.byref(outs),
+            self.buf.data_ptr(), self.bytes, st.cuda_stream, ctypes.byref(nl)))
+        self.launches = nl.value
+        return losses, self._outs(outs)
+
+
+def total_loss(pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits, instruments_target,
+               mode_logits, mode_target, bpm_pred, bpm_target, normalize=False):
+    """get_total_loss on device tensors with a leading sample dim -> (N, 16) loss leaves."""
+    import torch
+    _lib.require_gpu()
+    N, C, B, nb = pitched_pred.shape[:4]
+    shape = ModelShape(int(N), int(C), int(B), int(nb), int(unpitched_pred is not None))
+    f = lambda t: None if t is None else t.contiguous().float()
+    keep = [f(t) for t in (pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits,
+                           instruments_target, mode_logits, mode_target, bpm_pred, bpm_target)]
+    li = LossIn(*[None if t is None else t.data_ptr() for t in keep], int(bool(normalize)), 0)
+    wsb = _L().mst_model_loss_workspace_bytes(ctypes.byref(shape))
+    ws = torch.empty(wsb, dtype=torch.uint8, device=pitched_pred.device)
+    out = torch.empty(int(N), N_LOSS_LEAVES, dtype=torch.float32, device=pitched_pred.device)
+    _lib.check(_L().mst_model_loss(ctypes.byref(shape), ctypes.byref(li), out.data_ptr(), ws.data_ptr(), wsb,
+                                   torch.cuda.current_stream(pitched_pred.device).cuda_stream))
+    return out
+
+
+def adam_step(params, grads, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0, zero_grad=True, stream=None):
+    """torch.optim.Adam.step on the flat buffers (in place)."""
+    import torch
+    _lib.require_gpu()
+    st = torch.cuda.current_stream(params.device) if stream is None else stream
+    _lib.check(_L().mst_adam_step(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), params.numel(), int(step),
+                                  float(lr), float(beta1), float(beta2), float(eps), float(grad_scale), int(bool(zero_grad)),
+                                  st.cuda_stream))
