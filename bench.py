@@ -100,6 +100,127 @@ class ClockSampler:
                 'reasons': sorted(reasons), 'samples': len(sm)}
 
 
+TRAIN_SHAPE = dict(C=4, B=200, nb=4, drums=True)     # the 800 channel-bar crop of train-model.py:101
+
+
+def training_config(per_gpu, world):
+    return {'workload': 'configs[3]: synthetic-batch training of the style model (C=4 pitched channels x B=200 bars, 4/4, '
+                        'drums present, Bernoulli(0.003) grids, seed-108 weights), forward + get_total_loss + backward + '
+                        'all-reduce + Adam per step', 'per_gpu_batch': per_gpu, 'global_batch': per_gpu * world,
+            'gradient': 'sum over samples (iter_size semantics)', 'parallelism': f'dp{world}',
+            'l2_policy': 'inputs larger than L2: >=155 MB of grids + >=0.8 GB of activations per step'}
+
+
+def algorithmic_bytes_per_sample(C, B, nb, drums):
+    """read the input grids twice (fwd, bwd) + write and read the prediction grids once each."""
+    return 4 * 4 * nb * 10 * (280 * C + (94 if drums else 0)) * B
+
+
+def run_training(args, world, rank, torch, dist):
+    """Training leg (BASELINE.json configs[3]): samples/s over all ranks, device-timed, max over ranks."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import model_oracle as mo            # synthetic sample generator + seed-108 weights (data, not compute)
+    from mst_native import trainer as tr
+    N = args.train_batch
+    sh = TRAIN_SHAPE
+    distinct = [mo.synthetic_sample(seed=7 + 100 * rank + i, **sh) for i in range(min(N, 4))]
+    pick = lambda k: torch.cat([distinct[i % len(distinct)][k] for i in range(N)]).contiguous()
+    host = {k: pick(k).pin_memory() for k in ('pitched', 'unpitched', 'feats', 'mode', 'bpm')}
+    host['it'] = torch.cat([mo.used_instruments(distinct[i % len(distinct)]['feats'], distinct[0]['unpitched'])
+                            for i in range(N)]).pin_memory()
+    host['bt'] = torch.full((N,), 120.).pin_memory()
+    dev = {k: v.cuda() for k, v in host.items()}
+    t = tr.Trainer(mo.make_state_dict(108))
+    losses = torch.empty(N, 16, device='cuda')
+    h_losses = torch.empty(N, 16).pin_memory()
+
+    def step():
+        t.accumulate(dev['pitched'], dev['unpitched'], dev['feats'], dev['mode'], dev['bpm'], dev['it'], dev['bt'], losses)
+        t.optimizer_step()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.train_steps):
+        step()
+    ev1.record()
+    barrier()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    s_per_step = float(ms.item()) / 1e3 / args.train_steps
+    value = N * world / s_per_step
+    launches = t.launches
+    loss0 = float(losses[0, 0])
+
+    # e2e: pinned host inputs -> H2D -> step -> D2H of the loss leaves, every step
+    def e2e_step():
+        for k in dev:
+            dev[k].copy_(host[k], non_blocking=True)
+        step()
+        h_losses.copy_(losses, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.train_steps):
+        e2e_step()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+    barrier()
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    h2d = int(sum(v.numel() * v.element_size() for v in host.values()))
+    peak, peak_src = measured_peak_hbm()
+    alg = algorithmic_bytes_per_sample(**sh)
+    out = {
+        'metric': 'training samples/sec', 'value': value, 'unit': 'samples/s', 'ms_per_step': s_per_step * 1e3,
+        'steps': args.train_steps, 'config': training_config(N, world), 'dtype': 'f32',
+        'loss_total_sample0': loss0, 'gpu_launches_per_step': launches,
+        'roofline': {'kernel': 'whole training step (all kernels)', 'bound': 'hbm',
+                     'achieved': alg * N / s_per_step / 1e9, 'peak': peak, 'unit': 'GB/s',
+                     'frac': alg * N / s_per_step / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
+                     'algorithmic_bytes_per_sample': alg},
+        'e2e': {'value': N * world * args.train_steps / float(e2e_s.item()), 'unit': 'samples/s',
+                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': int(h_losses.numel() * 4)},
+    }
+    del t
+    torch.cuda.empty_cache()
+    return out
+
+
+def cpu_training_baseline(threads, steps=2):
+    """The reference's training iteration on the host cores: torch-CPU autograd over the model oracle (the plain-torch
+    restatement of style/model.py, pinned to it) + torch.optim.Adam, one sample of TRAIN_SHAPE per iteration."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import torch
+    import model_oracle as mo
+    torch.set_num_threads(threads)
+    s = mo.synthetic_sample(seed=7, **TRAIN_SHAPE)
+    sd = {k: v.clone().requires_grad_(True) for k, v in mo.make_state_dict(108).items()}
+    opt = torch.optim.Adam(list(sd.values()), lr=0.01)
+
+    def it():
+        losses, _ = mo.training_losses(sd, s['mode'], s['bpm'], s['pitched'], s['feats'], s['unpitched'], s['bpm_target'])
+        losses['total'].sum().backward()
+        opt.step(); opt.zero_grad()
+
+    it()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        it()
+    dt = (time.perf_counter() - t0) / steps
+    return {'value': 1.0 / dt, 'unit': 'samples/s', 'cores': threads, 'kind': 'port',
+            'sample': f'{steps} iterations of one C=4 x B=200 sample (fwd + loss + bwd + Adam), torch CPU, {threads} threads'}
+
+
 def run_reference(args):
     """CPU arm: the oracle port (oracle/mst_oracle.c, pthreads over all host cores).  The reference
     itself is pure Python and cannot travel to the GPU box (its dependencies are not in the image);
@@ -124,8 +245,10 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = bars / dt
     cfg = workload_config(args)
+    training = cpu_training_baseline(cores, steps=2)
+    training['config'] = training_config(1, 1)
     print(json.dumps({
-        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'impl': 'reference', 'training': training, 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64 quantise -> f32 grid',
         'data': 'synthetic', 'config': cfg,
@@ -143,9 +266,13 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--batch', type=int, default=512, help='songs per step per GPU')
     ap.add_argument('--pool', type=int, default=1024, help='distinct songs generated per GPU')
+    ap.add_argument('--train-batch', type=int, default=16, help='training samples per step per GPU')
+    ap.add_argument('--train-steps', type=int, default=0, help='timed training steps (default: min(steps, 10))')
+    ap.add_argument('--no-train', action='store_true', help='skip the training leg')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     args.pool = max(args.pool, args.batch)
+    args.train_steps = args.train_steps or max(1, min(args.steps, 10))
     if args.impl == 'reference':
         run_reference(args)
         return
@@ -279,6 +406,13 @@ def main():
            'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
            'note': 'grids stay in HBM for the training consumer (device tensors, SURVEY.md 8(b)); '
                    'infos are read back every step'}
+    # ---- training leg (configs[3]); frees the encode buffers first
+    training = None
+    if not args.no_train:
+        del arena, ws, batches, h_events, h_songs
+        torch.cuda.empty_cache()
+        training = run_training(args, world, rank, torch, dist)
+        t_load1 = time.time()
     clocks = sampler.stop(t_load0, t_load1) if sampler else None
 
     # ---- CPU baseline (rank 0, N=1): the oracle port, one thread, bounded sample
@@ -294,6 +428,8 @@ def main():
         cpu_baseline = {'value': float(infos['n_bars_out'][infos['status'] == 0].sum()) / dt, 'unit': UNIT,
                         'cores': 1, 'kind': 'port',
                         'sample': f'first {sample} songs of batch 0 (same generator, same filter), one pass'}
+        if training is not None:
+            training['cpu_baseline'] = cpu_training_baseline(min(os.cpu_count() or 1, 32), steps=2)
 
     if rank == 0:
         print(json.dumps({
@@ -303,7 +439,9 @@ def main():
             'config': workload_config(args),
             'channel_bars_per_s': float(total_chan_bars.item()) / elapsed_s,
             'roofline': roofline, 'e2e': e2e, 'cpu_baseline': cpu_baseline, 'clocks': clocks,
-            'gpu_launches': KERNELS_PER_STEP * args.steps,
+            'gpu_launches': KERNELS_PER_STEP * args.steps +
+            (training['gpu_launches_per_step'] * args.train_steps if training else 0),
+            'training': training,
         }))
     if world > 1:
         dist.destroy_process_group()

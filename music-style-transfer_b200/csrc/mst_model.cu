@@ -264,7 +264,9 @@ struct Launcher {
     }
     // dW[N,K] += dY[M,N]^T·X[M,K]   (atomic accumulate, K-dimension of the GEMM = M rows, split over CTAs)
     void linear_dw(const float *dY, long long ldy, const float *X, long long ldx, float *dW, long long ldw, int M, int N, int K) {
-        const int split = (int)std::max(1, std::min(64, M / 2048));
+        // few output tiles, long reduction: split the rows over enough CTAs to fill the 148 SMs twice
+        const int tiles = ((N + kGemmTile - 1) / kGemmTile) * ((K + kGemmTile - 1) / kGemmTile);
+        const int split = std::max(1, std::min(std::min(512, M / 128), (2 * 148 + tiles - 1) / tiles));
         gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
     }
     void colsum(const float *in, float *out, long long rows, int cols) {

@@ -344,7 +344,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         // gT[k][o] = sum_m im2col(P)[m][k] * d_conv[m][o]   (AMODE 2 gathers the transposed operand), split over m
         {
             const int Mrows = (int)(Rb * 8);
-            const int split = (int)std::max(1, std::min(148, Mrows / 1024));
+            const int split = (int)std::max(1, std::min(64, Mrows / 256));   // 11 output tiles x 64 splits
             L.gemm(c.P, 0, 0, d_conv, 57, 1, gT, 57, 700, 57, Mrows, nullptr, 0, 2, split, 2);
             if (!L.dry) { k_conv_wgrad_unpack<<<grid_for(57 * 700), 256, 0, L.st>>>(gT, GRD(c, pce_conv_w)); L.check(); }
         }
