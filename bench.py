@@ -100,6 +100,79 @@ class ClockSampler:
                 'reasons': sorted(reasons), 'samples': len(sm)}
 
 
+def run_decode(args, world, rank, torch, dist, L, lib, abi, batch, filt, arena):
+    """Decode leg (the inverse path of style_transfer.py: hard_output gate + compaction + ordering) over the grids the
+    encoder just wrote: one step = mst_decode_batch_device over one batch of songs, grids resident in HBM."""
+    batch.encode(filt, arena)
+    infos = batch.infos()
+    dsongs = []
+    for info in infos:
+        C = min(int(info['n_pitched']), 15)
+        dsongs.append(abi.make_decode_song(info, C, int(info['n_unpitched']) > 0, int(info['n_bars_out']),
+                                           instrument_ids=list(info['pitched_instruments'][:C]), duration=int(info['duration']),
+                                           write_back=False, pitched_offset=int(info['pitched_offset']),
+                                           unpitched_offset=int(info['unpitched_offset'])))
+    dsongs = np.array(dsongs, dtype=abi.DECODE_SONG_DTYPE)
+    S, n_chunks = len(dsongs), lib.decode_chunks(dsongs)
+    grid_bytes = float(sum(4 * int(d['n_bars']) * int(d['n_beats']) * (int(d['n_pitched']) * abi.PITCHED_BEAT_FLOATS +
+                                                                      int(d['has_unpitched']) * abi.UNPITCHED_BEAT_FLOATS)
+                           for d in dsongs))
+    res, msgs = lib.decode_batch(arena, dsongs)           # sizing pass (+ correctness: every song decodes)
+    assert (res['status'] == 0).all(), 'decode leg: non-OK song'
+    n_msgs = int(res['n_messages'].astype(np.int64).sum())
+    cap = n_msgs + 1024
+    d_songs = torch.from_numpy(dsongs.view(np.uint8).reshape(-1)).cuda()
+    d_res = torch.empty(S * abi.DECODE_RESULT_DTYPE.itemsize, dtype=torch.uint8, device='cuda')
+    d_msgs = torch.empty(cap * abi.OUT_MSG_DTYPE.itemsize, dtype=torch.uint8, device='cuda')
+    wsb = L.mst_decode_workspace_bytes(S, n_chunks, cap)
+    ws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
+    stream = torch.cuda.current_stream().cuda_stream
+    h_res = torch.empty(S * abi.DECODE_RESULT_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    h_msgs = torch.empty(cap * abi.OUT_MSG_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+
+    def step():
+        lib.check(L.mst_decode_batch_device(arena.data_ptr(), d_songs.data_ptr(), S, n_chunks, d_msgs.data_ptr(), cap,
+                                            d_res.data_ptr(), ws.data_ptr(), wsb, stream))
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device='cuda')
+    tot = torch.tensor([grid_bytes, float(n_msgs)], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    s_per_step = float(ms.item()) / 1e3 / args.steps
+    # e2e: results + messages read back to pinned host memory every step (the grids come from the model on device)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+        h_res.copy_(d_res, non_blocking=True)
+        h_msgs.copy_(d_msgs, non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    peak, peak_src = measured_peak_hbm()
+    alg = grid_bytes + 12.0 * n_msgs
+    return {
+        'metric': 'grid cells/sec decoded', 'value': float(tot[0].item()) / 20 / s_per_step, 'unit': 'cells/s',
+        'messages_per_s': float(tot[1].item()) / s_per_step, 'ms_per_step': s_per_step * 1e3, 'songs_per_step': S,
+        'messages_per_step': n_msgs, 'gpu_launches_per_step': 6,
+        'roofline': {'kernel': 'decode pipeline (k_dec_scan dominant: reads the grid once)', 'bound': 'hbm',
+                     'achieved': alg / s_per_step / 1e9, 'peak': peak, 'unit': 'GB/s', 'frac': alg / s_per_step / 1e9 / peak,
+                     'traffic': None, 'peak_source': peak_src, 'algorithmic_bytes_per_step': alg},
+        'e2e': {'value': float(tot[0].item()) / 20 / e2e_s, 'unit': 'cells/s', 'h2d_bytes_per_step': 0,
+                'd2h_bytes_per_step': int(h_res.numel() + n_msgs * abi.OUT_MSG_DTYPE.itemsize)},
+    }
+
+
 TRAIN_SHAPE = dict(C=4, B=200, nb=4, drums=True)     # SURVEY.md 8(d) config 4: the 800 channel-bar crop of train-model.py:101
 
 
@@ -288,6 +361,7 @@ def main():
         raise SystemExit('bench.py needs a CUDA device: the B200 path has no CPU fallback')
     torch.cuda.set_device(local_rank)
     if world > 1:
+        os.environ['NCCL_DEBUG'] = os.environ.get('MST_NCCL_DEBUG', 'WARN')   # keep NCCL's banner off stdout: ONE JSON line
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     L = lib.require_gpu()
 
@@ -406,6 +480,8 @@ def main():
            'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
            'note': 'grids stay in HBM for the training consumer (device tensors, SURVEY.md 8(b)); '
                    'infos are read back every step'}
+    # ---- decode leg over the grids of batch 0 (round trip of the encoder's output)
+    decode = run_decode(args, world, rank, torch, dist, L, lib, abi, batches[0], filt, arena)
     # ---- training leg (configs[3]); frees the encode buffers first
     training = None
     if not args.no_train:
@@ -441,7 +517,7 @@ def main():
             'roofline': roofline, 'e2e': e2e, 'cpu_baseline': cpu_baseline, 'clocks': clocks,
             'gpu_launches': KERNELS_PER_STEP * args.steps +
             (training['gpu_launches_per_step'] * args.train_steps if training else 0),
-            'training': training,
+            'decode': decode, 'training': training,
         }))
     if world > 1:
         dist.destroy_process_group()
