@@ -376,7 +376,7 @@ struct Ctx {
     LstmBuf sim_l1, sim_l2;
     float *sim_h1, *sim_last1, *sim_h2, *sim_rf, *sim_si, *sim_ri, *sim_instr, *sim_sm, *sim_rm, *sim_mode, *sim_sb, *sim_rb, *sim_bpm_pre, *sim_bpm;
     // PSA / USA
-    float *psa_s66, *psa_r10, *psa_i12, *psa_zs, *psa_zr, *psa_zi, *psa_out;
+    float *psa_s66, *psa_r10, *psa_i12, *psa_zs, *psa_zr, *psa_zi, *psa_zci, *psa_out;
     float *usa_s650, *usa_r17, *usa_zs, *usa_zr, *usa_h, *usa_out;
     // backward scratch (carved by plan_backward)
     float *scratch[8]; long long scratch_floats[8];
@@ -425,7 +425,7 @@ size_t plan_forward(Ctx &c, Arena &ar) {
     c.sim_sm = ar.take(N * 2); c.sim_rm = ar.take(N * 2); c.sim_mode = ar.take(N * 2);
     c.sim_sb = ar.take(N * 2); c.sim_rb = ar.take(N * 2); c.sim_bpm_pre = ar.take(N); c.sim_bpm = ar.take(N);
     c.psa_s66 = ar.take(N * 66); c.psa_r10 = ar.take(Rbf * 10); c.psa_i12 = ar.take(NC * 12);
-    c.psa_zs = ar.take(N * 450); c.psa_zr = ar.take(Rbf * 450); c.psa_zi = ar.take(NC * 450); c.psa_out = ar.take(Rf * 56 * 5);
+    c.psa_zs = ar.take(N * 450); c.psa_zr = ar.take(Rbf * 450); c.psa_zi = ar.take(NC * 450); c.psa_zci = ar.take(NC * 450); c.psa_out = ar.take(Rf * 56 * 5);
     if (c.U) {
         c.usa_s650 = ar.take(N * 650); c.usa_r17 = ar.take(Rbf * 17); c.usa_zs = ar.take(N * 10 * 376); c.usa_zr = ar.take(Rbf * 376);
         c.usa_h = ar.take(Rbf * 376); c.usa_out = ar.take(Rbf * 47 * 2);
@@ -602,6 +602,16 @@ void forward_song_info(Launcher &L, Ctx &c) {   // SongInfoModel (model.py:513-5
     k_bpm_head<<<(N + 63) / 64, 64, 0, L.st>>>(c.sim_bpm_pre, c.sim_bpm, N); L.check();
 }
 
+// melody_linear / linear of the PitchedStyleApplier into the constant bank (device -> device, stream ordered)
+void load_psa_constants(Launcher &L, const Ctx &c) {
+    if (L.dry) return;
+    const struct { ParamId id; int off, n; } parts[4] = {{psa_ml_w, kPsaWm, 160}, {psa_ml_b, kPsaBm, 20}, {psa_lin_w, kPsaWl, 250}, {psa_lin_b, kPsaBl, 5}};
+    for (auto &p : parts) {
+        cudaError_t e = cudaMemcpyToSymbolAsync(c_psa, PRM(c, p.id), p.n * sizeof(float), p.off * sizeof(float), cudaMemcpyDeviceToDevice, L.st);
+        if (e != cudaSuccess && L.err == cudaSuccess) L.err = e;
+    }
+}
+
 void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
     const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
     const long long Rbf = c.Rbf;
@@ -614,10 +624,12 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
     L.linear(c.psa_r10, 10, pow_ + 66, 88, nullptr, c.psa_zr, 450, (int)Rbf, 450, 10, 0);
     L.linear(c.psa_i12, 12, pow_ + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
     {
-        PsaArgs a{};
-        a.w = PsaParams{PRM(c, psa_oct_b), PRM(c, psa_ml_w), PRM(c, psa_ml_b), PRM(c, psa_lin_w), PRM(c, psa_lin_b)};
-        a.Zr = c.psa_zr; a.Zi = c.psa_zi; a.Zs = c.psa_zs; a.melody = c.melody; a.out = c.psa_out; a.N = N; a.C = C; a.B = B; a.T = T;
-        k_psa_fwd<<<(int)std::min<long long>(Rbf, 148 * 8), 256, (size_t)C * 450 * sizeof(float), L.st>>>(a); L.check();
+        load_psa_constants(L, c);
+        k_psa_zci<<<grid_for((long long)NC * 450), 256, 0, L.st>>>(PRM(c, psa_oct_b), c.psa_zi, c.psa_zs, c.psa_zci, N, C); L.check();
+        PsaArgs2 a{c.psa_zr, c.psa_zci, c.melody, c.psa_out, N, C, B, T};
+        const size_t smem = sizeof(PsaWarpSmem) * kPsaWarps;
+        cudaFuncSetAttribute(k_psa_fwd2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_psa_fwd2<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148 * 2), kPsaWarps * 32, smem, L.st>>>(a); L.check();
     }
     if (unpitched) {
         // ---------------- UnpitchedStyleApplier (model.py:703-724)

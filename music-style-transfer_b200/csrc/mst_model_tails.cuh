@@ -205,6 +205,122 @@ k_psa_fwd(PsaArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// PitchedStyleApplier tail, v2: ONE WARP per (n, b, t, f) unit, no block-level synchronisation.
+//   * the small weights (melody_linear 20x8, linear 5x50 and their biases) sit in the constant bank, so every FFMA
+//     takes its weight as an immediate c[bank][offset] operand: no load instruction per multiply;
+//   * the melody branch (mf = leaky(bm + Wm.mel), its share of the final linear) is computed once per (unit, note)
+//     and shared by all channels: y = snote + Wl[:, :30].a;
+//   * lane = (channel-in-group c, octave o): the octave row of the outer add lives in 30 registers, the degree row
+//     is a broadcast shared-memory read, the loop runs over the 7 degrees; 4 channels x 8 octaves fill the warp;
+//   * the (C, 56, 5) output tile is staged in shared memory and written with 16-byte coalesced stores.
+// Zci[n,c][450] = od_bias + Zi[n,c] + Zs[n] is pre-summed by k_psa_zci (tiny).
+// ------------------------------------------------------------------------------------------------
+constexpr int kPsaWm = 0, kPsaBm = 160, kPsaWl = 180, kPsaBl = 430, kPsaConst = 440;
+__constant__ float c_psa[kPsaConst];
+
+__global__ void __launch_bounds__(256)
+k_psa_zci(const float *__restrict__ bias, const float *__restrict__ Zi, const float *__restrict__ Zs, float *__restrict__ Zci, int N, int C) {
+    const int total = N * C * 450;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int j = i % 450, n = i / (450 * C);
+        Zci[i] = bias[j] + Zi[i] + Zs[n * 450 + j];
+    }
+}
+
+constexpr int kPsaWarps = 8;
+struct PsaWarpSmem {
+    float od[4 * 450];       // post-activation octave/degree rows of the current channel group
+    float snote[56 * 5];     // bl + Wl[:, 30:].mf per note
+    float out[4 * 280];      // output staging
+};
+
+// phase 1 for one note: mf[20] and snote[5] from the melody vector
+__device__ __forceinline__ void psa_note(const float *mel8, float *mf, float *sn) {
+#pragma unroll
+    for (int j = 0; j < 20; j++) {
+        float v = c_psa[kPsaBm + j];
+#pragma unroll
+        for (int p = 0; p < 8; p++) v = fmaf(c_psa[kPsaWm + j * 8 + p], mel8[p], v);
+        mf[j] = leaky(v);
+    }
+#pragma unroll
+    for (int e = 0; e < 5; e++) {
+        float v = c_psa[kPsaBl + e];
+#pragma unroll
+        for (int j = 0; j < 20; j++) v = fmaf(c_psa[kPsaWl + e * 50 + 30 + j], mf[j], v);
+        sn[e] = v;
+    }
+}
+
+struct PsaArgs2 {
+    const float *Zr, *Zci;       // (N,B,T,10,450), (N,C,450)
+    const float *melody;         // (N,B,T,10,56,8)
+    float *out;                  // (N,C,B,T,10,56,5)
+    int N, C, B, T;
+};
+
+__global__ void __launch_bounds__(kPsaWarps * 32)
+k_psa_fwd2(PsaArgs2 a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    PsaWarpSmem &s = reinterpret_cast<PsaWarpSmem *>(smem_raw)[warp];
+    const long long per_n = (long long)a.B * a.T * 10;
+    const long long units = (long long)a.N * per_n;
+    const int c_l = lane >> 3, o = lane & 7;
+    for (long long u = (long long)blockIdx.x * kPsaWarps + warp; u < units; u += (long long)gridDim.x * kPsaWarps) {
+        const int n = (int)(u / per_n);
+        const long long btf = u - (long long)n * per_n;
+        __syncwarp();
+        // phase 1: per-note melody branch
+        for (int note = lane; note < 56; note += 32) {
+            const float4 *mp = reinterpret_cast<const float4 *>(a.melody + (u * 56 + note) * 8);
+            const float4 m0 = mp[0], m1 = mp[1];
+            const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            float mf[20], sn[5];
+            psa_note(mel8, mf, sn);
+#pragma unroll
+            for (int e = 0; e < 5; e++) s.snote[note * 5 + e] = sn[e];
+        }
+        const float *zr = a.Zr + u * 450;
+        for (int c0 = 0; c0 < a.C; c0 += 4) {
+            const int cg = min(4, a.C - c0);
+            __syncwarp();
+            for (int j = lane; j < 450; j += 32) {
+                const float z = zr[j];
+                for (int c = 0; c < cg; c++) s.od[c * 450 + j] = leaky(z + a.Zci[((long long)n * a.C + c0 + c) * 450 + j]);
+            }
+            __syncwarp();
+            if (c_l < cg) {
+                float oct[30];
+#pragma unroll
+                for (int q = 0; q < 30; q++) oct[q] = s.od[c_l * 450 + o * 30 + q];
+                const float *deg = s.od + c_l * 450 + 240;
+                for (int d = 0; d < 7; d++) {
+                    const int note = o * 7 + d;
+                    float y[5];
+#pragma unroll
+                    for (int e = 0; e < 5; e++) y[e] = s.snote[note * 5 + e];
+#pragma unroll
+                    for (int q = 0; q < 30; q++) {
+                        const float v = leaky(oct[q] + deg[d * 30 + q]);
+#pragma unroll
+                        for (int e = 0; e < 5; e++) y[e] = fmaf(c_psa[kPsaWl + e * 50 + q], v, y[e]);
+                    }
+#pragma unroll
+                    for (int e = 0; e < 5; e++) s.out[c_l * 280 + note * 5 + e] = sigmoidf(y[e]) * (e == 0 ? 6.f : 1.f);
+                }
+            }
+            __syncwarp();
+            for (int c = 0; c < cg; c++) {
+                float4 *dst = reinterpret_cast<float4 *>(a.out + ((((long long)n * a.C + c0 + c) * per_n) + btf) * 280);
+                const float4 *src = reinterpret_cast<const float4 *>(s.out + c * 280);
+                for (int i = lane; i < 70; i += 32) dst[i] = src[i];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // UnpitchedStyleApplier tail.  Row (n, b, t, f): h[376] = leaky(bias + Zr[n,b,t,f] + Zs[n,f]) viewed (47, 8);
 // y[note] = bl + Wl·h[note] (2) -> duration 6*sigmoid, velocity sigmoid.  H is kept for the backward pass.
 // ------------------------------------------------------------------------------------------------
