@@ -160,15 +160,15 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     {
         float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
         if (!L.dry) {
-            PsaBwdArgs a{};
-            a.f.w = PsaParams{PRM(c, psa_oct_b), PRM(c, psa_ml_w), PRM(c, psa_ml_b), PRM(c, psa_lin_w), PRM(c, psa_lin_b)};
-            a.f.Zr = c.psa_zr; a.f.Zi = c.psa_zi; a.f.Zs = c.psa_zs; a.f.melody = c.melody; a.f.out = nullptr;
-            a.f.N = N; a.f.C = C; a.f.B = B; a.f.T = T;
-            a.target = c.P; a.coef = lb.coef_p; a.dZr = dZr; a.dZi = dZi; a.dmelody = d_melody;
+            PsaBwdArgs2 a{};
+            a.Zr = c.psa_zr; a.Zci = c.psa_zci; a.melody = c.melody; a.target = c.P; a.coef = lb.coef_p;
+            a.dZr = dZr; a.dZi = dZi; a.dmelody = d_melody;
             a.gWm = GRD(c, psa_ml_w); a.gbm = GRD(c, psa_ml_b); a.gWl = GRD(c, psa_lin_w); a.gbl = GRD(c, psa_lin_b);
-            const size_t smem = psa_bwd_smem_bytes(C);
-            cudaFuncSetAttribute(k_psa_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            k_psa_bwd<<<(int)std::min<long long>(Rbf, 148 * 2), kPsaThreads, smem, L.st>>>(a); L.check();
+            a.N = N; a.C = C; a.B = B; a.T = T;
+            a.ctas_per_n = (int)std::max<long long>(1, std::min<long long>(148 / N, ((long long)B * T * 10 + kPsaBwdWarps - 1) / kPsaBwdWarps));
+            const size_t smem = psa_bwd2_smem_bytes(C);
+            cudaFuncSetAttribute(k_psa_bwd2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            k_psa_bwd2<<<N * a.ctas_per_n, kPsaBwdWarps * 32, smem, L.st>>>(a); L.check();
         }
         L.reduce_mid(dZi, dZs, N, C, 450, 0);
         L.colsum(dZs, GRD(c, psa_oct_b), N, 450);

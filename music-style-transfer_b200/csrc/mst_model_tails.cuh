@@ -123,89 +123,11 @@ k_me_fwd(MeArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// PitchedStyleApplier tail.  Row (n, c, b, t, f):  od[450] = leaky(bias + Zr[n,b,t,f] + Zi[n,c] + Zs[n])
+// PitchedStyleApplier tail (model.py:658-675).  Row (n, c, b, t, f): od[450] = leaky(bias + Zr[n,b,t,f] + Zi[n,c] + Zs[n])
 // (240 octave values = 8 x 30, then 210 degree values = 7 x 30), then per note:
-//   a[q] = leaky(oct[o][q] + deg[d][q]) (30), mf = leaky(bm + Wm·melody[n,b,t,f,note]) (20),
-//   y = bl + Wl·[a; mf] (5) -> duration 6*sigmoid, the rest sigmoid (model.py:565-579, 668-673).
-// ------------------------------------------------------------------------------------------------
-struct PsaParams { const float *od_bias, *Wm, *bm, *Wl, *bl; };   // (450), (20,8), (20), (5,50), (5)
-struct PsaArgs {
-    PsaParams w;
-    const float *Zr, *Zi, *Zs;   // (N,B,T,10,450), (N,C,450), (N,450)
-    const float *melody;         // (N,B,T,10,56,8)
-    float *out;                  // (N,C,B,T,10,56,5)
-    int N, C, B, T;
-};
-struct PsaSmemW { float Wm[160], bm[20], Wl[250], bl[5]; };
-
-__device__ __forceinline__ void psa_load_w(PsaSmemW &s, const PsaParams &w) {
-    for (int i = threadIdx.x; i < 160; i += blockDim.x) s.Wm[i] = w.Wm[i];
-    for (int i = threadIdx.x; i < 20; i += blockDim.x) s.bm[i] = w.bm[i];
-    for (int i = threadIdx.x; i < 250; i += blockDim.x) s.Wl[i] = w.Wl[i];
-    for (int i = threadIdx.x; i < 5; i += blockDim.x) s.bl[i] = w.bl[i];
-}
-
-// in50 = [a(30); mf(20)], y(5) = post-activation outputs
-__device__ __forceinline__ void psa_cell(const PsaSmemW &s, const float *od_row, const float *mel8, int note, float *in50, float *y) {
-    const int o = note / 7, d = note - o * 7;
-#pragma unroll
-    for (int q = 0; q < 30; q++) in50[q] = leaky(od_row[o * 30 + q] + od_row[240 + d * 30 + q]);
-#pragma unroll
-    for (int q = 0; q < 20; q++) {
-        float v = s.bm[q];
-#pragma unroll
-        for (int p = 0; p < 8; p++) v = fmaf(s.Wm[q * 8 + p], mel8[p], v);
-        in50[30 + q] = leaky(v);
-    }
-#pragma unroll
-    for (int e = 0; e < 5; e++) {
-        float v = s.bl[e];
-#pragma unroll
-        for (int q = 0; q < 50; q++) v = fmaf(s.Wl[e * 50 + q], in50[q], v);
-        y[e] = sigmoidf(v) * (e == 0 ? 6.f : 1.f);
-    }
-}
-
-// od rows of all channels of one (n, b, t, f) unit into shared memory
-__device__ __forceinline__ void psa_load_od(float *od_s, const PsaArgs &a, int n, long long btf) {
-    const float *zr = a.Zr + ((long long)n * a.B * a.T * 10 + btf) * 450;
-    const float *zs = a.Zs + (long long)n * 450;
-    for (int i = threadIdx.x; i < a.C * 450; i += blockDim.x) {
-        const int c = i / 450, j = i - c * 450;
-        od_s[i] = leaky(a.w.od_bias[j] + zr[j] + a.Zi[((long long)n * a.C + c) * 450 + j] + zs[j]);
-    }
-}
-
-// grid: persistent CTAs over (n, b, t, f) units; dynamic smem = C * 450 floats
-__global__ void __launch_bounds__(256)
-k_psa_fwd(PsaArgs a) {
-    extern __shared__ float od_s[];
-    __shared__ PsaSmemW sw;
-    psa_load_w(sw, a.w);
-    const long long per_n = (long long)a.B * a.T * 10;
-    const long long units = (long long)a.N * per_n;
-    for (long long u = blockIdx.x; u < units; u += gridDim.x) {
-        const int n = (int)(u / per_n);
-        const long long btf = u - (long long)n * per_n;
-        __syncthreads();
-        psa_load_od(od_s, a, n, btf);
-        __syncthreads();
-        for (int i = threadIdx.x; i < a.C * 56; i += blockDim.x) {
-            const int c = i / 56, note = i - c * 56;
-            float mel8[8], in50[50], y[5];
-            const float *m = a.melody + (u * 56 + note) * 8;
-#pragma unroll
-            for (int p = 0; p < 8; p++) mel8[p] = m[p];
-            psa_cell(sw, od_s + c * 450, mel8, note, in50, y);
-            float *o = a.out + (((((long long)n * a.C + c) * per_n) + btf) * 56 + note) * 5;
-#pragma unroll
-            for (int e = 0; e < 5; e++) o[e] = y[e];
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// PitchedStyleApplier tail, v2: ONE WARP per (n, b, t, f) unit, no block-level synchronisation.
+//   a[q] = leaky(oct[o][q] + deg[d][q]) (30), mf = leaky(bm + Wm.melody[n,b,t,f,note]) (20),
+//   y = bl + Wl.[a; mf] (5) -> duration 6*sigmoid, the rest sigmoid (model.py:565-579, 668-673).
+// ONE WARP per (n, b, t, f) unit, no block-level synchronisation.
 //   * the small weights (melody_linear 20x8, linear 5x50 and their biases) sit in the constant bank, so every FFMA
 //     takes its weight as an immediate c[bank][offset] operand: no load instruction per multiply;
 //   * the melody branch (mf = leaky(bm + Wm.mel), its share of the final linear) is computed once per (unit, note)
