@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <vector>
 
+#include "mst_model_sparse.cuh"
 #include "mst_model_tails_bwd.cuh"
 
 using namespace mstm;
@@ -354,7 +355,9 @@ struct Ctx {
     const float *prm;               // flat parameters
     float *grad;                    // flat gradients (may be null for inference)
     // permuted weights
-    float *wconv_p, *wpcelin_p, *wucelin_p;
+    float *wconv_p, *wpcelin_p, *wucelin_p, *wconv_t, *wprech_t;
+    // occupied cells of the pitched grid, CSR by beat row
+    uint32_t *cells_cnt, *cells_off; CellRec *cells_rec;
     // PCE
     float *pce_conv, *pce_il, *pce_zi, *pce_zc, *pce_x, *pce_beats, *pce_last, *pce_ss, *pce_bars_in, *pce_bars;
     LstmBuf pce_bl, pce_brf, pce_brr;
@@ -390,6 +393,9 @@ size_t plan_forward(Ctx &c, Arena &ar) {
     c.Rb = N * C * B * T; c.Rf = c.Rb * 10; c.Rbf = N * B * T * 10; c.Nb = N * B;
     const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb, NC = N * C;
     c.wconv_p = ar.take(57 * 700); c.wpcelin_p = ar.take(64 * 514); c.wucelin_p = ar.take(64 * 940);
+    c.wconv_t = ar.take(700 * 57); c.wprech_t = ar.take(280 * 16);
+    c.cells_cnt = (uint32_t *)ar.take(Rb); c.cells_off = (uint32_t *)ar.take(Rb + 1);
+    c.cells_rec = (CellRec *)ar.take(Rb * 560 * (long long)(sizeof(CellRec) / sizeof(float)));   // worst case: every cell occupied
     c.pce_conv = ar.take(Rb * 456); c.pce_il = ar.take(NC * 58); c.pce_zi = ar.take(NC * 64); c.pce_zc = ar.take(Rb * 64);
     c.pce_x = ar.take(Rb * 64); c.pce_beats = ar.take(Rb * 64); c.pce_last = ar.take(NC * B * 64); c.pce_ss = ar.take(NC);
     c.pce_bars_in = ar.take(Nb * 64); c.pce_bars = ar.take(Nb * 128);
@@ -442,6 +448,8 @@ void prep_lstm(Launcher &L, const Ctx &c, LstmBuf &lb, ParamId whh, ParamId bih,
 void prep_weights(Launcher &L, Ctx &c) {
     k_permute_cols<<<grid_for(57 * 700), 256, 0, L.st>>>(PRM(c, pce_conv_w), c.wconv_p, 57, 700, 0, 0, 0); L.check();
     k_permute_cols<<<grid_for(64 * 514), 256, 0, L.st>>>(PRM(c, pce_lin_w), c.wpcelin_p, 64, 514, 1, 0, 0); L.check();
+    k_transpose<<<grid_for(57 * 700), 256, 0, L.st>>>(c.wconv_p, c.wconv_t, 57, 700); L.check();
+    k_transpose<<<grid_for(16 * 280), 256, 0, L.st>>>(PRM(c, pre_ch_w), c.wprech_t, 16, 280); L.check();
     prep_lstm(L, c, c.pce_bl, pce_bl_whh, pce_bl_bih, pce_bl_bhh);
     prep_lstm(L, c, c.pce_brf, pce_br_whh, pce_br_bih, pce_br_bhh);
     prep_lstm(L, c, c.pce_brr, pce_br_whh_r, pce_br_bih_r, pce_br_bhh_r);
@@ -485,8 +493,15 @@ void forward_extract(Launcher &L, Ctx &c) {
     const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
     const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb;
     prep_weights(L, c);
-    // ---------------- PitchedChannelsEncoder (model.py:77-99)
-    L.gemm(c.P, 0, 0, c.wconv_p, 1, 700, c.pce_conv, 57, (int)(Rb * 8), 57, 700, PRM(c, pce_conv_b), 1, 0, 1, 1);   // beats_conv + leaky
+    // ---------------- occupied cells of the piano roll, CSR by beat row (mst_model_sparse.cuh)
+    {
+        const int g = (int)std::min<long long>((Rb + 7) / 8, 148 * 8);
+        k_cells_scan<0><<<g, 256, 0, L.st>>>(c.P, Rb, c.cells_cnt, nullptr, nullptr); L.check();
+        k_cells_offsets<<<1, 1024, 0, L.st>>>(c.cells_cnt, c.cells_off, Rb); L.check();
+        k_cells_scan<1><<<g, 256, 0, L.st>>>(c.P, Rb, nullptr, c.cells_off, c.cells_rec); L.check();
+        // ---------------- PitchedChannelsEncoder (model.py:77-99): beats_conv + leaky over the occupied cells
+        k_conv_sparse_fwd<<<g, 256, 0, L.st>>>(c.cells_off, c.cells_rec, c.wconv_t, PRM(c, pce_conv_b), c.pce_conv, Rb); L.check();
+    }
     L.linear(c.F, 51, PRM(c, pce_il_w), 51, PRM(c, pce_il_b), c.pce_il, 58, NC, 58, 51, 1);
     L.linear(c.pce_il, 58, c.wpcelin_p + 456, 514, nullptr, c.pce_zi, 64, NC, 64, 58, 0);
     L.linear(c.pce_conv, 456, c.wpcelin_p, 514, nullptr, c.pce_zc, 64, (int)Rb, 64, 456, 0);
@@ -501,7 +516,7 @@ void forward_extract(Launcher &L, Ctx &c) {
     const float *plw = PRM(c, pre_lin_w);
     L.linear(c.pce_beats, 64, PRM(c, pre_bl_w), 64, PRM(c, pre_bl_b), c.pre_a1, 48, (int)Rb, 48, 64, 1);
     L.linear(c.pce_bars, 128, PRM(c, pre_br_w), 128, PRM(c, pre_br_b), c.pre_a2, 40, (int)Nb, 40, 128, 1);
-    L.linear(c.P, 280, PRM(c, pre_ch_w), 280, PRM(c, pre_ch_b), c.pre_a3, 16, (int)Rf, 16, 280, 1);
+    k_chlin_sparse_fwd<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(c.cells_off, c.cells_rec, c.wprech_t, PRM(c, pre_ch_b), c.pre_a3, Rb); L.check();
     L.linear(c.F, 51, PRM(c, pre_il_w), 51, PRM(c, pre_il_b), c.pre_a4, 21, NC, 21, 51, 1);
     L.linear(c.mode, 2, PRM(c, pre_ml_w), 2, PRM(c, pre_ml_b), c.pre_a5, 5, N, 5, 2, 1);
     L.linear(c.bpm, 1, PRM(c, pre_bp_w), 1, PRM(c, pre_bp_b), c.pre_a6, 5, N, 5, 1, 1);

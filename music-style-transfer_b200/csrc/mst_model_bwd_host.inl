@@ -315,7 +315,17 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         w.reduce_to(dz3, Dims5{N, C, 1, 1, 1}, 32, M_N, dz4);
         w.branch_bwd(dz0, (int)Rb, 32, pre_lin_w, 0, 135, c.pre_a1, 48, c.pce_beats, 64, 64, pre_bl_w, pre_bl_b, d_pce_beats, 64, 1);
         w.branch_bwd(dz1, (int)Nb, 32, pre_lin_w, 48, 135, c.pre_a2, 40, c.pce_bars, 128, 128, pre_br_w, pre_br_b, d_pce_bars, 128, 1);
-        w.branch_bwd(d_x, (int)Rf, 32, pre_lin_w, 88, 135, c.pre_a3, 16, c.P, 280, 280, pre_ch_w, pre_ch_b, nullptr, 0, 0);
+        {   // channels branch: the weight gradient of channels_linear runs over the occupied cells only
+            float *d_a = w.A(Rf * 16);
+            L.linear_dw(d_x, 32, c.pre_a3, 16, GRD(c, pre_lin_w) + 88, 135, (int)Rf, 32, 16);
+            L.linear_dx(d_x, 32, PRM(c, pre_lin_w) + 88, 135, d_a, 16, (int)Rf, 32, 16, 0);
+            L.act_grad(d_a, c.pre_a3, d_a, Rf * 16);
+            L.colsum(d_a, GRD(c, pre_ch_b), Rf, 16);
+            if (!L.dry) {
+                k_chlin_sparse_wgrad<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(c.cells_off, c.cells_rec, d_a, GRD(c, pre_ch_w), Rb);
+                L.check();
+            }
+        }
         w.branch_bwd(dz3, NC, 32, pre_lin_w, 104, 135, c.pre_a4, 21, c.F, 51, 51, pre_il_w, pre_il_b, nullptr, 0, 0);
         w.branch_bwd(dz4, N, 32, pre_lin_w, 125, 135, c.pre_a5, 5, c.mode, 2, 2, pre_ml_w, pre_ml_b, nullptr, 0, 0);
         w.branch_bwd(dz4, N, 32, pre_lin_w, 130, 135, c.pre_a6, 5, c.bpm, 1, 1, pre_bp_w, pre_bp_b, nullptr, 0, 0);
@@ -341,12 +351,10 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         L.linear_dx(d_x, 64, c.wpcelin_p, 514, d_conv, 456, (int)Rb, 64, 456, 0);
         L.act_grad(d_conv, c.pce_conv, d_conv, Rb * 456);
         L.colsum(d_conv, GRD(c, pce_conv_b), Rb * 8, 57);
-        // gT[k][o] = sum_m im2col(P)[m][k] * d_conv[m][o]   (AMODE 2 gathers the transposed operand), split over m
-        {
-            const int Mrows = (int)(Rb * 8);
-            const int split = (int)std::max(1, std::min(64, Mrows / 256));   // 11 output tiles x 64 splits
-            L.gemm(c.P, 0, 0, d_conv, 57, 1, gT, 57, 700, 57, Mrows, nullptr, 0, 2, split, 2);
-            if (!L.dry) { k_conv_wgrad_unpack<<<grid_for(57 * 700), 256, 0, L.st>>>(gT, GRD(c, pce_conv_w)); L.check(); }
+        // gT[k][o] = sum over occupied cells of p[feat] * d_conv[row][oct][o]  (k = f * 70 + tap * 5 + feat)
+        if (!L.dry) {
+            k_conv_sparse_wgrad<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(c.cells_off, c.cells_rec, d_conv, gT, Rb); L.check();
+            k_conv_wgrad_unpack<<<grid_for(57 * 700), 256, 0, L.st>>>(gT, GRD(c, pce_conv_w)); L.check();
         }
     }
 }
