@@ -12,6 +12,7 @@
 
 #include "mst_model_sparse.cuh"
 #include "mst_model_tails_bwd.cuh"
+#include "mst_model_me.cuh"
 
 using namespace mstm;
 
@@ -489,6 +490,22 @@ void bcast_fwd(Launcher &L, Dims5 d, int cols, const float *bias, float *Y, int 
     L.bcast(a);
 }
 
+// channels_linear / linear of the MelodyEncoder into the constant bank (device -> device, stream ordered)
+void load_me_constants(Launcher &L, const Ctx &c) {
+    if (L.dry) return;
+    const struct { ParamId id; int off, n; } parts[4] = {{me_ch_w, kMeWc, 35}, {me_ch_b, kMeBc, 7}, {me_lin_w, kMeWl, 120}, {me_lin_b, kMeBl, 8}};
+    for (auto &p : parts) {
+        cudaError_t e = cudaMemcpyToSymbolAsync(c_me, PRM(c, p.id), p.n * sizeof(float), p.off * sizeof(float), cudaMemcpyDeviceToDevice, L.st);
+        if (e != cudaSuccess && L.err == cudaSuccess) L.err = e;
+    }
+}
+MeArgs2 me_args(const Ctx &c) {
+    MeArgs2 a{};
+    a.od = c.me_od; a.off = c.cells_off; a.recs = c.cells_rec; a.ss = c.me_ss; a.melody = c.melody;
+    a.N = c.N; a.C = c.C; a.B = c.B; a.T = c.T;
+    return a;
+}
+
 void forward_extract(Launcher &L, Ctx &c) {
     const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
     const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb;
@@ -590,12 +607,11 @@ void forward_extract(Launcher &L, Ctx &c) {
     bcast_fwd(L, Dims5{N, C, B, T, 1}, 120, PRM(c, me_oct_b), c.me_od, 1,
               {{c.me_z[0], M_N | M_C | M_B | M_T}, {c.me_z[1], M_N | M_B}, {c.me_z[2], M_N | M_C}});
     {
-        MeArgs a{};
-        a.w = MeParams{PRM(c, me_ch_w), PRM(c, me_ch_b), PRM(c, me_lin_w), PRM(c, me_lin_b)};
-        a.od = c.me_od; a.P = c.P; a.ss = c.me_ss; a.melody = c.melody; a.N = N; a.C = C; a.B = B; a.T = T;
+        load_me_constants(L, c);
+        MeArgs2 a = me_args(c);
         L.fill(c.me_ss, NC, 0.f);
-        k_me_sumsq<<<(int)std::min<long long>(Rb, 148 * 8), 256, 0, L.st>>>(a); L.check();
-        k_me_fwd<<<(int)std::min<long long>((long long)N * B * T, 148 * 8), 256, (size_t)C * 121 * sizeof(float), L.st>>>(a); L.check();
+        k_me_sumsq2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
+        k_me_fwd2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
     }
 }
 

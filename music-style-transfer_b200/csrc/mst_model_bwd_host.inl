@@ -217,16 +217,13 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     }
     // ---------------- MelodyEncoder (model.py:252-297)
     {
-        float *stats = w.Z((long long)N * (C + 1)), *dod = w.A(Rb * 120);
+        float *stats = w.Z((long long)N * (C + 1)), *dod = w.A(Rb * 120), *dsum = w.A((long long)N * B * T * 448);
         if (!L.dry) {
-            MeBwdArgs a{};
-            a.f.w = MeParams{PRM(c, me_ch_w), PRM(c, me_ch_b), PRM(c, me_lin_w), PRM(c, me_lin_b)};
-            a.f.od = c.me_od; a.f.P = c.P; a.f.ss = c.me_ss; a.f.melody = c.melody; a.f.N = N; a.f.C = C; a.f.B = B; a.f.T = T;
-            a.dmelody = d_melody; a.stats = stats; a.dod = dod;
+            MeArgs2 a = me_args(c);
+            a.dmelody = d_melody; a.dsum = dsum; a.stats = stats; a.dod = dod;
             a.gWc = GRD(c, me_ch_w); a.gbc = GRD(c, me_ch_b); a.gWl = GRD(c, me_lin_w); a.gbl = GRD(c, me_lin_b);
-            k_me_bwd_stats<<<(int)std::min<long long>((long long)N * B * T, 148 * 8), 256, (size_t)C * 120 * sizeof(float), L.st>>>(a); L.check();
-            cudaFuncSetAttribute(k_me_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MeBwdSmem));
-            k_me_bwd<<<(int)std::min<long long>(Rb, 148 * 3), 256, sizeof(MeBwdSmem), L.st>>>(a); L.check();
+            k_me_bwd_stats2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
+            k_me_bwd2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 4), 256, 0, L.st>>>(a); L.check();
         }
         const Dims5 d{N, C, B, T, 1};
         float *dz1 = w.Z(Nb * 120), *dz2 = w.Z((long long)NC * 120);

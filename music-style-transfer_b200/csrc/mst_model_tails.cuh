@@ -1,126 +1,10 @@
 // mst_model_tails.cuh — fused per-note kernels (forward): the (rows x 56 notes) tensors of the reference's
-// MelodyEncoder (model.py:284-297), PitchedStyleApplier (:658-675) and UnpitchedStyleApplier (:713-724)
+// PitchedStyleApplier (:658-675) and UnpitchedStyleApplier (:713-724) (the MelodyEncoder tail lives in mst_model_me.cuh)
 // are produced and consumed inside one kernel each; nothing of size note-rows x {15, 30, 50} reaches HBM.
 #pragma once
 #include "mst_model_kernels2.cuh"
 
 namespace mstm {
-
-// ------------------------------------------------------------------------------------------------
-// MelodyEncoder tail.  Per cell (n, c, b, t, f, note = o*7 + d):
-//   a[q]  = leaky(oct[n,c,b,t][o][q] + deg[n,c,b,t][d][q])          q < 8   (octave/degree vectors are per beat)
-//   bf[q] = leaky(bc[q] + Wc[q][:]·P[cell][:])                        q < 7   channels_linear (5 -> 7)
-//   x[e]  = leaky(bl[e] + Wl[e][:8]·a + Wl[e][8:]·bf)                 e < 8   linear (15 -> 8)
-// melody[n,b,t,f,note,:] = combine over c (weights from sum x^2 over the whole channel).
-// ------------------------------------------------------------------------------------------------
-struct MeParams {
-    const float *Wc, *bc, *Wl, *bl;   // (7,5), (7), (8,15), (8)
-};
-struct MeArgs {
-    MeParams w;
-    const float *od;      // (N, C, B, T, 120): 64 octave values then 56 degree values, post-leaky
-    const float *P;       // (N, C, B, T, 10, 56, 5)
-    float *ss;            // (N, C) sum of squares (zeroed before k_me_sumsq)
-    float *melody;        // (N, B, T, 10, 56, 8)
-    int N, C, B, T;
-};
-
-struct MeSmemW { float Wc[35], bc[7], Wl[120], bl[8]; };
-
-__device__ __forceinline__ void me_load_w(MeSmemW &s, const MeParams &w) {
-    for (int i = threadIdx.x; i < 35; i += blockDim.x) s.Wc[i] = w.Wc[i];
-    for (int i = threadIdx.x; i < 7; i += blockDim.x) s.bc[i] = w.bc[i];
-    for (int i = threadIdx.x; i < 120; i += blockDim.x) s.Wl[i] = w.Wl[i];
-    for (int i = threadIdx.x; i < 8; i += blockDim.x) s.bl[i] = w.bl[i];
-}
-
-// in15 = [a(8); bf(7)], x(8)
-__device__ __forceinline__ void me_cell(const MeSmemW &s, const float *od_row, const float *p5, int note, float *in15, float *x) {
-    const int o = note / 7, d = note - o * 7;
-#pragma unroll
-    for (int q = 0; q < 8; q++) in15[q] = leaky(od_row[o * 8 + q] + od_row[64 + d * 8 + q]);
-#pragma unroll
-    for (int q = 0; q < 7; q++) {
-        float v = s.bc[q];
-#pragma unroll
-        for (int p = 0; p < 5; p++) v = fmaf(s.Wc[q * 5 + p], p5[p], v);
-        in15[8 + q] = leaky(v);
-    }
-#pragma unroll
-    for (int e = 0; e < 8; e++) {
-        float v = s.bl[e];
-#pragma unroll
-        for (int q = 0; q < 15; q++) v = fmaf(s.Wl[e * 15 + q], in15[q], v);
-        x[e] = leaky(v);
-    }
-}
-
-// grid: one CTA per (n, c, b, t) beat row (560 cells)
-__global__ void __launch_bounds__(256)
-k_me_sumsq(MeArgs a) {
-    __shared__ MeSmemW sw;
-    __shared__ float od_s[120];
-    __shared__ float tmp[8];
-    me_load_w(sw, a.w);
-    const long long rows = (long long)a.N * a.C * a.B * a.T;
-    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-        __syncthreads();
-        for (int i = threadIdx.x; i < 120; i += blockDim.x) od_s[i] = a.od[row * 120 + i];
-        __syncthreads();
-        const float *Prow = a.P + row * 2800;
-        float s = 0.f;
-        for (int cell = threadIdx.x; cell < 560; cell += blockDim.x) {
-            float p5[5], in15[15], x[8];
-#pragma unroll
-            for (int p = 0; p < 5; p++) p5[p] = Prow[cell * 5 + p];
-            me_cell(sw, od_s, p5, cell % 56, in15, x);
-#pragma unroll
-            for (int e = 0; e < 8; e++) s = fmaf(x[e], x[e], s);
-        }
-        s = block_sum(s, tmp);
-        if (threadIdx.x == 0) atomicAdd(a.ss + row / ((long long)a.B * a.T), s);
-    }
-}
-
-// grid: one CTA per (n, b, t) (all channels): melody = sum_c x_c w_c / sum_c w_c
-__global__ void __launch_bounds__(256)
-k_me_fwd(MeArgs a) {
-    extern __shared__ float dyn[];        // [C][120] octave/degree rows, then [C] weights
-    __shared__ MeSmemW sw;
-    me_load_w(sw, a.w);
-    float *od_s = dyn, *w_s = dyn + a.C * 120;
-    const long long units = (long long)a.N * a.B * a.T;
-    for (long long u = blockIdx.x; u < units; u += gridDim.x) {
-        const int n = (int)(u / ((long long)a.B * a.T));
-        const long long bt = u - (long long)n * a.B * a.T;
-        __syncthreads();
-        for (int i = threadIdx.x; i < a.C * 120; i += blockDim.x) {
-            const int c = i / 120;
-            od_s[i] = a.od[(((long long)n * a.C + c) * a.B * a.T + bt) * 120 + (i - c * 120)];
-        }
-        if (threadIdx.x < a.C) w_s[threadIdx.x] = sqrtf(1.f + a.ss[n * a.C + threadIdx.x]);
-        __syncthreads();
-        float wsum = 0.f;
-        for (int c = 0; c < a.C; c++) wsum += w_s[c];
-        for (int cell = threadIdx.x; cell < 560; cell += blockDim.x) {
-            float acc[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) acc[e] = 0.f;
-            for (int c = 0; c < a.C; c++) {
-                const float *Pc = a.P + ((((long long)n * a.C + c) * a.B * a.T + bt) * 560 + cell) * 5;
-                float p5[5], in15[15], x[8];
-#pragma unroll
-                for (int p = 0; p < 5; p++) p5[p] = Pc[p];
-                me_cell(sw, od_s + c * 120, p5, cell % 56, in15, x);
-#pragma unroll
-                for (int e = 0; e < 8; e++) acc[e] = fmaf(x[e], w_s[c], acc[e]);
-            }
-            float *m = a.melody + (u * 560 + cell) * 8;
-#pragma unroll
-            for (int e = 0; e < 8; e++) m[e] = acc[e] / wsum;
-        }
-    }
-}
 
 // ------------------------------------------------------------------------------------------------
 // PitchedStyleApplier tail (model.py:658-675).  Row (n, c, b, t, f): od[450] = leaky(bias + Zr[n,b,t,f] + Zi[n,c] + Zs[n])

@@ -350,155 +350,4 @@ k_usa_bwd(UsaBwdArgs a) {
     else if (threadIdx.x < 18) atomicAdd(a.gbl + (threadIdx.x - 16), g_s[threadIdx.x]);
 }
 
-// ------------------------------------------------------------------------------------------------
-// MelodyEncoder tail backward.  melody = combine_c(x_c):  dx_c = dmel * w_c / S + (A_c - Bs) / (S w_c) * x_c with
-// A_c = sum dmel . x_c over the whole channel, Bs = sum dmel . melody over the sample (see k_combine_bwd).
-//   k_me_bwd_stats: A (N, C) and Bs (N) -> stats[n * (C + 1) + {c, C}]   (zeroed by the caller)
-//   k_me_bwd:       per beat row (n, c, b, t): d od_pre[row][120] and the channels_linear / linear gradients.
-// ------------------------------------------------------------------------------------------------
-struct MeBwdArgs {
-    MeArgs f;                   // melody read
-    const float *dmelody;       // (N,B,T,10,56,8)
-    float *stats;               // (N, C + 1)
-    float *dod;                 // (N,C,B,T,120) pre-activation gradient, written
-    float *gWc, *gbc, *gWl, *gbl;
-};
-
-// grid: persistent over (n, b, t) units
-__global__ void __launch_bounds__(256)
-k_me_bwd_stats(MeBwdArgs a) {
-    extern __shared__ float dyn[];        // [C][120] od rows, [C] partial A
-    __shared__ MeSmemW sw;
-    __shared__ float tmp[8];
-    const MeArgs &f = a.f;
-    me_load_w(sw, f.w);
-    float *od_s = dyn;
-    const long long units = (long long)f.N * f.B * f.T;
-    for (long long u = blockIdx.x; u < units; u += gridDim.x) {
-        const int n = (int)(u / ((long long)f.B * f.T));
-        const long long bt = u - (long long)n * f.B * f.T;
-        __syncthreads();
-        for (int i = threadIdx.x; i < f.C * 120; i += blockDim.x) {
-            const int c = i / 120;
-            od_s[i] = f.od[(((long long)n * f.C + c) * f.B * f.T + bt) * 120 + (i - c * 120)];
-        }
-        __syncthreads();
-        float bs = 0.f;
-        for (int c = -1; c < f.C; c++) {
-            float s = 0.f;
-            for (int cell = threadIdx.x; cell < 560; cell += blockDim.x) {
-                const float *dm = a.dmelody + (u * 560 + cell) * 8;
-                if (c < 0) {
-                    const float *m = f.melody + (u * 560 + cell) * 8;
-#pragma unroll
-                    for (int e = 0; e < 8; e++) s = fmaf(dm[e], m[e], s);
-                } else {
-                    const float *Pc = f.P + ((((long long)n * f.C + c) * f.B * f.T + bt) * 560 + cell) * 5;
-                    float p5[5], in15[15], x[8];
-#pragma unroll
-                    for (int p = 0; p < 5; p++) p5[p] = Pc[p];
-                    me_cell(sw, od_s + c * 120, p5, cell % 56, in15, x);
-#pragma unroll
-                    for (int e = 0; e < 8; e++) s = fmaf(dm[e], x[e], s);
-                }
-            }
-            s = block_sum(s, tmp);
-            if (threadIdx.x == 0) atomicAdd(a.stats + n * (f.C + 1) + (c < 0 ? f.C : c), s);
-        }
-        (void)bs;
-    }
-}
-
-struct MeBwdSmem {
-    MeSmemW w;
-    float od[120], dod[120];
-    float gW[176];              // [0,120) Wl, [120,128) bl, [128,163) Wc, [163,170) bc
-    float s_in[560 * 17];       // in15 ++ 1, padded to 17
-    float s_dx[560 * 8];
-};
-
-// grid: persistent over (n, c, b, t) beat rows
-__global__ void __launch_bounds__(256)
-k_me_bwd(MeBwdArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    MeBwdSmem &s = *reinterpret_cast<MeBwdSmem *>(smem_raw);
-    const MeArgs &f = a.f;
-    const int tid = threadIdx.x;
-    me_load_w(s.w, f.w);
-    for (int i = tid; i < 176; i += blockDim.x) s.gW[i] = 0.f;
-    float gbc[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // channels_linear bias gradient, reduced once at the end
-    const long long BT = (long long)f.B * f.T;
-    const long long rows = (long long)f.N * f.C * BT;
-    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-        const long long nc = row / BT, bt = row - nc * BT;
-        const int n = (int)(nc / f.C), c = (int)(nc - (long long)n * f.C);
-        __syncthreads();
-        for (int i = tid; i < 120; i += blockDim.x) { s.od[i] = f.od[row * 120 + i]; s.dod[i] = 0.f; }
-        // combine weights of this sample
-        float wsum = 0.f;
-        for (int k = 0; k < f.C; k++) wsum += sqrtf(1.f + f.ss[n * f.C + k]);
-        const float wc = sqrtf(1.f + f.ss[n * f.C + c]);
-        const float k1 = wc / wsum;
-        const float k2 = (a.stats[n * (f.C + 1) + c] - a.stats[n * (f.C + 1) + f.C]) / (wsum * wc);
-        __syncthreads();
-        const float *Prow = f.P + row * 2800;
-        const float *dmrow = a.dmelody + ((long long)n * BT + bt) * 560 * 8;
-        for (int cell = tid; cell < 560; cell += blockDim.x) {
-            const int note = cell % 56, o = note / 7, d = note - o * 7;
-            float p5[5], in15[15], x[8], dx[8];
-#pragma unroll
-            for (int p = 0; p < 5; p++) p5[p] = Prow[cell * 5 + p];
-            me_cell(s.w, s.od, p5, note, in15, x);
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-                dx[e] = (dmrow[cell * 8 + e] * k1 + k2 * x[e]) * leaky_grad_from_out(x[e]);
-                s.s_dx[cell * 8 + e] = dx[e];
-            }
-#pragma unroll
-            for (int q = 0; q < 15; q++) {
-                s.s_in[cell * 17 + q] = in15[q];
-                float din = 0.f;
-#pragma unroll
-                for (int e = 0; e < 8; e++) din = fmaf(s.w.Wl[e * 15 + q], dx[e], din);
-                din *= leaky_grad_from_out(in15[q]);
-                if (q < 8) {
-                    atomicAdd(&s.dod[o * 8 + q], din);
-                    atomicAdd(&s.dod[64 + d * 8 + q], din);
-                } else {
-                    // channels_linear (5 -> 7): the input is zero for almost every cell
-                    const int qq = q - 8;
-                    gbc[qq] += din;
-#pragma unroll
-                    for (int p = 0; p < 5; p++) if (p5[p] != 0.f) atomicAdd(&s.gW[128 + qq * 5 + p], din * p5[p]);
-                }
-            }
-            s.s_in[cell * 17 + 15] = 1.f;
-        }
-        __syncthreads();
-        // linear (8 x 15) + bias: thread = (e, q in 0..15, half); q == 15 is the bias column
-        {
-            const int half = tid >> 7, eq = tid & 127, e = eq >> 4, q = eq & 15;
-            float acc = 0.f;
-            for (int cell = half * 280; cell < (half + 1) * 280; cell++) acc = fmaf(s.s_dx[cell * 8 + e], s.s_in[cell * 17 + q], acc);
-            if (q < 15) atomicAdd(&s.gW[e * 15 + q], acc); else atomicAdd(&s.gW[120 + e], acc);
-        }
-        for (int i = tid; i < 120; i += blockDim.x) a.dod[row * 120 + i] = s.dod[i] * leaky_grad_from_out(s.od[i]);
-    }
-#pragma unroll
-    for (int q = 0; q < 7; q++) {
-        float v = gbc[q];
-        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((tid & 31) == 0) atomicAdd(&s.gW[163 + q], v);
-    }
-    __syncthreads();
-    for (int i = tid; i < 170; i += blockDim.x) {
-        const float v = s.gW[i];
-        if (v == 0.f) continue;
-        if (i < 120) atomicAdd(a.gWl + i, v);
-        else if (i < 128) atomicAdd(a.gbl + (i - 120), v);
-        else if (i < 163) atomicAdd(a.gWc + (i - 128), v);
-        else atomicAdd(a.gbc + (i - 163), v);
-    }
-}
-
 }  // namespace mstm
