@@ -292,22 +292,32 @@ struct Launcher {
     void put_last(const float *src, float *dst, long long S, int T, int H) { if (dry) return; k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }
 
     static size_t lstm_smem(int H, int G, bool w_smem) { return sizeof(float) * ((size_t)2 * G * H + (size_t)G * 4 * H + (w_smem ? (size_t)H * 4 * H : 0)); }
-    void lstm(LstmArgs a, bool backward) {
-        if (dry) return;
-        a.G = a.S >= 148 * 2 ? kLstmG : 1;
-        a.w_smem = ((size_t)a.H * 4 * a.H * sizeof(float) <= 96 * 1024) ? 1 : 0;
-        const size_t smem = lstm_smem(a.H, a.G, a.w_smem);
-        const int threads = std::max(32, (4 * a.H + 31) / 32 * 32);
-        const int blocks = (a.S + a.G - 1) / a.G;
+    // up to kLstmMaxJobs independent recurrences of equal H in one launch
+    void lstm_multi(LstmArgs *jobs, int n_jobs, bool backward) {
+        if (dry || n_jobs <= 0) return;
+        LstmJobs pack{};
+        int max_blocks = 0, G = kLstmG;
+        for (int i = 0; i < n_jobs; i++) if (jobs[i].S < 148 * 2) G = 1;
+        const int H = jobs[0].H;
+        const int w_smem = ((size_t)H * 4 * H * sizeof(float) <= 96 * 1024) ? 1 : 0;
+        for (int i = 0; i < n_jobs; i++) {
+            jobs[i].G = G; jobs[i].w_smem = w_smem;
+            pack.j[i] = jobs[i];
+            max_blocks = std::max(max_blocks, (jobs[i].S + G - 1) / G);
+        }
+        const size_t smem = lstm_smem(H, G, w_smem);
+        const int threads = std::max(32, (4 * H + 31) / 32 * 32);
+        dim3 grid(max_blocks, n_jobs);
         if (backward) {
             cudaFuncSetAttribute(k_lstm_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-            k_lstm_bwd<<<blocks, threads, smem, st>>>(a);
+            k_lstm_bwd<<<grid, threads, smem, st>>>(pack);
         } else {
             cudaFuncSetAttribute(k_lstm_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-            k_lstm_fwd<<<blocks, threads, smem, st>>>(a);
+            k_lstm_fwd<<<grid, threads, smem, st>>>(pack);
         }
         check();
     }
+    void lstm(LstmArgs a, bool backward) { lstm_multi(&a, 1, backward); }
     void combine_fwd(CombineArgs a) {
         if (dry) return;
         fill(a.ss, (long long)a.N * a.K, 0.f);
@@ -465,6 +475,15 @@ void prep_weights(Launcher &L, Ctx &c) {
     prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
 }
 
+// input projection of one LSTM direction for all time steps + the recurrence's arguments
+LstmArgs lstm_project(Launcher &L, const Ctx &c, LstmBuf &lb, const float *X, ParamId wih, float *out, long long out_ld, int out_off, int reverse) {
+    L.linear(X, lb.I, PRM(c, wih), lb.I, lb.bias_sum, lb.xproj, 4 * lb.H, lb.S * lb.T, 4 * lb.H, lb.I, 0);
+    LstmArgs a{};
+    a.xproj = lb.xproj; a.w = lb.wt; a.out = out; a.out_ld = out_ld; a.out_off = out_off;
+    a.gates = lb.gates; a.cells = lb.cells; a.hprev = lb.hprev; a.S = lb.S; a.T = lb.T; a.H = lb.H; a.reverse = reverse;
+    return a;
+}
+
 // run one LSTM direction: xproj = X·W_ih^T + (b_ih + b_hh), then the recurrence
 void lstm_forward(Launcher &L, const Ctx &c, LstmBuf &lb, const float *X, ParamId wih, float *out, long long out_ld, int out_off, int reverse) {
     L.linear(X, lb.I, PRM(c, wih), lb.I, lb.bias_sum, lb.xproj, 4 * lb.H, lb.S * lb.T, 4 * lb.H, lb.I, 0);
@@ -527,8 +546,24 @@ void forward_extract(Launcher &L, Ctx &c) {
     L.take_last(c.pce_beats, c.pce_last, (long long)NC * B, T, 64);
     { CombineArgs a{}; a.x = c.pce_last; a.n_stride = (long long)C * B * 64; a.k_stride = (long long)B * 64; a.N = N; a.K = C; a.M = (long long)B * 64;
       a.ss = c.pce_ss; a.out = c.pce_bars_in; L.combine_fwd(a); }
-    lstm_forward(L, c, c.pce_brf, c.pce_bars_in, pce_br_wih, c.pce_bars, 128, 0, 0);
-    lstm_forward(L, c, c.pce_brr, c.pce_bars_in, pce_br_wih_r, c.pce_bars, 128, 64, 1);
+    // the bar-axis BiLSTMs of both channel encoders are independent serial recurrences: one joint launch
+    {
+        LstmArgs jobs[4];
+        int nj = 0;
+        jobs[nj++] = lstm_project(L, c, c.pce_brf, c.pce_bars_in, pce_br_wih, c.pce_bars, 128, 0, 0);
+        jobs[nj++] = lstm_project(L, c, c.pce_brr, c.pce_bars_in, pce_br_wih_r, c.pce_bars, 128, 64, 1);
+        if (c.U) {
+            // ---------------- UnpitchedChannelsEncoder up to its bars input (model.py:128-138)
+            L.linear(c.Ug, 940, c.wucelin_p, 940, PRM(c, uce_lin_b), c.uce_lin, 64, (int)(Nb * T), 64, 940, 1);
+            lstm_forward(L, c, c.uce_bl, c.uce_lin, uce_bl_wih, c.uce_beats, 64, 0, 0);
+            L.take_last(c.uce_beats, c.uce_last, Nb, T, 64);
+            { CombineArgs a{}; a.x = c.uce_last; a.M = (long long)B * 64; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
+              a.ss = c.uce_ss; a.out = c.uce_bars_in; L.combine_fwd(a); }
+            jobs[nj++] = lstm_project(L, c, c.uce_brf, c.uce_bars_in, uce_br_wih, c.uce_bars, 128, 0, 0);
+            jobs[nj++] = lstm_project(L, c, c.uce_brr, c.uce_bars_in, uce_br_wih_r, c.uce_bars, 128, 64, 1);
+        }
+        L.lstm_multi(jobs, nj, false);
+    }
     // ---------------- PitchedRhythmEncoder (model.py:346-381)
     const float *plw = PRM(c, pre_lin_w);
     L.linear(c.pce_beats, 64, PRM(c, pre_bl_w), 64, PRM(c, pre_bl_b), c.pre_a1, 48, (int)Rb, 48, 64, 1);
@@ -550,14 +585,6 @@ void forward_extract(Launcher &L, Ctx &c) {
       a.ss = c.pre_ss; a.out = c.pre_out; L.combine_fwd(a); }
     c.bars = c.pce_bars; c.rhythm = c.pre_out;
     if (c.U) {
-        // ---------------- UnpitchedChannelsEncoder (model.py:128-141)
-        L.linear(c.Ug, 940, c.wucelin_p, 940, PRM(c, uce_lin_b), c.uce_lin, 64, (int)(Nb * T), 64, 940, 1);
-        lstm_forward(L, c, c.uce_bl, c.uce_lin, uce_bl_wih, c.uce_beats, 64, 0, 0);
-        L.take_last(c.uce_beats, c.uce_last, Nb, T, 64);
-        { CombineArgs a{}; a.x = c.uce_last; a.M = (long long)B * 64; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
-          a.ss = c.uce_ss; a.out = c.uce_bars_in; L.combine_fwd(a); }
-        lstm_forward(L, c, c.uce_brf, c.uce_bars_in, uce_br_wih, c.uce_bars, 128, 0, 0);
-        lstm_forward(L, c, c.uce_brr, c.uce_bars_in, uce_br_wih_r, c.uce_bars, 128, 64, 1);
         // ---------------- UnpitchedRhythmEncoder (model.py:418-443)
         const float *ulw = PRM(c, ure_lin_w);
         L.linear(c.uce_beats, 64, PRM(c, ure_bl_w), 64, PRM(c, ure_bl_b), c.ure_a1, 48, (int)(Nb * T), 48, 64, 1);

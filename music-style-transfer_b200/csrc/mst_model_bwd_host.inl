@@ -78,20 +78,27 @@ struct Bwd {
         L.linear_dx(dZ, Nout, PRM(c, W) + col_off, ldw, d_a, K, rows, Nout, K, 0);
         lin_bwd(d_a, a_s, rows, K, X, ldx, Kin, w2, 0, Kin, b2, dX, lddx, acc_dx);
     }
-    // one LSTM direction backward: dout -> dgates; gradients of W_ih, W_hh, both biases; dX (+)= dgates W_ih
-    void lstm_bwd(LstmBuf &lb, const float *dout, long long out_ld, int out_off, int reverse, const float *X,
-                  ParamId wih, ParamId whh, ParamId bih, ParamId bhh, float *dX, int acc_dx) {
+    // one LSTM direction backward: dout -> dgates (recurrence), then the gradients of W_ih, W_hh, both biases and
+    // dX (+)= dgates W_ih.  The two halves are separate so that independent recurrences can share one launch.
+    LstmArgs lstm_bwd_args(LstmBuf &lb, const float *dout, long long out_ld, int out_off, int reverse, ParamId whh) {
         LstmArgs a{};
         a.w = PRM(c, whh); a.dout = dout; a.out_ld = out_ld; a.out_off = out_off;
         a.gates = lb.gates; a.cells = lb.cells; a.hprev = lb.hprev; a.dgates = lb.dgates;
         a.S = lb.S; a.T = lb.T; a.H = lb.H; a.reverse = reverse;
-        L.lstm(a, true);
+        return a;
+    }
+    void lstm_bwd_grads(LstmBuf &lb, const float *X, ParamId wih, ParamId whh, ParamId bih, ParamId bhh, float *dX, int acc_dx) {
         const int rows = lb.S * lb.T, H4 = 4 * lb.H;
         L.linear_dw(lb.dgates, H4, X, lb.I, GRD(c, wih), lb.I, rows, H4, lb.I);
         L.linear_dw(lb.dgates, H4, lb.hprev, lb.H, GRD(c, whh), lb.H, rows, H4, lb.H);
         L.colsum(lb.dgates, GRD(c, bih), rows, H4);
         L.colsum(lb.dgates, GRD(c, bhh), rows, H4);
         if (dX) L.linear_dx(lb.dgates, H4, PRM(c, wih), lb.I, dX, lb.I, rows, H4, lb.I, acc_dx);
+    }
+    void lstm_bwd(LstmBuf &lb, const float *dout, long long out_ld, int out_off, int reverse, const float *X,
+                  ParamId wih, ParamId whh, ParamId bih, ParamId bhh, float *dX, int acc_dx) {
+        L.lstm(lstm_bwd_args(lb, dout, out_ld, out_off, reverse, whh), true);
+        lstm_bwd_grads(lb, X, wih, whh, bih, bhh, dX, acc_dx);
     }
     void combine_bwd(const float *x, long long n_stride, long long k_stride, int K, long long M, const float *ss,
                      const float *out, const float *dout, float *dx, int accumulate) {
@@ -166,9 +173,13 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             a.gWm = GRD(c, psa_ml_w); a.gbm = GRD(c, psa_ml_b); a.gWl = GRD(c, psa_lin_w); a.gbl = GRD(c, psa_lin_b);
             a.N = N; a.C = C; a.B = B; a.T = T;
             a.ctas_per_n = (int)std::max<long long>(1, std::min<long long>(148 / N, ((long long)B * T * 10 + kPsaBwdWarps - 1) / kPsaBwdWarps));
-            const size_t smem = psa_bwd2_smem_bytes(C);
+            // fewer warps per CTA when the dZi accumulators of a many-channel song would not fit beside the staging
+            int warps = kPsaBwdWarps;
+            while (warps > 1 && sizeof(PsaBwdWarpSmem) * warps + (size_t)C * 1800 > 227 * 1024) warps--;
+            const size_t smem = sizeof(PsaBwdWarpSmem) * warps + (size_t)C * 1800;
+            a.warps = warps;
             cudaFuncSetAttribute(k_psa_bwd2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            k_psa_bwd2<<<N * a.ctas_per_n, kPsaBwdWarps * 32, smem, L.st>>>(a); L.check();
+            k_psa_bwd2<<<N * a.ctas_per_n, warps * 32, smem, L.st>>>(a); L.check();
         }
         L.reduce_mid(dZi, dZs, N, C, 450, 0);
         L.colsum(dZs, GRD(c, psa_oct_b), N, 450);
@@ -283,19 +294,6 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             w.branch_bwd(d_x, (int)Rbf, 32, ure_lin_w, 88, 109, c.ure_a3, 16, c.Ug, 94, 94, ure_ch_w, ure_ch_b, nullptr, 0, 0);
             w.branch_bwd(dz3, N, 32, ure_lin_w, 104, 109, c.ure_a4, 5, c.bpm, 1, 1, ure_bp_w, ure_bp_b, nullptr, 0, 0);
         }
-        // ---------------- UnpitchedChannelsEncoder (model.py:128-141)
-        {
-            float *d_in = w.A(Nb * 64), *d_last = w.A(Nb * 64), *d_lin = w.A(Nb * T * 64), *gWp = w.Z(64 * 940);
-            w.lstm_bwd(c.uce_brf, d_uce_bars, 128, 0, 0, c.uce_bars_in, uce_br_wih, uce_br_whh, uce_br_bih, uce_br_bhh, d_in, 0);
-            w.lstm_bwd(c.uce_brr, d_uce_bars, 128, 64, 1, c.uce_bars_in, uce_br_wih_r, uce_br_whh_r, uce_br_bih_r, uce_br_bhh_r, d_in, 1);
-            w.combine_bwd(c.uce_last, (long long)B * 64, (long long)B * 64, 1, (long long)B * 64, c.uce_ss, c.uce_bars_in, d_in, d_last, 0);
-            L.put_last(d_last, d_uce_beats, Nb, T, 64);
-            w.lstm_bwd(c.uce_bl, d_uce_beats, 64, 0, 0, c.uce_lin, uce_bl_wih, uce_bl_whh, uce_bl_bih, uce_bl_bhh, d_lin, 0);
-            L.act_grad(d_lin, c.uce_lin, d_lin, Nb * T * 64);
-            L.colsum(d_lin, GRD(c, uce_lin_b), Nb * T, 64);
-            L.linear_dw(d_lin, 64, c.Ug, 940, gWp, 940, (int)(Nb * T), 64, 940);
-            if (!L.dry) { k_permute_cols<<<grid_for(64 * 940), 256, 0, L.st>>>(gWp, GRD(c, uce_lin_w), 64, 940, 2, 1, 1); L.check(); }
-        }
     }
     // ---------------- PitchedRhythmEncoder (model.py:346-381)
     {
@@ -327,11 +325,38 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         w.branch_bwd(dz4, N, 32, pre_lin_w, 125, 135, c.pre_a5, 5, c.mode, 2, 2, pre_ml_w, pre_ml_b, nullptr, 0, 0);
         w.branch_bwd(dz4, N, 32, pre_lin_w, 130, 135, c.pre_a6, 5, c.bpm, 1, 1, pre_bp_w, pre_bp_b, nullptr, 0, 0);
     }
+    // ---------------- bar-axis BiLSTMs of both channel encoders: their four recurrences are independent -> one launch
+    {
+        LstmArgs jobs[4];
+        int nj = 0;
+        jobs[nj++] = w.lstm_bwd_args(c.pce_brf, d_pce_bars, 128, 0, 0, pce_br_whh);
+        jobs[nj++] = w.lstm_bwd_args(c.pce_brr, d_pce_bars, 128, 64, 1, pce_br_whh_r);
+        if (U) {
+            jobs[nj++] = w.lstm_bwd_args(c.uce_brf, d_uce_bars, 128, 0, 0, uce_br_whh);
+            jobs[nj++] = w.lstm_bwd_args(c.uce_brr, d_uce_bars, 128, 64, 1, uce_br_whh_r);
+        }
+        L.lstm_multi(jobs, nj, true);
+    }
+    if (U) {
+        // ---------------- UnpitchedChannelsEncoder (model.py:128-141)
+        {
+            float *d_in = w.A(Nb * 64), *d_last = w.A(Nb * 64), *d_lin = w.A(Nb * T * 64), *gWp = w.Z(64 * 940);
+            w.lstm_bwd_grads(c.uce_brf, c.uce_bars_in, uce_br_wih, uce_br_whh, uce_br_bih, uce_br_bhh, d_in, 0);
+            w.lstm_bwd_grads(c.uce_brr, c.uce_bars_in, uce_br_wih_r, uce_br_whh_r, uce_br_bih_r, uce_br_bhh_r, d_in, 1);
+            w.combine_bwd(c.uce_last, (long long)B * 64, (long long)B * 64, 1, (long long)B * 64, c.uce_ss, c.uce_bars_in, d_in, d_last, 0);
+            L.put_last(d_last, d_uce_beats, Nb, T, 64);
+            w.lstm_bwd(c.uce_bl, d_uce_beats, 64, 0, 0, c.uce_lin, uce_bl_wih, uce_bl_whh, uce_bl_bih, uce_bl_bhh, d_lin, 0);
+            L.act_grad(d_lin, c.uce_lin, d_lin, Nb * T * 64);
+            L.colsum(d_lin, GRD(c, uce_lin_b), Nb * T, 64);
+            L.linear_dw(d_lin, 64, c.Ug, 940, gWp, 940, (int)(Nb * T), 64, 940);
+            if (!L.dry) { k_permute_cols<<<grid_for(64 * 940), 256, 0, L.st>>>(gWp, GRD(c, uce_lin_w), 64, 940, 2, 1, 1); L.check(); }
+        }
+    }
     // ---------------- PitchedChannelsEncoder (model.py:77-99)
     {
         float *d_in = w.A(Nb * 64), *d_last = w.A((long long)NC * B * 64), *d_x = w.A(Rb * 64);
-        w.lstm_bwd(c.pce_brf, d_pce_bars, 128, 0, 0, c.pce_bars_in, pce_br_wih, pce_br_whh, pce_br_bih, pce_br_bhh, d_in, 0);
-        w.lstm_bwd(c.pce_brr, d_pce_bars, 128, 64, 1, c.pce_bars_in, pce_br_wih_r, pce_br_whh_r, pce_br_bih_r, pce_br_bhh_r, d_in, 1);
+        w.lstm_bwd_grads(c.pce_brf, c.pce_bars_in, pce_br_wih, pce_br_whh, pce_br_bih, pce_br_bhh, d_in, 0);
+        w.lstm_bwd_grads(c.pce_brr, c.pce_bars_in, pce_br_wih_r, pce_br_whh_r, pce_br_bih_r, pce_br_bhh_r, d_in, 1);
         w.combine_bwd(c.pce_last, (long long)C * B * 64, (long long)B * 64, C, (long long)B * 64, c.pce_ss, c.pce_bars_in, d_in, d_last, 0);
         L.put_last(d_last, d_pce_beats, (long long)NC * B, T, 64);
         w.lstm_bwd(c.pce_bl, d_pce_beats, 64, 0, 0, c.pce_x, pce_bl_wih, pce_bl_whh, pce_bl_bih, pce_bl_bhh, d_x, 0);

@@ -28,7 +28,12 @@ struct LstmArgs {
     int w_smem;
 };
 
-__global__ void k_lstm_fwd(LstmArgs a) {
+constexpr int kLstmMaxJobs = 4;
+struct LstmJobs { LstmArgs j[kLstmMaxJobs]; };   // independent recurrences of equal H launched together (blockIdx.y = job)
+
+__global__ void k_lstm_fwd(LstmJobs jobs) {
+    const LstmArgs &a = jobs.j[blockIdx.y];
+    if (blockIdx.x * a.G >= a.S) return;
     extern __shared__ float sm[];
     const int H = a.H, H4 = 4 * a.H, G = a.G;
     float *h_s = sm;                 // [G][H]
@@ -42,12 +47,23 @@ __global__ void k_lstm_fwd(LstmArgs a) {
     if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
     __syncthreads();
     const float *w = a.w_smem ? w_s : a.w;
+    float xnext[kLstmG];      // input projection of the next step, fetched while this step computes
+    {
+        const int t0 = a.reverse ? a.T - 1 : 0;
+#pragma unroll
+        for (int g = 0; g < kLstmG; g++) xnext[g] = (j < H4 && g < ng) ? a.xproj[((long long)(s0 + g) * a.T + t0) * H4 + j] : 0.f;
+    }
     for (int step = 0; step < a.T; step++) {
         const int t = a.reverse ? a.T - 1 - step : step;
         if (j < H4) {
             float acc[kLstmG];
 #pragma unroll
-            for (int g = 0; g < kLstmG; g++) acc[g] = (g < ng) ? a.xproj[((long long)(s0 + g) * a.T + t) * H4 + j] : 0.f;
+            for (int g = 0; g < kLstmG; g++) acc[g] = xnext[g];
+            if (step + 1 < a.T) {
+                const int tn = a.reverse ? t - 1 : t + 1;
+#pragma unroll
+                for (int g = 0; g < kLstmG; g++) if (g < ng) xnext[g] = a.xproj[((long long)(s0 + g) * a.T + tn) * H4 + j];
+            }
             for (int k = 0; k < H; k++) {
                 const float wv = w[k * H4 + j];
 #pragma unroll
@@ -78,7 +94,9 @@ __global__ void k_lstm_fwd(LstmArgs a) {
     }
 }
 
-__global__ void k_lstm_bwd(LstmArgs a) {
+__global__ void k_lstm_bwd(LstmJobs jobs) {
+    const LstmArgs &a = jobs.j[blockIdx.y];
+    if (blockIdx.x * a.G >= a.S) return;
     extern __shared__ float sm[];
     const int H = a.H, H4 = 4 * a.H, G = a.G;
     float *dh_s = sm;                 // [G][H]  dL/dh carried from the later step

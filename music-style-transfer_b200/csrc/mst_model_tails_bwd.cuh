@@ -20,7 +20,7 @@ namespace mstm {
 //     place by its own pre-activation gradient, then reduced to dZr (per unit) and dZi (CTA-level shared accumulators,
 //     one global flush per CTA: a CTA never spans samples).
 // ------------------------------------------------------------------------------------------------
-constexpr int kPsaBwdWarps = 6;
+constexpr int kPsaBwdWarps = 8;      // 8 x 24.7 KB of per-warp staging + C x 1.8 KB of dZi accumulators (<= 227 KB up to C = 14)
 struct PsaBwdWarpSmem {
     float od[4 * 450];
     float snote[56 * 5];
@@ -32,7 +32,6 @@ struct PsaBwdWarpSmem {
     float dzr[452];          // 450 used; keeps the per-warp stride a multiple of 16 bytes
 };
 static_assert(sizeof(PsaBwdWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
-static inline size_t psa_bwd2_smem_bytes(int C) { return sizeof(PsaBwdWarpSmem) * kPsaBwdWarps + (size_t)C * 450 * sizeof(float); }
 
 __device__ __forceinline__ uint32_t to_tf32(float x) {
     uint32_t r;
@@ -63,7 +62,7 @@ struct PsaBwdArgs2 {
     float *dZr, *dZi;                 // (N,B,T,10,450) written; (N,C,450) atomically accumulated (zeroed by the caller)
     float *dmelody;                   // (N,B,T,10,56,8) written
     float *gWm, *gbm, *gWl, *gbl;     // parameter gradients (atomic accumulate)
-    int N, C, B, T, ctas_per_n;
+    int N, C, B, T, ctas_per_n, warps;
 };
 
 __global__ void __launch_bounds__(kPsaBwdWarps * 32)
@@ -71,7 +70,7 @@ k_psa_bwd2(PsaBwdArgs2 a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     PsaBwdWarpSmem &s = reinterpret_cast<PsaBwdWarpSmem *>(smem_raw)[warp];
-    float *dzi_s = reinterpret_cast<float *>(smem_raw + sizeof(PsaBwdWarpSmem) * kPsaBwdWarps);   // [C][450]
+    float *dzi_s = reinterpret_cast<float *>(smem_raw + sizeof(PsaBwdWarpSmem) * a.warps);   // [C][450]
     const int C = a.C;
     const int n = blockIdx.x / a.ctas_per_n, kcta = blockIdx.x - n * a.ctas_per_n;
     const long long per_n = (long long)a.B * a.T * 10;
@@ -95,7 +94,7 @@ k_psa_bwd2(PsaBwdArgs2 a) {
 #pragma unroll
     for (int j = 0; j < 20; j++) gbm[j] = 0.f;
 
-    for (long long btf = b_lo + warp; btf < b_hi; btf += kPsaBwdWarps) {
+    for (long long btf = b_lo + warp; btf < b_hi; btf += a.warps) {
         const long long u = (long long)n * per_n + btf;
         __syncwarp();
         // ---- phase 1: per-note melody branch (mf kept for the backward), zero the per-unit accumulators
