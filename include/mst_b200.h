@@ -328,6 +328,22 @@ int mst_model_train_step(const float *d_params, float *d_grads, const MstModelSh
                          float *d_losses, MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes,
                          void *stream, int *n_launches);
 
+/* predict_song_info + apply_style (style/model.py:775-782, as style_transfer.py:101-131 uses them) from caller-provided
+ * style (N,256), melody (N,B,nb,10,56,8) and rhythm (N,B,nb,10,32): the style vector may come from another song, and
+ * n_channels / d_features / has_unpitched describe the instruments to render.  Fills outputs->instruments, mode, bpm,
+ * pitched and unpitched (style / melody / rhythm echo the inputs). */
+int mst_model_predict_apply(const float *d_params, const MstModelShape *shape, const float *d_style, const float *d_melody,
+                            const float *d_rhythm, const float *d_features, MstModelOutputs *outputs,
+                            void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches);
+
+/* get_total_loss + loss.backward() on the workspace a preceding mst_model_forward(..., training = 1) call filled for the
+ * SAME shape, inputs and parameters (the reference's call pattern: model(...), get_total_loss(...), loss.backward(),
+ * train-model.py:113-126).  Nothing else may have used the workspace or run another forward on the device in between. */
+int mst_model_backward(const float *d_params, float *d_grads, const MstModelShape *shape, const float *d_pitched,
+                       const float *d_unpitched, const float *d_features, const float *d_mode, const float *d_bpm,
+                       const float *d_instruments_target, const float *d_bpm_target, int normalize,
+                       float *d_losses, void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches);
+
 /* get_total_loss alone (style/model.py:935-997) on caller-provided predictions / targets, N samples segmented. */
 typedef struct MstLossIn {
     const float *pitched_pred, *pitched_target;         /* (N,C,B,nb,10,56,5) */

@@ -798,6 +798,56 @@ extern "C" int mst_model_train_step(const float *d_params, float *d_grads, const
     return MST_OK;
 }
 
+extern "C" int mst_model_predict_apply(const float *d_params, const MstModelShape *shape, const float *d_style, const float *d_melody,
+                                       const float *d_rhythm, const float *d_features, MstModelOutputs *outputs,
+                                       void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches) {
+    if (!d_params || !shape || !d_style || !d_melody || !d_rhythm || !d_features || !outputs || !d_workspace) {
+        mst_set_error("mst_model_predict_apply: null pointer argument");
+        return MST_E_INVALID;
+    }
+    Ctx c;
+    int rc = setup_ctx(c, shape, d_workspace, workspace_bytes, false, false);
+    if (rc) return rc;
+    c.F = d_features; c.prm = d_params;
+    c.style = (float *)d_style; c.melody = (float *)d_melody; c.rhythm = d_rhythm;   // read only on this path
+    Launcher L; L.st = (cudaStream_t)stream;
+    prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
+    prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
+    forward_song_info(L, c);
+    forward_apply(L, c, c.U != 0);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_predict_apply: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    fill_outputs(c, outputs);
+    if (n_launches) *n_launches = L.launches;
+    return MST_OK;
+}
+
+extern "C" int mst_model_backward(const float *d_params, float *d_grads, const MstModelShape *shape, const float *d_pitched,
+                                  const float *d_unpitched, const float *d_features, const float *d_mode, const float *d_bpm,
+                                  const float *d_instruments_target, const float *d_bpm_target, int normalize,
+                                  float *d_losses, void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches) {
+    if (!d_params || !d_grads || !shape || !d_pitched || !d_features || !d_mode || !d_bpm || !d_instruments_target ||
+        !d_bpm_target || !d_losses || !d_workspace || (shape->has_unpitched && !d_unpitched)) {
+        mst_set_error("mst_model_backward: null pointer argument");
+        return MST_E_INVALID;
+    }
+    init_param_offsets();
+    Ctx c;
+    memset(&c, 0, sizeof(c));
+    c.N = shape->n_samples; c.C = shape->n_channels; c.B = shape->n_bars; c.T = shape->n_beats; c.U = shape->has_unpitched ? 1 : 0;
+    if (c.N < 1 || c.C < 1 || c.B < 1 || c.T < 1 || c.C > 64) { mst_set_error("mst_model: bad shape"); return MST_E_INVALID; }
+    if (mst_model_workspace_bytes(shape, 1) > workspace_bytes) { mst_set_error("mst_model_backward: workspace too small"); return MST_E_CAPACITY; }
+    Arena ar{(char *)d_workspace, 0, false};
+    plan_forward(c, ar);
+    c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
+    c.bars = c.U ? c.bars_c : c.pce_bars; c.rhythm = c.U ? c.rh_c : c.pre_out;     // as forward_extract left them
+    Launcher L; L.st = (cudaStream_t)stream;
+    TrainIn ti{d_instruments_target, d_bpm_target, normalize, d_losses};
+    backward(L, c, ar, ti);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_backward: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    if (n_launches) *n_launches = L.launches;
+    return MST_OK;
+}
+
 extern "C" size_t mst_model_loss_workspace_bytes(const MstModelShape *shape) {
     return (size_t)(shape ? shape->n_samples : 1) * 1024 + 4096;
 }

@@ -27,7 +27,9 @@ class LossIn(ctypes.Structure):
 
 
 EXPORTS = ['mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
-           'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_loss_workspace_bytes',
+           'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply',
+           'mst_model_backward',
+           'mst_model_loss_workspace_bytes',
            'mst_model_loss', 'mst_adam_step']
 
 N_LOSS_LEAVES = 16
@@ -64,6 +66,13 @@ def _L():
         L.mst_model_train_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ModelShape)] + \
             [ctypes.c_void_p] * 7 + [ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ModelOutputs), ctypes.c_void_p,
                                      ctypes.c_size_t, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        L.mst_model_predict_apply.restype = ctypes.c_int
+        L.mst_model_predict_apply.argtypes = [ctypes.c_void_p, ctypes.POINTER(ModelShape)] + [ctypes.c_void_p] * 4 + [
+            ctypes.POINTER(ModelOutputs), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        L.mst_model_backward.restype = ctypes.c_int
+        L.mst_model_backward.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ModelShape)] + \
+            [ctypes.c_void_p] * 7 + [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
+                                     ctypes.POINTER(ctypes.c_int)]
         L.mst_model_loss_workspace_bytes.restype = ctypes.c_size_t
         L.mst_model_loss_workspace_bytes.argtypes = [ctypes.POINTER(ModelShape)]
         L.mst_model_loss.restype = ctypes.c_int
@@ -162,6 +171,26 @@ class Workspace:
             style=self._view(outs.style, (N, 256)), melody=self._view(outs.melody, (N, B, nb, 10, 56, 8)),
             rhythm=self._view(outs.rhythm, (N, B, nb, 10, 32)))
 
+    def predict_apply(self, flat_params, style, melody, rhythm, feats, stream=None):
+        """predict_song_info + apply_style from given style / melody / rhythm tensors (contiguous float32 CUDA)."""
+        import torch
+        s = self.shape
+        N, C, B, nb = s.n_samples, s.n_channels, s.n_bars, s.n_beats
+        assert tuple(style.shape) == (N, 256) and tuple(melody.shape) == (N, B, nb, 10, 56, 8)
+        assert tuple(rhythm.shape) == (N, B, nb, 10, 32) and tuple(feats.shape) == (N, C, 51)
+        outs = ModelOutputs()
+        nl = ctypes.c_int(0)
+        st = torch.cuda.current_stream(self.device) if stream is None else stream
+        _lib.check(_L().mst_model_predict_apply(
+            flat_params.data_ptr(), ctypes.byref(s), style.contiguous().data_ptr(), melody.contiguous().data_ptr(),
+            rhythm.contiguous().data_ptr(), feats.contiguous().data_ptr(), ctypes.byref(outs), self.buf.data_ptr(), self.bytes,
+            st.cuda_stream, ctypes.byref(nl)))
+        self.launches = nl.value
+        return dict(
+            instruments=self._view(outs.instruments, (N, 41)), mode=self._view(outs.mode, (N, 2)),
+            bpm=self._view(outs.bpm, (N,)), pitched=self._view(outs.pitched, (N, C, B, nb, 10, 56, 5)),
+            unpitched=self._view(outs.unpitched, (N, 1, B, nb, 10, 47, 2)) if s.has_unpitched else None)
+
     def train_step(self, flat_params, flat_grads, pitched, unpitched, feats, mode, bpm, instruments_target,
                    bpm_target, losses=None, normalize=True, stream=None):
         """forward + get_total_loss + backward for N independent samples; gradients are ADDED into flat_grads.
@@ -188,6 +217,25 @@ class Workspace:
             self.buf.data_ptr(), self.bytes, st.cuda_stream, ctypes.byref(nl)))
         self.launches = nl.value
         return losses, self._outs(outs)
+
+
+def backward_from_forward(ws, flat_params, flat_grads, pitched, unpitched, feats, mode, bpm, instruments_target, bpm_target,
+                          normalize=True, losses=None, stream=None):
+    """get_total_loss + backward on the workspace `ws` that Workspace.forward (training=True) just filled."""
+    import torch
+    assert ws.training
+    s = ws.shape
+    if losses is None:
+        losses = torch.empty(s.n_samples, N_LOSS_LEAVES, dtype=torch.float32, device=ws.device)
+    nl = ctypes.c_int(0)
+    st = torch.cuda.current_stream(ws.device) if stream is None else stream
+    _lib.check(_L().mst_model_backward(
+        flat_params.data_ptr(), flat_grads.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
+        unpitched.data_ptr() if s.has_unpitched else None, feats.data_ptr(), mode.data_ptr(), bpm.data_ptr(),
+        instruments_target.data_ptr(), bpm_target.data_ptr(), int(bool(normalize)), losses.data_ptr(), ws.buf.data_ptr(),
+        ws.bytes, st.cuda_stream, ctypes.byref(nl)))
+    ws.launches += nl.value
+    return losses
 
 
 def total_loss(pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits, instruments_target,

@@ -1,0 +1,241 @@
+"""GPU tests of the drop-in `style` package: the reference's own call patterns (train-model.py's loop,
+style_transfer.transfer_style) run unchanged on the B200 path and are compared with what the UNMODIFIED reference
+produced for the same files and the same seed-108 weights (tests/golden/dropin.npz, oracle/gen_golden_dropin.py).
+
+Tolerances: files written by save() from encoded grids are byte-identical; loss leaves before the first optimizer
+step 2e-5 relative (fp32 summation order); after Adam steps 5e-3 (Adam divides by sqrt(v): a 1e-6 gradient difference
+on a near-zero gradient moves a weight by up to lr); files decoded from PREDICTED grids are compared note by note and
+the mismatch count is reported (a sigmoid output within 1e-6 of a rounding boundary may flip a velocity / duration)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+from test_dropin_cpu import build_model
+
+pytestmark = pytest.mark.gpu
+
+G = np.load(os.path.join(gu.GOLDEN_DIR, 'dropin.npz'))
+OUT = os.path.join(gu.ROOT, 'gpurun_out')
+
+
+@pytest.fixture(scope='module')
+def torch():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail('GPU tests need a CUDA device (no CPU fallback exists)')
+    return torch
+
+
+def write_inputs(tmp, golden='codec_synth', songs=None):
+    songs = songs or {str(x).split('=')[0]: int(str(x).split('=')[1]) for x in G['input_songs']}
+    all_songs = gu.load_songs(golden)
+    paths = {}
+    for name, i in songs.items():
+        paths[name] = os.path.join(str(tmp), name + '.mid')
+        with open(paths[name], 'wb') as f:
+            f.write(bytes(all_songs[i]['decoded_smf']))
+    return paths
+
+
+def note_events(data):
+    """SMF bytes -> (meta/program events, sorted note tuples) through the native parser."""
+    from mst_native import lib
+    events, tpb = lib.smf_parse(bytes(data))
+    rows = [tuple(int(v) for v in e.tolist()) for e in events]
+    return tpb, rows
+
+
+def test_transfer_style_matches_reference_files(torch, tmp_path):
+    from style import style_transfer as st
+    paths = write_inputs(tmp_path)
+    out = tmp_path / 'out'
+    model = build_model()
+    st.transfer_style(model, paths['songA'], [paths['songB'], paths['songC']], str(out))
+    names = [str(n) for n in G['transfer/names']]
+    got_names = sorted(os.path.relpath(os.path.join(r, f), out) for r, _, fs in os.walk(out) for f in fs)
+    assert got_names == names
+    report = []
+    for i, n in enumerate(names):
+        want = bytes(G[f'transfer/file{i:02d}'])
+        got = open(out / n, 'rb').read()
+        if '/original/' in n:
+            assert got == want, n                            # encode -> decode -> SMF writer: byte-identical
+            report.append(f'{n}: identical ({len(got)} bytes)')
+            continue
+        tpb_w, ev_w = note_events(want)
+        tpb_g, ev_g = note_events(got)
+        assert tpb_g == tpb_w
+        sw, sg = set(ev_w), set(ev_g)
+        miss = len(sw - sg) + len(sg - sw)
+        frac = miss / max(1, len(sw))
+        report.append(f'{n}: identical={got == want} events={len(ev_w)} vs {len(ev_g)} differing={miss} ({frac:.2e})')
+        assert frac < 5e-3, report[-1]
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, 'dropin_transfer_report.txt'), 'w') as f:
+        f.write('\n'.join(report) + '\n')
+    # the intermediate tensors of the composition
+    inp = st.get_model_input(paths['songA'])
+    style, melody, rhythm = st.extract_style(model, inp)
+    np.testing.assert_allclose(style.cpu().numpy(), G['transfer/style'], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(melody.cpu().numpy().ravel()[:256], G['transfer/melody_head'], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(rhythm.cpu().numpy().ravel()[:256], G['transfer/rhythm_head'], rtol=1e-4, atol=1e-5)
+    ins, mode, bpm = model.predict_song_info(style, rhythm)
+    np.testing.assert_allclose(ins.cpu().numpy(), G['transfer/instruments_pred'], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(mode.cpu().numpy(), G['transfer/mode_pred'], rtol=1e-4, atol=1e-5)
+    assert abs(float(bpm) - float(G['transfer/bpm_pred'])) < 1e-3 * abs(float(G['transfer/bpm_pred']))
+
+
+def reference_loop(torch, model, files, n_iterations, min_n_messages):
+    """The body of train-model.py:92-160 (reference call pattern, drop-in imports)."""
+    import math
+    from style import data as d, model as m
+    optimizer = torch.optim.Adam(model.parameters(), lr=.01)
+    scheduler = torch.optim.lr_scheduler.StepLR(optimizer, step_size=200, gamma=.9)
+    inputs = d.iter_inputs(files, d.included_instruments, min_n_messages=min_n_messages, shuffle=False, looped=True)
+    rows = []
+    optimizer.zero_grad()
+    for iteration in range(n_iterations):
+        input = next(inputs)
+        filename, (info, pitched_channels, instruments_features, instruments, unpitched_channels) = input
+        max_n_bars = 800 // pitched_channels.shape[0]
+        mode, bpm, pitched_channels, instruments_features, unpitched_channels = d.prepare_input(input, max_n_bars)
+        if unpitched_channels is not None and unpitched_channels.sum() == 0:
+            unpitched_channels = None
+        used = d.get_used_instruments(instruments_features, unpitched_channels)
+        (ip, mp, bp), pp, up = model(mode, bpm, pitched_channels, instruments_features, unpitched_channels)
+        losses = m.get_total_loss(ip, used, bp, info['bpm'], mp, mode, pp, pitched_channels, up, unpitched_channels,
+                                  normalize=True)
+        loss = losses['total']
+        assert not math.isnan(loss)
+        loss.backward()
+        row = {}
+
+        def walk(prefix, x):
+            if isinstance(x, dict):
+                for k, v in x.items():
+                    walk(prefix + [k], v)
+            else:
+                row['/'.join(prefix)] = float('nan') if x is None else float(x)
+        walk([], losses)
+        rows.append(row)
+        if (iteration + 1) % 2 == 0:
+            optimizer.step()
+            optimizer.zero_grad()
+            scheduler.step()
+    return rows
+
+
+def test_training_loop_matches_reference(torch, tmp_path):
+    paths = write_inputs(tmp_path)
+    model = build_model()
+    names = [str(n) for n in G['train/loss_names']]
+    want = G['train/losses']
+    rows = reference_loop(torch, model, [paths['songA'], paths['songB'], paths['songC']], len(want), 0)
+    report = []
+    for it, row in enumerate(rows):
+        tol = 2e-5 if it < 2 else 5e-3
+        worst = 0.0
+        for j, k in enumerate(names):
+            w, g = want[it, j], row.get(k, float('nan'))
+            if np.isnan(w):
+                assert np.isnan(g), (it, k)
+                continue
+            err = abs(g - w) / max(abs(w), 1e-6)
+            worst = max(worst, err)
+            assert err < tol, (it, k, g, w)
+        report.append(f'iteration {it}: total {row["total"]:.7f} (reference {want[it, names.index("total")]:.7f}) '
+                      f'worst leaf rel err {worst:.2e}')
+    sd = model.state_dict()
+    pn = [str(n) for n in G['train/param_names']]
+    norms = np.array([float(sd[k].double().norm()) for k in pn])
+    rel = np.abs(norms - G['train/param_norms']) / np.maximum(G['train/param_norms'], 1e-6)
+    report.append(f'weights after {len(want)} iterations / {len(want) // 2} Adam steps: worst norm rel err {rel.max():.2e} '
+                  f'({pn[int(rel.argmax())]})')
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, 'dropin_training_report.txt'), 'w') as f:
+        f.write('\n'.join(report) + '\n')
+    assert rel.max() < 2e-2, report[-1]
+
+
+def test_backward_entry_equals_train_step_and_predict_apply_equals_forward(torch):
+    import model_oracle as mo
+    from mst_native import model as mm
+    sd = mo.make_state_dict(108)
+    flat = mm.flatten_state_dict(sd)
+    for drums in (True, False):
+        s = mo.synthetic_sample(5, C=3, B=6, nb=4, drums=drums)
+        pitched, feats = s['pitched'].cuda().contiguous(), s['feats'].cuda().contiguous()
+        unp = s['unpitched'].cuda().contiguous() if drums else None
+        mode, bpm = s['mode'].cuda(), s['bpm'].cuda().reshape(-1)
+        used = mo.used_instruments(s['feats'], s['unpitched'] if drums else None).cuda().contiguous()
+        ws = mm.Workspace(1, 3, 6, 4, drums, training=True)
+        g1 = torch.zeros_like(flat)
+        l1, _ = ws.train_step(flat, g1, pitched, unp, feats, mode, bpm, used, bpm)
+        l1 = l1.clone()
+        g2 = torch.zeros_like(flat)
+        out = ws.forward(flat, pitched, unp, feats, mode, bpm)
+        keep = {k: v.clone() for k, v in out.items() if v is not None}
+        l2 = mm.backward_from_forward(ws, flat, g2, pitched, unp, feats, mode, bpm, used, bpm)
+        assert torch.equal(l1, l2)
+        # same kernels, but the sparse weight-gradient kernels accumulate with atomics: order differs run to run
+        assert float((g1 - g2).norm() / g1.norm()) < 1e-6
+        wi = mm.Workspace(1, 3, 6, 4, drums, training=False)
+        ap = wi.predict_apply(flat, keep['style'], keep['melody'], keep['rhythm'], feats)
+        for k in ('instruments', 'mode', 'bpm', 'pitched') + (('unpitched',) if drums else ()):
+            assert torch.equal(ap[k], keep[k]), k
+
+
+def test_model_pickle_roundtrip_and_grad_views(torch, tmp_path):
+    import model_oracle as mo
+    model = build_model()
+    s = mo.synthetic_sample(9, C=2, B=5, nb=4, drums=True)
+    args = (s['mode'].cuda(), s['bpm'].cuda(), s['pitched'].cuda(), s['feats'].cuda(), s['unpitched'].cuda())
+    from style import model as m, data as d
+    (ip, mp, bp), pp, up = model(*args)
+    used = d.get_used_instruments(args[3], args[4])
+    losses = m.get_total_loss(ip, used, bp, 120, mp, args[0], pp, args[2], up, args[4], normalize=True)
+    losses['total'].backward()
+    flat_g = model._flat_grads.clone()
+    assert float(flat_g.abs().sum()) > 0
+    for name, p in model.named_parameters():
+        assert p.grad is not None and p.grad.shape == p.shape
+    # oracle gradients for the same call
+    sd = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in model.state_dict().items()}
+    ol, _ = mo.training_losses(sd, s['mode'], s['bpm'], s['pitched'], s['feats'], s['unpitched'], torch.tensor([120.]))
+    ol['total'].backward()
+    for name, p in model.named_parameters():
+        ref = sd[name].grad
+        err = float((p.grad.cpu() - ref).norm() / (ref.norm() + 1e-12))
+        assert err < 2e-4, (name, err)
+    path = tmp_path / 'model.pkl'
+    with open(path, 'wb') as f:
+        torch.save(model, f)
+    loaded = torch.load(path, weights_only=False)
+    for (n1, p1), (n2, p2) in zip(model.named_parameters(), loaded.named_parameters()):
+        assert n1 == n2 and torch.equal(p1, p2)
+    with torch.no_grad():
+        a = model.extract_style(*args)
+        b = loaded.extract_style(*args)
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+
+
+def test_train_model_script_runs_unchanged(torch, tmp_path):
+    """train-model.py (the reference's script, drop-in imports) on two bundled-song fixtures: 4 iterations."""
+    data = tmp_path / 'midis'
+    data.mkdir()
+    write_inputs(data, 'codec_bundled', {'minuetto': 22, 'nocturne': 23})
+    env = dict(os.environ, MST_DATA_PATH=str(data) + '/', MST_N_ITERATIONS='4', PYTHONPATH=os.path.join(gu.ROOT, 'music-style-transfer_b200'))
+    r = subprocess.run([sys.executable, os.path.join(gu.ROOT, 'music-style-transfer_b200', 'train-model.py')], cwd=tmp_path,
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = open(tmp_path / 'training.csv').read().strip().splitlines()
+    assert len(lines) == 5, lines                       # header + 4 iterations
+    assert 'total' in lines[0]
+    first, last = float(lines[1].split(',')[lines[0].split(',').index('total')]), \
+        float(lines[4].split(',')[lines[0].split(',').index('total')])
+    assert np.isfinite(first) and np.isfinite(last)
+    assert os.path.exists(tmp_path / 'snapshots' / '0.pkl')
