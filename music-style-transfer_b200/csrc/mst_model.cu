@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "mst_model_sparse.cuh"
+#include "mst_model_gemm_tc.cuh"
 #include "mst_model_tails_bwd.cuh"
 #include "mst_model_me.cuh"
 
@@ -244,15 +245,29 @@ struct Launcher {
     void check() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && err == cudaSuccess) err = e; launches++; }
 
     // C[M,N] (op)= act(A·B + bias) with explicit strides
+    // tensor-core path (mst_model_gemm_tc.cuh) for everything but the tiny problems
+    static bool use_tc(int M, int N, int K) { return M >= 24 && (long long)M * N * K >= (1ll << 21); }
+    template <int BN>
+    void gemm_tc(const GemmArgs &g, int split_k) {
+        dim3 grid((g.N + BN - 1) / BN, (g.M + kTcBM - 1) / kTcBM, split_k);
+        const bool ak = g.a_sk == 1, bk = g.b_sk == 1;
+        if (ak && bk) k_gemm_tc<BN, true, true><<<grid, kTcThreads, 0, st>>>(g);
+        else if (ak) k_gemm_tc<BN, true, false><<<grid, kTcThreads, 0, st>>>(g);
+        else if (bk) k_gemm_tc<BN, false, true><<<grid, kTcThreads, 0, st>>>(g);
+        else k_gemm_tc<BN, false, false><<<grid, kTcThreads, 0, st>>>(g);
+    }
+    // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
-              int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int amode = 0) {
+              int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int kernel = 0) {
         if (dry || M <= 0 || N <= 0 || K <= 0) return;
         GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
         if (split_k > 1) g.accumulate = 2;
-        dim3 grid((N + kGemmTile - 1) / kGemmTile, (M + kGemmTile - 1) / kGemmTile, split_k);
-        if (amode == 0) k_gemm<0><<<grid, kGemmThreads, 0, st>>>(g);
-        else if (amode == 1) k_gemm<1><<<grid, kGemmThreads, 0, st>>>(g);
-        else k_gemm<2><<<grid, kGemmThreads, 0, st>>>(g);
+        if (kernel == 2 || (kernel == 0 && use_tc(M, N, K))) {
+            if (N <= 32) gemm_tc<32>(g, split_k); else gemm_tc<64>(g, split_k);
+        } else {
+            dim3 grid((N + kGemmTile - 1) / kGemmTile, (M + kGemmTile - 1) / kGemmTile, split_k);
+            k_gemm<0><<<grid, kGemmThreads, 0, st>>>(g);
+        }
         check();
     }
     // Y[M,N] = act(X[M,K]·W[N,K]^T + bias)      (nn.Linear); W row stride ldw (column block of a wider weight)
@@ -267,7 +282,9 @@ struct Launcher {
     // dW[N,K] += dY[M,N]^T·X[M,K]   (atomic accumulate, K-dimension of the GEMM = M rows, split over CTAs)
     void linear_dw(const float *dY, long long ldy, const float *X, long long ldx, float *dW, long long ldw, int M, int N, int K) {
         // few output tiles, long reduction: split the rows over enough CTAs to fill the 148 SMs twice
-        const int tiles = ((N + kGemmTile - 1) / kGemmTile) * ((K + kGemmTile - 1) / kGemmTile);
+        const bool tc = use_tc(N, K, M);
+        const int tm = tc ? kTcBM : kGemmTile, tn = tc ? (K <= 32 ? 32 : 64) : kGemmTile;
+        const int tiles = ((N + tm - 1) / tm) * ((K + tn - 1) / tn);
         const int split = std::max(1, std::min(std::min(512, M / 128), (2 * 148 + tiles - 1) / tiles));
         gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
     }
@@ -291,7 +308,7 @@ struct Launcher {
     void take_last(const float *in, float *out, long long S, int T, int H) { if (dry) return; k_take_last<<<grid_for(S * H), 256, 0, st>>>(in, out, S, T, H); check(); }
     void put_last(const float *src, float *dst, long long S, int T, int H) { if (dry) return; k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }
 
-    static size_t lstm_smem(int H, int G, bool w_smem) { return sizeof(float) * ((size_t)2 * G * H + (size_t)G * 4 * H + (w_smem ? (size_t)H * 4 * H : 0)); }
+    static size_t lstm_smem(int H, int G, bool w_smem) { return sizeof(float) * ((size_t)2 * G * H + (size_t)G * 4 * H + (size_t)4 * G * H + (w_smem ? (size_t)H * 4 * H : 0)); }
     // up to kLstmMaxJobs independent recurrences of equal H in one launch
     void lstm_multi(LstmArgs *jobs, int n_jobs, bool backward) {
         if (dry || n_jobs <= 0) return;
@@ -877,5 +894,20 @@ extern "C" int mst_adam_step(float *d_params, float *d_grads, float *d_m, float 
     k_adam<<<grid_for(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(d_params, d_grads, d_m, d_v, n, beta1, beta2, eps,
                                                                      (float)((double)lr / bc1), (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad);
     MST_LAUNCH_CHECK("k_adam");
+    return MST_OK;
+}
+
+extern "C" int mst_model_gemm(const float *d_A, long long a_si, long long a_sk, const float *d_B, long long b_sk, long long b_sj,
+                              float *d_C, long long c_si, int M, int N, int K, const float *d_bias, int act, int accumulate,
+                              int split_k, int kernel, void *stream) {
+    if (!d_A || !d_B || !d_C || M <= 0 || N <= 0 || K <= 0 || split_k < 1 || kernel < 0 || kernel > 2) {
+        mst_set_error("mst_model_gemm: bad argument");
+        return MST_E_INVALID;
+    }
+    if (mst_device_count() <= 0) { mst_set_error("mst_model_gemm: no CUDA device"); return MST_E_NO_DEVICE; }
+    Launcher L;
+    L.st = (cudaStream_t)stream;
+    L.gemm(d_A, a_si, a_sk, d_B, b_sk, b_sj, d_C, c_si, M, N, K, d_bias, act, accumulate, split_k, kernel);
+    if (L.err != cudaSuccess) { mst_set_error(cudaGetErrorString(L.err)); return MST_E_CUDA; }
     return MST_OK;
 }

@@ -64,10 +64,31 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
 #pragma unroll
                 for (int g = 0; g < kLstmG; g++) if (g < ng) xnext[g] = a.xproj[((long long)(s0 + g) * a.T + tn) * H4 + j];
             }
-            for (int k = 0; k < H; k++) {
-                const float wv = w[k * H4 + j];
+            if (ng == 1) {
+                // one sequence per CTA (few long sequences): W_hh streams from L2 every step, so keep 16 loads in flight
+                float a0 = acc[0], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                const float *wp = w + j;
+                int k = 0;
+                for (; k + 16 <= H; k += 16) {
+                    float wv[16];
 #pragma unroll
-                for (int g = 0; g < kLstmG; g++) if (g < ng) acc[g] = fmaf(wv, h_s[g * H + k], acc[g]);
+                    for (int u = 0; u < 16; u++) wv[u] = wp[(k + u) * H4];
+#pragma unroll
+                    for (int u = 0; u < 16; u += 4) {
+                        a0 = fmaf(wv[u], h_s[k + u], a0);
+                        a1 = fmaf(wv[u + 1], h_s[k + u + 1], a1);
+                        a2 = fmaf(wv[u + 2], h_s[k + u + 2], a2);
+                        a3 = fmaf(wv[u + 3], h_s[k + u + 3], a3);
+                    }
+                }
+                for (; k < H; k++) a0 = fmaf(wp[k * H4], h_s[k], a0);
+                acc[0] = (a0 + a1) + (a2 + a3);
+            } else {
+                for (int k = 0; k < H; k++) {
+                    const float wv = w[k * H4 + j];
+#pragma unroll
+                    for (int g = 0; g < kLstmG; g++) if (g < ng) acc[g] = fmaf(wv, h_s[g * H + k], acc[g]);
+                }
             }
             const bool is_tanh = (j >= 2 * H) && (j < 3 * H);
 #pragma unroll
@@ -102,7 +123,8 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
     float *dh_s = sm;                 // [G][H]  dL/dh carried from the later step
     float *dc_s = dh_s + G * H;       // [G][H]
     float *dg_s = dc_s + G * H;       // [G][4H]
-    float *w_s = dg_s + G * H4;       // [4H][H] if w_smem
+    float *part_s = dg_s + G * H4;    // [4][G][H] partial dh sums
+    float *w_s = part_s + 4 * G * H;  // [4H][H] if w_smem
     const int j = threadIdx.x;
     const int s0 = blockIdx.x * G;
     const int ng = min(G, a.S - s0);
@@ -134,12 +156,48 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
             ds[k] = d_i; ds[H + k] = d_f; ds[2 * H + k] = d_g; ds[3 * H + k] = d_o;
         }
         __syncthreads();
-        for (int i = j; i < ng * H; i += blockDim.x) {            // dh_{step-1} = W_hh^T · dgates
-            const int g = i / H, k = i - g * H;
-            const float *ds = dg_s + g * H4;
-            float acc = 0.f;
-            for (int r = 0; r < H4; r++) acc = fmaf(w[r * H + k], ds[r], acc);
-            dh_s[i] = acc;
+        // dh_{step-1} = W_hh^T · dgates.  With few sequences per CTA the 4H rows are split over `parts` thread groups
+        // (partials through shared memory) and every thread keeps 16 loads in flight.
+        const int items = ng * H;
+        const int parts = min(4, (int)blockDim.x / items);
+        if (parts >= 2) {
+            const int part = j / items, i = j - part * items;
+            if (part < parts) {
+                const int g = i / H, k = i - g * H;
+                const float *ds = dg_s + g * H4;
+                const int r_lo = (int)((long long)H4 * part / parts), r_hi = (int)((long long)H4 * (part + 1) / parts);
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                const float *wp = w + k;
+                int r = r_lo;
+                for (; r + 16 <= r_hi; r += 16) {
+                    float wv[16];
+#pragma unroll
+                    for (int u = 0; u < 16; u++) wv[u] = wp[(r + u) * H];
+#pragma unroll
+                    for (int u = 0; u < 16; u += 4) {
+                        a0 = fmaf(wv[u], ds[r + u], a0);
+                        a1 = fmaf(wv[u + 1], ds[r + u + 1], a1);
+                        a2 = fmaf(wv[u + 2], ds[r + u + 2], a2);
+                        a3 = fmaf(wv[u + 3], ds[r + u + 3], a3);
+                    }
+                }
+                for (; r < r_hi; r++) a0 = fmaf(wp[r * H], ds[r], a0);
+                part_s[part * items + i] = (a0 + a1) + (a2 + a3);
+            }
+            __syncthreads();
+            if (j < items) {
+                float v = part_s[j];
+                for (int q = 1; q < parts; q++) v += part_s[q * items + j];
+                dh_s[j] = v;
+            }
+        } else {
+            for (int i = j; i < items; i += blockDim.x) {
+                const int g = i / H, k = i - g * H;
+                const float *ds = dg_s + g * H4;
+                float acc = 0.f;
+                for (int r = 0; r < H4; r++) acc = fmaf(w[r * H + k], ds[r], acc);
+                dh_s[i] = acc;
+            }
         }
         __syncthreads();
     }

@@ -30,7 +30,7 @@ EXPORTS = ['mst_model_param_count', 'mst_model_param_name', 'mst_model_param_num
            'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply',
            'mst_model_backward',
            'mst_model_loss_workspace_bytes',
-           'mst_model_loss', 'mst_adam_step']
+           'mst_model_loss', 'mst_adam_step', 'mst_model_gemm']
 
 N_LOSS_LEAVES = 16
 # index of every leaf of get_total_loss's nested dict in the (N, 16) loss buffer (include/mst_b200.h MST_LOSS_*)
@@ -81,6 +81,11 @@ def _L():
         L.mst_adam_step.restype = ctypes.c_int
         L.mst_adam_step.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_longlong, ctypes.c_int] + [ctypes.c_float] * 5 + [
             ctypes.c_int, ctypes.c_void_p]
+        L.mst_model_gemm.restype = ctypes.c_int
+        L.mst_model_gemm.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong,
+                                     ctypes.c_longlong, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_int,
+                                     ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                     ctypes.c_void_p]
         _ready = True
     return L
 
@@ -265,3 +270,14 @@ def adam_step(params, grads, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, g
     _lib.check(_L().mst_adam_step(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), params.numel(), int(step),
                                   float(lr), float(beta1), float(beta2), float(eps), float(grad_scale), int(bool(zero_grad)),
                                   st.cuda_stream))
+
+
+def gemm(A, a_si, a_sk, B, b_sk, b_sj, C, c_si, M, N, K, bias=None, act=0, accumulate=0, split_k=1, kernel=0, stream=None):
+    """mst_model_gemm on float32 CUDA tensors with explicit element strides (see include/mst_b200.h)."""
+    import torch
+    _lib.require_gpu()
+    st = torch.cuda.current_stream(C.device) if stream is None else stream
+    _lib.check(_L().mst_model_gemm(A.data_ptr(), a_si, a_sk, B.data_ptr(), b_sk, b_sj, C.data_ptr(), c_si, M, N, K,
+                                   None if bias is None else bias.data_ptr(), act, accumulate, split_k, kernel,
+                                   st.cuda_stream))
+    return C

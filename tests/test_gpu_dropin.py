@@ -220,7 +220,8 @@ def test_model_pickle_roundtrip_and_grad_views(torch, tmp_path):
     with torch.no_grad():
         a = model.extract_style(*args)
         b = loaded.extract_style(*args)
-    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    # the combine norms are summed with float atomics: run-to-run differences of an ulp or two are expected
+    assert all(torch.allclose(x, y, rtol=1e-5, atol=1e-6) for x, y in zip(a, b))
 
 
 def test_train_model_script_runs_unchanged(torch, tmp_path):
