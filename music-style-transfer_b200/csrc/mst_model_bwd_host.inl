@@ -167,10 +167,12 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     {
         float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
         if (!L.dry) {
-            PsaBwdArgs2 a{};
+            // the per-note channel sums of the pre-sigmoid gradient travel through the (not yet written) dmelody buffer
+            PsaBwdArgs3 a{};
             a.Zr = c.psa_zr; a.Zci = c.psa_zci; a.melody = c.melody; a.target = c.P; a.coef = lb.coef_p;
-            a.dZr = dZr; a.dZi = dZi; a.dmelody = d_melody;
-            a.gWm = GRD(c, psa_ml_w); a.gbm = GRD(c, psa_ml_b); a.gWl = GRD(c, psa_lin_w); a.gbl = GRD(c, psa_lin_b);
+            a.Wl = PRM(c, psa_lin_w);
+            a.dZr = dZr; a.dZi = dZi; a.dps = d_melody; a.dps_stride = 448;
+            a.gWl = GRD(c, psa_lin_w);
             a.N = N; a.C = C; a.B = B; a.T = T;
             a.ctas_per_n = (int)std::max<long long>(1, std::min<long long>(148 / N, ((long long)B * T * 10 + kPsaBwdWarps - 1) / kPsaBwdWarps));
             // fewer warps per CTA when the dZi accumulators of a many-channel song would not fit beside the staging
@@ -178,8 +180,15 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             while (warps > 1 && sizeof(PsaBwdWarpSmem) * warps + (size_t)C * 1800 > 227 * 1024) warps--;
             const size_t smem = sizeof(PsaBwdWarpSmem) * warps + (size_t)C * 1800;
             a.warps = warps;
-            cudaFuncSetAttribute(k_psa_bwd2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            k_psa_bwd2<<<N * a.ctas_per_n, warps * 32, smem, L.st>>>(a); L.check();
+            cudaFuncSetAttribute(k_psa_bwd3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            k_psa_bwd3<<<N * a.ctas_per_n, warps * 32, smem, L.st>>>(a); L.check();
+            PsaMelBwdArgs m{};
+            m.melody = c.melody; m.dps = d_melody; m.dps_stride = 448; m.dmelody = d_melody;
+            m.gWm = GRD(c, psa_ml_w); m.gbm = GRD(c, psa_ml_b); m.gWl = GRD(c, psa_lin_w); m.gbl = GRD(c, psa_lin_b);
+            m.units = Rbf;
+            const size_t msmem = sizeof(PsaMelWarpSmem) * kPsaMelWarps;
+            cudaFuncSetAttribute(k_psa_mel_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem);
+            k_psa_mel_bwd<<<(int)std::min<long long>((Rbf + kPsaMelWarps - 1) / kPsaMelWarps, 148), kPsaMelWarps * 32, msmem, L.st>>>(m); L.check();
         }
         L.reduce_mid(dZi, dZs, N, C, 450, 0);
         L.colsum(dZs, GRD(c, psa_oct_b), N, 450);

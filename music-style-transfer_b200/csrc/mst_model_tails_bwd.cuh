@@ -10,26 +10,31 @@
 namespace mstm {
 
 // ------------------------------------------------------------------------------------------------
-// PitchedStyleApplier tail backward (pairs with k_psa_fwd2): one warp per (n, b, t, f) unit, lane = (channel, octave),
-// loop over the 7 degrees.  Everything is recomputed from Zr / Zci / melody; the loss derivative is evaluated per cell.
-//   * per-lane registers: the octave row (30), its gradient (30), the tensor-core accumulators (24);
-//   * weight gradients are real contractions over cells and go to the tensor cores (mma.sync m16n8k8, 3xTF32 split so
-//     the result is fp32-accurate):  gWl[:, :30] += a^T.dpre per 32-cell step, gWl[:, 30:] (+ bias) += mf^T.dps and
-//     gWm += dmf^T.mel once per unit; operands are staged in shared memory in conflict-free layouts;
+// PitchedStyleApplier tail backward (pairs with k_psa_fwd2), two kernels.
+//
+// k_psa_bwd3 — one warp per (n, b, t, f) unit, lane = (channel, octave), loop over the 7 degrees; everything is
+// recomputed from Zr / Zci / melody.  The loss derivative (mst_model_loss.cuh: loss_cell_grad) reaches the duration and
+// accidental outputs only where the TARGET holds a note (velocity > 0: 0.1-0.6 % of the cells); everywhere else only
+// the velocity output carries gradient.  So:
+//   * dense part, every cell: velocity row of the final linear only (30 FFMA forward, 30 backward), its weight
+//     gradient gWl[1, :30] in 30 per-lane registers;
+//   * cells with a target note (found by ballot, handled one at a time by the WHOLE warp, lane = column q of the
+//     30-wide row): the other four outputs, their loss derivative, their share of the input gradient and
+//     gWl[{0,2,3,4}, q] in 4 per-lane registers.  Exact: nothing is dropped, only zeros are skipped;
 //   * the degree-row gradient (sum over the 8 octave lanes) is a shared-memory transposition; od is overwritten in
 //     place by its own pre-activation gradient, then reduced to dZr (per unit) and dZi (CTA-level shared accumulators,
-//     one global flush per CTA: a CTA never spans samples).
+//     one global flush per CTA: a CTA never spans samples);
+//   * dps[note][e] = sum over channels of the pre-sigmoid gradient goes to global for k_psa_mel_bwd.
+// k_psa_mel_bwd — the melody branch (melody_linear 8 -> 20, its 20 columns of the final linear): weight gradients on the
+// tensor cores (mma.sync m16n8k8, 3xTF32 split = fp32-accurate), dmelody written per note.
 // ------------------------------------------------------------------------------------------------
-constexpr int kPsaBwdWarps = 8;      // 8 x 24.7 KB of per-warp staging + C x 1.8 KB of dZi accumulators (<= 227 KB up to C = 14)
+constexpr int kPsaBwdWarps = 12;
 struct PsaBwdWarpSmem {
     float od[4 * 450];
     float snote[56 * 5];
-    float mf[56 * 24];       // mf (col 20 = 1 for the bias row), later the pre-activation gradient dmf
-    float mel[56 * 8];
-    float dps[56 * 8];       // sum over channels of dpre per note; cols 5..7 stay 0
-    float sa[32 * 36];       // [q][lane] staging (rows 30, 31 stay 0)
-    float sd[32 * 8];        // dpre per lane; cols 5..7 stay 0
-    float dzr[452];          // 450 used; keeps the per-warp stride a multiple of 16 bytes
+    float dps[56 * 5];
+    float sa[30 * 36];       // [q][lane] input-gradient staging of the current degree step
+    float exq[32];           // a target-note cell's extra input gradient, handed back to its owner lane
 };
 static_assert(sizeof(PsaBwdWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
 
@@ -55,18 +60,20 @@ __device__ __forceinline__ void mma_tf32x3(float *d, const float *a, const float
 #undef MST_MMA
 }
 
-struct PsaBwdArgs2 {
+struct PsaBwdArgs3 {
     const float *Zr, *Zci, *melody;   // as k_psa_fwd2
     const float *target;              // P (N,C,B,T,10,56,5)
     const float *coef;                // (N, kLossCoefs)
+    const float *Wl;                  // final linear (5, 50), global copy for per-lane column access
     float *dZr, *dZi;                 // (N,B,T,10,450) written; (N,C,450) atomically accumulated (zeroed by the caller)
-    float *dmelody;                   // (N,B,T,10,56,8) written
-    float *gWm, *gbm, *gWl, *gbl;     // parameter gradients (atomic accumulate)
+    float *dps;                       // per unit (56, 5) at stride dps_stride: sum over channels of the pre-sigmoid gradient
+    long long dps_stride;
+    float *gWl;                       // (5, 50): columns 0..29 accumulated here
     int N, C, B, T, ctas_per_n, warps;
 };
 
-__global__ void __launch_bounds__(kPsaBwdWarps * 32)
-k_psa_bwd2(PsaBwdArgs2 a) {
+__global__ void __launch_bounds__(kPsaBwdWarps * 32, 1)
+k_psa_bwd3(PsaBwdArgs3 a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     PsaBwdWarpSmem &s = reinterpret_cast<PsaBwdWarpSmem *>(smem_raw)[warp];
@@ -77,27 +84,24 @@ k_psa_bwd2(PsaBwdArgs2 a) {
     const long long chunk = (per_n + a.ctas_per_n - 1) / a.ctas_per_n;
     const long long b_lo = (long long)kcta * chunk, b_hi = min(per_n, b_lo + chunk);
     for (int i = threadIdx.x; i < C * 450; i += blockDim.x) dzi_s[i] = 0.f;
-    for (int i = lane; i < 32 * 36; i += 32) s.sa[i] = 0.f;
-    for (int i = lane; i < 32 * 8; i += 32) s.sd[i] = 0.f;
-    for (int i = lane; i < 56 * 8; i += 32) s.dps[i] = 0.f;
-    for (int i = lane; i < 56 * 24; i += 32) s.mf[i] = 0.f;
+    for (int i = lane; i < 30 * 36; i += 32) s.sa[i] = 0.f;
     __syncthreads();
     float cf[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) cf[i] = a.coef[n * kLossCoefs + i];
-    const int c_l = lane >> 3, o = lane & 7, g = lane >> 2, t = lane & 3;
-    float accW[2][4], accM[2][4], accWm[2][4], gbm[20];
+    const int c_l = lane >> 3, o = lane & 7;
+    // lane = column q of the final linear for the target-note cells: its four non-velocity weights and their gradients
+    const int qx = min(lane, 29);
+    const float wx0 = a.Wl[0 * 50 + qx], wx2 = a.Wl[2 * 50 + qx], wx3 = a.Wl[3 * 50 + qx], wx4 = a.Wl[4 * 50 + qx];
+    float gwx0 = 0.f, gwx2 = 0.f, gwx3 = 0.f, gwx4 = 0.f;
+    float gw1[30];
 #pragma unroll
-    for (int i = 0; i < 2; i++)
-#pragma unroll
-        for (int j = 0; j < 4; j++) { accW[i][j] = 0.f; accM[i][j] = 0.f; accWm[i][j] = 0.f; }
-#pragma unroll
-    for (int j = 0; j < 20; j++) gbm[j] = 0.f;
+    for (int q = 0; q < 30; q++) gw1[q] = 0.f;
 
     for (long long btf = b_lo + warp; btf < b_hi; btf += a.warps) {
         const long long u = (long long)n * per_n + btf;
         __syncwarp();
-        // ---- phase 1: per-note melody branch (mf kept for the backward), zero the per-unit accumulators
+        // ---- per-note melody branch of the forward (bl + Wl[:, 30:].mf), zero the per-unit accumulator
         for (int note = lane; note < 56; note += 32) {
             const float4 *mp = reinterpret_cast<const float4 *>(a.melody + (u * 56 + note) * 8);
             const float4 m0 = mp[0], m1 = mp[1];
@@ -105,15 +109,10 @@ k_psa_bwd2(PsaBwdArgs2 a) {
             float mf[20], sn[5];
             psa_note(mel8, mf, sn);
 #pragma unroll
-            for (int e = 0; e < 5; e++) { s.snote[note * 5 + e] = sn[e]; s.dps[note * 8 + e] = 0.f; }
-#pragma unroll
-            for (int p = 0; p < 8; p++) s.mel[note * 8 + p] = mel8[p];
-#pragma unroll
-            for (int j = 0; j < 20; j++) s.mf[note * 24 + j] = mf[j];
-            s.mf[note * 24 + 20] = 1.f;
+            for (int e = 0; e < 5; e++) { s.snote[note * 5 + e] = sn[e]; s.dps[note * 5 + e] = 0.f; }
         }
-        for (int j = lane; j < 450; j += 32) s.dzr[j] = 0.f;
         const float *zr = a.Zr + u * 450;
+        float *dzr = a.dZr + u * 450;
         for (int c0 = 0; c0 < C; c0 += 4) {
             const int cg = min(4, C - c0);
             __syncwarp();
@@ -125,8 +124,6 @@ k_psa_bwd2(PsaBwdArgs2 a) {
             if (!active) {
 #pragma unroll
                 for (int q = 0; q < 30; q++) s.sa[q * 36 + lane] = 0.f;
-#pragma unroll
-                for (int e = 0; e < 5; e++) s.sd[lane * 8 + e] = 0.f;
             }
             __syncwarp();
             float oct[30], doct[30];
@@ -136,58 +133,80 @@ k_psa_bwd2(PsaBwdArgs2 a) {
             const float *tg = a.target + ((((long long)n * C + c0 + c_l) * per_n) + btf) * 280;
             for (int d = 0; d < 7; d++) {
                 const int note = o * 7 + d;
-                float dpre[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+                float dpre1 = 0.f;
+                bool has_note = false;
                 if (active) {
-                    float y[5], t5[5];
-#pragma unroll
-                    for (int e = 0; e < 5; e++) { y[e] = s.snote[note * 5 + e]; t5[e] = tg[note * 5 + e]; }
+                    // dense part: velocity output only
+                    float av[30];
+                    float y1 = s.snote[note * 5 + 1];
 #pragma unroll
                     for (int q = 0; q < 30; q++) {
                         const float v = leaky(oct[q] + deg[d * 30 + q]);
-                        s.sa[q * 36 + lane] = v;
-#pragma unroll
-                        for (int e = 0; e < 5; e++) y[e] = fmaf(c_psa[kPsaWl + e * 50 + q], v, y[e]);
+                        av[q] = v;
+                        y1 = fmaf(c_psa[kPsaWl + 50 + q], v, y1);
                     }
-#pragma unroll
-                    for (int e = 0; e < 5; e++) y[e] = sigmoidf(y[e]) * (e == 0 ? 6.f : 1.f);
-                    loss_cell_grad<5>(y, t5, cf, dpre);
-#pragma unroll
-                    for (int e = 0; e < 5; e++) s.sd[lane * 8 + e] = dpre[e];
-                }
-                // dps[note] += sum over the channel lanes (lane = c * 8 + o: xor 8, 16)
-#pragma unroll
-                for (int e = 0; e < 5; e++) {
-                    float v = dpre[e];
-                    v += __shfl_xor_sync(0xffffffffu, v, 8);
-                    v += __shfl_xor_sync(0xffffffffu, v, 16);
-                    if (c_l == 0) s.dps[note * 8 + e] += v;
-                }
-                __syncwarp();
-                // gWl[:, :30] += a^T . dpre over the 32 cells of this step (tensor cores)
-#pragma unroll
-                for (int ks = 0; ks < 4; ks++) {
-                    const float bf[2] = {s.sd[(ks * 8 + t) * 8 + g], s.sd[(ks * 8 + t + 4) * 8 + g]};
-#pragma unroll
-                    for (int mt = 0; mt < 2; mt++) {
-                        const float *r0 = s.sa + (mt * 16 + g) * 36 + ks * 8 + t;
-                        const float af[4] = {r0[0], r0[8 * 36], r0[4], r0[8 * 36 + 4]};
-                        mma_tf32x3(accW[mt], af, bf);
-                    }
-                }
-                __syncwarp();
-                // input gradient of the outer add: din[q] = (Wl[:, q] . dpre) * leaky'(a[q])
-                if (active) {
+                    const float p = sigmoidf(y1), tv = tg[note * 5 + 1];
+                    has_note = tv > 0.f;
+                    float dv = cf[0] * (p < tv ? 1.f : (p == tv ? 0.5f : 0.f)) + (p > tv ? cf[1] : 0.f) - (tv > p ? cf[2] : 0.f);
+                    if (has_note) dv += cf[3] * 2.f * (p - tv);
+                    dpre1 = dv * p * (1.f - p);
+                    const float dpre1s = kSlope * dpre1;
 #pragma unroll
                     for (int q = 0; q < 30; q++) {
-                        float din = 0.f;
-#pragma unroll
-                        for (int e = 0; e < 5; e++) din = fmaf(c_psa[kPsaWl + e * 50 + q], dpre[e], din);
-                        din *= leaky_grad_from_out(s.sa[q * 36 + lane]);
+                        const float din = c_psa[kPsaWl + 50 + q] * (av[q] > 0.f ? dpre1 : dpre1s);
                         doct[q] += din;
+                        gw1[q] = fmaf(av[q], dpre1, gw1[q]);
                         s.sa[q * 36 + lane] = din;
                     }
                 }
+                {   // dps[note][1] += sum over the channel lanes (lane = c * 8 + o: xor 8, 16)
+                    float v = dpre1;
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    if (c_l == 0) s.dps[note * 5 + 1] += v;
+                }
+                unsigned todo = __ballot_sync(0xffffffffu, has_note);
                 __syncwarp();
+                // cells with a target note: the four other outputs, cooperatively (lane = column q)
+                while (todo) {
+                    const int m = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int cm = m >> 3, om = m & 7, note_m = om * 7 + d;
+                    const float am = lane < 30 ? leaky(s.od[cm * 450 + om * 30 + lane] + s.od[cm * 450 + 240 + d * 30 + lane]) : 0.f;
+                    float y0 = wx0 * am, y2 = wx2 * am, y3 = wx3 * am, y4 = wx4 * am;
+#pragma unroll
+                    for (int sft = 16; sft; sft >>= 1) {
+                        y0 += __shfl_xor_sync(0xffffffffu, y0, sft);
+                        y2 += __shfl_xor_sync(0xffffffffu, y2, sft);
+                        y3 += __shfl_xor_sync(0xffffffffu, y3, sft);
+                        y4 += __shfl_xor_sync(0xffffffffu, y4, sft);
+                    }
+                    const float *sn = s.snote + note_m * 5;
+                    const float *tm = a.target + ((((long long)n * C + c0 + cm) * per_n) + btf) * 280 + note_m * 5;
+                    y0 = sigmoidf(y0 + sn[0]) * 6.f;
+                    y2 = sigmoidf(y2 + sn[2]); y3 = sigmoidf(y3 + sn[3]); y4 = sigmoidf(y4 + sn[4]);
+                    const float d0 = cf[4] * 2.f * (y0 - fminf(tm[0], 6.f)) / 36.f * y0 * (1.f - y0 / 6.f);
+                    const float q2 = y2 * (1.f - y2), q3 = y3 * (1.f - y3), q4 = y4 * (1.f - y4);
+                    const float d2 = cf[5] * (y2 - tm[2]) / fmaxf(q2, 1e-12f) * q2;
+                    const float d3 = cf[5] * (y3 - tm[3]) / fmaxf(q3, 1e-12f) * q3;
+                    const float d4 = cf[5] * (y4 - tm[4]) / fmaxf(q4, 1e-12f) * q4;
+                    if (lane < 30) {
+                        const float ex = (wx0 * d0 + wx2 * d2 + wx3 * d3 + wx4 * d4) * leaky_grad_from_out(am);
+                        s.sa[lane * 36 + m] += ex;
+                        s.exq[lane] = ex;
+                        gwx0 = fmaf(am, d0, gwx0); gwx2 = fmaf(am, d2, gwx2); gwx3 = fmaf(am, d3, gwx3); gwx4 = fmaf(am, d4, gwx4);
+                    }
+                    if (lane == 0) {
+                        float *dp = s.dps + note_m * 5;
+                        dp[0] += d0; dp[2] += d2; dp[3] += d3; dp[4] += d4;
+                    }
+                    __syncwarp();
+                    if (lane == m) {
+#pragma unroll
+                        for (int q = 0; q < 30; q++) doct[q] += s.exq[q];
+                    }
+                    __syncwarp();
+                }
                 // degree-row gradient: sum over the 8 octave lanes of each channel, written over od in place
                 for (int i = lane; i < cg * 30; i += 32) {
                     const int c = i / 30, q = i - c * 30;
@@ -211,13 +230,82 @@ k_psa_bwd2(PsaBwdArgs2 a) {
                     sum += v;
                     atomicAdd(&dzi_s[(c0 + c) * 450 + j], v);
                 }
-                s.dzr[j] += sum;
+                dzr[j] = c0 == 0 ? sum : dzr[j] + sum;
             }
         }
         __syncwarp();
-        for (int j = lane; j < 450; j += 32) a.dZr[u * 450 + j] = s.dzr[j];
-        // ---- melody branch.  gWl[:, 30:50] (+ bias through the all-ones column 20) += mf^T . dps
+        float *dps = a.dps + u * a.dps_stride;
+        for (int i = lane; i < 280; i += 32) dps[i] = s.dps[i];
+    }
+    // ---- flush the per-lane weight-gradient accumulators
 #pragma unroll
+    for (int q = 0; q < 30; q++) {
+        float v = gw1[q];
+        for (int sft = 16; sft; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
+        if (lane == 0 && v != 0.f) atomicAdd(a.gWl + 50 + q, v);
+    }
+    if (lane < 30) {
+        if (gwx0 != 0.f) atomicAdd(a.gWl + 0 * 50 + lane, gwx0);
+        if (gwx2 != 0.f) atomicAdd(a.gWl + 2 * 50 + lane, gwx2);
+        if (gwx3 != 0.f) atomicAdd(a.gWl + 3 * 50 + lane, gwx3);
+        if (gwx4 != 0.f) atomicAdd(a.gWl + 4 * 50 + lane, gwx4);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < C * 450; i += blockDim.x)
+        if (dzi_s[i] != 0.f) atomicAdd(a.dZi + (long long)n * C * 450 + i, dzi_s[i]);
+}
+
+// melody branch of the PitchedStyleApplier backward: one warp per unit, operands staged for the tensor cores
+constexpr int kPsaMelWarps = 16;
+struct PsaMelWarpSmem {
+    float mf[56 * 24];       // mf (col 20 = 1 for the bias row, 21..23 = 0), later the pre-activation gradient dmf
+    float mel[56 * 8];
+    float dps[56 * 8];       // cols 5..7 stay 0
+};
+static_assert(sizeof(PsaMelWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
+
+struct PsaMelBwdArgs {
+    const float *melody;              // (units, 56, 8)
+    const float *dps;                 // per unit (56, 5) at stride dps_stride (may alias dmelody: read before written)
+    long long dps_stride;
+    float *dmelody;                   // (units, 56, 8) written
+    float *gWm, *gbm, *gWl, *gbl;     // melody_linear (20, 8), (20); final linear columns 30..49 of (5, 50), (5)
+    long long units;
+};
+
+__global__ void __launch_bounds__(kPsaMelWarps * 32, 1)
+k_psa_mel_bwd(PsaMelBwdArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    PsaMelWarpSmem &s = reinterpret_cast<PsaMelWarpSmem *>(smem_raw)[warp];
+    for (int i = lane; i < 56 * 8; i += 32) s.dps[i] = 0.f;
+    for (int i = lane; i < 56 * 24; i += 32) s.mf[i] = 0.f;
+    const int g = lane >> 2, t = lane & 3;
+    float accM[2][4], accWm[2][4], gbm = 0.f;       // gbm: lane j < 20 owns melody_linear.bias[j]
+#pragma unroll
+    for (int i = 0; i < 2; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) { accM[i][j] = 0.f; accWm[i][j] = 0.f; }
+    for (long long u = (long long)blockIdx.x * kPsaMelWarps + warp; u < a.units; u += (long long)gridDim.x * kPsaMelWarps) {
+        __syncwarp();
+        const float *dpg = a.dps + u * a.dps_stride;
+        for (int i = lane; i < 280; i += 32) { const int note = i / 5; s.dps[note * 8 + (i - note * 5)] = dpg[i]; }
+#pragma unroll 1
+        for (int note = lane; note < 56; note += 32) {
+            const float4 *mp = reinterpret_cast<const float4 *>(a.melody + (u * 56 + note) * 8);
+            const float4 m0 = mp[0], m1 = mp[1];
+            const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            float mf[20], sn[5];
+            psa_note(mel8, mf, sn);
+#pragma unroll
+            for (int p = 0; p < 8; p++) s.mel[note * 8 + p] = mel8[p];
+#pragma unroll
+            for (int j = 0; j < 20; j++) s.mf[note * 24 + j] = mf[j];
+            s.mf[note * 24 + 20] = 1.f;
+        }
+        __syncwarp();
+        // gWl[:, 30:50] (+ bias through the all-ones column 20) += mf^T . dps
+#pragma unroll 1
         for (int ks = 0; ks < 7; ks++) {
             const float bf[2] = {s.dps[(ks * 8 + t) * 8 + g], s.dps[(ks * 8 + t + 4) * 8 + g]};
             const float *r0 = s.mf + (ks * 8 + t) * 24 + g;
@@ -227,6 +315,7 @@ k_psa_bwd2(PsaBwdArgs2 a) {
             mma_tf32x3(accM[1], a1, bf);
         }
         __syncwarp();
+#pragma unroll 1
         for (int note = lane; note < 56; note += 32) {
             float dmf[20], dp[5];
 #pragma unroll
@@ -238,9 +327,9 @@ k_psa_bwd2(PsaBwdArgs2 a) {
                 for (int e = 0; e < 5; e++) v = fmaf(c_psa[kPsaWl + e * 50 + 30 + j], dp[e], v);
                 v *= leaky_grad_from_out(s.mf[note * 24 + j]);
                 dmf[j] = v;
-                gbm[j] += v;
                 s.mf[note * 24 + j] = v;
             }
+            s.mf[note * 24 + 20] = 0.f;
             float dm[8];
 #pragma unroll
             for (int p = 0; p < 8; p++) {
@@ -254,8 +343,14 @@ k_psa_bwd2(PsaBwdArgs2 a) {
             dst[1] = make_float4(dm[4], dm[5], dm[6], dm[7]);
         }
         __syncwarp();
+        if (lane < 20) {
+            float v = 0.f;
+#pragma unroll 8
+            for (int note = 0; note < 56; note++) v += s.mf[note * 24 + lane];
+            gbm += v;
+        }
         // gWm += dmf^T . mel
-#pragma unroll
+#pragma unroll 1
         for (int ks = 0; ks < 7; ks++) {
             const float bf[2] = {s.mel[(ks * 8 + t) * 8 + g], s.mel[(ks * 8 + t + 4) * 8 + g]};
             const float *r0 = s.mf + (ks * 8 + t) * 24 + g;
@@ -265,28 +360,19 @@ k_psa_bwd2(PsaBwdArgs2 a) {
             mma_tf32x3(accWm[1], a1, bf);
         }
     }
-    // ---- flush the per-lane accumulators (fragment layout: rows g / g + 8, columns 2t / 2t + 1)
+    // ---- flush (fragment layout: rows g / g + 8, columns 2t / 2t + 1)
 #pragma unroll
     for (int mt = 0; mt < 2; mt++)
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             const int row = mt * 16 + g + (i >> 1) * 8, col = 2 * t + (i & 1);
             if (col < 5) {
-                if (row < 30 && accW[mt][i] != 0.f) atomicAdd(a.gWl + col * 50 + row, accW[mt][i]);
                 if (row < 20 && accM[mt][i] != 0.f) atomicAdd(a.gWl + col * 50 + 30 + row, accM[mt][i]);
                 if (row == 20 && accM[mt][i] != 0.f) atomicAdd(a.gbl + col, accM[mt][i]);
             }
             if (row < 20 && accWm[mt][i] != 0.f) atomicAdd(a.gWm + row * 8 + col, accWm[mt][i]);
         }
-#pragma unroll
-    for (int j = 0; j < 20; j++) {
-        float v = gbm[j];
-        for (int sft = 16; sft; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
-        if (lane == 0 && v != 0.f) atomicAdd(a.gbm + j, v);
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < C * 450; i += blockDim.x)
-        if (dzi_s[i] != 0.f) atomicAdd(a.dZi + (long long)n * C * 450 + i, dzi_s[i]);
+    if (lane < 20 && gbm != 0.f) atomicAdd(a.gbm + lane, gbm);
 }
 
 // ------------------------------------------------------------------------------------------------
