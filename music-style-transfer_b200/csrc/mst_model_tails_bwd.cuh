@@ -35,9 +35,17 @@ struct PsaBwdWarpSmem {
     float dps[56 * 5];
     float sa[30 * 36];       // [q][lane] input-gradient staging of the current degree step
     float exq[32];           // a target-note cell's extra input gradient, handed back to its owner lane
+    float mel[56 * 8];       // this unit's melody rows / Zr row, fetched with cp.async during the previous unit
+    float zr[452];
 };
 static_assert(sizeof(PsaBwdWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
 
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
+}
 __device__ __forceinline__ uint32_t to_tf32(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
@@ -98,12 +106,20 @@ k_psa_bwd3(PsaBwdArgs3 a) {
 #pragma unroll
     for (int q = 0; q < 30; q++) gw1[q] = 0.f;
 
+    auto prefetch = [&](long long uu) {           // Zr rows are 1800 bytes: 8-byte aligned
+        const float *mg = a.melody + uu * 448, *zg = a.Zr + uu * 450;
+        for (int i = lane; i < 112; i += 32) cp_async16(s.mel + i * 4, mg + i * 4);
+        for (int i = lane; i < 225; i += 32) cp_async8(s.zr + i * 2, zg + i * 2);
+        asm volatile("cp.async.commit_group;");
+    };
+    if (b_lo + warp < b_hi) prefetch((long long)n * per_n + b_lo + warp);
     for (long long btf = b_lo + warp; btf < b_hi; btf += a.warps) {
         const long long u = (long long)n * per_n + btf;
+        asm volatile("cp.async.wait_group 0;");
         __syncwarp();
         // ---- per-note melody branch of the forward (bl + Wl[:, 30:].mf), zero the per-unit accumulator
         for (int note = lane; note < 56; note += 32) {
-            const float4 *mp = reinterpret_cast<const float4 *>(a.melody + (u * 56 + note) * 8);
+            const float4 *mp = reinterpret_cast<const float4 *>(s.mel + note * 8);
             const float4 m0 = mp[0], m1 = mp[1];
             const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
             float mf[20], sn[5];
@@ -111,14 +127,17 @@ k_psa_bwd3(PsaBwdArgs3 a) {
 #pragma unroll
             for (int e = 0; e < 5; e++) { s.snote[note * 5 + e] = sn[e]; s.dps[note * 5 + e] = 0.f; }
         }
-        const float *zr = a.Zr + u * 450;
         float *dzr = a.dZr + u * 450;
         for (int c0 = 0; c0 < C; c0 += 4) {
             const int cg = min(4, C - c0);
             __syncwarp();
             for (int j = lane; j < 450; j += 32) {
-                const float z = zr[j];
+                const float z = s.zr[j];
                 for (int c = 0; c < cg; c++) s.od[c * 450 + j] = leaky(z + a.Zci[((long long)n * C + c0 + c) * 450 + j]);
+            }
+            if (c0 + 4 >= C && btf + a.warps < b_hi) {       // both staging rows are consumed: fetch the next unit's
+                __syncwarp();
+                prefetch(u + a.warps);
             }
             const bool active = c_l < cg;
             if (!active) {
@@ -131,21 +150,33 @@ k_psa_bwd3(PsaBwdArgs3 a) {
             for (int q = 0; q < 30; q++) { oct[q] = active ? s.od[c_l * 450 + o * 30 + q] : 0.f; doct[q] = 0.f; }
             const float *deg = s.od + c_l * 450 + 240;
             const float *tg = a.target + ((((long long)n * C + c0 + c_l) * per_n) + btf) * 280;
+            float tvel[7];                                   // target velocities of this lane's 7 cells, fetched up front
+#pragma unroll
+            for (int d = 0; d < 7; d++) tvel[d] = active ? tg[(o * 7 + d) * 5 + 1] : 0.f;
+#pragma unroll 1
             for (int d = 0; d < 7; d++) {
                 const int note = o * 7 + d;
                 float dpre1 = 0.f;
                 bool has_note = false;
                 if (active) {
-                    // dense part: velocity output only
+                    // dense part: velocity output only (three partial sums keep the FFMA pipe busy)
                     float av[30];
-                    float y1 = s.snote[note * 5 + 1];
+                    float y1 = s.snote[note * 5 + 1], y1b = 0.f, y1c = 0.f;
 #pragma unroll
-                    for (int q = 0; q < 30; q++) {
-                        const float v = leaky(oct[q] + deg[d * 30 + q]);
-                        av[q] = v;
-                        y1 = fmaf(c_psa[kPsaWl + 50 + q], v, y1);
+                    for (int q = 0; q < 30; q += 3) {
+                        const float v0 = leaky(oct[q] + deg[d * 30 + q]);
+                        const float v1 = leaky(oct[q + 1] + deg[d * 30 + q + 1]);
+                        const float v2 = leaky(oct[q + 2] + deg[d * 30 + q + 2]);
+                        av[q] = v0; av[q + 1] = v1; av[q + 2] = v2;
+                        y1 = fmaf(c_psa[kPsaWl + 50 + q], v0, y1);
+                        y1b = fmaf(c_psa[kPsaWl + 50 + q + 1], v1, y1b);
+                        y1c = fmaf(c_psa[kPsaWl + 50 + q + 2], v2, y1c);
                     }
-                    const float p = sigmoidf(y1), tv = tg[note * 5 + 1];
+                    y1 += y1b + y1c;
+                    float tv = tvel[0];
+#pragma unroll
+                    for (int dd = 1; dd < 7; dd++) tv = d == dd ? tvel[dd] : tv;
+                    const float p = sigmoidf(y1);
                     has_note = tv > 0.f;
                     float dv = cf[0] * (p < tv ? 1.f : (p == tv ? 0.5f : 0.f)) + (p > tv ? cf[1] : 0.f) - (tv > p ? cf[2] : 0.f);
                     if (has_note) dv += cf[3] * 2.f * (p - tv);
@@ -255,19 +286,20 @@ k_psa_bwd3(PsaBwdArgs3 a) {
         if (dzi_s[i] != 0.f) atomicAdd(a.dZi + (long long)n * C * 450 + i, dzi_s[i]);
 }
 
-// melody branch of the PitchedStyleApplier backward: one warp per unit, operands staged for the tensor cores
+// melody branch of the PitchedStyleApplier backward: one warp per unit, operands staged for the tensor cores; the next
+// unit's melody rows and dps rows are fetched with cp.async while the current unit is processed
 constexpr int kPsaMelWarps = 16;
 struct PsaMelWarpSmem {
     float mf[56 * 24];       // mf (col 20 = 1 for the bias row, 21..23 = 0), later the pre-activation gradient dmf
-    float mel[56 * 8];
-    float dps[56 * 8];       // cols 5..7 stay 0
+    float mel[2][56 * 8];    // double-buffered global rows, used in place as MMA operands
+    float dps[2][56 * 5];
 };
 static_assert(sizeof(PsaMelWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
 
 struct PsaMelBwdArgs {
     const float *melody;              // (units, 56, 8)
     const float *dps;                 // per unit (56, 5) at stride dps_stride (may alias dmelody: read before written)
-    long long dps_stride;
+    long long dps_stride;             // multiple of 4 floats (16-byte copies)
     float *dmelody;                   // (units, 56, 8) written
     float *gWm, *gbm, *gWl, *gbl;     // melody_linear (20, 8), (20); final linear columns 30..49 of (5, 50), (5)
     long long units;
@@ -278,7 +310,6 @@ k_psa_mel_bwd(PsaMelBwdArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     PsaMelWarpSmem &s = reinterpret_cast<PsaMelWarpSmem *>(smem_raw)[warp];
-    for (int i = lane; i < 56 * 8; i += 32) s.dps[i] = 0.f;
     for (int i = lane; i < 56 * 24; i += 32) s.mf[i] = 0.f;
     const int g = lane >> 2, t = lane & 3;
     float accM[2][4], accWm[2][4], gbm = 0.f;       // gbm: lane j < 20 owns melody_linear.bias[j]
@@ -286,19 +317,27 @@ k_psa_mel_bwd(PsaMelBwdArgs a) {
     for (int i = 0; i < 2; i++)
 #pragma unroll
         for (int j = 0; j < 4; j++) { accM[i][j] = 0.f; accWm[i][j] = 0.f; }
-    for (long long u = (long long)blockIdx.x * kPsaMelWarps + warp; u < a.units; u += (long long)gridDim.x * kPsaMelWarps) {
+    auto prefetch = [&](long long u, int buf) {
+        const float *mg = a.melody + u * 448, *dg = a.dps + u * a.dps_stride;
+        for (int i = lane; i < 112; i += 32) cp_async16(s.mel[buf] + i * 4, mg + i * 4);
+        for (int i = lane; i < 70; i += 32) cp_async16(s.dps[buf] + i * 4, dg + i * 4);
+        asm volatile("cp.async.commit_group;");
+    };
+    const long long u0 = (long long)blockIdx.x * kPsaMelWarps + warp, ustep = (long long)gridDim.x * kPsaMelWarps;
+    if (u0 < a.units) prefetch(u0, 0);
+    int buf = 0;
+    for (long long u = u0; u < a.units; u += ustep, buf ^= 1) {
         __syncwarp();
-        const float *dpg = a.dps + u * a.dps_stride;
-        for (int i = lane; i < 280; i += 32) { const int note = i / 5; s.dps[note * 8 + (i - note * 5)] = dpg[i]; }
+        if (u + ustep < a.units) { prefetch(u + ustep, buf ^ 1); asm volatile("cp.async.wait_group 1;"); }
+        else asm volatile("cp.async.wait_group 0;");
+        __syncwarp();
+        const float *mel = s.mel[buf], *dps = s.dps[buf];
 #pragma unroll 1
         for (int note = lane; note < 56; note += 32) {
-            const float4 *mp = reinterpret_cast<const float4 *>(a.melody + (u * 56 + note) * 8);
-            const float4 m0 = mp[0], m1 = mp[1];
+            const float4 m0 = *reinterpret_cast<const float4 *>(mel + note * 8), m1 = *reinterpret_cast<const float4 *>(mel + note * 8 + 4);
             const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
             float mf[20], sn[5];
             psa_note(mel8, mf, sn);
-#pragma unroll
-            for (int p = 0; p < 8; p++) s.mel[note * 8 + p] = mel8[p];
 #pragma unroll
             for (int j = 0; j < 20; j++) s.mf[note * 24 + j] = mf[j];
             s.mf[note * 24 + 20] = 1.f;
@@ -307,7 +346,7 @@ k_psa_mel_bwd(PsaMelBwdArgs a) {
         // gWl[:, 30:50] (+ bias through the all-ones column 20) += mf^T . dps
 #pragma unroll 1
         for (int ks = 0; ks < 7; ks++) {
-            const float bf[2] = {s.dps[(ks * 8 + t) * 8 + g], s.dps[(ks * 8 + t + 4) * 8 + g]};
+            const float bf[2] = {g < 5 ? dps[(ks * 8 + t) * 5 + g] : 0.f, g < 5 ? dps[(ks * 8 + t + 4) * 5 + g] : 0.f};
             const float *r0 = s.mf + (ks * 8 + t) * 24 + g;
             const float a0[4] = {r0[0], r0[8], r0[4 * 24], r0[4 * 24 + 8]};
             const float a1[4] = {r0[16], 0.f, r0[4 * 24 + 16], 0.f};
@@ -319,7 +358,7 @@ k_psa_mel_bwd(PsaMelBwdArgs a) {
         for (int note = lane; note < 56; note += 32) {
             float dmf[20], dp[5];
 #pragma unroll
-            for (int e = 0; e < 5; e++) dp[e] = s.dps[note * 8 + e];
+            for (int e = 0; e < 5; e++) dp[e] = dps[note * 5 + e];
 #pragma unroll
             for (int j = 0; j < 20; j++) {
                 float v = 0.f;
@@ -352,7 +391,7 @@ k_psa_mel_bwd(PsaMelBwdArgs a) {
         // gWm += dmf^T . mel
 #pragma unroll 1
         for (int ks = 0; ks < 7; ks++) {
-            const float bf[2] = {s.mel[(ks * 8 + t) * 8 + g], s.mel[(ks * 8 + t + 4) * 8 + g]};
+            const float bf[2] = {mel[(ks * 8 + t) * 8 + g], mel[(ks * 8 + t + 4) * 8 + g]};
             const float *r0 = s.mf + (ks * 8 + t) * 24 + g;
             const float a0[4] = {r0[0], r0[8], r0[4 * 24], r0[4 * 24 + 8]};
             const float a1[4] = {r0[16], 0.f, r0[4 * 24 + 16], 0.f};
