@@ -244,6 +244,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             a.gWc = GRD(c, me_ch_w); a.gbc = GRD(c, me_ch_b); a.gWl = GRD(c, me_lin_w); a.gbl = GRD(c, me_lin_b);
             k_me_bwd_stats2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
             k_me_bwd2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 4), 256, 0, L.st>>>(a); L.check();
+            k_me_bwd_cells<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 2), 256, 0, L.st>>>(a); L.check();
         }
         const Dims5 d{N, C, B, T, 1};
         float *dz1 = w.Z(Nb * 120), *dz2 = w.Z((long long)NC * 120);

@@ -250,11 +250,12 @@ k_me_bwd_stats2(MeArgs2 a) {
     }
 }
 
-struct MeBwdWarpSmem { float od[120], dod[120], dxp[56 * 8], dxa[56 * 8], g2[56 + 7 + 35 + 2]; };
+struct MeBwdWarpSmem { float od[120], dxp[56 * 8], dxa[56 * 8]; };
 
 // warp per beat row (n, c, b, t).  Per note (all 10 fractions treated as empty cells):
 //   dxs = (k1 dsum + 10 k2 xe) leaky'(xe);  occupied cells replace their empty share by the true one.
 //   dxp multiplies the empty input [ae; bfe], dxa = dxp + sum of the true cells' dx multiplies ae (shared by both).
+// The weight gradients that only the occupied cells feed (channels_linear, linear.weight[:, 8:]) are k_me_bwd_cells'.
 __global__ void __launch_bounds__(256)
 k_me_bwd2(MeArgs2 a) {
     __shared__ MeBwdWarpSmem sm[8];
@@ -267,7 +268,6 @@ k_me_bwd2(MeArgs2 a) {
     for (int i = 0; i < 64; i++) gWa[i] = 0.f;
 #pragma unroll
     for (int e = 0; e < 8; e++) { Sp[e] = 0.f; Sa[e] = 0.f; }
-    for (int i = lane; i < 100; i += 32) s.g2[i] = 0.f;     // [0,56) linear.weight[:, 8:] (occupied), [56,63) bc, [63,98) Wc
     for (long long row = (long long)blockIdx.x * 8 + warp; row < rows; row += (long long)gridDim.x * 8) {
         const long long nc = row / BT, bt = row - nc * BT;
         const int n = (int)(nc / a.C), c = (int)(nc - (long long)n * a.C);
@@ -278,7 +278,7 @@ k_me_bwd2(MeArgs2 a) {
         const float k2 = (a.stats[n * (a.C + 1) + c] - a.stats[n * (a.C + 1) + a.C]) / (wsum * wc);
         const long long u = (long long)n * BT + bt;
         __syncwarp();
-        for (int i = lane; i < 120; i += 32) { s.od[i] = a.od[row * 120 + i]; s.dod[i] = 0.f; }
+        for (int i = lane; i < 120; i += 32) s.od[i] = a.od[row * 120 + i];
         __syncwarp();
         // phase A: per-note empty-cell gradient
         for (int note = lane; note < 56; note += 32) {
@@ -296,11 +296,11 @@ k_me_bwd2(MeArgs2 a) {
             }
         }
         __syncwarp();
-        // phase B: occupied cells
+        // phase B: occupied cells swap their empty share for the true one (two cells of a row may share a note: atomics)
         for (uint32_t i = a.off[row] + lane; i < a.off[row + 1]; i += 32) {
             const CellRec r = a.recs[i];
             const int note = (int)(r.cell % 56);
-            float ae[8], xp[8], bf[7], xt[8], dxt[8];
+            float ae[8], xp[8], bf[7], xt[8];
             me_note(k, s.od, note, ae, xp);
             me_occupied(k, r.p, xp, bf, xt);
             const float *d = a.dmelody + u * 4480 + r.cell * 8;
@@ -308,49 +308,46 @@ k_me_bwd2(MeArgs2 a) {
             for (int e = 0; e < 8; e++) {
                 const float xe = leaky(xp[e]), x = leaky(xt[e]);
                 const float de = (k1 * d[e] + k2 * xe) * leaky_grad_from_out(xe);
-                dxt[e] = (k1 * d[e] + k2 * x) * leaky_grad_from_out(x);
+                const float dxt = (k1 * d[e] + k2 * x) * leaky_grad_from_out(x);
                 atomicAdd(&s.dxp[note * 8 + e], -de);
-                atomicAdd(&s.dxa[note * 8 + e], dxt[e] - de);
-            }
-#pragma unroll
-            for (int q = 0; q < 7; q++) {
-                float dbf = 0.f;
-#pragma unroll
-                for (int e = 0; e < 8; e++) {
-                    atomicAdd(&s.g2[e * 7 + q], dxt[e] * bf[q]);
-                    dbf = fmaf(c_me[kMeWl + e * 15 + 8 + q], dxt[e], dbf);
-                }
-                dbf *= leaky_grad_from_out(bf[q]);
-                atomicAdd(&s.g2[56 + q], dbf);
-#pragma unroll
-                for (int p = 0; p < 5; p++) if (r.p[p] != 0.f) atomicAdd(&s.g2[63 + q * 5 + p], dbf * r.p[p]);
+                atomicAdd(&s.dxa[note * 8 + e], dxt - de);
             }
         }
         __syncwarp();
-        // phase C: outer products with the per-note input and the gradient of the outer add
+        // phase C: outer products with the per-note input; the outer add's gradient per note overwrites dxp
         for (int note = lane; note < 56; note += 32) {
-            const int o = note / 7, d = note - o * 7;
-            float ae[8], xp[8];
+            float ae[8], xp[8], da[8];
             me_note(k, s.od, note, ae, xp);
 #pragma unroll
             for (int e = 0; e < 8; e++) {
-                const float dp = s.dxp[note * 8 + e], da = s.dxa[note * 8 + e];
-                Sp[e] += dp; Sa[e] += da;
+                da[e] = s.dxa[note * 8 + e];
+                Sp[e] += s.dxp[note * 8 + e]; Sa[e] += da[e];
 #pragma unroll
-                for (int q = 0; q < 8; q++) gWa[e * 8 + q] = fmaf(da, ae[q], gWa[e * 8 + q]);
+                for (int q = 0; q < 8; q++) gWa[e * 8 + q] = fmaf(da[e], ae[q], gWa[e * 8 + q]);
             }
 #pragma unroll
             for (int q = 0; q < 8; q++) {
                 float v = 0.f;
 #pragma unroll
-                for (int e = 0; e < 8; e++) v = fmaf(c_me[kMeWl + e * 15 + q], s.dxa[note * 8 + e], v);
-                v *= leaky_grad_from_out(ae[q]);
-                atomicAdd(&s.dod[o * 8 + q], v);
-                atomicAdd(&s.dod[64 + d * 8 + q], v);
+                for (int e = 0; e < 8; e++) v = fmaf(c_me[kMeWl + e * 15 + q], da[e], v);
+                s.dxp[note * 8 + q] = v * leaky_grad_from_out(ae[q]);
             }
         }
         __syncwarp();
-        for (int i = lane; i < 120; i += 32) a.dod[row * 120 + i] = s.dod[i] * leaky_grad_from_out(s.od[i]);
+        // octave rows sum over the 7 degrees, degree rows over the 8 octaves (note = o * 7 + d)
+        for (int i = lane; i < 120; i += 32) {
+            float v = 0.f;
+            if (i < 64) {
+                const int o = i >> 3, q = i & 7;
+#pragma unroll
+                for (int d = 0; d < 7; d++) v += s.dxp[(o * 7 + d) * 8 + q];
+            } else {
+                const int d = (i - 64) >> 3, q = i & 7;
+#pragma unroll
+                for (int o = 0; o < 8; o++) v += s.dxp[(o * 7 + d) * 8 + q];
+            }
+            a.dod[row * 120 + i] = v * leaky_grad_from_out(s.od[i]);
+        }
     }
     // ---- flush: warp-reduce the register accumulators, add the empty-cell share of the bf branch
     __syncwarp();
@@ -367,7 +364,7 @@ k_me_bwd2(MeArgs2 a) {
             if (Sa[e] != 0.f) atomicAdd(a.gbl + e, Sa[e]);
 #pragma unroll
             for (int q = 0; q < 7; q++) {
-                const float v = Sp[e] * k.bfe[q] + s.g2[e * 7 + q];
+                const float v = Sp[e] * k.bfe[q];
                 if (v != 0.f) atomicAdd(a.gWl + e * 15 + 8 + q, v);
             }
         }
@@ -376,10 +373,81 @@ k_me_bwd2(MeArgs2 a) {
             float dbf = 0.f;
 #pragma unroll
             for (int e = 0; e < 8; e++) dbf = fmaf(c_me[kMeWl + e * 15 + 8 + q], Sp[e], dbf);
-            const float v = dbf * leaky_grad_from_out(k.bfe[q]) + s.g2[56 + q];
+            const float v = dbf * leaky_grad_from_out(k.bfe[q]);
             if (v != 0.f) atomicAdd(a.gbc + q, v);
         }
-        for (int i = 0; i < 35; i++) if (s.g2[63 + i] != 0.f) atomicAdd(a.gWc + i, s.g2[63 + i]);
+    }
+}
+
+// warp per beat row, lane per occupied cell: gradients of linear.weight[:, 8:] (56), channels_linear bias (7) and
+// weight (35) in per-lane registers, reduced once per CTA
+__global__ void __launch_bounds__(256)
+k_me_bwd_cells(MeArgs2 a) {
+    __shared__ float od_s[8][120];
+    __shared__ float red[98];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const MeConsts k = me_consts();
+    const long long BT = (long long)a.B * a.T, rows = (long long)a.N * a.C * BT;
+    float g2[98];                       // [0,56) linear.weight[e][8 + q] at e * 7 + q, [56,63) bc, [63,98) Wc[q][p]
+#pragma unroll
+    for (int i = 0; i < 98; i++) g2[i] = 0.f;
+    if (threadIdx.x < 98) red[threadIdx.x] = 0.f;
+    for (long long row = (long long)blockIdx.x * 8 + warp; row < rows; row += (long long)gridDim.x * 8) {
+        const uint32_t lo = a.off[row], hi = a.off[row + 1];
+        if (lo == hi) continue;
+        const long long nc = row / BT, bt = row - nc * BT;
+        const int n = (int)(nc / a.C), c = (int)(nc - (long long)n * a.C);
+        float wsum = 0.f;
+        for (int j = 0; j < a.C; j++) wsum += sqrtf(1.f + a.ss[n * a.C + j]);
+        const float wc = sqrtf(1.f + a.ss[n * a.C + c]);
+        const float k1 = wc / wsum;
+        const float k2 = (a.stats[n * (a.C + 1) + c] - a.stats[n * (a.C + 1) + a.C]) / (wsum * wc);
+        const long long u = (long long)n * BT + bt;
+        __syncwarp();
+        for (int i = lane; i < 120; i += 32) od_s[warp][i] = a.od[row * 120 + i];
+        __syncwarp();
+        for (uint32_t i = lo + lane; i < hi; i += 32) {
+            const CellRec r = a.recs[i];
+            const int note = (int)(r.cell % 56);
+            float ae[8], xp[8], bf[7], xt[8], dxt[8];
+            me_note(k, od_s[warp], note, ae, xp);
+            me_occupied(k, r.p, xp, bf, xt);
+            const float *d = a.dmelody + u * 4480 + r.cell * 8;
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const float x = leaky(xt[e]);
+                dxt[e] = (k1 * d[e] + k2 * x) * leaky_grad_from_out(x);
+            }
+#pragma unroll
+            for (int q = 0; q < 7; q++) {
+                float dbf = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    g2[e * 7 + q] = fmaf(dxt[e], bf[q], g2[e * 7 + q]);
+                    dbf = fmaf(c_me[kMeWl + e * 15 + 8 + q], dxt[e], dbf);
+                }
+                dbf *= leaky_grad_from_out(bf[q]);
+                g2[56 + q] += dbf;
+#pragma unroll
+                for (int p = 0; p < 5; p++) g2[63 + q * 5 + p] = fmaf(dbf, r.p[p], g2[63 + q * 5 + p]);
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 98; i++) {
+        const float v = warp_sum(g2[i]);
+        if (lane == 0 && v != 0.f) atomicAdd(&red[i], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < 98) {
+        const float v = red[threadIdx.x];
+        const int i = threadIdx.x;
+        if (v != 0.f) {
+            if (i < 56) atomicAdd(a.gWl + (i / 7) * 15 + 8 + (i % 7), v);
+            else if (i < 63) atomicAdd(a.gbc + (i - 56), v);
+            else atomicAdd(a.gWc + (i - 63), v);
+        }
     }
 }
 
