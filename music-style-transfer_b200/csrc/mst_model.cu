@@ -302,8 +302,10 @@ struct Launcher {
     }
     void bcast(BcastArgs &a) {
         if (dry) return;
-        const long long total = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f * a.cols;
-        k_bcast_add<<<grid_for(total), 256, 0, st>>>(a); check();
+        const long long rows = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f;
+        int lpr = 32;
+        while (lpr > 1 && lpr / 2 >= a.cols) lpr /= 2;
+        k_bcast_add<<<grid_for(rows * lpr), 256, 0, st>>>(a, lpr); check();
     }
     void take_last(const float *in, float *out, long long S, int T, int H) { if (dry) return; k_take_last<<<grid_for(S * H), 256, 0, st>>>(in, out, S, T, H); check(); }
     void put_last(const float *src, float *dst, long long S, int T, int H) { if (dry) return; k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }

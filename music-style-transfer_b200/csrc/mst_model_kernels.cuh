@@ -143,24 +143,32 @@ __device__ __forceinline__ long long src_row(const Dims5 &d, int mask, int n, in
     return r;
 }
 
+// `lpr` lanes per row (32, or a smaller power of two for narrow rows): the five coordinates and the source rows are
+// decoded once per row, the columns are a coalesced loop
 __global__ void __launch_bounds__(256)
-k_bcast_add(BcastArgs a) {
+k_bcast_add(BcastArgs a, int lpr) {
     const long long rows = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f;
-    const long long total = rows * a.cols;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
-        const long long row = idx / a.cols;
-        const int j = (int)(idx - row * a.cols);
+    const int sub = threadIdx.x & (lpr - 1);
+    const long long g0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / lpr, n_groups = ((long long)gridDim.x * blockDim.x) / lpr;
+    for (long long row = g0; row < rows; row += n_groups) {
         long long r = row;
         const int f = (int)(r % a.d.f); r /= a.d.f;
         const int t = (int)(r % a.d.t); r /= a.d.t;
         const int b = (int)(r % a.d.b); r /= a.d.b;
         const int c = (int)(r % a.d.c); r /= a.d.c;
         const int n = (int)r;
-        float v = a.bias ? a.bias[j] : 0.f;
+        const float *sp[kMaxSources];
 #pragma unroll
         for (int s = 0; s < kMaxSources; s++)
-            if (s < a.n_src) v += a.src[s][src_row(a.d, a.mask[s], n, c, b, t, f) * a.cols + j];
-        a.Y[idx] = a.act ? leaky(v) : v;
+            sp[s] = s < a.n_src ? a.src[s] + src_row(a.d, a.mask[s], n, c, b, t, f) * a.cols : nullptr;
+        float *y = a.Y + row * a.cols;
+        for (int j = sub; j < a.cols; j += lpr) {
+            float v = a.bias ? a.bias[j] : 0.f;
+#pragma unroll
+            for (int s = 0; s < kMaxSources; s++)
+                if (s < a.n_src) v += sp[s][j];
+            y[j] = a.act ? leaky(v) : v;
+        }
     }
 }
 

@@ -84,10 +84,16 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
                 for (; k < H; k++) a0 = fmaf(wp[k * H4], h_s[k], a0);
                 acc[0] = (a0 + a1) + (a2 + a3);
             } else {
+                // G == kLstmG sequences: h is kept k-major ([k][G]) so one step reads the 8 states with two 16-byte loads
+#pragma unroll 4
                 for (int k = 0; k < H; k++) {
                     const float wv = w[k * H4 + j];
-#pragma unroll
-                    for (int g = 0; g < kLstmG; g++) if (g < ng) acc[g] = fmaf(wv, h_s[g * H + k], acc[g]);
+                    const float4 h0 = *reinterpret_cast<const float4 *>(h_s + k * kLstmG);
+                    const float4 h1 = *reinterpret_cast<const float4 *>(h_s + k * kLstmG + 4);
+                    acc[0] = fmaf(wv, h0.x, acc[0]); acc[1] = fmaf(wv, h0.y, acc[1]);
+                    acc[2] = fmaf(wv, h0.z, acc[2]); acc[3] = fmaf(wv, h0.w, acc[3]);
+                    acc[4] = fmaf(wv, h1.x, acc[4]); acc[5] = fmaf(wv, h1.y, acc[5]);
+                    acc[6] = fmaf(wv, h1.z, acc[6]); acc[7] = fmaf(wv, h1.w, acc[7]);
                 }
             }
             const bool is_tanh = (j >= 2 * H) && (j < 3 * H);
@@ -103,11 +109,12 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
             const int g = i / H, k = i - g * H;
             const float *gs = g_s + g * H4;
             const long long row = (long long)(s0 + g) * a.T + t;
-            a.hprev[row * H + k] = h_s[i];
+            const int hi = G == 1 ? k : k * kLstmG + g;          // k-major state when several sequences share the CTA
+            a.hprev[row * H + k] = h_s[hi];
             const float c = gs[H + k] * c_s[i] + gs[k] * gs[2 * H + k];
             const float h = gs[3 * H + k] * tanhf(c);
             c_s[i] = c;
-            h_s[i] = h;
+            h_s[hi] = h;
             a.cells[row * H + k] = c;
             a.out[row * a.out_ld + a.out_off + k] = h;
         }
@@ -152,15 +159,49 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
             dc_s[i] = dc * gf;
             float *dgo = a.dgates + row * H4;
             dgo[k] = d_i; dgo[H + k] = d_f; dgo[2 * H + k] = d_g; dgo[3 * H + k] = d_o;
-            float *ds = dg_s + g * H4;
-            ds[k] = d_i; ds[H + k] = d_f; ds[2 * H + k] = d_g; ds[3 * H + k] = d_o;
+            if (G == 1) {
+                float *ds = dg_s;
+                ds[k] = d_i; ds[H + k] = d_f; ds[2 * H + k] = d_g; ds[3 * H + k] = d_o;
+            } else {                                              // r-major: [4H][G]
+                dg_s[k * kLstmG + g] = d_i; dg_s[(H + k) * kLstmG + g] = d_f;
+                dg_s[(2 * H + k) * kLstmG + g] = d_g; dg_s[(3 * H + k) * kLstmG + g] = d_o;
+            }
         }
         __syncthreads();
         // dh_{step-1} = W_hh^T · dgates.  With few sequences per CTA the 4H rows are split over `parts` thread groups
         // (partials through shared memory) and every thread keeps 16 loads in flight.
         const int items = ng * H;
         const int parts = min(4, (int)blockDim.x / items);
-        if (parts >= 2) {
+        if (G > 1) {
+            // thread (part, k): the 8 sequences' dh[k] over a quarter of the 4H rows, 16-byte loads of the r-major dgates
+            const int qparts = min(4, (int)blockDim.x / H);
+            const int part = j / H, k = j - part * H;
+            if (part < qparts) {
+                const int r_lo = (int)((long long)H4 * part / qparts), r_hi = (int)((long long)H4 * (part + 1) / qparts);
+                float acc[kLstmG];
+#pragma unroll
+                for (int g = 0; g < kLstmG; g++) acc[g] = 0.f;
+#pragma unroll 4
+                for (int r = r_lo; r < r_hi; r++) {
+                    const float wv = w[r * H + k];
+                    const float4 d0 = *reinterpret_cast<const float4 *>(dg_s + r * kLstmG);
+                    const float4 d1 = *reinterpret_cast<const float4 *>(dg_s + r * kLstmG + 4);
+                    acc[0] = fmaf(wv, d0.x, acc[0]); acc[1] = fmaf(wv, d0.y, acc[1]);
+                    acc[2] = fmaf(wv, d0.z, acc[2]); acc[3] = fmaf(wv, d0.w, acc[3]);
+                    acc[4] = fmaf(wv, d1.x, acc[4]); acc[5] = fmaf(wv, d1.y, acc[5]);
+                    acc[6] = fmaf(wv, d1.z, acc[6]); acc[7] = fmaf(wv, d1.w, acc[7]);
+                }
+#pragma unroll
+                for (int g = 0; g < kLstmG; g++) part_s[(part * kLstmG + g) * H + k] = acc[g];
+            }
+            __syncthreads();
+            for (int i = j; i < items; i += blockDim.x) {
+                const int g = i / H, k = i - g * H;
+                float v = 0.f;
+                for (int q = 0; q < qparts; q++) v += part_s[(q * kLstmG + g) * H + k];
+                dh_s[i] = v;
+            }
+        } else if (parts >= 2) {
             const int part = j / items, i = j - part * items;
             if (part < parts) {
                 const int g = i / H, k = i - g * H;
