@@ -12,6 +12,7 @@
 
 #include "mst_model_sparse.cuh"
 #include "mst_model_gemm_tc.cuh"
+#include "mst_model_lstm_cluster.cuh"
 #include "mst_model_tails_bwd.cuh"
 #include "mst_model_me.cuh"
 
@@ -319,6 +320,20 @@ struct Launcher {
         for (int i = 0; i < n_jobs; i++) if (jobs[i].S < 148 * 2) G = 1;
         const int H = jobs[0].H;
         const int w_smem = ((size_t)H * 4 * H * sizeof(float) <= 96 * 1024) ? 1 : 0;
+        // wide state, few sequences: 4-CTA cluster with W_hh resident in (distributed) shared memory
+        if (!w_smem && n_jobs == 1 && H % kClSize == 0 && H * kClFwdParts <= 1024 && jobs[0].S <= 148 &&
+            std::max(lstm_cl_fwd_smem(H), lstm_cl_bwd_smem(H)) <= 227 * 1024) {
+            const int grid = (jobs[0].S + kClG - 1) / kClG * kClSize;
+            if (backward) {
+                cudaFuncSetAttribute(k_lstm_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_bwd_smem(H));
+                k_lstm_bwd_cl<<<grid, H / kClSize * kClBwdParts, lstm_cl_bwd_smem(H), st>>>(jobs[0]);
+            } else {
+                cudaFuncSetAttribute(k_lstm_fwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_fwd_smem(H));
+                k_lstm_fwd_cl<<<grid, H * kClFwdParts, lstm_cl_fwd_smem(H), st>>>(jobs[0]);
+            }
+            check();
+            return;
+        }
         for (int i = 0; i < n_jobs; i++) {
             jobs[i].G = G; jobs[i].w_smem = w_smem;
             pack.j[i] = jobs[i];

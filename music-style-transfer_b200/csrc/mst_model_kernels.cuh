@@ -150,13 +150,20 @@ k_bcast_add(BcastArgs a, int lpr) {
     const long long rows = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f;
     const int sub = threadIdx.x & (lpr - 1);
     const long long g0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / lpr, n_groups = ((long long)gridDim.x * blockDim.x) / lpr;
-    for (long long row = g0; row < rows; row += n_groups) {
-        long long r = row;
-        const int f = (int)(r % a.d.f); r /= a.d.f;
-        const int t = (int)(r % a.d.t); r /= a.d.t;
-        const int b = (int)(r % a.d.b); r /= a.d.b;
-        const int c = (int)(r % a.d.c); r /= a.d.c;
-        const int n = (int)r;
+    // each lane group walks a contiguous run of rows: one division chain at the start, then carries
+    const long long per = (rows + n_groups - 1) / n_groups;
+    const long long r_lo = g0 * per, r_hi = min(rows, r_lo + per);
+    if (r_lo >= r_hi) return;
+    int f, t, b, c, n;
+    {
+        long long r = r_lo;
+        f = (int)(r % a.d.f); r /= a.d.f;
+        t = (int)(r % a.d.t); r /= a.d.t;
+        b = (int)(r % a.d.b); r /= a.d.b;
+        c = (int)(r % a.d.c); r /= a.d.c;
+        n = (int)r;
+    }
+    for (long long row = r_lo; row < r_hi; row++) {
         const float *sp[kMaxSources];
 #pragma unroll
         for (int s = 0; s < kMaxSources; s++)
@@ -169,6 +176,7 @@ k_bcast_add(BcastArgs a, int lpr) {
                 if (s < a.n_src) v += sp[s][j];
             y[j] = a.act ? leaky(v) : v;
         }
+        if (++f == a.d.f) { f = 0; if (++t == a.d.t) { t = 0; if (++b == a.d.b) { b = 0; if (++c == a.d.c) { c = 0; n++; } } } }
     }
 }
 
