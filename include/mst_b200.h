@@ -369,7 +369,8 @@ int mst_adam_step(float *d_params, float *d_grads, float *d_m, float *d_v, long 
  * explicit element strides (A(i,k) = A[i*a_si + k*a_sk], B(k,j) = B[k*b_sk + j*b_sj], C row stride c_si).  This is the
  * nn.Linear / Distributed(Linear) forward (model.py:23-33), input-gradient and weight-gradient product.
  * act: 0 none, 1 LeakyReLU(.01).  accumulate: 0 store, 1 +=, 2 atomic +=.  split_k > 1 splits K over CTAs (atomic).
- * kernel: 0 = the library's own choice, 1 = fp32 SIMT tiles, 2 = tensor cores (mma.sync TF32, 3-term split: fp32-accurate). */
+ * kernel: 0 = the library's own choice, 1 = fp32 SIMT tiles, 2 = mma.sync TF32 (3-term split: fp32-accurate),
+ * 3 = tcgen05.mma kind::tf32 with the accumulator in TMEM (same 3-term split). */
 int mst_model_gemm(const float *d_A, long long a_si, long long a_sk, const float *d_B, long long b_sk, long long b_sj,
                    float *d_C, long long c_si, int M, int N, int K, const float *d_bias, int act, int accumulate,
                    int split_k, int kernel, void *stream);

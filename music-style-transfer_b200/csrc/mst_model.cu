@@ -12,6 +12,7 @@
 
 #include "mst_model_sparse.cuh"
 #include "mst_model_gemm_tc.cuh"
+#include "mst_model_gemm_t5.cuh"
 #include "mst_model_lstm_cluster.cuh"
 #include "mst_model_tails_bwd.cuh"
 #include "mst_model_me.cuh"
@@ -257,13 +258,22 @@ struct Launcher {
         else if (bk) k_gemm_tc<BN, false, true><<<grid, kTcThreads, 0, st>>>(g);
         else k_gemm_tc<BN, false, false><<<grid, kTcThreads, 0, st>>>(g);
     }
+    template <int BN>
+    void gemm_t5(const GemmArgs &g, int split_k) {
+        dim3 grid((g.N + BN - 1) / BN, (g.M + kT5BM - 1) / kT5BM, split_k);
+        static bool attr_set = false;
+        if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN>()); attr_set = true; }
+        k_gemm_t5<BN><<<grid, kT5Threads, t5_smem_bytes<BN>(), st>>>(g);
+    }
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
               int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int kernel = 0) {
         if (dry || M <= 0 || N <= 0 || K <= 0) return;
         GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
         if (split_k > 1) g.accumulate = 2;
-        if (kernel == 2 || (kernel == 0 && use_tc(M, N, K))) {
+        if (kernel == 3 || (kernel == 0 && use_tc(M, N, K) && K >= 24)) {
+            if (N <= 16) gemm_t5<16>(g, split_k); else if (N <= 32) gemm_t5<32>(g, split_k); else gemm_t5<64>(g, split_k);
+        } else if (kernel == 2 || (kernel == 0 && use_tc(M, N, K))) {
             if (N <= 32) gemm_tc<32>(g, split_k); else gemm_tc<64>(g, split_k);
         } else {
             dim3 grid((N + kGemmTile - 1) / kGemmTile, (M + kGemmTile - 1) / kGemmTile, split_k);
@@ -284,7 +294,7 @@ struct Launcher {
     void linear_dw(const float *dY, long long ldy, const float *X, long long ldx, float *dW, long long ldw, int M, int N, int K) {
         // few output tiles, long reduction: split the rows over enough CTAs to fill the 148 SMs twice
         const bool tc = use_tc(N, K, M);
-        const int tm = tc ? kTcBM : kGemmTile, tn = tc ? (K <= 32 ? 32 : 64) : kGemmTile;
+        const int tm = tc ? kTcBM : kGemmTile, tn = tc ? (K <= 16 ? 16 : (K <= 32 ? 32 : 64)) : kGemmTile;
         const int tiles = ((N + tm - 1) / tm) * ((K + tn - 1) / tn);
         const int split = std::max(1, std::min(std::min(512, M / 128), (2 * 148 + tiles - 1) / tiles));
         gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
@@ -917,7 +927,7 @@ extern "C" int mst_adam_step(float *d_params, float *d_grads, float *d_m, float 
 extern "C" int mst_model_gemm(const float *d_A, long long a_si, long long a_sk, const float *d_B, long long b_sk, long long b_sj,
                               float *d_C, long long c_si, int M, int N, int K, const float *d_bias, int act, int accumulate,
                               int split_k, int kernel, void *stream) {
-    if (!d_A || !d_B || !d_C || M <= 0 || N <= 0 || K <= 0 || split_k < 1 || kernel < 0 || kernel > 2) {
+    if (!d_A || !d_B || !d_C || M <= 0 || N <= 0 || K <= 0 || split_k < 1 || kernel < 0 || kernel > 3) {
         mst_set_error("mst_model_gemm: bad argument");
         return MST_E_INVALID;
     }

@@ -1,0 +1,269 @@
+// mst_model_gemm_t5.cuh — the row-space GEMMs on the 5th-generation tensor cores (tcgen05.mma, accumulator in TMEM).
+//
+// Same contract as k_gemm / k_gemm_tc (GemmArgs: explicit strides, bias / leaky epilogue, store / += / atomic split-K).
+// fp32 accuracy is kept with the 3-term TF32 split  a.b ~ a_lo.b_hi + a_hi.b_lo + a_hi.b_hi  (a_hi = tf32(a), a_lo =
+// tf32(a - a_hi)); the legacy mma.sync path tops out near 120 TFLOP/s of TF32 on this part (measured, tools/mma_probe.py),
+// which with three products per term made k_gemm_tc MMA-bound at ~2 TB/s of operand traffic.  tcgen05 removes that
+// bound: the kernel is a streaming producer (global -> split -> shared) in front of one MMA-issuing thread.
+//
+//   * CTA tile 128 x BN (BN = 16 / 32 / 64), K slab 32, two shared-memory stages; each stage holds A_hi, A_lo (128 x 32)
+//     and B_hi, B_lo (BN x 32) in the canonical K-major no-swizzle UMMA layout: 8-row x 16-byte core matrices, the 8
+//     K-chunks of a row group 144 B apart (LBO), row groups 1152 B apart (SBO);
+//   * all 256 threads load the next slab into registers (any operand strides; the lane order follows the operand's
+//     contiguous direction, 16 / 8-byte loads when aligned), split it, store 16-byte chunks (conflict-free for both
+//     orders thanks to the 144-byte LBO), fence.proxy.async, barrier;
+//     thread 0 then issues 4 k-steps x 3 products of tcgen05.mma.kind::tf32 (M = 128, N = BN, K = 8) and commits to the
+//     stage's mbarrier, which gates the reuse of that stage two slabs later;
+//   * epilogue: tcgen05.ld (32 lanes x 32 bit, warp w reads TMEM lanes 32 (w % 4) ...) -> shared tile -> coalesced
+//     stores with bias / leaky / accumulate (16-byte where the destination allows).
+#pragma once
+#include "mst_model_kernels.cuh"
+
+namespace mstm {
+
+constexpr int kT5BM = 128, kT5BK = 32, kT5Threads = 256;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && ++spins > (1u << 26)) __trap();      // a lost arrival must fail loudly, not hang the device
+    }
+}
+// K-major, no swizzle: start address, LBO (between the two 16-byte K chunks of one MMA), SBO (between 8-row groups)
+__device__ __forceinline__ uint64_t t5_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+           (1ull << 46);                                   // descriptor version 1 (sm_100), layout type 0 = no swizzle
+}
+__device__ __forceinline__ void t5_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void t5_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void t5_split4(const float *v, float4 &hi, float4 &lo) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h[i]) : "f"(v[i]));
+        const float r = v[i] - __uint_as_float(h[i]);
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l[i]) : "f"(r));
+    }
+    hi = make_float4(__uint_as_float(h[0]), __uint_as_float(h[1]), __uint_as_float(h[2]), __uint_as_float(h[3]));
+    lo = make_float4(__uint_as_float(l[0]), __uint_as_float(l[1]), __uint_as_float(l[2]), __uint_as_float(l[3]));
+}
+
+// shared layout of one (rows x 32) operand tile: 16-byte chunk (row r, k-chunk kc) at (r / 8) * SBO + kc * LBO + (r % 8) * 16.
+// LBO = 144 (not 128) so that BOTH loader mappings store without bank conflicts: 8 lanes on one row (kc = 0..7) hit
+// kc * 144 = kc * 16 mod 128, 8 lanes on consecutive rows hit r * 16.
+constexpr uint32_t kT5LBO = 144, kT5SBO = 8 * kT5LBO;
+__host__ __device__ constexpr int t5_tile_bytes(int rows) { return rows / 8 * (int)kT5SBO; }
+
+// 4 consecutive k of one row -> registers (vector load when the address allows, zero fill outside [.., k_hi))
+__device__ __forceinline__ void t5_load4(const float *p, long long sk, int k, int k_hi, bool row_ok, int vec, float *v) {
+    if (!row_ok || k >= k_hi) { v[0] = v[1] = v[2] = v[3] = 0.f; return; }
+    if (k + 3 < k_hi && vec == 4) {
+        const float4 x = __ldg(reinterpret_cast<const float4 *>(p));
+        v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+    } else if (k + 3 < k_hi && vec == 2) {
+        const float2 x = __ldg(reinterpret_cast<const float2 *>(p)), y = __ldg(reinterpret_cast<const float2 *>(p + 2));
+        v[0] = x.x; v[1] = x.y; v[2] = y.x; v[3] = y.y;
+    } else {
+#pragma unroll
+        for (int e = 0; e < 4; e++) v[e] = k + e < k_hi ? __ldg(p + e * sk) : 0.f;
+    }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kT5Threads, 2)
+k_gemm_t5(GemmArgs g) {
+    constexpr int BM = kT5BM, KT = kT5BK;
+    constexpr int A_BYTES = t5_tile_bytes(BM), B_BYTES = t5_tile_bytes(BN);   // one hi or lo tile
+    constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+    constexpr int A_CH = BM * 8 / kT5Threads;                                  // 16-byte chunks per thread: 4
+    constexpr int B_CH = (BN * 8 + kT5Threads - 1) / kT5Threads;               // 2 / 1 / 1 (BN = 16: threads < 128)
+    constexpr int TM_COLS = BN < 32 ? 32 : BN;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bars[3];
+    __shared__ uint32_t tmem_base_s;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int i0 = blockIdx.y * BM, j0 = blockIdx.x * BN;
+    const int kz = gridDim.z;
+    const int k_per = ((g.K + kz - 1) / kz + KT - 1) / KT * KT;
+    const int k_lo = blockIdx.z * k_per, k_hi = min(g.K, k_lo + k_per);
+    if (k_lo >= k_hi) return;
+    const int n_slabs = (k_hi - k_lo + KT - 1) / KT;
+
+    const uint32_t bar0 = smem_u32(&bars[0]);
+    if (tid == 0) {
+        mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_init(bar0 + 16, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "n"(TM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_base_s;
+
+    // ---- loader roles.  A k-contiguous operand is walked chunk-fastest (8 lanes = one row's 128 bytes), a row-contiguous
+    // one row-fastest (32 lanes = 32 consecutive rows of one k); either way thread-chunk i is (row, kc) below.
+    const bool a_kc = g.a_sk == 1, b_kc = g.b_sk == 1;
+    const int a_vec = !a_kc ? 1 : (((g.a_si & 3) == 0 && (reinterpret_cast<uintptr_t>(g.A) & 15) == 0) ? 4
+                                   : (((g.a_si & 1) == 0 && (reinterpret_cast<uintptr_t>(g.A) & 7) == 0) ? 2 : 1));
+    const int b_vec = !b_kc ? 1 : (((g.b_sj & 3) == 0 && (reinterpret_cast<uintptr_t>(g.B) & 15) == 0) ? 4
+                                   : (((g.b_sj & 1) == 0 && (reinterpret_cast<uintptr_t>(g.B) & 7) == 0) ? 2 : 1));
+    int a_row[A_CH], a_kc4[A_CH], b_row[B_CH], b_kc4[B_CH];
+#pragma unroll
+    for (int i = 0; i < A_CH; i++) {
+        const int c = tid + i * kT5Threads;
+        if (a_kc) { a_kc4[i] = c & 7; a_row[i] = c >> 3; } else { a_row[i] = c & (BM - 1); a_kc4[i] = c / BM; }
+    }
+#pragma unroll
+    for (int i = 0; i < B_CH; i++) {
+        const int c = tid + i * kT5Threads;
+        if (b_kc) { b_kc4[i] = c & 7; b_row[i] = c >> 3; } else { b_row[i] = c % BN; b_kc4[i] = c / BN; }
+    }
+    float ra[A_CH][4], rb[B_CH][4];
+    auto load_slab = [&](int s) {
+        const int kb = k_lo + s * KT;
+#pragma unroll
+        for (int i = 0; i < A_CH; i++) {
+            const int gi = i0 + a_row[i], k = kb + a_kc4[i] * 4;
+            t5_load4(g.A + (long long)gi * g.a_si + (long long)k * g.a_sk, g.a_sk, k, k_hi, gi < g.M, a_vec, ra[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < B_CH; i++) {
+            const int gj = j0 + b_row[i], k = kb + b_kc4[i] * 4;
+            const bool ok = tid + i * kT5Threads < BN * 8 && gj < g.N;
+            t5_load4(g.B + (long long)k * g.b_sk + (long long)gj * g.b_sj, g.b_sk, k, k_hi, ok, b_vec, rb[i]);
+        }
+    };
+    auto store_slab = [&](int stage) {
+        unsigned char *st = smem + stage * STAGE_BYTES;
+#pragma unroll
+        for (int i = 0; i < A_CH; i++) {
+            float4 hi, lo;
+            t5_split4(ra[i], hi, lo);
+            const uint32_t off = (uint32_t)(a_row[i] >> 3) * kT5SBO + (uint32_t)a_kc4[i] * kT5LBO + (uint32_t)(a_row[i] & 7) * 16;
+            *reinterpret_cast<float4 *>(st + off) = hi;
+            *reinterpret_cast<float4 *>(st + A_BYTES + off) = lo;
+        }
+#pragma unroll
+        for (int i = 0; i < B_CH; i++) {
+            if (tid + i * kT5Threads < BN * 8) {
+                float4 hi, lo;
+                t5_split4(rb[i], hi, lo);
+                const uint32_t off = (uint32_t)(b_row[i] >> 3) * kT5SBO + (uint32_t)b_kc4[i] * kT5LBO + (uint32_t)(b_row[i] & 7) * 16;
+                *reinterpret_cast<float4 *>(st + 2 * A_BYTES + off) = hi;
+                *reinterpret_cast<float4 *>(st + 2 * A_BYTES + B_BYTES + off) = lo;
+            }
+        }
+    };
+    // instruction descriptor: D = f32, A = B = tf32, both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+    constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    const uint32_t smem_base = smem_u32(smem);
+
+    load_slab(0);
+    for (int s = 0; s < n_slabs; s++) {
+        const int stage = s & 1;
+        if (s >= 2) mbar_wait(bar0 + 8 * stage, (uint32_t)(((s >> 1) - 1) & 1));     // the MMAs of slab s - 2 have read this stage
+        store_slab(stage);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (s + 1 < n_slabs) load_slab(s + 1);
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + 2 * A_BYTES;
+#pragma unroll
+            for (int ks = 0; ks < KT / 8; ks++) {
+                const uint32_t ko = ks * 2 * kT5LBO;
+                const uint64_t a_hi = t5_desc(sa + ko, kT5LBO, kT5SBO), a_lo = t5_desc(sa + A_BYTES + ko, kT5LBO, kT5SBO);
+                const uint64_t b_hi = t5_desc(sb + ko, kT5LBO, kT5SBO), b_lo = t5_desc(sb + B_BYTES + ko, kT5LBO, kT5SBO);
+                t5_mma(tmem, a_lo, b_hi, idesc, (s | ks) != 0);
+                t5_mma(tmem, a_hi, b_lo, idesc, 1);
+                t5_mma(tmem, a_hi, b_hi, idesc, 1);
+            }
+            t5_commit(bar0 + 8 * stage);
+            if (s + 1 == n_slabs) t5_commit(bar0 + 16);
+        }
+    }
+    mbar_wait(bar0 + 16, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    // ---- epilogue: TMEM -> registers (warp w reads lanes 32 (w % 4) .. + 31 = tile rows; warps 0-3 / 4-7 split the
+    // columns) -> shared tile [128][BN + 4] -> coalesced global stores with bias / leaky / accumulate
+    constexpr int LD = BN + 4;
+    float *tile = reinterpret_cast<float *>(smem);            // the operand stages are idle now (all MMAs completed)
+    constexpr int CW = BN >= 32 ? BN / 2 : BN;                // columns per warp (BN = 16: warps 4-7 idle)
+    const int col0 = (BN >= 32 && warp >= 4) ? CW : 0;
+    if (BN >= 32 || warp < 4) {
+        const int r = (warp & 3) * 32 + lane;
+#pragma unroll
+        for (int cb = 0; cb < CW; cb += 8) {
+            uint32_t v[8];
+            const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(col0 + cb);
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            float4 *d = reinterpret_cast<float4 *>(tile + r * LD + col0 + cb);
+            d[0] = make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3]));
+            d[1] = make_float4(__uint_as_float(v[4]), __uint_as_float(v[5]), __uint_as_float(v[6]), __uint_as_float(v[7]));
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TM_COLS) : "memory");
+    const bool vec_ok = g.accumulate != 2 && (g.c_si & 3) == 0 && ((reinterpret_cast<uintptr_t>(g.C) & 15) == 0);
+    if (vec_ok) {
+        for (int c = tid; c < BM * (BN / 4); c += kT5Threads) {
+            const int r = c / (BN / 4), c4 = (c - r * (BN / 4)) * 4;
+            const int gi = i0 + r, gj = j0 + c4;
+            if (gi >= g.M || gj >= g.N) continue;
+            float4 x = *reinterpret_cast<const float4 *>(tile + r * LD + c4);
+            float o[4] = {x.x, x.y, x.z, x.w};
+            float *dst = g.C + (long long)gi * g.c_si + gj;
+            if (gj + 3 < g.N) {
+                if (g.bias && blockIdx.z == 0) { o[0] += g.bias[gj]; o[1] += g.bias[gj + 1]; o[2] += g.bias[gj + 2]; o[3] += g.bias[gj + 3]; }
+                if (g.act == 1) { o[0] = leaky(o[0]); o[1] = leaky(o[1]); o[2] = leaky(o[2]); o[3] = leaky(o[3]); }
+                float4 *d4 = reinterpret_cast<float4 *>(dst);
+                if (g.accumulate == 1) { const float4 p = *d4; o[0] += p.x; o[1] += p.y; o[2] += p.z; o[3] += p.w; }
+                *d4 = make_float4(o[0], o[1], o[2], o[3]);
+            } else {
+                for (int e = 0; e < 4 && gj + e < g.N; e++) {
+                    float v = o[e];
+                    if (g.bias && blockIdx.z == 0) v += g.bias[gj + e];
+                    if (g.act == 1) v = leaky(v);
+                    dst[e] = g.accumulate == 1 ? dst[e] + v : v;
+                }
+            }
+        }
+    } else {
+        for (int c = tid; c < BM * BN; c += kT5Threads) {
+            const int r = c / BN, cc = c - r * BN;
+            const int gi = i0 + r, gj = j0 + cc;
+            if (gi >= g.M || gj >= g.N) continue;
+            float v = tile[r * LD + cc];
+            if (g.bias && blockIdx.z == 0) v += g.bias[gj];
+            if (g.act == 1) v = leaky(v);
+            float *dst = g.C + (long long)gi * g.c_si + gj;
+            if (g.accumulate == 0) *dst = v;
+            else if (g.accumulate == 1) *dst += v;
+            else atomicAdd(dst, v);
+        }
+    }
+}
+
+template <int BN> constexpr size_t t5_smem_bytes() { return 2 * (2 * t5_tile_bytes(kT5BM) + 2 * t5_tile_bytes(BN)); }
+
+}  // namespace mstm

@@ -30,7 +30,7 @@ CASES = [  # (M, N, K, layout, split_k, bias, act, accumulate)
 ]
 
 
-@pytest.mark.parametrize('kernel', [1, 2])
+@pytest.mark.parametrize('kernel', [1, 2, 3])
 @pytest.mark.parametrize('case', CASES)
 def test_gemm_matches_float64(torch, case, kernel):
     from mst_native import model as mm
@@ -54,7 +54,7 @@ def test_gemm_matches_float64(torch, case, kernel):
         At, W = r(K, M + pad), r(N, K + pad)
         A, a_si, a_sk, B, b_sk, b_sj = At, 1, M + pad, W, 1, K + pad
         A64, B64 = At[:, :M].double().t(), W[:, :K].double().t()
-    bias = r(N) if use_bias else None
+    bias = r(N + 1)[1:] if use_bias else None           # parameters sit at arbitrary float offsets of the flat buffer
     C = r(M, N + pad)
     C0 = C.clone()
     mm.gemm(A, a_si, a_sk, B, b_sk, b_sj, C, N + pad, M, N, K, bias=bias, act=act, accumulate=accumulate, split_k=split,
