@@ -339,7 +339,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--batch', type=int, default=512, help='songs per step per GPU')
     ap.add_argument('--pool', type=int, default=1024, help='distinct songs generated per GPU')
-    ap.add_argument('--train-batch', type=int, default=16, help='training samples per step per GPU')
+    ap.add_argument('--train-batch', type=int, default=64, help='training samples per step per GPU')
     ap.add_argument('--train-steps', type=int, default=0, help='timed training steps (default: min(steps, 10))')
     ap.add_argument('--no-train', action='store_true', help='skip the training leg')
     args = ap.parse_args()
@@ -445,47 +445,76 @@ def main():
                      'whole_step_achieved_GBps': (g_bytes + ev_bytes) / (elapsed_s / args.steps) / 1e9},
     }
 
-    # ---- e2e: host buffers through the C ABI (H2D of events + song table, kernels, D2H of the infos)
+    # ---- e2e: host buffers through the C ABI (H2D of events + song table, kernels, D2H of the infos), every step.
+    # Two slots (stream + workspace + arena + info buffer) alternate, so the H2D of batch i + 1 overlaps the kernels of
+    # batch i: the same prefetch the reference does with a thread (utils/parallel.py:34-39).  All copies are timed.
     h_events = [torch.from_numpy(h[0].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
     h_songs = [torch.from_numpy(h[1].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
-    h_info = torch.empty(args.batch * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     n_ev = [len(h[0]) for h in host_batches]
     wsb = max(L.mst_encode_host_workspace_bytes(n, args.batch, arena.numel()) for n in n_ev)
     for b in batches:
-        b._ws = None   # release the device-path workspaces before allocating the host-path one
-    ws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
-    stream = torch.cuda.current_stream().cuda_stream
+        b._ws = None   # release the device-path workspaces before allocating the host-path ones
+    n_slots = 2
+    slots = []
+    for k in range(n_slots):
+        slots.append({'stream': torch.cuda.Stream(),
+                      'ws': torch.empty(wsb, dtype=torch.uint8, device='cuda'),
+                      'arena': arena if k == 0 else torch.empty_like(arena),
+                      'info': torch.empty(args.batch * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory()})
+    e2e_bars = [0]
+
+    def e2e_drain(sl):
+        """Wait for the slot's batch and consume its infos (what a caller does before handing the grids on)."""
+        sl['stream'].synchronize()
+        if sl.get('busy'):
+            info = sl['info'].numpy().view(abi.SONG_INFO_DTYPE)
+            ok = info['status'] == 0
+            e2e_bars[0] += int(info['n_bars_out'][ok].sum())
+            sl['busy'] = False
 
     def e2e_step(i):
         j = i % n_batches
-        lib.check(L.mst_encode_batch_host(
+        sl = slots[i % n_slots]
+        e2e_drain(sl)
+        lib.check(L.mst_encode_batch_host_async(
             h_events[j].data_ptr(), n_ev[j], h_songs[j].data_ptr(), args.batch, filt.reshape(1).ctypes.data,
-            h_info.data_ptr(), arena.data_ptr(), arena.numel(), None, ws.data_ptr(), wsb, stream))
+            sl['info'].data_ptr(), sl['arena'].data_ptr(), sl['arena'].numel(), sl['ws'].data_ptr(), wsb,
+            sl['stream'].cuda_stream))
+        sl['busy'] = True
 
     for i in range(2):
         e2e_step(i)
+    for sl in slots:
+        e2e_drain(sl)
+    e2e_bars[0] = 0
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         e2e_step(i)
+    for sl in slots:
+        e2e_drain(sl)
     torch.cuda.synchronize()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
     barrier()
     t_load1 = time.time()
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = float(total_bars.item()) / float(e2e_s.item())
+    e2e_total = torch.tensor([float(e2e_bars[0])], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(e2e_total, op=dist.ReduceOp.SUM)
+    e2e_value = float(e2e_total.item()) / float(e2e_s.item())
     e2e = {'value': e2e_value, 'unit': UNIT,
            'h2d_bytes_per_step': int(statistics.mean(n_ev) * 16 + args.batch * 16),
            'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
-           'note': 'grids stay in HBM for the training consumer (device tensors, SURVEY.md 8(b)); '
-                   'infos are read back every step'}
+           'note': 'mst_encode_batch_host_async on two alternating slots (H2D of batch i+1 overlaps the kernels of '
+                   'batch i); grids stay in HBM for the training consumer (SURVEY.md 8(b)); infos are read back and '
+                   'consumed every step'}
     # ---- decode leg over the grids of batch 0 (round trip of the encoder's output)
     decode = run_decode(args, world, rank, torch, dist, L, lib, abi, batches[0], filt, arena)
     # ---- training leg (configs[3]); frees the encode buffers first
     training = None
     if not args.no_train:
-        del arena, ws, batches, h_events, h_songs
+        del arena, slots, batches, h_events, h_songs
         torch.cuda.empty_cache()
         training = run_training(args, world, rank, torch, dist)
         t_load1 = time.time()

@@ -190,6 +190,19 @@ int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events_total,
                           void *d_workspace, size_t workspace_bytes,
                           void *stream);
 
+/* The same without the final synchronisation (grids stay in d_arena): copies and kernels are only ENQUEUED on `stream`,
+ * so a caller that alternates two streams / workspaces / arenas overlaps the H2D of batch i + 1 with the kernels of
+ * batch i (what the prefetch thread of the reference, utils/parallel.py:34-39, does for its Python encoder).
+ * h_events / h_songs / h_info must be page-locked and stay valid until the stream has drained; h_info is only
+ * readable after that. */
+int mst_encode_batch_host_async(const MstEvent *h_events, uint64_t n_events_total,
+                                const MstSongIn *h_songs, uint32_t n_songs,
+                                const MstFilter *h_filter,
+                                MstSongInfo *h_info,
+                                float *d_arena, uint64_t arena_floats,
+                                void *d_workspace, size_t workspace_bytes,
+                                void *stream);
+
 
 /* ---------------------------------------------------------------- decode (grids -> MIDI events) */
 /* Replaces hard_output (style/model.py:818-832), ChannelConverter.vchannel2channel

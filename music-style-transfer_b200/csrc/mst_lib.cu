@@ -30,11 +30,11 @@ extern "C" size_t mst_encode_host_workspace_bytes(uint64_t n_events_total, uint3
            mst_align_up((size_t)(n_songs ? n_songs : 1) * sizeof(MstSongInfo), 256);
 }
 
-extern "C" int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events_total,
-                                     const MstSongIn *h_songs, uint32_t n_songs,
-                                     const MstFilter *h_filter, MstSongInfo *h_info,
-                                     float *d_arena, uint64_t arena_floats, float *h_arena,
-                                     void *d_workspace, size_t workspace_bytes, void *stream_) {
+extern "C" int mst_encode_batch_host_async(const MstEvent *h_events, uint64_t n_events_total,
+                                           const MstSongIn *h_songs, uint32_t n_songs,
+                                           const MstFilter *h_filter, MstSongInfo *h_info,
+                                           float *d_arena, uint64_t arena_floats,
+                                           void *d_workspace, size_t workspace_bytes, void *stream_) {
     if (mst_device_count() == 0) { mst_set_error("no CUDA device: libmst_b200 has no CPU fallback"); return MST_E_NO_DEVICE; }
     if (!h_songs || !h_info || !d_workspace || (!h_events && n_events_total)) {
         mst_set_error("mst_encode_batch_host: null pointer argument");
@@ -59,6 +59,18 @@ extern "C" int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events
                                      d_workspace, inner, stream_);
     if (rc != MST_OK) return rc;
     MST_CUDA_CHECK(cudaMemcpyAsync(h_info, d_info, (size_t)n_songs * sizeof(MstSongInfo), cudaMemcpyDeviceToHost, stream));
+    return MST_OK;
+}
+
+extern "C" int mst_encode_batch_host(const MstEvent *h_events, uint64_t n_events_total,
+                                     const MstSongIn *h_songs, uint32_t n_songs,
+                                     const MstFilter *h_filter, MstSongInfo *h_info,
+                                     float *d_arena, uint64_t arena_floats, float *h_arena,
+                                     void *d_workspace, size_t workspace_bytes, void *stream_) {
+    int rc = mst_encode_batch_host_async(h_events, n_events_total, h_songs, n_songs, h_filter, h_info, d_arena, arena_floats,
+                                         d_workspace, workspace_bytes, stream_);
+    if (rc != MST_OK || n_songs == 0) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
     MST_CUDA_CHECK(cudaStreamSynchronize(stream));
     if (h_arena) {
         // grids are contiguous from offset 0 in song order: copy the used prefix

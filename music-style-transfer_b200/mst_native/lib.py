@@ -21,7 +21,7 @@ EXPORTS = [
     'mst_profile_enable', 'mst_profile_encode_ms',
     'mst_smf_parse',
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
-    'mst_encode_host_workspace_bytes', 'mst_encode_batch_host',
+    'mst_encode_host_workspace_bytes', 'mst_encode_batch_host', 'mst_encode_batch_host_async',
     'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write',
     'mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
     'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply', 'mst_model_backward', 'mst_model_loss_workspace_bytes',
@@ -64,6 +64,10 @@ def load():
     L.mst_encode_batch_host.argtypes = [
         ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
         ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    L.mst_encode_batch_host_async.restype = ctypes.c_int
+    L.mst_encode_batch_host_async.argtypes = [
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
     L.mst_decode_workspace_bytes.restype = ctypes.c_size_t
     L.mst_decode_workspace_bytes.argtypes = [ctypes.c_uint32, ctypes.c_uint64, ctypes.c_uint64]
     L.mst_decode_batch_device.restype = ctypes.c_int

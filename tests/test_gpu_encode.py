@@ -171,3 +171,43 @@ def test_host_entry_point(torch):
     lib.check(rc)
     assert np.array_equal(h_arena, arena.cpu().numpy())
     np.testing.assert_array_equal(h_info['pitched_offset'], infos['pitched_offset'])
+
+
+def test_host_async_entry_point_two_slots(torch):
+    """mst_encode_batch_host_async on two alternating streams / workspaces / arenas (the pipelined host path of
+    bench.py's e2e leg): every batch's infos and grids equal the synchronous device path's."""
+    L = lib.load()
+    filt = abi.make_filter(synth.POPULAR, 0)
+    batches = []
+    for seed in (21, 22, 23, 24):
+        events, songs = synth.synth_corpus(3, seed=seed, n_bars=12, n_tracks=5)
+        infos, arena = lib.encode_songs(synth.split_songs(events, songs), songs['ticks_per_beat'], filt)
+        batches.append((events, songs, infos, arena))
+    n = max(b[3].numel() for b in batches)
+    wsb = max(L.mst_encode_host_workspace_bytes(len(b[0]), len(b[1]), n) for b in batches)
+    slots = [dict(stream=torch.cuda.Stream(), ws=torch.empty(wsb, dtype=torch.uint8, device='cuda'),
+                  arena=torch.empty(n, dtype=torch.float32, device='cuda'),
+                  info=torch.zeros(3 * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory(), job=None) for _ in range(2)]
+    pinned = [(torch.from_numpy(b[0].view(np.uint8).reshape(-1).copy()).pin_memory(),
+               torch.from_numpy(b[1].view(np.uint8).reshape(-1).copy()).pin_memory()) for b in batches]
+
+    def drain(sl):
+        sl['stream'].synchronize()
+        if sl['job'] is not None:
+            events, songs, infos, arena = batches[sl['job']]
+            got = sl['info'].numpy().view(abi.SONG_INFO_DTYPE)
+            for k in ('status', 'n_pitched', 'n_bars_out', 'pitched_offset', 'unpitched_offset', 'tonic', 'mode'):
+                np.testing.assert_array_equal(got[k], infos[k])
+            assert torch.equal(sl['arena'][:arena.numel()], arena)
+            sl['job'] = None
+
+    for rep in range(2):
+        for i, (ev, sg) in enumerate(pinned):
+            sl = slots[i % 2]
+            drain(sl)
+            lib.check(L.mst_encode_batch_host_async(ev.data_ptr(), len(batches[i][0]), sg.data_ptr(), 3,
+                                                    filt.reshape(1).ctypes.data, sl['info'].data_ptr(), sl['arena'].data_ptr(), n,
+                                                    sl['ws'].data_ptr(), wsb, sl['stream'].cuda_stream))
+            sl['job'] = i
+    for sl in slots:
+        drain(sl)
