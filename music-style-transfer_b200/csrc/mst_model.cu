@@ -248,7 +248,7 @@ struct Launcher {
 
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     // tensor-core path (mst_model_gemm_tc.cuh) for everything but the tiny problems
-    static bool use_tc(int M, int N, int K) { return M >= 24 && (long long)M * N * K >= (1ll << 21); }
+    static bool use_tc(int M, int N, int K) { return (long long)M * N * K >= (1ll << 21); }
     template <int BN>
     void gemm_tc(const GemmArgs &g, int split_k) {
         dim3 grid((g.N + BN - 1) / BN, (g.M + kTcBM - 1) / kTcBM, split_k);
