@@ -299,10 +299,15 @@ struct Launcher {
         const int split = std::max(1, std::min(std::min(512, M / 128), (2 * 148 + tiles - 1) / tiles));
         gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
     }
-    void colsum(const float *in, float *out, long long rows, int cols) {
+    void colsum(const float *in, float *out, long long rows, int cols, float *out2 = nullptr) {
         if (dry || rows <= 0) return;
         dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((rows + 63) / 64, 256)), (cols + 31) / 32);
-        k_colsum<<<grid, 256, 0, st>>>(in, out, rows, cols); check();
+        k_colsum<<<grid, 256, 0, st>>>(in, out, rows, cols, out2); check();
+    }
+    void act_grad_colsum(const float *dY, const float *Y, float *dPre, float *out, long long rows, int cols) {
+        if (dry || rows <= 0) return;
+        dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((rows + 63) / 64, 148 * 4 / ((cols + 31) / 32) + 1)), (cols + 31) / 32);
+        k_act_grad_colsum<<<grid, 256, 0, st>>>(dY, Y, dPre, out, rows, cols); check();
     }
     void fill(float *p, long long n, float v) { if (!dry && n > 0) { k_fill<<<grid_for(n), 256, 0, st>>>(p, n, v); check(); } }
     void axpy(float *y, const float *x, long long n) { if (!dry && n > 0) { k_axpy<<<grid_for(n), 256, 0, st>>>(y, x, n); check(); } }

@@ -64,8 +64,11 @@ struct Bwd {
     //   gb += colsum, gW += dpre^T X, dX (+)= dpre W.   Yact == nullptr: no activation.
     void lin_bwd(float *dY, const float *Yact, int M, int Nout, const float *X, long long ldx, int K,
                  ParamId w, int w_col_off, int ldw, int bias /* ParamId or -1 */, float *dX, long long lddx, int acc_dx) {
-        if (Yact) L.act_grad(dY, Yact, dY, (long long)M * Nout);
-        if (bias >= 0) L.colsum(dY, GRD(c, (ParamId)bias), M, Nout);
+        if (Yact && bias >= 0) L.act_grad_colsum(dY, Yact, dY, GRD(c, (ParamId)bias), M, Nout);
+        else {
+            if (Yact) L.act_grad(dY, Yact, dY, (long long)M * Nout);
+            if (bias >= 0) L.colsum(dY, GRD(c, (ParamId)bias), M, Nout);
+        }
         L.linear_dw(dY, Nout, X, ldx, GRD(c, w) + w_col_off, ldw, M, Nout, K);
         if (dX) L.linear_dx(dY, Nout, PRM(c, w) + w_col_off, ldw, dX, lddx, M, Nout, K, acc_dx);
     }
@@ -91,8 +94,7 @@ struct Bwd {
         const int rows = lb.S * lb.T, H4 = 4 * lb.H;
         L.linear_dw(lb.dgates, H4, X, lb.I, GRD(c, wih), lb.I, rows, H4, lb.I);
         L.linear_dw(lb.dgates, H4, lb.hprev, lb.H, GRD(c, whh), lb.H, rows, H4, lb.H);
-        L.colsum(lb.dgates, GRD(c, bih), rows, H4);
-        L.colsum(lb.dgates, GRD(c, bhh), rows, H4);
+        L.colsum(lb.dgates, GRD(c, bih), rows, H4, GRD(c, bhh));      // b_ih and b_hh see the same gradient
         if (dX) L.linear_dx(lb.dgates, H4, PRM(c, wih), lb.I, dX, lb.I, rows, H4, lb.I, acc_dx);
     }
     void lstm_bwd(LstmBuf &lb, const float *dout, long long out_ld, int out_off, int reverse, const float *X,

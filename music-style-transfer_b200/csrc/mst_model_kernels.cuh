@@ -235,7 +235,7 @@ k_adam(float *__restrict__ p, float *__restrict__ g, float *__restrict__ m, floa
 
 // column sums of a [rows, cols] matrix into out[cols] (atomic accumulate) — bias gradients
 __global__ void __launch_bounds__(256)
-k_colsum(const float *__restrict__ in, float *__restrict__ out, long long rows, int cols) {
+k_colsum(const float *__restrict__ in, float *__restrict__ out, long long rows, int cols, float *__restrict__ out2 = nullptr) {
     // blockDim = 256 = 8 row-lanes x 32 col-lanes (cols handled in chunks of 32)
     __shared__ float part[8][33];
     const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
@@ -244,6 +244,36 @@ k_colsum(const float *__restrict__ in, float *__restrict__ out, long long rows, 
         float s = 0.f;
         if (c < cols)
             for (long long r = (long long)blockIdx.x * 8 + rl; r < rows; r += (long long)gridDim.x * 8) s += in[r * cols + c];
+        part[rl][cl] = s;
+        __syncthreads();
+        if (rl == 0 && c < cols) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; k++) t += part[k][cl];
+            atomicAdd(out + c, t);
+            if (out2) atomicAdd(out2 + c, t);
+        }
+        __syncthreads();
+    }
+}
+
+// dPre = dY * act'(Y) (in place allowed) and out[cols] += column sums of dPre, in ONE pass: the activation backward and
+// the bias gradient of a Linear layer (same thread layout as k_colsum)
+__global__ void __launch_bounds__(256)
+k_act_grad_colsum(const float *__restrict__ dY, const float *__restrict__ Y, float *__restrict__ dPre, float *__restrict__ out,
+                  long long rows, int cols) {
+    __shared__ float part[8][33];
+    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    for (int c0 = blockIdx.y * 32; c0 < cols; c0 += gridDim.y * 32) {
+        const int c = c0 + cl;
+        float s = 0.f;
+        if (c < cols)
+            for (long long r = (long long)blockIdx.x * 8 + rl; r < rows; r += (long long)gridDim.x * 8) {
+                const long long i = r * cols + c;
+                const float v = dY[i] * leaky_grad_from_out(Y[i]);
+                dPre[i] = v;
+                s += v;
+            }
         part[rl][cl] = s;
         __syncthreads();
         if (rl == 0 && c < cols) {
