@@ -736,7 +736,7 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
         PsaArgs2 a{c.psa_zr, c.psa_zci, c.melody, c.psa_out, N, C, B, T};
         const size_t smem = sizeof(PsaWarpSmem) * kPsaWarps;
         cudaFuncSetAttribute(k_psa_fwd2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_psa_fwd2<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148 * 2), kPsaWarps * 32, smem, L.st>>>(a); L.check();
+        k_psa_fwd2<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
     }
     if (unpitched) {
         // ---------------- UnpitchedStyleApplier (model.py:703-724)

@@ -33,12 +33,21 @@ k_psa_zci(const float *__restrict__ bias, const float *__restrict__ Zi, const fl
     }
 }
 
-constexpr int kPsaWarps = 8;
+constexpr int kPsaWarps = 16;
 struct PsaWarpSmem {
-    float od[4 * 450];       // post-activation octave/degree rows of the current channel group
+    float od[4 * 450];       // post-activation octave/degree rows of the current channel group; then the output staging
     float snote[56 * 5];     // bl + Wl[:, 30:].mf per note
-    float out[4 * 280];      // output staging
+    float mel[56 * 8];       // this unit's melody rows / Zr row, fetched with cp.async during the previous unit
+    float zr[452];
 };
+static_assert(sizeof(PsaWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
+}
 
 // phase 1 for one note: mf[20] and snote[5] from the melody vector
 __device__ __forceinline__ void psa_note(const float *mel8, float *mf, float *sn) {
@@ -65,7 +74,7 @@ struct PsaArgs2 {
     int N, C, B, T;
 };
 
-__global__ void __launch_bounds__(kPsaWarps * 32)
+__global__ void __launch_bounds__(kPsaWarps * 32, 1)
 k_psa_fwd2(PsaArgs2 a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -73,13 +82,22 @@ k_psa_fwd2(PsaArgs2 a) {
     const long long per_n = (long long)a.B * a.T * 10;
     const long long units = (long long)a.N * per_n;
     const int c_l = lane >> 3, o = lane & 7;
-    for (long long u = (long long)blockIdx.x * kPsaWarps + warp; u < units; u += (long long)gridDim.x * kPsaWarps) {
+    auto prefetch = [&](long long uu) {           // Zr rows are 1800 bytes: 8-byte aligned
+        const float *mg = a.melody + uu * 448, *zg = a.Zr + uu * 450;
+        for (int i = lane; i < 112; i += 32) cp_async16(s.mel + i * 4, mg + i * 4);
+        for (int i = lane; i < 225; i += 32) cp_async8(s.zr + i * 2, zg + i * 2);
+        asm volatile("cp.async.commit_group;");
+    };
+    const long long u0 = (long long)blockIdx.x * kPsaWarps + warp, ustep = (long long)gridDim.x * kPsaWarps;
+    if (u0 < units) prefetch(u0);
+    for (long long u = u0; u < units; u += ustep) {
         const int n = (int)(u / per_n);
         const long long btf = u - (long long)n * per_n;
+        asm volatile("cp.async.wait_group 0;");
         __syncwarp();
         // phase 1: per-note melody branch
         for (int note = lane; note < 56; note += 32) {
-            const float4 *mp = reinterpret_cast<const float4 *>(a.melody + (u * 56 + note) * 8);
+            const float4 *mp = reinterpret_cast<const float4 *>(s.mel + note * 8);
             const float4 m0 = mp[0], m1 = mp[1];
             const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
             float mf[20], sn[5];
@@ -87,39 +105,50 @@ k_psa_fwd2(PsaArgs2 a) {
 #pragma unroll
             for (int e = 0; e < 5; e++) s.snote[note * 5 + e] = sn[e];
         }
-        const float *zr = a.Zr + u * 450;
         for (int c0 = 0; c0 < a.C; c0 += 4) {
             const int cg = min(4, a.C - c0);
             __syncwarp();
             for (int j = lane; j < 450; j += 32) {
-                const float z = zr[j];
+                const float z = s.zr[j];
                 for (int c = 0; c < cg; c++) s.od[c * 450 + j] = leaky(z + a.Zci[((long long)n * a.C + c0 + c) * 450 + j]);
             }
+            if (c0 + 4 >= a.C && u + ustep < units) {       // both staging rows are consumed: fetch the next unit's
+                __syncwarp();
+                prefetch(u + ustep);
+            }
             __syncwarp();
+            float y[7][5];
             if (c_l < cg) {
                 float oct[30];
 #pragma unroll
                 for (int q = 0; q < 30; q++) oct[q] = s.od[c_l * 450 + o * 30 + q];
                 const float *deg = s.od + c_l * 450 + 240;
+#pragma unroll
                 for (int d = 0; d < 7; d++) {
                     const int note = o * 7 + d;
-                    float y[5];
 #pragma unroll
-                    for (int e = 0; e < 5; e++) y[e] = s.snote[note * 5 + e];
+                    for (int e = 0; e < 5; e++) y[d][e] = s.snote[note * 5 + e];
 #pragma unroll
                     for (int q = 0; q < 30; q++) {
                         const float v = leaky(oct[q] + deg[d * 30 + q]);
 #pragma unroll
-                        for (int e = 0; e < 5; e++) y[e] = fmaf(c_psa[kPsaWl + e * 50 + q], v, y[e]);
+                        for (int e = 0; e < 5; e++) y[d][e] = fmaf(c_psa[kPsaWl + e * 50 + q], v, y[d][e]);
                     }
 #pragma unroll
-                    for (int e = 0; e < 5; e++) s.out[c_l * 280 + note * 5 + e] = sigmoidf(y[e]) * (e == 0 ? 6.f : 1.f);
+                    for (int e = 0; e < 5; e++) y[d][e] = sigmoidf(y[d][e]) * (e == 0 ? 6.f : 1.f);
                 }
+            }
+            __syncwarp();                                   // every lane is done with od: it becomes the output staging
+            if (c_l < cg) {
+#pragma unroll
+                for (int d = 0; d < 7; d++)
+#pragma unroll
+                    for (int e = 0; e < 5; e++) s.od[c_l * 280 + (o * 7 + d) * 5 + e] = y[d][e];
             }
             __syncwarp();
             for (int c = 0; c < cg; c++) {
                 float4 *dst = reinterpret_cast<float4 *>(a.out + ((((long long)n * a.C + c0 + c) * per_n) + btf) * 280);
-                const float4 *src = reinterpret_cast<const float4 *>(s.out + c * 280);
+                const float4 *src = reinterpret_cast<const float4 *>(s.od + c * 280);
                 for (int i = lane; i < 70; i += 32) dst[i] = src[i];
             }
         }
