@@ -184,6 +184,17 @@ def training_config(per_gpu, world):
             'l2_policy': 'inputs larger than L2: >=155 MB of grids + >=0.8 GB of activations per step'}
 
 
+def k_grid_traffic(songs_per_step):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_grid launch from the committed ncu capture
+    (profiles/r1_k_grid_traffic.json); only valid for the batch size it was captured at."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'r1_k_grid_traffic.json')) as f:
+            t = json.load(f)
+        return int(t['dram_bytes_per_launch']) if int(t['songs_per_step']) == int(songs_per_step) else None
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def algorithmic_bytes_per_sample(C, B, nb, drums):
     """read the input grids twice (fwd, bwd) + write and read the prediction grids once each."""
     return 4 * 4 * nb * 10 * (280 * C + (94 if drums else 0)) * B
@@ -438,7 +449,7 @@ def main():
     ev_bytes = statistics.mean(len(h[0]) * 16 for h in host_batches)
     roofline = {
         'kernel': 'k_grid', 'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-        'frac': achieved / peak, 'traffic': None, 'peak_source': peak_src,
+        'frac': achieved / peak, 'traffic': k_grid_traffic(args.batch), 'peak_source': peak_src,
         'algorithmic_bytes_per_launch': g_bytes, 'ms_per_launch': g_ms,
         'share_of_step': g_ms / (g_ms + statistics.mean(front_ms)),
         'pipeline': {'front_end_ms': statistics.mean(front_ms),
