@@ -748,7 +748,7 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
         UsaArgs a{};
         a.bias = PRM(c, usa_nl_b); a.Wl = PRM(c, usa_lin_w); a.bl = PRM(c, usa_lin_b); a.Zr = c.usa_zr; a.Zs = c.usa_zs;
         a.H = c.usa_h; a.out = c.usa_out; a.N = N; a.B = B; a.T = T;
-        k_usa_fwd<<<(int)std::min<long long>(Rbf, 148 * 16), 64, 0, L.st>>>(a); L.check();
+        k_usa_fwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
     }
 }
 

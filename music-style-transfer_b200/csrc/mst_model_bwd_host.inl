@@ -206,7 +206,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             a.f.bias = PRM(c, usa_nl_b); a.f.Wl = PRM(c, usa_lin_w); a.f.bl = PRM(c, usa_lin_b); a.f.Zr = c.usa_zr; a.f.Zs = c.usa_zs;
             a.f.H = c.usa_h; a.f.out = nullptr; a.f.N = N; a.f.B = B; a.f.T = T;
             a.target = c.Ug; a.coef = lb.coef_u; a.dHpre = dH; a.gWl = GRD(c, usa_lin_w); a.gbl = GRD(c, usa_lin_b);
-            k_usa_bwd<<<(int)std::min<long long>(Rbf, 148 * 16), 64, 0, L.st>>>(a); L.check();
+            k_usa_bwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
         }
         L.colsum(dH, GRD(c, usa_nl_b), Rbf, 376);
         w.reduce_to(dH, Dims5{N, 1, B, T, 10}, 376, M_N | M_F, dZs);

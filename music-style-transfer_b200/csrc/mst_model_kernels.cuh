@@ -23,8 +23,7 @@ __device__ __forceinline__ float sigmoidf(float x) { return 1.f / (1.f + expf(-x
 //   A(i, k) = A[i * a_si + k * a_sk],  B(k, j) = B[k * b_sk + j * b_sj],  C[i * c_si + j]
 // 64 x 64 x 16 tiles, 256 threads, 4 x 4 outputs per thread.  gridDim.z splits K (atomic accumulate).
 // Covers X·W^T (forward), dY·W (input grad) and dY^T·X (weight grad, K = rows, split over z).
-// AMODE 1 = implicit im2col of the pitched grid for beats_conv (model.py:46-52): row m = (beat-row, octave),
-// k = (fraction, tap, feature); A(m, k) = P[row][f][(oct*7 + tap - 4)][feat] or 0 outside the 56 notes.
+// (beats_conv, model.py:46-52, is evaluated over the occupied cells: mst_model_sparse.cuh.)
 // ------------------------------------------------------------------------------------------------
 struct GemmArgs {
     const float *A, *B, *bias;
@@ -39,16 +38,7 @@ constexpr int kGemmTile = 64, kGemmK = 16, kGemmThreads = 256;
 
 template <int AMODE>
 __device__ __forceinline__ float gemm_load_a(const GemmArgs &g, int i, int k) {
-    if (AMODE == 0) return g.A[(long long)i * g.a_si + (long long)k * g.a_sk];
-    // AMODE 2 is the transposed gather (i = im2col column, k = (beat-row, octave)): the weight-gradient GEMM
-    if (AMODE == 2) { const int t = i; i = k; k = t; }
-    // conv gather: k = f * 70 + tap * 5 + feat over the (10, 56, 5) beat block
-    const int row = i >> 3, oct = i & 7;
-    const int f = k / 70, r = k - f * 70;
-    const int tap = r / 5, feat = r - tap * 5;
-    const int note = oct * 7 + tap - 4;
-    if (note < 0 || note >= 56) return 0.f;
-    return g.A[(long long)row * 2800 + f * 280 + note * 5 + feat];
+    return g.A[(long long)i * g.a_si + (long long)k * g.a_sk];
 }
 
 template <int AMODE>
@@ -68,7 +58,7 @@ k_gemm(GemmArgs g) {
 #pragma unroll
         for (int b = 0; b < 4; b++) acc[a][b] = 0.f;
     // load mapping: pick the contiguous direction of each operand for coalescing
-    const bool a_k_contig = (AMODE == 1) || (g.a_sk == 1);
+    const bool a_k_contig = g.a_sk == 1;
     const bool b_j_contig = (g.b_sj == 1);
     for (int k0 = k_lo; k0 < k_hi; k0 += kGemmK) {
 #pragma unroll

@@ -167,30 +167,52 @@ struct UsaArgs {
     int N, B, T;
 };
 
-__global__ void __launch_bounds__(64)
+// warp per unit; the next unit's Zr row arrives by cp.async while the current one is processed
+constexpr int kUsaWarps = 8;
+struct UsaWarpSmem { float row[2][376]; float h[376]; };
+static_assert(sizeof(UsaWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
+
+__global__ void __launch_bounds__(kUsaWarps * 32)
 k_usa_fwd(UsaArgs a) {
-    __shared__ float h_s[376];
+    __shared__ __align__(16) UsaWarpSmem sm[kUsaWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    UsaWarpSmem &s = sm[warp];
     const long long per_n = (long long)a.B * a.T * 10;
     const long long units = (long long)a.N * per_n;
-    for (long long u = blockIdx.x; u < units; u += gridDim.x) {
+    auto prefetch = [&](long long uu, int buf) {
+        const float *zg = a.Zr + uu * 376;
+        for (int i = lane; i < 94; i += 32) cp_async16(s.row[buf] + i * 4, zg + i * 4);
+        asm volatile("cp.async.commit_group;");
+    };
+    const long long u0 = (long long)blockIdx.x * kUsaWarps + warp, ustep = (long long)gridDim.x * kUsaWarps;
+    if (u0 < units) prefetch(u0, 0);
+    int buf = 0;
+    for (long long u = u0; u < units; u += ustep, buf ^= 1) {
         const int n = (int)(u / per_n);
         const int f = (int)((u - (long long)n * per_n) % 10);
-        __syncthreads();
-        for (int j = threadIdx.x; j < 376; j += blockDim.x) {
-            const float v = leaky(a.bias[j] + a.Zr[u * 376 + j] + a.Zs[((long long)n * 10 + f) * 376 + j]);
-            h_s[j] = v;
+        __syncwarp();
+        if (u + ustep < units) { prefetch(u + ustep, buf ^ 1); asm volatile("cp.async.wait_group 1;"); }
+        else asm volatile("cp.async.wait_group 0;");
+        __syncwarp();
+        const float *zs = a.Zs + ((long long)n * 10 + f) * 376;
+        for (int j = lane; j < 376; j += 32) {
+            const float v = leaky(a.bias[j] + s.row[buf][j] + zs[j]);
+            s.h[j] = v;
             a.H[u * 376 + j] = v;
         }
-        __syncthreads();
-        if (threadIdx.x < 47) {
-            const float *h = h_s + threadIdx.x * 8;
+        __syncwarp();
+        for (int note = lane; note < 47; note += 32) {
+            const float4 h0 = *reinterpret_cast<const float4 *>(s.h + note * 8), h1 = *reinterpret_cast<const float4 *>(s.h + note * 8 + 4);
+            const float h[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+            float y[2];
 #pragma unroll
             for (int e = 0; e < 2; e++) {
                 float v = a.bl[e];
 #pragma unroll
                 for (int q = 0; q < 8; q++) v = fmaf(a.Wl[e * 8 + q], h[q], v);
-                a.out[(u * 47 + threadIdx.x) * 2 + e] = sigmoidf(v) * (e == 0 ? 6.f : 1.f);
+                y[e] = sigmoidf(v) * (e == 0 ? 6.f : 1.f);
             }
+            *reinterpret_cast<float2 *>(a.out + (u * 47 + note) * 2) = make_float2(y[0], y[1]);
         }
     }
 }

@@ -419,49 +419,68 @@ struct UsaBwdArgs {
     float *gWl, *gbl;          // (2,8), (2)
 };
 
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(kUsaWarps * 32)
 k_usa_bwd(UsaBwdArgs a) {
+    __shared__ __align__(16) UsaWarpSmem sm[kUsaWarps];
     __shared__ float g_s[18];
     const UsaArgs &f = a.f;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    UsaWarpSmem &s = sm[warp];
     if (threadIdx.x < 18) g_s[threadIdx.x] = 0.f;
     __syncthreads();
     const long long per_n = (long long)f.B * f.T * 10;
     const long long units = (long long)f.N * per_n;
+    float wl[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) wl[i] = f.Wl[i];
+    const float bl0 = f.bl[0], bl1 = f.bl[1];
     float gw[18];
 #pragma unroll
     for (int i = 0; i < 18; i++) gw[i] = 0.f;
-    for (long long u = blockIdx.x; u < units; u += gridDim.x) {
+    auto prefetch = [&](long long uu, int buf) {
+        const float *hg = f.H + uu * 376;
+        for (int i = lane; i < 94; i += 32) cp_async16(s.row[buf] + i * 4, hg + i * 4);
+        asm volatile("cp.async.commit_group;");
+    };
+    const long long u0 = (long long)blockIdx.x * kUsaWarps + warp, ustep = (long long)gridDim.x * kUsaWarps;
+    if (u0 < units) prefetch(u0, 0);
+    int buf = 0;
+    for (long long u = u0; u < units; u += ustep, buf ^= 1) {
         const int n = (int)(u / per_n);
-        if (threadIdx.x < 47) {
-            const int note = threadIdx.x;
-            const float *h = f.H + u * 376 + note * 8;
-            float hv[8], y[2], t2[2], dpre[2];
+        __syncwarp();
+        if (u + ustep < units) { prefetch(u + ustep, buf ^ 1); asm volatile("cp.async.wait_group 1;"); }
+        else asm volatile("cp.async.wait_group 0;");
+        __syncwarp();
+        const float *cf = a.coef + n * kLossCoefs;
+        for (int note = lane; note < 47; note += 32) {
+            const float4 h0 = *reinterpret_cast<const float4 *>(s.row[buf] + note * 8), h1 = *reinterpret_cast<const float4 *>(s.row[buf] + note * 8 + 4);
+            const float hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+            float y[2], t2[2], dpre[2];
+            float v0 = bl0, v1 = bl1;
 #pragma unroll
-            for (int q = 0; q < 8; q++) hv[q] = h[q];
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-                float v = f.bl[e];
-#pragma unroll
-                for (int q = 0; q < 8; q++) v = fmaf(f.Wl[e * 8 + q], hv[q], v);
-                y[e] = sigmoidf(v) * (e == 0 ? 6.f : 1.f);
-                t2[e] = a.target[(u * 47 + note) * 2 + e];
-            }
-            loss_cell_grad<2>(y, t2, a.coef + n * kLossCoefs, dpre);
+            for (int q = 0; q < 8; q++) { v0 = fmaf(wl[q], hv[q], v0); v1 = fmaf(wl[8 + q], hv[q], v1); }
+            y[0] = sigmoidf(v0) * 6.f; y[1] = sigmoidf(v1);
+            const float2 tt = *reinterpret_cast<const float2 *>(a.target + (u * 47 + note) * 2);
+            t2[0] = tt.x; t2[1] = tt.y;
+            loss_cell_grad<2>(y, t2, cf, dpre);
+            float dh[8];
 #pragma unroll
             for (int q = 0; q < 8; q++) {
-                const float dh = f.Wl[q] * dpre[0] + f.Wl[8 + q] * dpre[1];
-                a.dHpre[u * 376 + note * 8 + q] = dh * leaky_grad_from_out(hv[q]);
+                dh[q] = (wl[q] * dpre[0] + wl[8 + q] * dpre[1]) * leaky_grad_from_out(hv[q]);
                 gw[q] = fmaf(dpre[0], hv[q], gw[q]);
                 gw[8 + q] = fmaf(dpre[1], hv[q], gw[8 + q]);
             }
             gw[16] += dpre[0]; gw[17] += dpre[1];
+            float4 *dst = reinterpret_cast<float4 *>(a.dHpre + u * 376 + note * 8);
+            dst[0] = make_float4(dh[0], dh[1], dh[2], dh[3]);
+            dst[1] = make_float4(dh[4], dh[5], dh[6], dh[7]);
         }
     }
 #pragma unroll
     for (int i = 0; i < 18; i++) {
         float v = gw[i];
         for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if ((threadIdx.x & 31) == 0) atomicAdd(&g_s[i], v);
+        if (lane == 0) atomicAdd(&g_s[i], v);
     }
     __syncthreads();
     if (threadIdx.x < 16) atomicAdd(a.gWl + threadIdx.x, g_s[threadIdx.x]);
