@@ -263,7 +263,7 @@ struct Launcher {
         dim3 grid((g.N + BN - 1) / BN, (g.M + kT5BM - 1) / kT5BM, split_k);
         static bool attr_set = false;
         if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN>()); attr_set = true; }
-        k_gemm_t5<BN><<<grid, kT5Threads, t5_smem_bytes<BN>(), st>>>(g);
+        k_gemm_t5<BN><<<grid, kT5Block, t5_smem_bytes<BN>(), st>>>(g);
     }
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,

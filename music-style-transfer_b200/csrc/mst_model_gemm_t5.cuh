@@ -9,11 +9,11 @@
 //   * CTA tile 128 x BN (BN = 16 / 32 / 64), K slab 32, two shared-memory stages; each stage holds A_hi, A_lo (128 x 32)
 //     and B_hi, B_lo (BN x 32) in the canonical K-major no-swizzle UMMA layout: 8-row x 16-byte core matrices, the 8
 //     K-chunks of a row group 144 B apart (LBO), row groups 1152 B apart (SBO);
-//   * all 256 threads load the next slab into registers (any operand strides; the lane order follows the operand's
+//   * 8 producer warps load the next slab into registers (any operand strides; the lane order follows the operand's
 //     contiguous direction, 16 / 8-byte loads when aligned), split it, store 16-byte chunks (conflict-free for both
-//     orders thanks to the 144-byte LBO), fence.proxy.async, barrier;
-//     thread 0 then issues 4 k-steps x 3 products of tcgen05.mma.kind::tf32 (M = 128, N = BN, K = 8) and commits to the
-//     stage's mbarrier, which gates the reuse of that stage two slabs later;
+//     orders thanks to the 144-byte LBO), fence.proxy.async, and arrive on the stage's "full" mbarrier (no CTA barrier);
+//     a ninth warp's elected thread waits on it, issues 4 k-steps x 3 products of tcgen05.mma.kind::tf32 (M = 128,
+//     N = BN, K = 8) and commits to the stage's "empty" mbarrier, which gates the reuse of that stage two slabs later;
 //   * epilogue: tcgen05.ld (32 lanes x 32 bit, warp w reads TMEM lanes 32 (w % 4) ...) -> shared tile -> coalesced
 //     stores with bias / leaky / accumulate (16-byte where the destination allows).
 #pragma once
@@ -21,7 +21,7 @@
 
 namespace mstm {
 
-constexpr int kT5BM = 128, kT5BK = 32, kT5Threads = 256;
+constexpr int kT5BM = 128, kT5BK = 32, kT5Threads = 256, kT5Block = kT5Threads + 32;   // 8 loader warps + the MMA warp
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -82,7 +82,7 @@ __device__ __forceinline__ void t5_load4(const float *p, long long sk, int k, in
 }
 
 template <int BN>
-__global__ void __launch_bounds__(kT5Threads, 2)
+__global__ void __launch_bounds__(kT5Block, 2)
 k_gemm_t5(GemmArgs g) {
     constexpr int BM = kT5BM, KT = kT5BK;
     constexpr int A_BYTES = t5_tile_bytes(BM), B_BYTES = t5_tile_bytes(BN);   // one hi or lo tile
@@ -91,7 +91,7 @@ k_gemm_t5(GemmArgs g) {
     constexpr int B_CH = (BN * 8 + kT5Threads - 1) / kT5Threads;               // 2 / 1 / 1 (BN = 16: threads < 128)
     constexpr int TM_COLS = BN < 32 ? 32 : BN;
     extern __shared__ __align__(1024) unsigned char smem[];
-    __shared__ __align__(8) uint64_t bars[3];
+    __shared__ __align__(8) uint64_t bars[5];          // full[2] (8 loader warps), empty[2] (tcgen05.commit), done
     __shared__ uint32_t tmem_base_s;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -103,8 +103,10 @@ k_gemm_t5(GemmArgs g) {
     const int n_slabs = (k_hi - k_lo + KT - 1) / KT;
 
     const uint32_t bar0 = smem_u32(&bars[0]);
+    const uint32_t bar_full = bar0, bar_empty = bar0 + 16, bar_done = bar0 + 32;
     if (tid == 0) {
-        mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_init(bar0 + 16, 1);
+        mbar_init(bar_full, 8); mbar_init(bar_full + 8, 8);
+        mbar_init(bar_empty, 1); mbar_init(bar_empty + 8, 1); mbar_init(bar_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -174,15 +176,23 @@ k_gemm_t5(GemmArgs g) {
     constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
     const uint32_t smem_base = smem_u32(smem);
 
-    load_slab(0);
-    for (int s = 0; s < n_slabs; s++) {
-        const int stage = s & 1;
-        if (s >= 2) mbar_wait(bar0 + 8 * stage, (uint32_t)(((s >> 1) - 1) & 1));     // the MMAs of slab s - 2 have read this stage
-        store_slab(stage);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        if (s + 1 < n_slabs) load_slab(s + 1);
-        __syncthreads();
-        if (tid == 0) {
+    if (warp < 8) {
+        // ---- producers: split + store slab s, publish it on the stage's "full" barrier, then fetch slab s + 1
+        load_slab(0);
+        for (int s = 0; s < n_slabs; s++) {
+            const int stage = s & 1;
+            if (s >= 2) mbar_wait(bar_empty + 8 * stage, (uint32_t)(((s >> 1) - 1) & 1));   // MMAs of slab s - 2 have read it
+            store_slab(stage);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_full + 8 * stage) : "memory");
+            if (s + 1 < n_slabs) load_slab(s + 1);
+        }
+    } else if (lane == 0) {
+        // ---- consumer: one thread issues the MMAs of a slab as soon as all 8 producer warps have published it
+        for (int s = 0; s < n_slabs; s++) {
+            const int stage = s & 1;
+            mbar_wait(bar_full + 8 * stage, (uint32_t)((s >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + 2 * A_BYTES;
 #pragma unroll
@@ -194,11 +204,12 @@ k_gemm_t5(GemmArgs g) {
                 t5_mma(tmem, a_hi, b_lo, idesc, 1);
                 t5_mma(tmem, a_hi, b_hi, idesc, 1);
             }
-            t5_commit(bar0 + 8 * stage);
-            if (s + 1 == n_slabs) t5_commit(bar0 + 16);
+            t5_commit(bar_empty + 8 * stage);
+            if (s + 1 == n_slabs) t5_commit(bar_done);
         }
     }
-    mbar_wait(bar0 + 16, 0);
+    __syncwarp();
+    mbar_wait(bar_done, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
     // ---- epilogue: TMEM -> registers (warp w reads lanes 32 (w % 4) .. + 31 = tile rows; warps 0-3 / 4-7 split the
@@ -207,7 +218,7 @@ k_gemm_t5(GemmArgs g) {
     float *tile = reinterpret_cast<float *>(smem);            // the operand stages are idle now (all MMAs completed)
     constexpr int CW = BN >= 32 ? BN / 2 : BN;                // columns per warp (BN = 16: warps 4-7 idle)
     const int col0 = (BN >= 32 && warp >= 4) ? CW : 0;
-    if (BN >= 32 || warp < 4) {
+    if (warp < 8 && (BN >= 32 || warp < 4)) {
         const int r = (warp & 3) * 32 + lane;
 #pragma unroll
         for (int cb = 0; cb < CW; cb += 8) {
@@ -226,7 +237,7 @@ k_gemm_t5(GemmArgs g) {
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TM_COLS) : "memory");
     const bool vec_ok = g.accumulate != 2 && (g.c_si & 3) == 0 && ((reinterpret_cast<uintptr_t>(g.C) & 15) == 0);
     if (vec_ok) {
-        for (int c = tid; c < BM * (BN / 4); c += kT5Threads) {
+        for (int c = tid; c < BM * (BN / 4); c += kT5Block) {
             const int r = c / (BN / 4), c4 = (c - r * (BN / 4)) * 4;
             const int gi = i0 + r, gj = j0 + c4;
             if (gi >= g.M || gj >= g.N) continue;
@@ -249,7 +260,7 @@ k_gemm_t5(GemmArgs g) {
             }
         }
     } else {
-        for (int c = tid; c < BM * BN; c += kT5Threads) {
+        for (int c = tid; c < BM * BN; c += kT5Block) {
             const int r = c / BN, cc = c - r * BN;
             const int gi = i0 + r, gj = j0 + cc;
             if (gi >= g.M || gj >= g.N) continue;
