@@ -6,6 +6,8 @@
 // sample, and gradients are summed over samples — exactly train-model.py's iter_size accumulation.
 #include <math.h>
 #include <string.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <vector>
@@ -268,6 +270,8 @@ struct Launcher {
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
               int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int kernel = 0) {
+        static const bool log_shapes = getenv("MST_GEMM_LOG") != nullptr;      // development aid: list the step's GEMMs
+        if (log_shapes && dry) fprintf(stderr, "gemm M=%d N=%d K=%d a=(%lld,%lld) b=(%lld,%lld) c=%lld act=%d acc=%d split=%d\n", M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate, split_k);
         if (dry || M <= 0 || N <= 0 || K <= 0) return;
         GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
         if (split_k > 1) g.accumulate = 2;
