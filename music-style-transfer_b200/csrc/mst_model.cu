@@ -739,8 +739,8 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
         k_psa_zci<<<grid_for((long long)NC * 450), 256, 0, L.st>>>(PRM(c, psa_oct_b), c.psa_zi, c.psa_zs, c.psa_zci, N, C); L.check();
         PsaArgs2 a{c.psa_zr, c.psa_zci, c.melody, c.psa_out, N, C, B, T};
         const size_t smem = sizeof(PsaWarpSmem) * kPsaWarps;
-        cudaFuncSetAttribute(k_psa_fwd2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_psa_fwd2<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
+        cudaFuncSetAttribute(k_psa_fwd3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_psa_fwd3<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
     }
     if (unpitched) {
         // ---------------- UnpitchedStyleApplier (model.py:703-724)

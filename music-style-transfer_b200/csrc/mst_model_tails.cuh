@@ -22,7 +22,7 @@ namespace mstm {
 // Zci[n,c][450] = od_bias + Zi[n,c] + Zs[n] is pre-summed by k_psa_zci (tiny).
 // ------------------------------------------------------------------------------------------------
 constexpr int kPsaWm = 0, kPsaBm = 160, kPsaWl = 180, kPsaBl = 430, kPsaConst = 440;
-__constant__ float c_psa[kPsaConst];
+__constant__ __align__(16) float c_psa[kPsaConst];
 
 __global__ void __launch_bounds__(256)
 k_psa_zci(const float *__restrict__ bias, const float *__restrict__ Zi, const float *__restrict__ Zs, float *__restrict__ Zci, int N, int C) {
@@ -33,7 +33,7 @@ k_psa_zci(const float *__restrict__ bias, const float *__restrict__ Zi, const fl
     }
 }
 
-constexpr int kPsaWarps = 16;
+constexpr int kPsaWarps = 12;
 struct PsaWarpSmem {
     float od[4 * 450];       // post-activation octave/degree rows of the current channel group; then the output staging
     float snote[56 * 5];     // bl + Wl[:, 30:].mf per note
@@ -49,22 +49,63 @@ __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
 }
 
-// phase 1 for one note: mf[20] and snote[5] from the melody vector
-__device__ __forceinline__ void psa_note(const float *mel8, float *mf, float *sn) {
+// ---- packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2): one issue slot carries two fp32 operations.  These kernels are
+// issue-bound, not FMA-pipe-bound (profiles/r1_ffma2_issue_probe.txt), so the pairs run over the contraction index and
+// the two partial sums are added once at the end.  A pair is a 64-bit register: .x = low word, .y = high word.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ float sum2(f32x2 v) { float lo, hi; upk2(v, lo, hi); return lo + hi; }
+// leaky_relu of both halves: max(x, slope * x) equals the select form for every finite x (0 < slope < 1)
+__device__ __forceinline__ f32x2 leaky2(f32x2 x) {
+    float xl, xh, tl, th;
+    upk2(x, xl, xh);
+    upk2(mul2(x, pk2(kSlope, kSlope)), tl, th);
+    return pk2(fmaxf(xl, tl), fmaxf(xh, th));
+}
+__device__ __forceinline__ f32x2 ld2(const float *p) { return *reinterpret_cast<const f32x2 *>(p); }      // 8-byte aligned
+#define MST_CPSA2(off) (*reinterpret_cast<const f32x2 *>(&c_psa[off]))                                    // even offsets
+// sigmoid from the SFU approximations (ex2.approx, rcp.approx: ~2 ulp each, far inside the 1e-5 loss tolerance)
+__device__ __forceinline__ float sigmoid_fast(float x) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+    return r;
+}
+
+// phase 1 for one note: mf[20] (as 10 pairs) and snote[5] from the melody vector (4 pairs)
+__device__ __forceinline__ void psa_note2(const f32x2 *mel, f32x2 *mf2, float *sn) {
 #pragma unroll
-    for (int j = 0; j < 20; j++) {
-        float v = c_psa[kPsaBm + j];
+    for (int jp = 0; jp < 10; jp++) {
+        float m[2];
 #pragma unroll
-        for (int p = 0; p < 8; p++) v = fmaf(c_psa[kPsaWm + j * 8 + p], mel8[p], v);
-        mf[j] = leaky(v);
+        for (int h = 0; h < 2; h++) {
+            const int j = jp * 2 + h;
+            f32x2 v = pk2(c_psa[kPsaBm + j], 0.f);
+#pragma unroll
+            for (int pp = 0; pp < 4; pp++) v = fma2(MST_CPSA2(kPsaWm + j * 8 + pp * 2), mel[pp], v);
+            m[h] = sum2(v);
+        }
+        mf2[jp] = leaky2(pk2(m[0], m[1]));
     }
 #pragma unroll
     for (int e = 0; e < 5; e++) {
-        float v = c_psa[kPsaBl + e];
+        f32x2 v = pk2(c_psa[kPsaBl + e], 0.f);
 #pragma unroll
-        for (int j = 0; j < 20; j++) v = fmaf(c_psa[kPsaWl + e * 50 + 30 + j], mf[j], v);
-        sn[e] = v;
+        for (int jp = 0; jp < 10; jp++) v = fma2(MST_CPSA2(kPsaWl + e * 50 + 30 + jp * 2), mf2[jp], v);
+        sn[e] = sum2(v);
     }
+}
+// scalar form (the backward kernels use it)
+__device__ __forceinline__ void psa_note(const float *mel8, float *mf, float *sn) {
+    const f32x2 mel[4] = {pk2(mel8[0], mel8[1]), pk2(mel8[2], mel8[3]), pk2(mel8[4], mel8[5]), pk2(mel8[6], mel8[7])};
+    f32x2 mf2[10];
+    psa_note2(mel, mf2, sn);
+#pragma unroll
+    for (int jp = 0; jp < 10; jp++) upk2(mf2[jp], mf[jp * 2], mf[jp * 2 + 1]);
 }
 
 struct PsaArgs2 {
@@ -74,8 +115,17 @@ struct PsaArgs2 {
     int N, C, B, T;
 };
 
+// od rows of one channel group: od[c][j] = leaky(zr[j] + Zci[n, c0 + c][j]), two columns per lane and step
+__device__ __forceinline__ void psa_build_od(float *od, const float *zr, const float *zci, int cg, int lane) {
+    for (int jp = lane; jp < 225; jp += 32) {
+        const f32x2 z = ld2(zr + jp * 2);
+        for (int c = 0; c < cg; c++)
+            *reinterpret_cast<f32x2 *>(od + c * 450 + jp * 2) = leaky2(add2(z, ld2(zci + c * 450 + jp * 2)));
+    }
+}
+
 __global__ void __launch_bounds__(kPsaWarps * 32, 1)
-k_psa_fwd2(PsaArgs2 a) {
+k_psa_fwd3(PsaArgs2 a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     PsaWarpSmem &s = reinterpret_cast<PsaWarpSmem *>(smem_raw)[warp];
@@ -99,19 +149,17 @@ k_psa_fwd2(PsaArgs2 a) {
         for (int note = lane; note < 56; note += 32) {
             const float4 *mp = reinterpret_cast<const float4 *>(s.mel + note * 8);
             const float4 m0 = mp[0], m1 = mp[1];
-            const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-            float mf[20], sn[5];
-            psa_note(mel8, mf, sn);
+            const f32x2 mel[4] = {pk2(m0.x, m0.y), pk2(m0.z, m0.w), pk2(m1.x, m1.y), pk2(m1.z, m1.w)};
+            f32x2 mf2[10];
+            float sn[5];
+            psa_note2(mel, mf2, sn);
 #pragma unroll
             for (int e = 0; e < 5; e++) s.snote[note * 5 + e] = sn[e];
         }
         for (int c0 = 0; c0 < a.C; c0 += 4) {
             const int cg = min(4, a.C - c0);
             __syncwarp();
-            for (int j = lane; j < 450; j += 32) {
-                const float z = s.zr[j];
-                for (int c = 0; c < cg; c++) s.od[c * 450 + j] = leaky(z + a.Zci[((long long)n * a.C + c0 + c) * 450 + j]);
-            }
+            psa_build_od(s.od, s.zr, a.Zci + ((long long)n * a.C + c0) * 450, cg, lane);
             if (c0 + 4 >= a.C && u + ustep < units) {       // both staging rows are consumed: fetch the next unit's
                 __syncwarp();
                 prefetch(u + ustep);
@@ -119,24 +167,31 @@ k_psa_fwd2(PsaArgs2 a) {
             __syncwarp();
             float y[7][5];
             if (c_l < cg) {
-                float oct[30];
+                // acc[d][e] = (sum over even q, sum over odd q) of Wl[e][q] . leaky(oct[q] + deg[d][q]); q pairs outermost
+                // so that the five weight pairs of a step are fetched once for the seven degrees
+                f32x2 acc[7][5];
 #pragma unroll
-                for (int q = 0; q < 30; q++) oct[q] = s.od[c_l * 450 + o * 30 + q];
-                const float *deg = s.od + c_l * 450 + 240;
+                for (int d = 0; d < 7; d++)
 #pragma unroll
-                for (int d = 0; d < 7; d++) {
-                    const int note = o * 7 + d;
+                    for (int e = 0; e < 5; e++) acc[d][e] = pk2(s.snote[(o * 7 + d) * 5 + e], 0.f);
+                const float *oct = s.od + c_l * 450 + o * 30, *deg = s.od + c_l * 450 + 240;
 #pragma unroll
-                    for (int e = 0; e < 5; e++) y[d][e] = s.snote[note * 5 + e];
+                for (int qp = 0; qp < 15; qp++) {
+                    const f32x2 oc = ld2(oct + qp * 2);
+                    f32x2 w[5];
 #pragma unroll
-                    for (int q = 0; q < 30; q++) {
-                        const float v = leaky(oct[q] + deg[d * 30 + q]);
+                    for (int e = 0; e < 5; e++) w[e] = MST_CPSA2(kPsaWl + e * 50 + qp * 2);
 #pragma unroll
-                        for (int e = 0; e < 5; e++) y[d][e] = fmaf(c_psa[kPsaWl + e * 50 + q], v, y[d][e]);
+                    for (int d = 0; d < 7; d++) {
+                        const f32x2 v = leaky2(add2(oc, ld2(deg + d * 30 + qp * 2)));
+#pragma unroll
+                        for (int e = 0; e < 5; e++) acc[d][e] = fma2(w[e], v, acc[d][e]);
                     }
-#pragma unroll
-                    for (int e = 0; e < 5; e++) y[d][e] = sigmoidf(y[d][e]) * (e == 0 ? 6.f : 1.f);
                 }
+#pragma unroll
+                for (int d = 0; d < 7; d++)
+#pragma unroll
+                    for (int e = 0; e < 5; e++) y[d][e] = sigmoid_fast(sum2(acc[d][e])) * (e == 0 ? 6.f : 1.f);
             }
             __syncwarp();                                   // every lane is done with od: it becomes the output staging
             if (c_l < cg) {
