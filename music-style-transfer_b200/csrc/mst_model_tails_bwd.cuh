@@ -33,7 +33,7 @@ struct PsaBwdWarpSmem {
     float od[4 * 450];
     float snote[56 * 5];
     float dps[56 * 5];
-    float sa[30 * 36];       // [q][lane] input-gradient staging of the current degree step
+    float sa[32 * 34];       // [lane][q] input-gradient staging of the current degree step (row stride 34: conflict-free 8-byte stores)
     float exq[32];           // a target-note cell's extra input gradient, handed back to its owner lane
     float mel[56 * 8];       // this unit's melody rows / Zr row, fetched with cp.async during the previous unit
     float zr[452];
@@ -86,7 +86,7 @@ k_psa_bwd3(PsaBwdArgs3 a) {
     const long long chunk = (per_n + a.ctas_per_n - 1) / a.ctas_per_n;
     const long long b_lo = (long long)kcta * chunk, b_hi = min(per_n, b_lo + chunk);
     for (int i = threadIdx.x; i < C * 450; i += blockDim.x) dzi_s[i] = 0.f;
-    for (int i = lane; i < 30 * 36; i += 32) s.sa[i] = 0.f;
+    for (int i = lane; i < 32 * 34; i += 32) s.sa[i] = 0.f;
     __syncthreads();
     float cf[6];
 #pragma unroll
@@ -96,9 +96,9 @@ k_psa_bwd3(PsaBwdArgs3 a) {
     const int qx = min(lane, 29);
     const float wx0 = a.Wl[0 * 50 + qx], wx2 = a.Wl[2 * 50 + qx], wx3 = a.Wl[3 * 50 + qx], wx4 = a.Wl[4 * 50 + qx];
     float gwx0 = 0.f, gwx2 = 0.f, gwx3 = 0.f, gwx4 = 0.f;
-    float gw1[30];
+    f32x2 gw1[15];                                    // velocity-row weight gradient, columns (2 qp, 2 qp + 1)
 #pragma unroll
-    for (int q = 0; q < 30; q++) gw1[q] = 0.f;
+    for (int qp = 0; qp < 15; qp++) gw1[qp] = pk2(0.f, 0.f);
 
     auto prefetch = [&](long long uu) {           // Zr rows are 1800 bytes: 8-byte aligned
         const float *mg = a.melody + uu * 448, *zg = a.Zr + uu * 450;
@@ -115,9 +115,10 @@ k_psa_bwd3(PsaBwdArgs3 a) {
         for (int note = lane; note < 56; note += 32) {
             const float4 *mp = reinterpret_cast<const float4 *>(s.mel + note * 8);
             const float4 m0 = mp[0], m1 = mp[1];
-            const float mel8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-            float mf[20], sn[5];
-            psa_note(mel8, mf, sn);
+            const f32x2 mel[4] = {pk2(m0.x, m0.y), pk2(m0.z, m0.w), pk2(m1.x, m1.y), pk2(m1.z, m1.w)};
+            f32x2 mf2[10];
+            float sn[5];
+            psa_note2(mel, mf2, sn);
 #pragma unroll
             for (int e = 0; e < 5; e++) { s.snote[note * 5 + e] = sn[e]; s.dps[note * 5 + e] = 0.f; }
         }
@@ -125,10 +126,7 @@ k_psa_bwd3(PsaBwdArgs3 a) {
         for (int c0 = 0; c0 < C; c0 += 4) {
             const int cg = min(4, C - c0);
             __syncwarp();
-            for (int j = lane; j < 450; j += 32) {
-                const float z = s.zr[j];
-                for (int c = 0; c < cg; c++) s.od[c * 450 + j] = leaky(z + a.Zci[((long long)n * C + c0 + c) * 450 + j]);
-            }
+            psa_build_od(s.od, s.zr, a.Zci + ((long long)n * C + c0) * 450, cg, lane);
             if (c0 + 4 >= C && btf + a.warps < b_hi) {       // both staging rows are consumed: fetch the next unit's
                 __syncwarp();
                 prefetch(u + a.warps);
@@ -136,12 +134,15 @@ k_psa_bwd3(PsaBwdArgs3 a) {
             const bool active = c_l < cg;
             if (!active) {
 #pragma unroll
-                for (int q = 0; q < 30; q++) s.sa[q * 36 + lane] = 0.f;
+                for (int qp = 0; qp < 15; qp++) *reinterpret_cast<f32x2 *>(s.sa + lane * 34 + qp * 2) = pk2(0.f, 0.f);
             }
             __syncwarp();
-            float oct[30], doct[30];
+            f32x2 oct[15], doct[15];
 #pragma unroll
-            for (int q = 0; q < 30; q++) { oct[q] = active ? s.od[c_l * 450 + o * 30 + q] : 0.f; doct[q] = 0.f; }
+            for (int qp = 0; qp < 15; qp++) {
+                oct[qp] = active ? ld2(s.od + c_l * 450 + o * 30 + qp * 2) : pk2(0.f, 0.f);
+                doct[qp] = pk2(0.f, 0.f);
+            }
             const float *deg = s.od + c_l * 450 + 240;
             const float *tg = a.target + ((((long long)n * C + c0 + c_l) * per_n) + btf) * 280;
             float tvel[7];                                   // target velocities of this lane's 7 cells, fetched up front
@@ -153,35 +154,37 @@ k_psa_bwd3(PsaBwdArgs3 a) {
                 float dpre1 = 0.f;
                 bool has_note = false;
                 if (active) {
-                    // dense part: velocity output only (three partial sums keep the FFMA pipe busy)
-                    float av[30];
-                    float y1 = s.snote[note * 5 + 1], y1b = 0.f, y1c = 0.f;
+                    // dense part: velocity output only (three partial sums keep the FMA pipe busy)
+                    f32x2 av[15];
+                    f32x2 ya = pk2(s.snote[note * 5 + 1], 0.f), yb = pk2(0.f, 0.f), yc = pk2(0.f, 0.f);
 #pragma unroll
-                    for (int q = 0; q < 30; q += 3) {
-                        const float v0 = leaky(oct[q] + deg[d * 30 + q]);
-                        const float v1 = leaky(oct[q + 1] + deg[d * 30 + q + 1]);
-                        const float v2 = leaky(oct[q + 2] + deg[d * 30 + q + 2]);
-                        av[q] = v0; av[q + 1] = v1; av[q + 2] = v2;
-                        y1 = fmaf(c_psa[kPsaWl + 50 + q], v0, y1);
-                        y1b = fmaf(c_psa[kPsaWl + 50 + q + 1], v1, y1b);
-                        y1c = fmaf(c_psa[kPsaWl + 50 + q + 2], v2, y1c);
+                    for (int qp = 0; qp < 15; qp += 3) {
+                        av[qp] = leaky2(add2(oct[qp], ld2(deg + d * 30 + qp * 2)));
+                        av[qp + 1] = leaky2(add2(oct[qp + 1], ld2(deg + d * 30 + qp * 2 + 2)));
+                        av[qp + 2] = leaky2(add2(oct[qp + 2], ld2(deg + d * 30 + qp * 2 + 4)));
+                        ya = fma2(MST_CPSA2(kPsaWl + 50 + qp * 2), av[qp], ya);
+                        yb = fma2(MST_CPSA2(kPsaWl + 50 + qp * 2 + 2), av[qp + 1], yb);
+                        yc = fma2(MST_CPSA2(kPsaWl + 50 + qp * 2 + 4), av[qp + 2], yc);
                     }
-                    y1 += y1b + y1c;
+                    const float y1 = sum2(add2(ya, add2(yb, yc)));
                     float tv = tvel[0];
 #pragma unroll
                     for (int dd = 1; dd < 7; dd++) tv = d == dd ? tvel[dd] : tv;
-                    const float p = sigmoidf(y1);
+                    const float p = sigmoid_fast(y1);
                     has_note = tv > 0.f;
                     float dv = cf[0] * (p < tv ? 1.f : (p == tv ? 0.5f : 0.f)) + (p > tv ? cf[1] : 0.f) - (tv > p ? cf[2] : 0.f);
                     if (has_note) dv += cf[3] * 2.f * (p - tv);
                     dpre1 = dv * p * (1.f - p);
                     const float dpre1s = kSlope * dpre1;
+                    const f32x2 dp2 = pk2(dpre1, dpre1);
 #pragma unroll
-                    for (int q = 0; q < 30; q++) {
-                        const float din = c_psa[kPsaWl + 50 + q] * (av[q] > 0.f ? dpre1 : dpre1s);
-                        doct[q] += din;
-                        gw1[q] = fmaf(av[q], dpre1, gw1[q]);
-                        s.sa[q * 36 + lane] = din;
+                    for (int qp = 0; qp < 15; qp++) {
+                        float al, ah;
+                        upk2(av[qp], al, ah);
+                        const f32x2 din = mul2(MST_CPSA2(kPsaWl + 50 + qp * 2), pk2(al > 0.f ? dpre1 : dpre1s, ah > 0.f ? dpre1 : dpre1s));
+                        doct[qp] = add2(doct[qp], din);
+                        gw1[qp] = fma2(av[qp], dp2, gw1[qp]);
+                        *reinterpret_cast<f32x2 *>(s.sa + lane * 34 + qp * 2) = din;
                     }
                 }
                 {   // dps[note][1] += sum over the channel lanes (lane = c * 8 + o: xor 8, 16)
@@ -217,7 +220,7 @@ k_psa_bwd3(PsaBwdArgs3 a) {
                     const float d4 = cf[5] * (y4 - tm[4]) / fmaxf(q4, 1e-12f) * q4;
                     if (lane < 30) {
                         const float ex = (wx0 * d0 + wx2 * d2 + wx3 * d3 + wx4 * d4) * leaky_grad_from_out(am);
-                        s.sa[lane * 36 + m] += ex;
+                        s.sa[m * 34 + lane] += ex;
                         s.exq[lane] = ex;
                         gwx0 = fmaf(am, d0, gwx0); gwx2 = fmaf(am, d2, gwx2); gwx3 = fmaf(am, d3, gwx3); gwx4 = fmaf(am, d4, gwx4);
                     }
@@ -228,34 +231,43 @@ k_psa_bwd3(PsaBwdArgs3 a) {
                     __syncwarp();
                     if (lane == m) {
 #pragma unroll
-                        for (int q = 0; q < 30; q++) doct[q] += s.exq[q];
+                        for (int qp = 0; qp < 15; qp++) doct[qp] = add2(doct[qp], ld2(s.exq + qp * 2));
                     }
                     __syncwarp();
                 }
-                // degree-row gradient: sum over the 8 octave lanes of each channel, written over od in place
-                for (int i = lane; i < cg * 30; i += 32) {
-                    const int c = i / 30, q = i - c * 30;
-                    const float4 v0 = *reinterpret_cast<const float4 *>(s.sa + q * 36 + c * 8);
-                    const float4 v1 = *reinterpret_cast<const float4 *>(s.sa + q * 36 + c * 8 + 4);
-                    const float sum = ((v0.x + v0.y) + (v0.z + v0.w)) + ((v1.x + v1.y) + (v1.z + v1.w));
-                    float *p = s.od + c * 450 + 240 + d * 30 + q;
-                    *p = sum * leaky_grad_from_out(*p);
+                // degree-row gradient: sum over the 8 octave lanes of each channel (lane = column q), written over od in place
+                if (lane < 30) {
+                    for (int c = 0; c < cg; c++) {
+                        const float *col = s.sa + c * 8 * 34 + lane;
+                        const float sum = ((col[0] + col[34]) + (col[68] + col[102])) + ((col[136] + col[170]) + (col[204] + col[238]));
+                        float *p = s.od + c * 450 + 240 + d * 30 + lane;
+                        *p = sum * leaky_grad_from_out(*p);
+                    }
                 }
                 __syncwarp();
             }
             if (active) {
 #pragma unroll
-                for (int q = 0; q < 30; q++) s.od[c_l * 450 + o * 30 + q] = doct[q] * leaky_grad_from_out(oct[q]);
+                for (int qp = 0; qp < 15; qp++) {
+                    float ol, oh;
+                    upk2(oct[qp], ol, oh);
+                    *reinterpret_cast<f32x2 *>(s.od + c_l * 450 + o * 30 + qp * 2) =
+                        mul2(doct[qp], pk2(leaky_grad_from_out(ol), leaky_grad_from_out(oh)));
+                }
             }
             __syncwarp();
-            for (int j = lane; j < 450; j += 32) {
-                float sum = 0.f;
+            for (int jp = lane; jp < 225; jp += 32) {
+                f32x2 sum = pk2(0.f, 0.f);
                 for (int c = 0; c < cg; c++) {
-                    const float v = s.od[c * 450 + j];
-                    sum += v;
-                    atomicAdd(&dzi_s[(c0 + c) * 450 + j], v);
+                    const f32x2 v = ld2(s.od + c * 450 + jp * 2);
+                    float vl, vh;
+                    upk2(v, vl, vh);
+                    sum = add2(sum, v);
+                    atomicAdd(&dzi_s[(c0 + c) * 450 + jp * 2], vl);
+                    atomicAdd(&dzi_s[(c0 + c) * 450 + jp * 2 + 1], vh);
                 }
-                dzr[j] = c0 == 0 ? sum : dzr[j] + sum;
+                f32x2 *dst = reinterpret_cast<f32x2 *>(dzr + jp * 2);
+                *dst = c0 == 0 ? sum : add2(*dst, sum);
             }
         }
         __syncwarp();
@@ -265,7 +277,9 @@ k_psa_bwd3(PsaBwdArgs3 a) {
     // ---- flush the per-lane weight-gradient accumulators
 #pragma unroll
     for (int q = 0; q < 30; q++) {
-        float v = gw1[q];
+        float lo, hi;
+        upk2(gw1[q >> 1], lo, hi);
+        float v = (q & 1) ? hi : lo;
         for (int sft = 16; sft; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
         if (lane == 0 && v != 0.f) atomicAdd(a.gWl + 50 + q, v);
     }
