@@ -322,10 +322,15 @@ struct Launcher {
     }
     void bcast(BcastArgs &a) {
         if (dry) return;
-        const long long rows = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f;
+        const long long prefixes = (long long)a.d.n * a.d.c * a.d.b * a.d.t;
+        bool vec = a.cols % 4 == 0 && (reinterpret_cast<uintptr_t>(a.Y) & 15) == 0;
+        for (int s = 0; s < a.n_src; s++) vec = vec && (reinterpret_cast<uintptr_t>(a.src[s]) & 15) == 0;
+        const int cv = vec ? a.cols / 4 : a.cols;
         int lpr = 32;
-        while (lpr > 1 && lpr / 2 >= a.cols) lpr /= 2;
-        k_bcast_add<<<grid_for(rows * lpr), 256, 0, st>>>(a, lpr); check();
+        while (lpr > 1 && lpr / 2 >= cv) lpr /= 2;
+        if (vec) k_bcast_add<4><<<grid_for(prefixes * lpr), 256, 0, st>>>(a, lpr);
+        else k_bcast_add<1><<<grid_for(prefixes * lpr), 256, 0, st>>>(a, lpr);
+        check();
     }
     void take_last(const float *in, float *out, long long S, int T, int H) { if (dry) return; k_take_last<<<grid_for(S * H), 256, 0, st>>>(in, out, S, T, H); check(); }
     void put_last(const float *src, float *dst, long long S, int T, int H) { if (dry) return; k_put_last<<<grid_for(S * H), 256, 0, st>>>(src, dst, S, T, H); check(); }

@@ -133,40 +133,62 @@ __device__ __forceinline__ long long src_row(const Dims5 &d, int mask, int n, in
     return r;
 }
 
-// `lpr` lanes per row (32, or a smaller power of two for narrow rows): the five coordinates and the source rows are
-// decoded once per row, the columns are a coalesced loop
+// One lane group (`lpr` lanes, a power of two) per (n, c, b, t) prefix: the source rows are decoded once per prefix, the
+// sources that do not depend on f are summed once per column chunk and reused for the d.f rows of the prefix, so a row
+// costs one load per f-dependent source and one store.  VEC = 4 moves 16 bytes per lane (cols % 4 == 0, 16-byte
+// aligned sources and destination; the bias may sit at any float offset and is read with scalar loads).
+template <int VEC>
 __global__ void __launch_bounds__(256)
 k_bcast_add(BcastArgs a, int lpr) {
-    const long long rows = (long long)a.d.n * a.d.c * a.d.b * a.d.t * a.d.f;
+    const long long prefixes = (long long)a.d.n * a.d.c * a.d.b * a.d.t;
+    const int F = a.d.f, cv = a.cols / VEC;
     const int sub = threadIdx.x & (lpr - 1);
     const long long g0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / lpr, n_groups = ((long long)gridDim.x * blockDim.x) / lpr;
-    // each lane group walks a contiguous run of rows: one division chain at the start, then carries
-    const long long per = (rows + n_groups - 1) / n_groups;
-    const long long r_lo = g0 * per, r_hi = min(rows, r_lo + per);
-    if (r_lo >= r_hi) return;
-    int f, t, b, c, n;
-    {
-        long long r = r_lo;
-        f = (int)(r % a.d.f); r /= a.d.f;
-        t = (int)(r % a.d.t); r /= a.d.t;
-        b = (int)(r % a.d.b); r /= a.d.b;
-        c = (int)(r % a.d.c); r /= a.d.c;
-        n = (int)r;
-    }
-    for (long long row = r_lo; row < r_hi; row++) {
+    for (long long p = g0; p < prefixes; p += n_groups) {
+        unsigned r = (unsigned)p;
+        const int t = (int)(r % (unsigned)a.d.t); r /= (unsigned)a.d.t;
+        const int b = (int)(r % (unsigned)a.d.b); r /= (unsigned)a.d.b;
+        const int c = (int)(r % (unsigned)a.d.c); r /= (unsigned)a.d.c;
+        const int n = (int)r;
         const float *sp[kMaxSources];
 #pragma unroll
-        for (int s = 0; s < kMaxSources; s++)
-            sp[s] = s < a.n_src ? a.src[s] + src_row(a.d, a.mask[s], n, c, b, t, f) * a.cols : nullptr;
-        float *y = a.Y + row * a.cols;
-        for (int j = sub; j < a.cols; j += lpr) {
-            float v = a.bias ? a.bias[j] : 0.f;
+        for (int s = 0; s < kMaxSources; s++) {
+            // row of the prefix in source s; an f-dependent source holds d.f consecutive rows from there
+            const long long row = s < a.n_src ? src_row(a.d, a.mask[s] & ~1, n, c, b, t, 0) * ((a.mask[s] & 1) ? F : 1) : 0;
+            sp[s] = s < a.n_src ? a.src[s] + row * a.cols : nullptr;
+        }
+        float *y = a.Y + p * F * a.cols;
+        for (int j = sub; j < cv; j += lpr) {
+            float base[VEC];
+#pragma unroll
+            for (int e = 0; e < VEC; e++) base[e] = a.bias ? a.bias[j * VEC + e] : 0.f;
 #pragma unroll
             for (int s = 0; s < kMaxSources; s++)
-                if (s < a.n_src) v += sp[s][j];
-            y[j] = a.act ? leaky(v) : v;
+                if (s < a.n_src && !(a.mask[s] & 1)) {
+                    if (VEC == 4) { const float4 v = *reinterpret_cast<const float4 *>(sp[s] + j * 4); base[0] += v.x; base[1] += v.y; base[2] += v.z; base[3] += v.w; }
+                    else base[0] += sp[s][j];
+                }
+#pragma unroll 2
+            for (int f = 0; f < F; f++) {
+                float v[VEC];
+#pragma unroll
+                for (int e = 0; e < VEC; e++) v[e] = base[e];
+#pragma unroll
+                for (int s = 0; s < kMaxSources; s++)
+                    if (s < a.n_src && (a.mask[s] & 1)) {
+                        const float *q = sp[s] + (long long)f * a.cols + j * VEC;
+                        if (VEC == 4) { const float4 w = *reinterpret_cast<const float4 *>(q); v[0] += w.x; v[1] += w.y; v[2] += w.z; v[3] += w.w; }
+                        else v[0] += q[0];
+                    }
+                if (a.act) {
+#pragma unroll
+                    for (int e = 0; e < VEC; e++) v[e] = leaky(v[e]);
+                }
+                float *dst = y + (long long)f * a.cols + j * VEC;
+                if (VEC == 4) *reinterpret_cast<float4 *>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+                else dst[0] = v[0];
+            }
         }
-        if (++f == a.d.f) { f = 0; if (++t == a.d.t) { t = 0; if (++b == a.d.b) { b = 0; if (++c == a.d.c) { c = 0; n++; } } } }
     }
 }
 
