@@ -365,7 +365,9 @@ struct Launcher {
         }
         const size_t smem = lstm_smem(H, G, w_smem);
         const int threads = std::max(32, (4 * H + 31) / 32 * 32);
-        dim3 grid(max_blocks, n_jobs);
+        // the kernels loop over the sequence groups: enough CTAs to fill every SM, W_hh staged once per CTA
+        const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2048 / threads, (227 * 1024) / (smem + 1024)));
+        dim3 grid(std::min(max_blocks, std::max(1, 148 * per_sm / n_jobs)), n_jobs);
         if (backward) {
             cudaFuncSetAttribute(k_lstm_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
             k_lstm_bwd<<<grid, threads, smem, st>>>(pack);

@@ -48,16 +48,14 @@ __device__ __forceinline__ void t5_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
 __device__ __forceinline__ void t5_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// x = hi + lo exactly (hi = tf32(x) rounded to nearest, lo = x - hi); the tensor core reads only the tf32 bits of lo, i.e.
+// truncates it: |lo| <= 2^-11 |x|, so the dropped part is below 2^-21 |x|
 __device__ __forceinline__ void t5_split4(const float *v, float4 &hi, float4 &lo) {
-    uint32_t h[4], l[4];
+    uint32_t h[4];
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h[i]) : "f"(v[i]));
-        const float r = v[i] - __uint_as_float(h[i]);
-        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l[i]) : "f"(r));
-    }
+    for (int i = 0; i < 4; i++) asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h[i]) : "f"(v[i]));
     hi = make_float4(__uint_as_float(h[0]), __uint_as_float(h[1]), __uint_as_float(h[2]), __uint_as_float(h[3]));
-    lo = make_float4(__uint_as_float(l[0]), __uint_as_float(l[1]), __uint_as_float(l[2]), __uint_as_float(l[3]));
+    lo = make_float4(v[0] - hi.x, v[1] - hi.y, v[2] - hi.z, v[3] - hi.w);
 }
 
 // shared layout of one (rows x 32) operand tile: 16-byte chunk (row r, k-chunk kc) at (r / 8) * SBO + kc * LBO + (r % 8) * 16.
@@ -125,31 +123,67 @@ k_gemm_t5(GemmArgs g) {
                                    : (((g.a_si & 1) == 0 && (reinterpret_cast<uintptr_t>(g.A) & 7) == 0) ? 2 : 1));
     const int b_vec = !b_kc ? 1 : (((g.b_sj & 3) == 0 && (reinterpret_cast<uintptr_t>(g.B) & 15) == 0) ? 4
                                    : (((g.b_sj & 1) == 0 && (reinterpret_cast<uintptr_t>(g.B) & 7) == 0) ? 2 : 1));
-    int a_row[A_CH], a_kc4[A_CH], b_row[B_CH], b_kc4[B_CH];
+    // per-thread chunk slots: global pointer of the chunk's first element in the current slab (rows clamped into the
+    // matrix: rows / columns past the edge compute garbage that the epilogue never stores), its k offset inside a slab
+    // and its shared-memory offset.  A full slab of a 16-byte-aligned or row-contiguous operand takes the lean path: one
+    // 16-byte load (or four coalesced 4-byte loads) per chunk, no bounds tests.
+    const float *pa[A_CH], *pb[B_CH];
+    int a_k[A_CH], b_k[B_CH];
+    uint32_t a_off[A_CH], b_off[B_CH];
 #pragma unroll
     for (int i = 0; i < A_CH; i++) {
         const int c = tid + i * kT5Threads;
-        if (a_kc) { a_kc4[i] = c & 7; a_row[i] = c >> 3; } else { a_row[i] = c & (BM - 1); a_kc4[i] = c / BM; }
+        int row, kc4;
+        if (a_kc) { kc4 = c & 7; row = c >> 3; } else { row = c & (BM - 1); kc4 = c / BM; }
+        a_k[i] = kc4 * 4;
+        a_off[i] = (uint32_t)(row >> 3) * kT5SBO + (uint32_t)kc4 * kT5LBO + (uint32_t)(row & 7) * 16;
+        pa[i] = g.A + (long long)min(i0 + row, g.M - 1) * g.a_si + (long long)(k_lo + kc4 * 4) * g.a_sk;
     }
 #pragma unroll
     for (int i = 0; i < B_CH; i++) {
-        const int c = tid + i * kT5Threads;
-        if (b_kc) { b_kc4[i] = c & 7; b_row[i] = c >> 3; } else { b_row[i] = c % BN; b_kc4[i] = c / BN; }
+        const int c = min(tid + i * kT5Threads, BN * 8 - 1);          // BN = 16: the upper threads repeat the last chunk
+        int row, kc4;
+        if (b_kc) { kc4 = c & 7; row = c >> 3; } else { row = c % BN; kc4 = c / BN; }
+        b_k[i] = kc4 * 4;
+        b_off[i] = (uint32_t)(2 * A_BYTES) + (uint32_t)(row >> 3) * kT5SBO + (uint32_t)kc4 * kT5LBO + (uint32_t)(row & 7) * 16;
+        pb[i] = g.B + (long long)(k_lo + kc4 * 4) * g.b_sk + (long long)min(j0 + row, g.N - 1) * g.b_sj;
     }
+    const bool a_lean = a_vec == 4 || !a_kc, b_lean = b_vec == 4 || !b_kc;
+    const long long a_step = (long long)KT * g.a_sk, b_step = (long long)KT * g.b_sk;
     float ra[A_CH][4], rb[B_CH][4];
     auto load_slab = [&](int s) {
         const int kb = k_lo + s * KT;
+        const bool full = kb + KT <= k_hi;
+        if (full && a_lean) {
 #pragma unroll
-        for (int i = 0; i < A_CH; i++) {
-            const int gi = i0 + a_row[i], k = kb + a_kc4[i] * 4;
-            t5_load4(g.A + (long long)gi * g.a_si + (long long)k * g.a_sk, g.a_sk, k, k_hi, gi < g.M, a_vec, ra[i]);
+            for (int i = 0; i < A_CH; i++) {
+                if (a_kc) { const float4 x = __ldg(reinterpret_cast<const float4 *>(pa[i])); ra[i][0] = x.x; ra[i][1] = x.y; ra[i][2] = x.z; ra[i][3] = x.w; }
+                else {
+#pragma unroll
+                    for (int e = 0; e < 4; e++) ra[i][e] = __ldg(pa[i] + e * g.a_sk);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < A_CH; i++) t5_load4(pa[i], g.a_sk, kb + a_k[i], k_hi, true, a_vec, ra[i]);
+        }
+        if (full && b_lean) {
+#pragma unroll
+            for (int i = 0; i < B_CH; i++) {
+                if (b_kc) { const float4 x = __ldg(reinterpret_cast<const float4 *>(pb[i])); rb[i][0] = x.x; rb[i][1] = x.y; rb[i][2] = x.z; rb[i][3] = x.w; }
+                else {
+#pragma unroll
+                    for (int e = 0; e < 4; e++) rb[i][e] = __ldg(pb[i] + e * g.b_sk);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < B_CH; i++) t5_load4(pb[i], g.b_sk, kb + b_k[i], k_hi, true, b_vec, rb[i]);
         }
 #pragma unroll
-        for (int i = 0; i < B_CH; i++) {
-            const int gj = j0 + b_row[i], k = kb + b_kc4[i] * 4;
-            const bool ok = tid + i * kT5Threads < BN * 8 && gj < g.N;
-            t5_load4(g.B + (long long)k * g.b_sk + (long long)gj * g.b_sj, g.b_sk, k, k_hi, ok, b_vec, rb[i]);
-        }
+        for (int i = 0; i < A_CH; i++) pa[i] += a_step;
+#pragma unroll
+        for (int i = 0; i < B_CH; i++) pb[i] += b_step;
     };
     auto store_slab = [&](int stage) {
         unsigned char *st = smem + stage * STAGE_BYTES;
@@ -157,18 +191,16 @@ k_gemm_t5(GemmArgs g) {
         for (int i = 0; i < A_CH; i++) {
             float4 hi, lo;
             t5_split4(ra[i], hi, lo);
-            const uint32_t off = (uint32_t)(a_row[i] >> 3) * kT5SBO + (uint32_t)a_kc4[i] * kT5LBO + (uint32_t)(a_row[i] & 7) * 16;
-            *reinterpret_cast<float4 *>(st + off) = hi;
-            *reinterpret_cast<float4 *>(st + A_BYTES + off) = lo;
+            *reinterpret_cast<float4 *>(st + a_off[i]) = hi;
+            *reinterpret_cast<float4 *>(st + A_BYTES + a_off[i]) = lo;
         }
 #pragma unroll
         for (int i = 0; i < B_CH; i++) {
-            if (tid + i * kT5Threads < BN * 8) {
+            if (BN * 8 >= kT5Threads * (i + 1) || tid + i * kT5Threads < BN * 8) {
                 float4 hi, lo;
                 t5_split4(rb[i], hi, lo);
-                const uint32_t off = (uint32_t)(b_row[i] >> 3) * kT5SBO + (uint32_t)b_kc4[i] * kT5LBO + (uint32_t)(b_row[i] & 7) * 16;
-                *reinterpret_cast<float4 *>(st + 2 * A_BYTES + off) = hi;
-                *reinterpret_cast<float4 *>(st + 2 * A_BYTES + B_BYTES + off) = lo;
+                *reinterpret_cast<float4 *>(st + b_off[i]) = hi;
+                *reinterpret_cast<float4 *>(st + B_BYTES + b_off[i]) = lo;
             }
         }
     };

@@ -33,7 +33,6 @@ struct LstmJobs { LstmArgs j[kLstmMaxJobs]; };   // independent recurrences of e
 
 __global__ void k_lstm_fwd(LstmJobs jobs) {
     const LstmArgs &a = jobs.j[blockIdx.y];
-    if (blockIdx.x * a.G >= a.S) return;
     extern __shared__ float sm[];
     const int H = a.H, H4 = 4 * a.H, G = a.G;
     float *h_s = sm;                 // [G][H]
@@ -41,12 +40,13 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
     float *g_s = c_s + G * H;        // [G][4H]
     float *w_s = g_s + G * H4;       // [H][4H] if w_smem
     const int j = threadIdx.x;
-    const int s0 = blockIdx.x * G;
+    if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
+    const float *w = a.w_smem ? w_s : a.w;
+    // persistent over the sequence groups: W_hh is staged once per CTA
+    for (int s0 = blockIdx.x * G; s0 < a.S; s0 += gridDim.x * G) {
     const int ng = min(G, a.S - s0);
     for (int i = j; i < G * H; i += blockDim.x) { h_s[i] = 0.f; c_s[i] = 0.f; }
-    if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
     __syncthreads();
-    const float *w = a.w_smem ? w_s : a.w;
     float xnext[kLstmG];      // input projection of the next step, fetched while this step computes
     {
         const int t0 = a.reverse ? a.T - 1 : 0;
@@ -85,21 +85,24 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
                 acc[0] = (a0 + a1) + (a2 + a3);
             } else {
                 // G == kLstmG sequences: h is kept k-major ([k][G]) so one step reads the 8 states with two 16-byte loads
+                // (packed fp32: four FFMA2 per k for the eight sequences)
+                f32x2 ac2[4] = {pk2(acc[0], acc[1]), pk2(acc[2], acc[3]), pk2(acc[4], acc[5]), pk2(acc[6], acc[7])};
 #pragma unroll 4
                 for (int k = 0; k < H; k++) {
                     const float wv = w[k * H4 + j];
-                    const float4 h0 = *reinterpret_cast<const float4 *>(h_s + k * kLstmG);
-                    const float4 h1 = *reinterpret_cast<const float4 *>(h_s + k * kLstmG + 4);
-                    acc[0] = fmaf(wv, h0.x, acc[0]); acc[1] = fmaf(wv, h0.y, acc[1]);
-                    acc[2] = fmaf(wv, h0.z, acc[2]); acc[3] = fmaf(wv, h0.w, acc[3]);
-                    acc[4] = fmaf(wv, h1.x, acc[4]); acc[5] = fmaf(wv, h1.y, acc[5]);
-                    acc[6] = fmaf(wv, h1.z, acc[6]); acc[7] = fmaf(wv, h1.w, acc[7]);
+                    const f32x2 ww = pk2(wv, wv);
+                    const ulonglong2 h0 = *reinterpret_cast<const ulonglong2 *>(h_s + k * kLstmG);
+                    const ulonglong2 h1 = *reinterpret_cast<const ulonglong2 *>(h_s + k * kLstmG + 4);
+                    ac2[0] = fma2(ww, h0.x, ac2[0]); ac2[1] = fma2(ww, h0.y, ac2[1]);
+                    ac2[2] = fma2(ww, h1.x, ac2[2]); ac2[3] = fma2(ww, h1.y, ac2[3]);
                 }
+#pragma unroll
+                for (int g2 = 0; g2 < 4; g2++) upk2(ac2[g2], acc[g2 * 2], acc[g2 * 2 + 1]);
             }
             const bool is_tanh = (j >= 2 * H) && (j < 3 * H);
 #pragma unroll
             for (int g = 0; g < kLstmG; g++) if (g < ng) {
-                const float v = is_tanh ? tanhf(acc[g]) : sigmoidf(acc[g]);
+                const float v = is_tanh ? tanhf(acc[g]) : sigmoid_fast(acc[g]);
                 g_s[g * H4 + j] = v;
                 a.gates[((long long)(s0 + g) * a.T + t) * H4 + j] = v;
             }
@@ -120,11 +123,11 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
         }
         __syncthreads();
     }
+    }
 }
 
 __global__ void k_lstm_bwd(LstmJobs jobs) {
     const LstmArgs &a = jobs.j[blockIdx.y];
-    if (blockIdx.x * a.G >= a.S) return;
     extern __shared__ float sm[];
     const int H = a.H, H4 = 4 * a.H, G = a.G;
     float *dh_s = sm;                 // [G][H]  dL/dh carried from the later step
@@ -133,12 +136,12 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
     float *part_s = dg_s + G * H4;    // [4][G][H] partial dh sums
     float *w_s = part_s + 4 * G * H;  // [4H][H] if w_smem
     const int j = threadIdx.x;
-    const int s0 = blockIdx.x * G;
+    if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
+    const float *w = a.w_smem ? w_s : a.w;
+    for (int s0 = blockIdx.x * G; s0 < a.S; s0 += gridDim.x * G) {          // persistent over the sequence groups
     const int ng = min(G, a.S - s0);
     for (int i = j; i < G * H; i += blockDim.x) { dh_s[i] = 0.f; dc_s[i] = 0.f; }
-    if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
     __syncthreads();
-    const float *w = a.w_smem ? w_s : a.w;
     for (int step = a.T - 1; step >= 0; step--) {
         const int t = a.reverse ? a.T - 1 - step : step;          // time index of forward step `step`
         const int t_prev = a.reverse ? t + 1 : t - 1;             // where c_{step-1} lives
@@ -178,19 +181,19 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
             const int part = j / H, k = j - part * H;
             if (part < qparts) {
                 const int r_lo = (int)((long long)H4 * part / qparts), r_hi = (int)((long long)H4 * (part + 1) / qparts);
-                float acc[kLstmG];
-#pragma unroll
-                for (int g = 0; g < kLstmG; g++) acc[g] = 0.f;
+                f32x2 ac2[4] = {pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f)};
 #pragma unroll 4
                 for (int r = r_lo; r < r_hi; r++) {
                     const float wv = w[r * H + k];
-                    const float4 d0 = *reinterpret_cast<const float4 *>(dg_s + r * kLstmG);
-                    const float4 d1 = *reinterpret_cast<const float4 *>(dg_s + r * kLstmG + 4);
-                    acc[0] = fmaf(wv, d0.x, acc[0]); acc[1] = fmaf(wv, d0.y, acc[1]);
-                    acc[2] = fmaf(wv, d0.z, acc[2]); acc[3] = fmaf(wv, d0.w, acc[3]);
-                    acc[4] = fmaf(wv, d1.x, acc[4]); acc[5] = fmaf(wv, d1.y, acc[5]);
-                    acc[6] = fmaf(wv, d1.z, acc[6]); acc[7] = fmaf(wv, d1.w, acc[7]);
+                    const f32x2 ww = pk2(wv, wv);
+                    const ulonglong2 d0 = *reinterpret_cast<const ulonglong2 *>(dg_s + r * kLstmG);
+                    const ulonglong2 d1 = *reinterpret_cast<const ulonglong2 *>(dg_s + r * kLstmG + 4);
+                    ac2[0] = fma2(ww, d0.x, ac2[0]); ac2[1] = fma2(ww, d0.y, ac2[1]);
+                    ac2[2] = fma2(ww, d1.x, ac2[2]); ac2[3] = fma2(ww, d1.y, ac2[3]);
                 }
+                float acc[kLstmG];
+#pragma unroll
+                for (int g2 = 0; g2 < 4; g2++) upk2(ac2[g2], acc[g2 * 2], acc[g2 * 2 + 1]);
 #pragma unroll
                 for (int g = 0; g < kLstmG; g++) part_s[(part * kLstmG + g) * H + k] = acc[g];
             }
@@ -241,6 +244,7 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
             }
         }
         __syncthreads();
+    }
     }
 }
 

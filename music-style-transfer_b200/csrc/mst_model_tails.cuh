@@ -49,33 +49,7 @@ __device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
 }
 
-// ---- packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2): one issue slot carries two fp32 operations.  These kernels are
-// issue-bound, not FMA-pipe-bound (profiles/r1_ffma2_issue_probe.txt), so the pairs run over the contraction index and
-// the two partial sums are added once at the end.  A pair is a 64-bit register: .x = low word, .y = high word.
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-__device__ __forceinline__ void upk2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ float sum2(f32x2 v) { float lo, hi; upk2(v, lo, hi); return lo + hi; }
-// leaky_relu of both halves: max(x, slope * x) equals the select form for every finite x (0 < slope < 1)
-__device__ __forceinline__ f32x2 leaky2(f32x2 x) {
-    float xl, xh, tl, th;
-    upk2(x, xl, xh);
-    upk2(mul2(x, pk2(kSlope, kSlope)), tl, th);
-    return pk2(fmaxf(xl, tl), fmaxf(xh, th));
-}
-__device__ __forceinline__ f32x2 ld2(const float *p) { return *reinterpret_cast<const f32x2 *>(p); }      // 8-byte aligned
 #define MST_CPSA2(off) (*reinterpret_cast<const f32x2 *>(&c_psa[off]))                                    // even offsets
-// sigmoid from the SFU approximations (ex2.approx, rcp.approx: ~2 ulp each, far inside the 1e-5 loss tolerance)
-__device__ __forceinline__ float sigmoid_fast(float x) {
-    float e, r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
-    return r;
-}
-
 // phase 1 for one note: mf[20] (as 10 pairs) and snote[5] from the melody vector (4 pairs)
 __device__ __forceinline__ void psa_note2(const f32x2 *mel, f32x2 *mf2, float *sn) {
 #pragma unroll
