@@ -260,12 +260,28 @@ struct Launcher {
         else if (bk) k_gemm_tc<BN, false, true><<<grid, kTcThreads, 0, st>>>(g);
         else k_gemm_tc<BN, false, false><<<grid, kTcThreads, 0, st>>>(g);
     }
+    // operand access mode of the tcgen05 GEMM (mst_model_gemm_t5.cuh): 0 = k-contiguous rows on 16-byte boundaries,
+    // 1 = on 8-byte boundaries, 2 = any strides
+    static int t5_mode(const float *p, long long s_row, long long s_k) {
+        if (s_k != 1) return 2;
+        if ((s_row & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) return 0;
+        if ((s_row & 1) == 0 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) return 1;
+        return 2;
+    }
+    template <int BN, int AM, int BMD>
+    void gemm_t5_launch(const GemmArgs &g, dim3 grid) {
+        static bool attr_set = false;
+        if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN, AM, BMD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN>()); attr_set = true; }
+        k_gemm_t5<BN, AM, BMD><<<grid, kT5Block, t5_smem_bytes<BN>(), st>>>(g);
+    }
     template <int BN>
     void gemm_t5(const GemmArgs &g, int split_k) {
         dim3 grid((g.N + BN - 1) / BN, (g.M + kT5BM - 1) / kT5BM, split_k);
-        static bool attr_set = false;
-        if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN>()); attr_set = true; }
-        k_gemm_t5<BN><<<grid, kT5Block, t5_smem_bytes<BN>(), st>>>(g);
+        const int am = t5_mode(g.A, g.a_si, g.a_sk);
+        const int bm = t5_mode(g.B, g.b_sj, g.b_sk) == 0 ? 0 : 2;          // the small operand: aligned or generic
+        if (am == 0) { if (bm == 0) gemm_t5_launch<BN, 0, 0>(g, grid); else gemm_t5_launch<BN, 0, 2>(g, grid); }
+        else if (am == 1) { if (bm == 0) gemm_t5_launch<BN, 1, 0>(g, grid); else gemm_t5_launch<BN, 1, 2>(g, grid); }
+        else { if (bm == 0) gemm_t5_launch<BN, 2, 0>(g, grid); else gemm_t5_launch<BN, 2, 2>(g, grid); }
     }
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
@@ -275,7 +291,19 @@ struct Launcher {
         if (dry || M <= 0 || N <= 0 || K <= 0) return;
         GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
         if (split_k > 1) g.accumulate = 2;
-        if (kernel == 3 || (kernel == 0 && use_tc(M, N, K) && K >= 24)) {
+        if (kernel == 0 && K <= kSkMaxK && N <= 512 && N >= 128 && M >= 4096 && a_sk == 1 && split_k == 1 && accumulate != 2) {
+            // short contraction, wide output, many rows: the row-streaming kernel (mst_model_gemm_tc.cuh)
+            const int threads = (N + 31) / 32 * 32;
+            const int blocks = std::min((M + kSkRows - 1) / kSkRows, 148 * (threads <= 512 ? 2 : 1));
+            switch ((K + 3) / 4) {
+                case 1: k_gemm_smallk<4><<<blocks, threads, 0, st>>>(g); break;
+                case 2: k_gemm_smallk<8><<<blocks, threads, 0, st>>>(g); break;
+                case 3: k_gemm_smallk<12><<<blocks, threads, 0, st>>>(g); break;
+                case 4: k_gemm_smallk<16><<<blocks, threads, 0, st>>>(g); break;
+                case 5: k_gemm_smallk<20><<<blocks, threads, 0, st>>>(g); break;
+                default: k_gemm_smallk<24><<<blocks, threads, 0, st>>>(g); break;
+            }
+        } else if (kernel == 3 || (kernel == 0 && use_tc(M, N, K) && K >= 24)) {
             if (N <= 16) gemm_t5<16>(g, split_k); else if (N <= 32) gemm_t5<32>(g, split_k); else gemm_t5<64>(g, split_k);
         } else if (kernel == 2 || (kernel == 0 && use_tc(M, N, K))) {
             if (N <= 32) gemm_tc<32>(g, split_k); else gemm_tc<64>(g, split_k);

@@ -48,13 +48,10 @@ __device__ __forceinline__ void t5_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
 __device__ __forceinline__ void t5_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-// x = hi + lo exactly (hi = tf32(x) rounded to nearest, lo = x - hi); the tensor core reads only the tf32 bits of lo, i.e.
-// truncates it: |lo| <= 2^-11 |x|, so the dropped part is below 2^-21 |x|
+// x = hi + lo exactly: hi = tf32_rna(x) (mst_model_kernels.cuh), lo = x - hi.  The tensor core reads only the tf32 bits of lo, i.e. truncates it:
+// |lo| <= 2^-11 |x|, so the dropped part is below 2^-21 |x|.
 __device__ __forceinline__ void t5_split4(const float *v, float4 &hi, float4 &lo) {
-    uint32_t h[4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h[i]) : "f"(v[i]));
-    hi = make_float4(__uint_as_float(h[0]), __uint_as_float(h[1]), __uint_as_float(h[2]), __uint_as_float(h[3]));
+    hi = make_float4(tf32_rna(v[0]), tf32_rna(v[1]), tf32_rna(v[2]), tf32_rna(v[3]));
     lo = make_float4(v[0] - hi.x, v[1] - hi.y, v[2] - hi.z, v[3] - hi.w);
 }
 
@@ -64,22 +61,30 @@ __device__ __forceinline__ void t5_split4(const float *v, float4 &hi, float4 &lo
 constexpr uint32_t kT5LBO = 144, kT5SBO = 8 * kT5LBO;
 __host__ __device__ constexpr int t5_tile_bytes(int rows) { return rows / 8 * (int)kT5SBO; }
 
-// 4 consecutive k of one row -> registers (vector load when the address allows, zero fill outside [.., k_hi))
-__device__ __forceinline__ void t5_load4(const float *p, long long sk, int k, int k_hi, bool row_ok, int vec, float *v) {
-    if (!row_ok || k >= k_hi) { v[0] = v[1] = v[2] = v[3] = 0.f; return; }
-    if (k + 3 < k_hi && vec == 4) {
+// operand access modes (chosen on the host from strides and alignment, compile-time in the kernel so that the slab loop
+// holds exactly the loads it executes): 0 = k-contiguous, 16-byte aligned rows (one 16-byte load per chunk), 1 =
+// k-contiguous, 8-byte aligned rows (two 8-byte loads), 2 = any strides (four 4-byte loads `sk` apart; coalesced over
+// the lanes in whichever direction is contiguous)
+template <int MODE>
+__device__ __forceinline__ void t5_load_full(const float *p, long long sk, float *v) {
+    if (MODE == 0) {
         const float4 x = __ldg(reinterpret_cast<const float4 *>(p));
         v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
-    } else if (k + 3 < k_hi && vec == 2) {
+    } else if (MODE == 1) {
         const float2 x = __ldg(reinterpret_cast<const float2 *>(p)), y = __ldg(reinterpret_cast<const float2 *>(p + 2));
         v[0] = x.x; v[1] = x.y; v[2] = y.x; v[3] = y.y;
     } else {
 #pragma unroll
-        for (int e = 0; e < 4; e++) v[e] = k + e < k_hi ? __ldg(p + e * sk) : 0.f;
+        for (int e = 0; e < 4; e++) v[e] = __ldg(p + e * sk);
     }
 }
+// the last, partial slab: zero fill at and beyond k_hi
+__device__ __forceinline__ void t5_load_tail(const float *p, long long sk, int k, int k_hi, float *v) {
+#pragma unroll
+    for (int e = 0; e < 4; e++) v[e] = k + e < k_hi ? __ldg(p + e * sk) : 0.f;
+}
 
-template <int BN>
+template <int BN, int AMODE, int BMODE>
 __global__ void __launch_bounds__(kT5Block, 2)
 k_gemm_t5(GemmArgs g) {
     constexpr int BM = kT5BM, KT = kT5BK;
@@ -118,15 +123,10 @@ k_gemm_t5(GemmArgs g) {
 
     // ---- loader roles.  A k-contiguous operand is walked chunk-fastest (8 lanes = one row's 128 bytes), a row-contiguous
     // one row-fastest (32 lanes = 32 consecutive rows of one k); either way thread-chunk i is (row, kc) below.
-    const bool a_kc = g.a_sk == 1, b_kc = g.b_sk == 1;
-    const int a_vec = !a_kc ? 1 : (((g.a_si & 3) == 0 && (reinterpret_cast<uintptr_t>(g.A) & 15) == 0) ? 4
-                                   : (((g.a_si & 1) == 0 && (reinterpret_cast<uintptr_t>(g.A) & 7) == 0) ? 2 : 1));
-    const int b_vec = !b_kc ? 1 : (((g.b_sj & 3) == 0 && (reinterpret_cast<uintptr_t>(g.B) & 15) == 0) ? 4
-                                   : (((g.b_sj & 1) == 0 && (reinterpret_cast<uintptr_t>(g.B) & 7) == 0) ? 2 : 1));
-    // per-thread chunk slots: global pointer of the chunk's first element in the current slab (rows clamped into the
+    // Per-thread chunk slots: global pointer of the chunk's first element in the current slab (rows clamped into the
     // matrix: rows / columns past the edge compute garbage that the epilogue never stores), its k offset inside a slab
-    // and its shared-memory offset.  A full slab of a 16-byte-aligned or row-contiguous operand takes the lean path: one
-    // 16-byte load (or four coalesced 4-byte loads) per chunk, no bounds tests.
+    // and its shared-memory offset.
+    const bool a_kc = g.a_sk == 1, b_kc = g.b_sk == 1;
     const float *pa[A_CH], *pb[B_CH];
     int a_k[A_CH], b_k[B_CH];
     uint32_t a_off[A_CH], b_off[B_CH];
@@ -134,7 +134,7 @@ k_gemm_t5(GemmArgs g) {
     for (int i = 0; i < A_CH; i++) {
         const int c = tid + i * kT5Threads;
         int row, kc4;
-        if (a_kc) { kc4 = c & 7; row = c >> 3; } else { row = c & (BM - 1); kc4 = c / BM; }
+        if (AMODE < 2 || a_kc) { kc4 = c & 7; row = c >> 3; } else { row = c & (BM - 1); kc4 = c / BM; }
         a_k[i] = kc4 * 4;
         a_off[i] = (uint32_t)(row >> 3) * kT5SBO + (uint32_t)kc4 * kT5LBO + (uint32_t)(row & 7) * 16;
         pa[i] = g.A + (long long)min(i0 + row, g.M - 1) * g.a_si + (long long)(k_lo + kc4 * 4) * g.a_sk;
@@ -143,47 +143,26 @@ k_gemm_t5(GemmArgs g) {
     for (int i = 0; i < B_CH; i++) {
         const int c = min(tid + i * kT5Threads, BN * 8 - 1);          // BN = 16: the upper threads repeat the last chunk
         int row, kc4;
-        if (b_kc) { kc4 = c & 7; row = c >> 3; } else { row = c % BN; kc4 = c / BN; }
+        if (BMODE < 2 || b_kc) { kc4 = c & 7; row = c >> 3; } else { row = c % BN; kc4 = c / BN; }
         b_k[i] = kc4 * 4;
         b_off[i] = (uint32_t)(2 * A_BYTES) + (uint32_t)(row >> 3) * kT5SBO + (uint32_t)kc4 * kT5LBO + (uint32_t)(row & 7) * 16;
         pb[i] = g.B + (long long)(k_lo + kc4 * 4) * g.b_sk + (long long)min(j0 + row, g.N - 1) * g.b_sj;
     }
-    const bool a_lean = a_vec == 4 || !a_kc, b_lean = b_vec == 4 || !b_kc;
     const long long a_step = (long long)KT * g.a_sk, b_step = (long long)KT * g.b_sk;
+    const int n_full = (k_hi - k_lo) / KT;                            // slabs that need no zero fill
     float ra[A_CH][4], rb[B_CH][4];
-    auto load_slab = [&](int s) {
-        const int kb = k_lo + s * KT;
-        const bool full = kb + KT <= k_hi;
-        if (full && a_lean) {
+    auto load_full = [&]() {
 #pragma unroll
-            for (int i = 0; i < A_CH; i++) {
-                if (a_kc) { const float4 x = __ldg(reinterpret_cast<const float4 *>(pa[i])); ra[i][0] = x.x; ra[i][1] = x.y; ra[i][2] = x.z; ra[i][3] = x.w; }
-                else {
+        for (int i = 0; i < A_CH; i++) { t5_load_full<AMODE>(pa[i], g.a_sk, ra[i]); pa[i] += a_step; }
 #pragma unroll
-                    for (int e = 0; e < 4; e++) ra[i][e] = __ldg(pa[i] + e * g.a_sk);
-                }
-            }
-        } else {
+        for (int i = 0; i < B_CH; i++) { t5_load_full<BMODE>(pb[i], g.b_sk, rb[i]); pb[i] += b_step; }
+    };
+    auto load_tail = [&]() {
+        const int kb = k_lo + n_full * KT;
 #pragma unroll
-            for (int i = 0; i < A_CH; i++) t5_load4(pa[i], g.a_sk, kb + a_k[i], k_hi, true, a_vec, ra[i]);
-        }
-        if (full && b_lean) {
+        for (int i = 0; i < A_CH; i++) t5_load_tail(pa[i], g.a_sk, kb + a_k[i], k_hi, ra[i]);
 #pragma unroll
-            for (int i = 0; i < B_CH; i++) {
-                if (b_kc) { const float4 x = __ldg(reinterpret_cast<const float4 *>(pb[i])); rb[i][0] = x.x; rb[i][1] = x.y; rb[i][2] = x.z; rb[i][3] = x.w; }
-                else {
-#pragma unroll
-                    for (int e = 0; e < 4; e++) rb[i][e] = __ldg(pb[i] + e * g.b_sk);
-                }
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < B_CH; i++) t5_load4(pb[i], g.b_sk, kb + b_k[i], k_hi, true, b_vec, rb[i]);
-        }
-#pragma unroll
-        for (int i = 0; i < A_CH; i++) pa[i] += a_step;
-#pragma unroll
-        for (int i = 0; i < B_CH; i++) pb[i] += b_step;
+        for (int i = 0; i < B_CH; i++) t5_load_tail(pb[i], g.b_sk, kb + b_k[i], k_hi, rb[i]);
     };
     auto store_slab = [&](int stage) {
         unsigned char *st = smem + stage * STAGE_BYTES;
@@ -210,7 +189,7 @@ k_gemm_t5(GemmArgs g) {
 
     if (warp < 8) {
         // ---- producers: split + store slab s, publish it on the stage's "full" barrier, then fetch slab s + 1
-        load_slab(0);
+        if (n_full > 0) load_full(); else load_tail();
         for (int s = 0; s < n_slabs; s++) {
             const int stage = s & 1;
             if (s >= 2) mbar_wait(bar_empty + 8 * stage, (uint32_t)(((s >> 1) - 1) & 1));   // MMAs of slab s - 2 have read it
@@ -218,7 +197,8 @@ k_gemm_t5(GemmArgs g) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_full + 8 * stage) : "memory");
-            if (s + 1 < n_slabs) load_slab(s + 1);
+            if (s + 1 < n_full) load_full();
+            else if (s + 1 < n_slabs) load_tail();
         }
     } else if (lane == 0) {
         // ---- consumer: one thread issues the MMAs of a slab as soon as all 8 producer warps have published it

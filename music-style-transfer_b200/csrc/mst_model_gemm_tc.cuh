@@ -21,9 +21,9 @@ namespace mstm {
 constexpr int kTcBM = 128, kTcBK = 16, kTcThreads = 256, kTcStages = 3;
 
 __device__ __forceinline__ void tc_split(float x, uint32_t &hi, uint32_t &lo) {
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-    const float r = x - __uint_as_float(hi);
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+    const float h = tf32_rna(x);
+    hi = __float_as_uint(h);
+    lo = __float_as_uint(tf32_rna(x - h));
 }
 
 __device__ __forceinline__ void tc_mma(float *d, const uint32_t *a, const uint32_t *b) {
@@ -169,6 +169,75 @@ k_gemm_tc(GemmArgs g) {
                 else if (g.accumulate == 1) { dst[0] += v0; if (has1) dst[1] += v1; }
                 else { atomicAdd(dst, v0); if (has1) atomicAdd(dst + 1, v1); }
             }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_gemm_smallk — C[M, N] (op)= act(A[M, K] . B + bias) for a SHORT contraction (K <= kSkMaxK) over a huge row count:
+// the Zr projections of the style appliers (rhythm features, K = 10 / 17, to 450 / 376 columns).  These are pure
+// output streams (0.9 GB written, ~20 MB read): the tensor-core kernels pay their staging and epilogue for nothing.
+// Thread j owns output column j: its K weights sit in registers as (w, w) pairs for the whole (persistent) CTA; rows
+// are taken four at a time from a transposed shared tile ([k][row], one broadcast 16-byte load per k) and multiplied as
+// two packed FFMA2; a warp stores 128 contiguous bytes per row.  A rows must be k-contiguous (a_sk == 1).
+// ------------------------------------------------------------------------------------------------
+constexpr int kSkMaxK = 24, kSkRows = 64;
+
+// KP = K rounded up to a multiple of 4 (compile-time trip count; the padding weights and tile rows are zero)
+template <int KP>
+__global__ void __launch_bounds__(512, 2)
+k_gemm_smallk(GemmArgs g) {
+    __shared__ __align__(16) float xs[2][KP][kSkRows];
+    const int j = threadIdx.x, K = g.K;
+    const bool col_ok = j < g.N;
+    for (int i = threadIdx.x; i < 2 * (KP - K) * kSkRows; i += blockDim.x)
+        xs[i / ((KP - K) * kSkRows)][K + (i / kSkRows) % (KP - K)][i % kSkRows] = 0.f;
+    f32x2 w[KP];
+#pragma unroll
+    for (int k = 0; k < KP; k++) {
+        const float v = (col_ok && k < K) ? g.B[(long long)k * g.b_sk + (long long)j * g.b_sj] : 0.f;
+        w[k] = pk2(v, v);
+    }
+    const float bias = (col_ok && g.bias) ? g.bias[j] : 0.f;
+    const f32x2 bias2 = pk2(bias, bias);
+    const int n_blocks = (g.M + kSkRows - 1) / kSkRows;
+    // x tile of block b -> xs[buf] transposed; rows past M are clamped (their outputs are never stored)
+    auto stage = [&](int b, int buf) {
+        const int r0 = b * kSkRows;
+        for (int i = threadIdx.x; i < kSkRows * K; i += blockDim.x) {
+            const int r = i / K, k = i - r * K;
+            xs[buf][k][r] = g.A[(long long)min(r0 + r, g.M - 1) * g.a_si + k];
+        }
+    };
+    int buf = 0;
+    if ((int)blockIdx.x < n_blocks) stage(blockIdx.x, 0);
+    __syncthreads();
+    for (int b = blockIdx.x; b < n_blocks; b += gridDim.x, buf ^= 1) {
+        if (b + (int)gridDim.x < n_blocks) stage(b + gridDim.x, buf ^ 1);
+        if (col_ok) {
+            const int r0 = b * kSkRows;
+#pragma unroll 2
+            for (int r = 0; r < kSkRows; r += 4) {
+                f32x2 a0 = bias2, a1 = bias2;
+#pragma unroll
+                for (int k = 0; k < KP; k++) {
+                    const ulonglong2 x = *reinterpret_cast<const ulonglong2 *>(&xs[buf][k][r]);
+                    a0 = fma2(x.x, w[k], a0);
+                    a1 = fma2(x.y, w[k], a1);
+                }
+                float v[4];
+                upk2(a0, v[0], v[1]);
+                upk2(a1, v[2], v[3]);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    if (r0 + r + e < g.M) {
+                        float o = g.act == 1 ? leaky(v[e]) : v[e];
+                        float *dst = g.C + (long long)(r0 + r + e) * g.c_si + j;
+                        *dst = g.accumulate == 1 ? *dst + o : o;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
 }
 
 }  // namespace mstm

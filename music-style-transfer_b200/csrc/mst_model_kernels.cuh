@@ -21,6 +21,11 @@ __device__ __forceinline__ float sigmoidf(float x) { return 1.f / (1.f + expf(-x
 // ---- packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2): one issue slot carries two fp32 operations.  These kernels are
 // issue-bound, not FMA-pipe-bound (profiles/r1_ffma2_issue_probe.txt), so the pairs run over the contraction index and
 // the two partial sums are added once at the end.  A pair is a 64-bit register: .x = low word, .y = high word.
+// fp32 -> tf32, round to nearest with ties away (add half an ulp of the 10-bit mantissa to the bit pattern, clear the 13
+// low bits): what cvt.rna.tf32.f32 computes for finite x, in two integer instructions where the cvt expands to four
+// (add, |x| < inf test, select, mask) on sm_100
+__device__ __forceinline__ float tf32_rna(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
+
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 __device__ __forceinline__ void upk2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }

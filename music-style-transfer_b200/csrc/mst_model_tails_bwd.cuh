@@ -40,11 +40,7 @@ struct PsaBwdWarpSmem {
 };
 static_assert(sizeof(PsaBwdWarpSmem) % 16 == 0, "per-warp shared block must stay 16-byte aligned");
 
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
+__device__ __forceinline__ uint32_t to_tf32(float x) { return __float_as_uint(tf32_rna(x)); }
 // D (16x8, fp32) += A (16x8) . B (8x8) with fp32 inputs split into tf32 hi + lo parts (3 MMAs: lo.hi + hi.lo + hi.hi)
 __device__ __forceinline__ void mma_tf32x3(float *d, const float *a, const float *b) {
     uint32_t ah[4], al[4], bh[2], bl[2];

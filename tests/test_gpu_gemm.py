@@ -28,10 +28,16 @@ CASES = [  # (M, N, K, layout, split_k, bias, act, accumulate)
     (2048, 256, 192, 'dx', 1, False, 0, 1),
     (5, 7, 3, 'linear', 1, True, 0, 0),
 ]
+# short contractions over many rows: kernel 0 (auto) routes them to the row-streaming k_gemm_smallk
+SMALLK_CASES = [
+    (5003, 450, 10, 'linear', 1, True, 0, 0),
+    (4100, 376, 17, 'linear', 1, True, 1, 0),
+    (4099, 130, 24, 'linear', 1, False, 0, 1),
+    (4160, 512, 4, 'dx', 1, False, 0, 0),
+]
 
 
-@pytest.mark.parametrize('kernel', [1, 2, 3])
-@pytest.mark.parametrize('case', CASES)
+@pytest.mark.parametrize('case,kernel', [(c, k) for c in CASES for k in (1, 2, 3)] + [(c, 0) for c in CASES + SMALLK_CASES])
 def test_gemm_matches_float64(torch, case, kernel):
     from mst_native import model as mm
     M, N, K, layout, split, use_bias, act, accumulate = case
