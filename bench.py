@@ -174,14 +174,17 @@ def run_decode(args, world, rank, torch, dist, L, lib, abi, batch, filt, arena):
 
 
 TRAIN_SHAPE = dict(C=4, B=200, nb=4, drums=True)     # the 800 channel-bar crop of train-model.py:101
+LONG_SHAPE = dict(C=8, B=800, nb=4, drums=True)      # 8x the default sequence length (C.B = 6400)
 
 
-def training_config(per_gpu, world):
-    return {'workload': 'configs[3]: synthetic-batch training of the style model (C=4 pitched channels x B=200 bars, 4/4, '
+def training_config(per_gpu, world, sh=None):
+    sh = sh or TRAIN_SHAPE
+    name = 'configs[4]: long-sequence training' if sh['C'] * sh['B'] > 800 else 'configs[3]: synthetic-batch training'
+    return {'workload': f'{name} of the style model (C={sh["C"]} pitched channels x B={sh["B"]} bars, 4/4, '
                         'drums present, Bernoulli(0.003) grids, seed-108 weights), forward + get_total_loss + backward + '
                         'all-reduce + Adam per step', 'per_gpu_batch': per_gpu, 'global_batch': per_gpu * world,
             'gradient': 'sum over samples (iter_size semantics)', 'parallelism': f'dp{world}',
-            'l2_policy': 'inputs larger than L2: >=155 MB of grids + >=0.8 GB of activations per step'}
+            'l2_policy': 'inputs larger than L2: >=155 MB of grids + >=0.8 GB of activations per sample'}
 
 
 def k_grid_traffic(songs_per_step):
@@ -200,13 +203,14 @@ def algorithmic_bytes_per_sample(C, B, nb, drums):
     return 4 * 4 * nb * 10 * (280 * C + (94 if drums else 0)) * B
 
 
-def run_training(args, world, rank, torch, dist):
-    """Training leg (BASELINE.json configs[3]): samples/s over all ranks, device-timed, max over ranks."""
+def run_training(args, world, rank, torch, dist, sh=None, N=None):
+    """Training leg (BASELINE.json configs[3], or configs[4] with sh=LONG_SHAPE): samples/s over all ranks,
+    device-timed, max over ranks."""
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import model_oracle as mo            # synthetic sample generator + seed-108 weights (data, not compute)
     from mst_native import trainer as tr
-    N = args.train_batch
-    sh = TRAIN_SHAPE
+    N = N or args.train_batch
+    sh = sh or TRAIN_SHAPE
     distinct = [mo.synthetic_sample(seed=7 + 100 * rank + i, **sh) for i in range(min(N, 4))]
     pick = lambda k: torch.cat([distinct[i % len(distinct)][k] for i in range(N)]).contiguous()
     host = {k: pick(k).pin_memory() for k in ('pitched', 'unpitched', 'feats', 'mode', 'bpm')}
@@ -299,7 +303,7 @@ def run_training(args, world, rank, torch, dist):
     alg = algorithmic_bytes_per_sample(**sh)
     out = {
         'metric': 'training samples/sec', 'value': value, 'unit': 'samples/s', 'ms_per_step': s_per_step * 1e3,
-        'steps': args.train_steps, 'config': training_config(N, world), 'dtype': 'f32',
+        'steps': args.train_steps, 'config': training_config(N, world, sh), 'dtype': 'f32',
         'loss_total_sample0': loss0, 'gpu_launches_per_step': launches,
         'roofline': {'kernel': 'whole training step (all kernels)', 'bound': 'hbm',
                      'achieved': alg * N / s_per_step / 1e9, 'peak': peak, 'unit': 'GB/s',
@@ -388,6 +392,8 @@ def main():
     ap.add_argument('--train-batch', type=int, default=64, help='training samples per step per GPU')
     ap.add_argument('--train-steps', type=int, default=0, help='timed training steps (default: min(steps, 10))')
     ap.add_argument('--no-train', action='store_true', help='skip the training leg')
+    ap.add_argument('--long-batch', type=int, default=8, help='long-sequence (C=8, B=800) samples per step per GPU')
+    ap.add_argument('--no-long', action='store_true', help='skip the long-sequence training leg')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     args.pool = max(args.pool, args.batch)
@@ -558,11 +564,13 @@ def main():
     # ---- decode leg over the grids of batch 0 (round trip of the encoder's output)
     decode = run_decode(args, world, rank, torch, dist, L, lib, abi, batches[0], filt, arena)
     # ---- training leg (configs[3]); frees the encode buffers first
-    training = None
+    training = training_long = None
     if not args.no_train:
         del arena, slots, batches, h_events, h_songs
         torch.cuda.empty_cache()
         training = run_training(args, world, rank, torch, dist)
+        if not args.no_long:
+            training_long = run_training(args, world, rank, torch, dist, sh=LONG_SHAPE, N=args.long_batch)
         t_load1 = time.time()
     clocks = sampler.stop(t_load0, t_load1) if sampler else None
 
@@ -591,8 +599,9 @@ def main():
             'channel_bars_per_s': float(total_chan_bars.item()) / elapsed_s,
             'roofline': roofline, 'e2e': e2e, 'cpu_baseline': cpu_baseline, 'clocks': clocks,
             'gpu_launches': KERNELS_PER_STEP * args.steps +
-            (training['gpu_launches_per_step'] * args.train_steps if training else 0),
-            'decode': decode, 'training': training,
+            (training['gpu_launches_per_step'] * args.train_steps if training else 0) +
+            (training_long['gpu_launches_per_step'] * args.train_steps if training_long else 0),
+            'decode': decode, 'training': training, 'training_long': training_long,
         }))
     if world > 1:
         dist.destroy_process_group()

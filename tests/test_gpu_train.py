@@ -123,6 +123,27 @@ def test_losses_and_gradients_match_oracle(torch, weights, case):
     assert not bad, '\n'.join(bad[:60])
 
 
+FULL_SIZE = [dict(C=4, B=200, nb=4, drums=True), dict(C=8, B=800, nb=4, drums=True)]
+
+
+@pytest.mark.parametrize('case', FULL_SIZE, ids=['config4_C4_B200', 'config5_long_C8_B800'])
+def test_full_size_shapes_match_oracle(torch, weights, case):
+    """BASELINE.json configs[3] / configs[4] at their full per-sample sizes (800 and 6400 channel-bars, the latter
+    1.4e7 note rows and 800-step bar LSTMs): every loss leaf and every parameter gradient against the CPU oracle."""
+    import model_oracle as mo
+    from mst_native import model as mm
+    sd, flat = weights
+    samples = [mo.synthetic_sample(seed=7, **case)]
+    ref_leaves, ref_grads = oracle_step(torch, sd, samples)
+    losses, grads, _ = run_ours(torch, flat, samples, case)
+    for k, v in ref_leaves[0].items():
+        got = float(losses[0, mm.LOSS_LEAVES[k]])
+        assert abs(got - v) <= LOSS_RTOL * abs(v) + 1e-9, (case, k, got, v)
+    bad = [f'grad {n}: rel err {e:.3e} (|ref| {rn:.3e}, |got| {gn:.3e})'
+           for n, e, rn, gn in grad_report(torch, grads, ref_grads) if (rn > 0 and e > GRAD_RTOL) or (rn == 0 and gn > 1e-8)]
+    assert not bad, '\n'.join(bad[:60])
+
+
 def test_training_matches_reference_goldens(torch, weights):
     """Loss leaves and per-parameter gradient norms / heads of the UNMODIFIED reference (oracle/gen_golden_model.py)."""
     import model_oracle as mo
