@@ -299,6 +299,9 @@ def run_training(args, world, rank, torch, dist, sh=None, N=None):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     h2d = int(sum(v.numel() * v.element_size() for v in host.values()))
+    del slots, dev
+    torch.cuda.empty_cache()
+    e2e_events = training_e2e_from_events(args, world, rank, torch, dist, t, sh, N, losses, barrier)
     peak, peak_src = measured_peak_hbm()
     alg = algorithmic_bytes_per_sample(**sh)
     out = {
@@ -309,12 +312,133 @@ def run_training(args, world, rank, torch, dist, sh=None, N=None):
                      'achieved': alg * N / s_per_step / 1e9, 'peak': peak, 'unit': 'GB/s',
                      'frac': alg * N / s_per_step / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
                      'algorithmic_bytes_per_sample': alg},
-        'e2e': {'value': N * world * args.train_steps / float(e2e_s.item()), 'unit': 'samples/s',
-                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': int(h_losses.numel() * 4),
-                'note': 'two device slots: H2D of batch i+1 (copy stream) overlaps the training step of batch i; '
-                        'losses of every step read back and consumed'},
+        'e2e': e2e_events,
+        'e2e_dense_grids': {'value': N * world * args.train_steps / float(e2e_s.item()), 'unit': 'samples/s',
+                            'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': int(h_losses.numel() * 4),
+                            'note': 'the same step fed with dense f32 grids from pinned host memory (what the reference '
+                                    'uploads, data.py:144-149): two device slots, H2D of batch i+1 overlaps the step of '
+                                    'batch i; PCIe-bound'},
     }
     del t
+    torch.cuda.empty_cache()
+    return out
+
+
+def training_e2e_from_events(args, world, rank, torch, dist, t, sh, N, losses, barrier):
+    """Training throughput through the drop-in pipeline with HOST event buffers (train-model.py:97-154 on the CUDA path):
+    every step uploads the songs' MIDI events (pinned host memory), encodes them on the device with prepare_input's crop
+    (mst_encode_batch_host_async, crop_channel_bars = C.B), gathers the batch tensors from the encoder's arena, runs
+    forward + loss + backward + all-reduce + Adam, and reads the loss leaves back.  The grids never cross PCIe.
+    Two slots: the upload + encode of batch i + 1 (side stream) overlaps the training step of batch i."""
+    sys.path.insert(0, os.path.join(ROOT, 'music-style-transfer_b200'))
+    import numpy as np
+    from mst_native import abi, lib, synth
+    from style import data as sdata
+    L = lib.load()
+    C, B, nb = sh['C'], sh['B'], sh['nb']
+    filt = abi.make_filter(synth.POPULAR, 100, crop_channel_bars=C * B)
+    # candidate songs: C pitched tracks + drums over B bars; keep those the encoder turns into exactly (C, B) + drums
+    # (tracks that drew the same program are merged by merge_nchannels, data.py:103-114)
+    ev, sg = synth.synth_corpus(2 * N + 8, seed=4321 + 17 * rank, n_bars=B, n_tracks=C + 1)
+    per_song = synth.split_songs(ev, sg)
+    cand = lib.DeviceBatch(ev, sg)
+    cand.encode(filt, None)
+    plan = cand.infos()
+    keep = [i for i, r in enumerate(plan) if int(r['status']) in (0, 8) and int(r['n_pitched']) == C
+            and int(r['n_unpitched']) == 1 and int(r['n_bars_out']) == B and int(r['n_beats']) == nb][:N]
+    assert len(keep) == N, f'only {len(keep)} of {len(plan)} synthetic songs have the ({C}, {B}) shape'
+    del cand
+    events, songs = lib.make_songs([per_song[i] for i in keep], [int(sg['ticks_per_beat'][i]) for i in keep])
+    recs = [plan[i] for i in keep]
+    P, U = C * B * nb * abi.PITCHED_BEAT_FLOATS, B * nb * abi.UNPITCHED_BEAT_FLOATS
+    h_events = torch.from_numpy(events.view(np.uint8).reshape(-1)).pin_memory()
+    h_songs = torch.from_numpy(songs.view(np.uint8).reshape(-1)).pin_memory()
+    # the small per-song tensors prepare_input / get_used_instruments derive from the song infos (data.py:122-169)
+    feats = torch.stack([torch.as_tensor(sdata.encode_instruments([int(x) for x in r['pitched_instruments'][:C]]),
+                                         dtype=torch.float32) for r in recs])
+    small = {'feats': feats,
+             'mode': torch.tensor([[1., 0.] if int(r['mode']) == 0 else [0., 1.] for r in recs]),
+             'bpm': torch.tensor([float(r['bpm']) for r in recs]),
+             'it': torch.cat([sdata.get_used_instruments(feats[i:i + 1], True) for i in range(N)]),
+             'bt': torch.tensor([float(r['bpm']) for r in recs])}
+    small = {k: v.contiguous().pin_memory() for k, v in small.items()}
+    arena_floats = N * (P + U)
+    wsb = L.mst_encode_host_workspace_bytes(len(events), N, arena_floats)
+    slots = []
+    for _ in range(2):
+        slots.append({'stream': torch.cuda.Stream(), 'ws': torch.empty(wsb, dtype=torch.uint8, device='cuda'),
+                      'arena': torch.empty(arena_floats, dtype=torch.float32, device='cuda'),
+                      'info': torch.empty(N * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory(),
+                      'pitched': torch.empty(N, C, B, nb, 10, 56, 5, device='cuda'),
+                      'unpitched': torch.empty(N, 1, B, nb, 10, 47, 2, device='cuda'),
+                      'small': {k: torch.empty_like(v, device='cuda') for k, v in small.items()},
+                      'h_loss': torch.empty(N, 16).pin_memory(),
+                      'ready': torch.cuda.Event(), 'free': torch.cuda.Event(), 'done': torch.cuda.Event()})
+    seen = [0.0, 0]
+
+    def produce(i):
+        sl = slots[i & 1]
+        st = sl['stream']
+        st.wait_event(sl['free'])                        # the training step that read this slot has finished
+        lib.check(L.mst_encode_batch_host_async(
+            h_events.data_ptr(), len(events), h_songs.data_ptr(), N, filt.reshape(1).ctypes.data, sl['info'].data_ptr(),
+            sl['arena'].data_ptr(), arena_floats, sl['ws'].data_ptr(), wsb, st.cuda_stream))
+        with torch.cuda.stream(st):
+            # songs are laid out one after the other, each (pitched, unpitched): gather the two batch tensors
+            per = sl['arena'].view(N, P + U)
+            sl['pitched'].view(N, P).copy_(per[:, :P])
+            sl['unpitched'].view(N, U).copy_(per[:, P:])
+            for k, v in small.items():
+                sl['small'][k].copy_(v, non_blocking=True)
+            sl['ready'].record(st)
+
+    def e2e_step(i):
+        sl = slots[i & 1]
+        produce(i + 1)
+        cur = torch.cuda.current_stream()
+        cur.wait_event(sl['ready'])
+        d = sl['small']
+        t.accumulate(sl['pitched'], sl['unpitched'], d['feats'], d['mode'], d['bpm'], d['it'], d['bt'], losses)
+        t.optimizer_step()
+        sl['free'].record(cur)
+        sl['h_loss'].copy_(losses, non_blocking=True)
+        sl['done'].record(cur)
+        if i > 0:
+            prev = slots[1 - (i & 1)]
+            prev['done'].synchronize()
+            seen[0] += float(prev['h_loss'][:, 0].sum())          # the host consumes the previous step's losses
+            info = prev['info'].numpy().view(abi.SONG_INFO_DTYPE)  # ... and its song infos
+            seen[1] += int((info['status'] == 0).sum())
+
+    for sl in slots:
+        sl['free'].record()
+    produce(0)
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    chk = slots[0]['info'].numpy().view(abi.SONG_INFO_DTYPE)
+    assert all(int(r['status']) == 0 and int(r['pitched_offset']) == i * (P + U) and int(r['unpitched_offset']) == i * (P + U) + P
+               for i, r in enumerate(chk)), 'arena layout differs from the batch gather'
+    seen[1] = 0
+    t0 = time.perf_counter()
+    for i in range(2, 2 + args.train_steps):
+        e2e_step(i)
+    slots[(1 + args.train_steps) & 1]['done'].synchronize()
+    torch.cuda.current_stream().synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+    torch.cuda.synchronize()
+    barrier()
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    assert seen[1] >= N * (args.train_steps - 1), 'the encoder rejected songs inside the timed region'
+    h2d = int(h_events.numel() + h_songs.numel() + sum(v.numel() * v.element_size() for v in small.values()))
+    out = {'value': N * world * args.train_steps / float(dt.item()), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d,
+           'd2h_bytes_per_step': int(N * 16 * 4 + N * abi.SONG_INFO_DTYPE.itemsize),
+           'events_per_step': int(len(events)), 'loss_total_sample0': float(slots[0]['h_loss'][0, 0]),
+           'note': 'host MIDI events -> H2D -> mst_encode_batch_host_async (crop = C.B channel-bars) -> batch gather -> '
+                   'training step -> D2H of loss leaves and song infos, every step; upload + encode of batch i+1 on a '
+                   'side stream overlap the training step of batch i; the grids never cross PCIe'}
+    del slots
     torch.cuda.empty_cache()
     return out
 

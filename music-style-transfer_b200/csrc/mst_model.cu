@@ -307,6 +307,11 @@ struct Launcher {
             if (N <= 16) gemm_t5<16>(g, split_k); else if (N <= 32) gemm_t5<32>(g, split_k); else gemm_t5<64>(g, split_k);
         } else if (kernel == 2 || (kernel == 0 && use_tc(M, N, K))) {
             if (N <= 32) gemm_tc<32>(g, split_k); else gemm_tc<64>(g, split_k);
+        } else if (kernel == 0 && ((N + kGemmTile - 1) / kGemmTile) * ((M + kGemmTile - 1) / kGemmTile) * split_k <= 16 &&
+                   (long long)M * N <= 8192) {
+            // a handful of 64 x 64 tiles would leave the machine idle: one warp per output element
+            dim3 grid((unsigned)(((long long)M * N + kGemmWarpThreads / 32 - 1) / (kGemmWarpThreads / 32)), split_k);
+            k_gemm_warp<<<grid, kGemmWarpThreads, 0, st>>>(g);
         } else {
             dim3 grid((N + kGemmTile - 1) / kGemmTile, (M + kGemmTile - 1) / kGemmTile, split_k);
             k_gemm<0><<<grid, kGemmThreads, 0, st>>>(g);

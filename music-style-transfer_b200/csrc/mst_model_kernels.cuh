@@ -137,6 +137,38 @@ k_gemm(GemmArgs g) {
     }
 }
 
+// Same contract for the problems whose 64 x 64 tiling would leave all but a handful of SMs idle (per-sample heads,
+// per-channel instrument rows, their weight gradients): one warp per output element, lanes stride over k, shuffle
+// reduction.  gridDim.y splits K like k_gemm's gridDim.z.
+constexpr int kGemmWarpThreads = 256;
+__global__ void __launch_bounds__(kGemmWarpThreads)
+k_gemm_warp(GemmArgs g) {
+    const int lane = threadIdx.x & 31;
+    const long long out = (long long)blockIdx.x * (kGemmWarpThreads / 32) + (threadIdx.x >> 5);
+    if (out >= (long long)g.M * g.N) return;
+    const int i = (int)(out / g.N), j = (int)(out - (long long)i * g.N);
+    const int k_per = (g.K + gridDim.y - 1) / gridDim.y;
+    const int k_lo = blockIdx.y * k_per, k_hi = min(g.K, k_lo + k_per);
+    const float *a = g.A + (long long)i * g.a_si, *b = g.B + (long long)j * g.b_sj;
+    float acc0 = 0.f, acc1 = 0.f;
+    int k = k_lo + lane;
+    for (; k + 32 < k_hi; k += 64) {
+        acc0 = fmaf(a[(long long)k * g.a_sk], b[(long long)k * g.b_sk], acc0);
+        acc1 = fmaf(a[(long long)(k + 32) * g.a_sk], b[(long long)(k + 32) * g.b_sk], acc1);
+    }
+    if (k < k_hi) acc0 = fmaf(a[(long long)k * g.a_sk], b[(long long)k * g.b_sk], acc0);
+    float v = acc0 + acc1;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane != 0) return;
+    if (g.bias && blockIdx.y == 0) v += g.bias[j];
+    if (g.act == 1) v = leaky(v);
+    float *dst = g.C + (long long)i * g.c_si + j;
+    if (g.accumulate == 0) *dst = v;
+    else if (g.accumulate == 1) *dst += v;
+    else atomicAdd(dst, v);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Broadcast add + activation over the row space (n, c, b, t, f):  Y[row, :] = act(bias + sum_s Z_s[map_s(row), :])
 // A source keeps a subset of the five coordinates (bit 4 = n, 3 = c, 2 = b, 1 = t, 0 = f); its rows are the
