@@ -268,26 +268,32 @@ struct Launcher {
         if ((s_row & 1) == 0 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) return 1;
         return 2;
     }
-    template <int BN, int AM, int BMD>
+    template <int BN, int AM, int BMD, int NS>
     void gemm_t5_launch(const GemmArgs &g, dim3 grid) {
         static bool attr_set = false;
-        if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN, AM, BMD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN>()); attr_set = true; }
-        k_gemm_t5<BN, AM, BMD><<<grid, kT5Block, t5_smem_bytes<BN>(), st>>>(g);
+        if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN, AM, BMD, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN, NS>()); attr_set = true; }
+        k_gemm_t5<BN, AM, BMD, NS><<<grid, kT5Block, t5_smem_bytes<BN, NS>(), st>>>(g);
+    }
+    template <int BN, int NS>
+    void gemm_t5_ns(const GemmArgs &g, dim3 grid) {
+        const int am = t5_mode(g.A, g.a_si, g.a_sk);
+        const int bm = t5_mode(g.B, g.b_sj, g.b_sk) == 0 ? 0 : 2;          // the small operand: aligned or generic
+        if (am == 0) { if (bm == 0) gemm_t5_launch<BN, 0, 0, NS>(g, grid); else gemm_t5_launch<BN, 0, 2, NS>(g, grid); }
+        else if (am == 1) { if (bm == 0) gemm_t5_launch<BN, 1, 0, NS>(g, grid); else gemm_t5_launch<BN, 1, 2, NS>(g, grid); }
+        else { if (bm == 0) gemm_t5_launch<BN, 2, 0, NS>(g, grid); else gemm_t5_launch<BN, 2, 2, NS>(g, grid); }
     }
     template <int BN>
     void gemm_t5(const GemmArgs &g, int split_k) {
         dim3 grid((g.N + BN - 1) / BN, (g.M + kT5BM - 1) / kT5BM, split_k);
-        const int am = t5_mode(g.A, g.a_si, g.a_sk);
-        const int bm = t5_mode(g.B, g.b_sj, g.b_sk) == 0 ? 0 : 2;          // the small operand: aligned or generic
-        if (am == 0) { if (bm == 0) gemm_t5_launch<BN, 0, 0>(g, grid); else gemm_t5_launch<BN, 0, 2>(g, grid); }
-        else if (am == 1) { if (bm == 0) gemm_t5_launch<BN, 1, 0>(g, grid); else gemm_t5_launch<BN, 1, 2>(g, grid); }
-        else { if (bm == 0) gemm_t5_launch<BN, 2, 0>(g, grid); else gemm_t5_launch<BN, 2, 2>(g, grid); }
+        // two stages, two CTAs per SM.  (A 4-stage ring at one CTA per SM was measured 5-30 % SLOWER on every training
+        // shape, tools/gemm_probe.py: the loaders are latency-bound, so resident loader warps matter more than ring depth.)
+        gemm_t5_ns<BN, 2>(g, grid);
     }
     // C[M,N] (op)= act(A·B + bias) with explicit strides
     void gemm(const float *A, long long a_si, long long a_sk, const float *B, long long b_sk, long long b_sj, float *C, long long c_si,
               int M, int N, int K, const float *bias, int act, int accumulate, int split_k = 1, int kernel = 0) {
-        static const bool log_shapes = getenv("MST_GEMM_LOG") != nullptr;      // development aid: list the step's GEMMs
-        if (log_shapes && dry) fprintf(stderr, "gemm M=%d N=%d K=%d a=(%lld,%lld) b=(%lld,%lld) c=%lld act=%d acc=%d split=%d\n", M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate, split_k);
+        static const int log_shapes = getenv("MST_GEMM_LOG") ? atoi(getenv("MST_GEMM_LOG")) : 0;   // development aid: list the step's GEMMs (1: planning pass, 2: launches)
+        if ((log_shapes == 1 && dry) || (log_shapes == 2 && !dry && M > 0 && N > 0 && K > 0)) fprintf(stderr, "gemm M=%d N=%d K=%d a=(%lld,%lld) b=(%lld,%lld) c=%lld act=%d acc=%d split=%d\n", M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate, split_k);
         if (dry || M <= 0 || N <= 0 || K <= 0) return;
         GemmArgs g{A, B, bias, C, M, N, K, a_si, a_sk, b_sk, b_sj, c_si, act, accumulate};
         if (split_k > 1) g.accumulate = 2;

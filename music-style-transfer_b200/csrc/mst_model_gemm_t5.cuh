@@ -6,10 +6,11 @@
 // which with three products per term made k_gemm_tc MMA-bound at ~2 TB/s of operand traffic.  tcgen05 removes that
 // bound: the kernel is a streaming producer (global -> split -> shared) in front of one MMA-issuing thread.
 //
-//   * CTA tile 128 x BN (BN = 16 / 32 / 64), K slab 32, two shared-memory stages; each stage holds A_hi, A_lo (128 x 32)
+//   * CTA tile 128 x BN (BN = 16 / 32 / 64), K slab 32, a ring of NS shared-memory stages (NS = 2 is what the host
+//     launches, two CTAs per SM); each stage holds A_hi, A_lo (128 x 32)
 //     and B_hi, B_lo (BN x 32) in the canonical K-major no-swizzle UMMA layout: 8-row x 16-byte core matrices, the 8
 //     K-chunks of a row group 144 B apart (LBO), row groups 1152 B apart (SBO);
-//   * 8 producer warps load the next slab into registers (any operand strides; the lane order follows the operand's
+//   * 8 producer warps keep the next TWO slabs in registers (any operand strides; the lane order follows the operand's
 //     contiguous direction, 16 / 8-byte loads when aligned), split it, store 16-byte chunks (conflict-free for both
 //     orders thanks to the 144-byte LBO), fence.proxy.async, and arrive on the stage's "full" mbarrier (no CTA barrier);
 //     a ninth warp's elected thread waits on it, issues 4 k-steps x 3 products of tcgen05.mma.kind::tf32 (M = 128,
@@ -84,8 +85,8 @@ __device__ __forceinline__ void t5_load_tail(const float *p, long long sk, int k
     for (int e = 0; e < 4; e++) v[e] = k + e < k_hi ? __ldg(p + e * sk) : 0.f;
 }
 
-template <int BN, int AMODE, int BMODE>
-__global__ void __launch_bounds__(kT5Block, 2)
+template <int BN, int AMODE, int BMODE, int NS>
+__global__ void __launch_bounds__(kT5Block, NS == 2 ? 2 : 1)
 k_gemm_t5(GemmArgs g) {
     constexpr int BM = kT5BM, KT = kT5BK;
     constexpr int A_BYTES = t5_tile_bytes(BM), B_BYTES = t5_tile_bytes(BN);   // one hi or lo tile
@@ -94,7 +95,7 @@ k_gemm_t5(GemmArgs g) {
     constexpr int B_CH = (BN * 8 + kT5Threads - 1) / kT5Threads;               // 2 / 1 / 1 (BN = 16: threads < 128)
     constexpr int TM_COLS = BN < 32 ? 32 : BN;
     extern __shared__ __align__(1024) unsigned char smem[];
-    __shared__ __align__(8) uint64_t bars[5];          // full[2] (8 loader warps), empty[2] (tcgen05.commit), done
+    __shared__ __align__(8) uint64_t bars[2 * NS + 1]; // full[NS] (8 loader warps), empty[NS] (tcgen05.commit), done
     __shared__ uint32_t tmem_base_s;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -106,10 +107,11 @@ k_gemm_t5(GemmArgs g) {
     const int n_slabs = (k_hi - k_lo + KT - 1) / KT;
 
     const uint32_t bar0 = smem_u32(&bars[0]);
-    const uint32_t bar_full = bar0, bar_empty = bar0 + 16, bar_done = bar0 + 32;
+    const uint32_t bar_full = bar0, bar_empty = bar0 + 8 * NS, bar_done = bar0 + 16 * NS;
     if (tid == 0) {
-        mbar_init(bar_full, 8); mbar_init(bar_full + 8, 8);
-        mbar_init(bar_empty, 1); mbar_init(bar_empty + 8, 1); mbar_init(bar_done, 1);
+#pragma unroll
+        for (int i = 0; i < NS; i++) { mbar_init(bar_full + 8 * i, 8); mbar_init(bar_empty + 8 * i, 1); }
+        mbar_init(bar_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -150,26 +152,30 @@ k_gemm_t5(GemmArgs g) {
     }
     const long long a_step = (long long)KT * g.a_sk, b_step = (long long)KT * g.b_sk;
     const int n_full = (k_hi - k_lo) / KT;                            // slabs that need no zero fill
-    float ra[A_CH][4], rb[B_CH][4];
-    auto load_full = [&]() {
+    // two register sets: slab s lives in set s & 1 and is fetched TWO slabs ahead of its store, so that every loader
+    // thread keeps two slabs of global loads in flight (one slab per thread is ~32 KB per SM, short of the
+    // latency x bandwidth product of HBM)
+    float ra[2][A_CH][4], rb[2][B_CH][4];
+    auto load_slab = [&](int t, float (&xa)[A_CH][4], float (&xb)[B_CH][4]) {
+        if (t < n_full) {
 #pragma unroll
-        for (int i = 0; i < A_CH; i++) { t5_load_full<AMODE>(pa[i], g.a_sk, ra[i]); pa[i] += a_step; }
+            for (int i = 0; i < A_CH; i++) { t5_load_full<AMODE>(pa[i], g.a_sk, xa[i]); pa[i] += a_step; }
 #pragma unroll
-        for (int i = 0; i < B_CH; i++) { t5_load_full<BMODE>(pb[i], g.b_sk, rb[i]); pb[i] += b_step; }
+            for (int i = 0; i < B_CH; i++) { t5_load_full<BMODE>(pb[i], g.b_sk, xb[i]); pb[i] += b_step; }
+        } else {
+            const int kb = k_lo + n_full * KT;
+#pragma unroll
+            for (int i = 0; i < A_CH; i++) t5_load_tail(pa[i], g.a_sk, kb + a_k[i], k_hi, xa[i]);
+#pragma unroll
+            for (int i = 0; i < B_CH; i++) t5_load_tail(pb[i], g.b_sk, kb + b_k[i], k_hi, xb[i]);
+        }
     };
-    auto load_tail = [&]() {
-        const int kb = k_lo + n_full * KT;
-#pragma unroll
-        for (int i = 0; i < A_CH; i++) t5_load_tail(pa[i], g.a_sk, kb + a_k[i], k_hi, ra[i]);
-#pragma unroll
-        for (int i = 0; i < B_CH; i++) t5_load_tail(pb[i], g.b_sk, kb + b_k[i], k_hi, rb[i]);
-    };
-    auto store_slab = [&](int stage) {
+    auto store_slab = [&](int stage, float (&xa)[A_CH][4], float (&xb)[B_CH][4]) {
         unsigned char *st = smem + stage * STAGE_BYTES;
 #pragma unroll
         for (int i = 0; i < A_CH; i++) {
             float4 hi, lo;
-            t5_split4(ra[i], hi, lo);
+            t5_split4(xa[i], hi, lo);
             *reinterpret_cast<float4 *>(st + a_off[i]) = hi;
             *reinterpret_cast<float4 *>(st + A_BYTES + a_off[i]) = lo;
         }
@@ -177,7 +183,7 @@ k_gemm_t5(GemmArgs g) {
         for (int i = 0; i < B_CH; i++) {
             if (BN * 8 >= kT5Threads * (i + 1) || tid + i * kT5Threads < BN * 8) {
                 float4 hi, lo;
-                t5_split4(rb[i], hi, lo);
+                t5_split4(xb[i], hi, lo);
                 *reinterpret_cast<float4 *>(st + b_off[i]) = hi;
                 *reinterpret_cast<float4 *>(st + B_BYTES + b_off[i]) = lo;
             }
@@ -188,23 +194,27 @@ k_gemm_t5(GemmArgs g) {
     const uint32_t smem_base = smem_u32(smem);
 
     if (warp < 8) {
-        // ---- producers: split + store slab s, publish it on the stage's "full" barrier, then fetch slab s + 1
-        if (n_full > 0) load_full(); else load_tail();
-        for (int s = 0; s < n_slabs; s++) {
-            const int stage = s & 1;
-            if (s >= 2) mbar_wait(bar_empty + 8 * stage, (uint32_t)(((s >> 1) - 1) & 1));   // MMAs of slab s - 2 have read it
-            store_slab(stage);
+        // ---- producers: split + store slab s, publish it on the stage's "full" barrier, then fetch slab s + 2
+        auto produce = [&](int s, float (&xa)[A_CH][4], float (&xb)[B_CH][4]) {
+            const int stage = s % NS;
+            if (s >= NS) mbar_wait(bar_empty + 8 * stage, (uint32_t)((s / NS - 1) & 1));    // MMAs of slab s - NS have read it
+            store_slab(stage, xa, xb);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_full + 8 * stage) : "memory");
-            if (s + 1 < n_full) load_full();
-            else if (s + 1 < n_slabs) load_tail();
+            if (s + 2 < n_slabs) load_slab(s + 2, xa, xb);
+        };
+        load_slab(0, ra[0], rb[0]);
+        if (n_slabs > 1) load_slab(1, ra[1], rb[1]);
+        for (int s = 0; s < n_slabs; s += 2) {
+            produce(s, ra[0], rb[0]);
+            if (s + 1 < n_slabs) produce(s + 1, ra[1], rb[1]);
         }
     } else if (lane == 0) {
         // ---- consumer: one thread issues the MMAs of a slab as soon as all 8 producer warps have published it
         for (int s = 0; s < n_slabs; s++) {
-            const int stage = s & 1;
-            mbar_wait(bar_full + 8 * stage, (uint32_t)((s >> 1) & 1));
+            const int stage = s % NS;
+            mbar_wait(bar_full + 8 * stage, (uint32_t)((s / NS) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + 2 * A_BYTES;
 #pragma unroll
@@ -287,6 +297,6 @@ k_gemm_t5(GemmArgs g) {
     }
 }
 
-template <int BN> constexpr size_t t5_smem_bytes() { return 2 * (2 * t5_tile_bytes(kT5BM) + 2 * t5_tile_bytes(BN)); }
+template <int BN, int NS> constexpr size_t t5_smem_bytes() { return NS * (2 * t5_tile_bytes(kT5BM) + 2 * t5_tile_bytes(BN)); }
 
 }  // namespace mstm

@@ -19,6 +19,8 @@ SHAPES = [  # name, layout, M, N, K, lda_pad, split
     ('sq dW', 'dw', 64, 64, 204800, 0, 296),
     ('lin 64x456', 'linear', 204800, 64, 456, 456, 1),
     ('lin 128x64', 'linear', 204800, 128, 64, 64, 1),
+    ('lin 456x64', 'linear', 204800, 456, 64, 64, 1),
+    ('lin 256x64', 'linear', 204800, 256, 64, 64, 1),
 ]
 
 
@@ -39,12 +41,12 @@ def run(name, layout, M, N, K, ld, split, kernel, reps=5):
     C = torch.zeros(M, N, device=dev)
     acc = 2 if split > 1 else 0
     for _ in range(2):
-        mm.gemm(*args, C, N, M, N, K, accumulate=acc, split_k=split, kernel=kernel)
+        mm.gemm(*args, C, N, M, N, K, act=int(os.environ.get('GEMM_ACT', '0')), accumulate=acc, split_k=split, kernel=kernel)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(reps):
-        mm.gemm(*args, C, N, M, N, K, accumulate=acc, split_k=split, kernel=kernel)
+        mm.gemm(*args, C, N, M, N, K, act=int(os.environ.get('GEMM_ACT', '0')), accumulate=acc, split_k=split, kernel=kernel)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     return ms, byts / ms / 1e6
