@@ -150,20 +150,44 @@ k_sort(const MstEvent *__restrict__ ev, const MstSongIn *__restrict__ songs, Wor
     const uint32_t n = songs[song].n_events;
     const MstEvent *e = ev + base;
     uint32_t *ka = ws.keys_a + base, *va = ws.vals_a + base, *kb = ws.keys_b + base, *vb = ws.vals_b + base;
+    // the sort key is packed to the bits this song needs: class << tb | tick with tb = bit length of the song's largest
+    // tick, so a 128-bar song at 480 ticks per beat (18 tick bits + 5 class bits) takes three 8-bit passes, not four
+    __shared__ uint32_t max_tick_s;
+    if (threadIdx.x == 0) max_tick_s = 1;
+    __syncthreads();
+    uint32_t mt = 0;
+    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {
+        const MstEvent x = e[i];
+        if (event_class(x) != kClassDropped) mt = max(mt, x.tick);
+    }
+    mt = (uint32_t)warp_reduce_max((int)mt);            // ticks are <= MST_MAX_TICK < 2^31
+    if (lane_id() == 0) atomicMax(&max_tick_s, mt);
+    __syncthreads();
+    const int tb = 32 - __clz(max_tick_s);
+    const uint32_t tick_mask = (1u << tb) - 1u;
     for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {
         MstEvent x = e[i];
         uint32_t cls = event_class(x);
-        ka[i] = (cls << 24) | (cls == kClassDropped ? 0u : x.tick);
+        ka[i] = (cls << tb) | (cls == kClassDropped ? 0u : x.tick);
         va[i] = i;
     }
     __syncthreads();
-    radix_pass(ka, va, kb, vb, n, 0, whist, scan_tmp, &skip_flag);
-    radix_pass(kb, vb, ka, va, n, 8, whist, scan_tmp, &skip_flag);
-    radix_pass(ka, va, kb, vb, n, 16, whist, scan_tmp, &skip_flag);
-    radix_pass(kb, vb, ka, va, n, 24, whist, scan_tmp, &skip_flag);
-    // gather the events into merged order and find the class segments
+    uint32_t *kin = ka, *vin = va, *kout = kb, *vout = vb;
+    for (int shift = 0; shift < tb + 5; shift += 8) {
+        radix_pass(kin, vin, kout, vout, n, shift, whist, scan_tmp, &skip_flag);
+        uint32_t *t = kin; kin = kout; kout = t;
+        t = vin; vin = vout; vout = t;
+    }
+    // gather the events into merged order, leave (class << 24 | tick, source index) in keys_a / vals_a for k_info, and
+    // find the class segments
     MstEvent *se = ws.sorted_ev + base;
-    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) se[i] = e[va[i]];
+    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {
+        const uint32_t k = kin[i], v = vin[i];
+        se[i] = e[v];
+        ka[i] = ((k >> tb) << 24) | (k & tick_mask);
+        va[i] = v;
+    }
+    __syncthreads();
     if (threadIdx.x <= kClassEnd) {
         uint32_t target = threadIdx.x << 24;
         uint32_t lo = 0, hi = n;
@@ -629,7 +653,7 @@ struct __align__(16) ScaleTerm {   // duration * velocity of one note, placed at
 };
 static_assert(sizeof(ScaleTerm) == sizeof(Cell), "ScaleTerm aliases the cell scratch");
 
-constexpr int kScaleThreads = 256;
+constexpr int kScaleThreads = 512;     // 16 warps: one per pitched instrument of a 15 + 1 track song in a single round
 
 __global__ void __launch_bounds__(kScaleThreads)
 k_scale(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out) {
@@ -671,6 +695,7 @@ k_scale(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
         const int p = L.out_slot;
         const Note *nt = notes + L.note_offset;
         const bool multi = inst_lists[p] > 1;
+#pragma unroll 4
         for (uint32_t j = threadIdx.x; j < L.n_notes; j += kScaleThreads) {
             const Note x = nt[j];
             uint32_t rank = j;
@@ -697,11 +722,13 @@ k_scale(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
     for (int p = warp; p < C; p += nwarps) {
         PySum acc; acc.started = false; acc.s = 0; acc.c = 0;
         const uint32_t t0 = inst_base[p], t1 = inst_base[p + 1];
+        // the next strip's terms are fetched while the current strip's dependent adds run
+        ScaleTerm nxt; nxt.prod = 0.0; nxt.key = -1;
+        if (t0 + lane < t1) nxt = terms[t0 + lane];
         for (uint32_t b = t0; b < t1; b += 32) {
-            const uint32_t i = b + lane;
-            const bool valid = i < t1;
-            double prod = 0.0; int key = -1;
-            if (valid) { ScaleTerm t = terms[i]; prod = t.prod; key = t.key; }
+            const double prod = nxt.prod; const int key = nxt.key;
+            nxt.prod = 0.0; nxt.key = -1;
+            if (b + 32 + lane < t1) nxt = terms[b + 32 + lane];
             unsigned mine = 0;
 #pragma unroll
             for (int k = 0; k < 12; k++) {

@@ -5,6 +5,7 @@
 
 constexpr int kSortThreads = 1024;
 constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kSortBatch = 8;       // strips whose keys a warp fetches together
 
 // One 8-bit pass.  Every warp owns a contiguous segment of the input, so the relative order of equal
 // digits is preserved: warp-private digit offsets come from a per-digit scan over the warps, ranks
@@ -17,16 +18,25 @@ __device__ inline void radix_pass(const uint32_t *kin, const uint32_t *vin, uint
     __syncthreads();
     const uint32_t per = ((n + kSortThreads - 1) / kSortThreads) * 32;
     const uint32_t lo = min(n, warp * per), hi = min(n, lo + per);
-    for (uint32_t b = lo; b < hi; b += 32) {
-        uint32_t i = b + lane;
-        bool valid = i < hi;
-        unsigned act = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            uint32_t d = (kin[i] >> shift) & 255u;
-            unsigned peers = __match_any_sync(act, d);
-            if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
+    // strips are handled in batches of kSortBatch: the batch's keys are fetched first (independent loads in flight), so
+    // a warp pays the L2 / HBM latency once per batch instead of once per strip
+    for (uint32_t b0 = lo; b0 < hi; b0 += 32 * kSortBatch) {
+        uint32_t kk[kSortBatch];
+#pragma unroll
+        for (int u = 0; u < kSortBatch; u++) { const uint32_t i = b0 + u * 32 + lane; kk[u] = i < hi ? kin[i] : 0u; }
+#pragma unroll
+        for (int u = 0; u < kSortBatch; u++) {
+            const uint32_t i = b0 + u * 32 + lane;
+            if (b0 + u * 32 >= hi) break;
+            const bool valid = i < hi;
+            const unsigned act = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const uint32_t d = (kk[u] >> shift) & 255u;
+                const unsigned peers = __match_any_sync(act, d);
+                if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
+            }
+            __syncwarp();
         }
-        __syncwarp();
     }
     __syncthreads();
     uint32_t total = 0;
@@ -48,21 +58,31 @@ __device__ inline void radix_pass(const uint32_t *kin, const uint32_t *vin, uint
         __syncthreads();
         return;
     }
-    for (uint32_t b = lo; b < hi; b += 32) {
-        uint32_t i = b + lane;
-        bool valid = i < hi;
-        unsigned act = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            uint32_t k = kin[i], v = vin[i];
-            uint32_t d = (k >> shift) & 255u;
-            unsigned peers = __match_any_sync(act, d);
-            uint32_t dst = whist[warp][d] + __popc(peers & lanemask_lt());
-            kout[dst] = k;
-            vout[dst] = v;
-            __syncwarp(act);
-            if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
+    for (uint32_t b0 = lo; b0 < hi; b0 += 32 * kSortBatch) {
+        uint32_t kk[kSortBatch], vv[kSortBatch];
+#pragma unroll
+        for (int u = 0; u < kSortBatch; u++) {
+            const uint32_t i = b0 + u * 32 + lane;
+            kk[u] = i < hi ? kin[i] : 0u;
+            vv[u] = i < hi ? vin[i] : 0u;
         }
-        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < kSortBatch; u++) {
+            const uint32_t i = b0 + u * 32 + lane;
+            if (b0 + u * 32 >= hi) break;
+            const bool valid = i < hi;
+            const unsigned act = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const uint32_t d = (kk[u] >> shift) & 255u;
+                const unsigned peers = __match_any_sync(act, d);
+                const uint32_t dst = whist[warp][d] + __popc(peers & lanemask_lt());
+                kout[dst] = kk[u];
+                vout[dst] = vv[u];
+                __syncwarp(act);
+                if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
+            }
+            __syncwarp();
+        }
     }
     __syncthreads();
 }
