@@ -155,37 +155,81 @@ k_sort(const MstEvent *__restrict__ ev, const MstSongIn *__restrict__ songs, Wor
     __shared__ uint32_t max_tick_s;
     if (threadIdx.x == 0) max_tick_s = 1;
     __syncthreads();
+    // events are read ONCE, four per thread and step so that four 16-byte loads are in flight per lane (a CTA streams
+    // ~0.5 MB of events: with one load per lane in flight the loop runs at the latency, not the bandwidth)
     uint32_t mt = 0;
-    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {
-        const MstEvent x = e[i];
-        if (event_class(x) != kClassDropped) mt = max(mt, x.tick);
+    for (uint32_t i0 = threadIdx.x; i0 < n; i0 += 4 * kSortThreads) {
+        MstEvent x[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) if (i0 + u * kSortThreads < n) x[u] = e[i0 + u * kSortThreads];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t i = i0 + u * kSortThreads;
+            if (i >= n) break;
+            const uint32_t cls = event_class(x[u]);
+            const uint32_t tick = cls == kClassDropped ? 0u : x[u].tick;
+            mt = max(mt, tick);
+            ka[i] = (cls << 24) | tick;
+        }
     }
     mt = (uint32_t)warp_reduce_max((int)mt);            // ticks are <= MST_MAX_TICK < 2^31
     if (lane_id() == 0) atomicMax(&max_tick_s, mt);
+    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) va[i] = i;
     __syncthreads();
-    const int tb = 32 - __clz(max_tick_s);
-    const uint32_t tick_mask = (1u << tb) - 1u;
-    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {
-        MstEvent x = e[i];
-        uint32_t cls = event_class(x);
-        ka[i] = (cls << tb) | (cls == kClassDropped ? 0u : x.tick);
-        va[i] = i;
+    // Fast path.  Every track is already in tick order (delta times are non-negative), so when no two tracks share a
+    // class (the usual format-1 layout: one channel per track; also any format-0 file) the stable partition by class IS
+    // the (class, tick) order.  One pass on the class byte (long runs of equal digits: near-coalesced scatter), then a
+    // sortedness check; only songs that fail it take the full radix sort below.
+    __shared__ int unsorted_s;
+    if (threadIdx.x == 0) unsorted_s = 0;
+    radix_pass(ka, va, kb, vb, n, 24, whist, scan_tmp, &skip_flag);       // ends with a CTA barrier
+    {
+        int bad = 0;
+        for (uint32_t i = threadIdx.x; i + 1 < n; i += kSortThreads) bad |= kb[i] > kb[i + 1];
+        if (bad) unsorted_s = 1;
     }
     __syncthreads();
-    uint32_t *kin = ka, *vin = va, *kout = kb, *vout = vb;
-    for (int shift = 0; shift < tb + 5; shift += 8) {
-        radix_pass(kin, vin, kout, vout, n, shift, whist, scan_tmp, &skip_flag);
-        uint32_t *t = kin; kin = kout; kout = t;
-        t = vin; vin = vout; vout = t;
+    int tb = 24;
+    uint32_t tick_mask = 0xFFFFFFu;
+    uint32_t *kin = kb, *vin = vb, *kout = ka, *vout = va;
+    if (unsorted_s) {
+        tb = 32 - __clz(max_tick_s);
+        tick_mask = (1u << tb) - 1u;
+        for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {  // own elements again: no barrier needed in between
+            const uint32_t k = ka[i];
+            ka[i] = ((k >> 24) << tb) | (k & 0xFFFFFFu);
+            va[i] = i;
+        }
+        __syncthreads();
+        kin = ka; vin = va; kout = kb; vout = vb;
+        for (int shift = 0; shift < tb + 5; shift += 8) {
+            radix_pass(kin, vin, kout, vout, n, shift, whist, scan_tmp, &skip_flag);
+            uint32_t *t = kin; kin = kout; kout = t;
+            t = vin; vin = vout; vout = t;
+        }
     }
     // gather the events into merged order, leave (class << 24 | tick, source index) in keys_a / vals_a for k_info, and
     // find the class segments
     MstEvent *se = ws.sorted_ev + base;
-    for (uint32_t i = threadIdx.x; i < n; i += kSortThreads) {
-        const uint32_t k = kin[i], v = vin[i];
-        se[i] = e[v];
-        ka[i] = ((k >> tb) << 24) | (k & tick_mask);
-        va[i] = v;
+    for (uint32_t i0 = threadIdx.x; i0 < n; i0 += 4 * kSortThreads) {
+        uint32_t k[4], v[4];
+        MstEvent x[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t i = i0 + u * kSortThreads;
+            k[u] = i < n ? kin[i] : 0u;
+            v[u] = i < n ? vin[i] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) if (i0 + u * kSortThreads < n) x[u] = e[v[u]];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t i = i0 + u * kSortThreads;
+            if (i >= n) break;
+            se[i] = x[u];
+            ka[i] = ((k[u] >> tb) << 24) | (k[u] & tick_mask);
+            va[i] = v[u];
+        }
     }
     __syncthreads();
     if (threadIdx.x <= kClassEnd) {

@@ -7,9 +7,22 @@ constexpr int kSortThreads = 1024;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kSortBatch = 8;       // strips whose keys a warp fetches together
 
+// lanes of `act` whose 8-bit digit equals mine.  Eight ballots instead of match.any: the hardware match instruction
+// serialises over the distinct values in the warp (32 for the low tick bytes), which made it the top stall of both
+// sort kernels (ncu: the instruction consuming its result held 40 % of k_sort's samples).  All 32 lanes must call.
+__device__ __forceinline__ unsigned match_digit8(unsigned act, uint32_t d) {
+    unsigned peers = act;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const unsigned m = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+        peers &= ((d >> b) & 1u) ? m : ~m;
+    }
+    return peers;
+}
+
 // One 8-bit pass.  Every warp owns a contiguous segment of the input, so the relative order of equal
 // digits is preserved: warp-private digit offsets come from a per-digit scan over the warps, ranks
-// inside a 32-element strip from match_any.  whist: [kSortWarps][256] words of shared memory.
+// inside a 32-element strip from match_digit8.  whist: [kSortWarps][256] words of shared memory.
 __device__ inline void radix_pass(const uint32_t *kin, const uint32_t *vin, uint32_t *kout, uint32_t *vout, uint32_t n,
                            int shift, uint32_t (*whist)[256], uint32_t *scan_tmp, int *skip_flag) {
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -30,11 +43,9 @@ __device__ inline void radix_pass(const uint32_t *kin, const uint32_t *vin, uint
             if (b0 + u * 32 >= hi) break;
             const bool valid = i < hi;
             const unsigned act = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                const uint32_t d = (kk[u] >> shift) & 255u;
-                const unsigned peers = __match_any_sync(act, d);
-                if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
-            }
+            const uint32_t d = (kk[u] >> shift) & 255u;
+            const unsigned peers = match_digit8(act, d);
+            if (valid && (peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
             __syncwarp();
         }
     }
@@ -72,15 +83,15 @@ __device__ inline void radix_pass(const uint32_t *kin, const uint32_t *vin, uint
             if (b0 + u * 32 >= hi) break;
             const bool valid = i < hi;
             const unsigned act = __ballot_sync(0xffffffffu, valid);
+            const uint32_t d = (kk[u] >> shift) & 255u;
+            const unsigned peers = match_digit8(act, d);
             if (valid) {
-                const uint32_t d = (kk[u] >> shift) & 255u;
-                const unsigned peers = __match_any_sync(act, d);
                 const uint32_t dst = whist[warp][d] + __popc(peers & lanemask_lt());
                 kout[dst] = kk[u];
                 vout[dst] = vv[u];
-                __syncwarp(act);
-                if ((peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
             }
+            __syncwarp();
+            if (valid && (peers & lanemask_lt()) == 0) whist[warp][d] += __popc(peers);
             __syncwarp();
         }
     }

@@ -92,6 +92,21 @@ def test_encode_quantisation_quirk_tpb(torch, tpb):
     _oracle_compare(torch, events, songs, abi.make_filter(synth.POPULAR, 0))
 
 
+def test_encode_tracks_sharing_channels_take_the_full_sort(torch):
+    """k_sort's fast path (class partition + sortedness check) only holds when no two tracks share a class: fold the
+    tracks of some songs onto three channels so that their class segments interleave in tick order and the full radix
+    sort has to run; the other songs of the same batch stay on the fast path."""
+    events, songs = synth.synth_corpus(4, seed=77, n_bars=24, n_tracks=8)
+    events = events.copy()
+    for sg in songs[::2]:
+        lo, hi = int(sg['event_offset']), int(sg['event_offset']) + int(sg['n_events'])
+        ev = events[lo:hi]
+        pitched = (ev['track'] > 0) & (ev['channel'] != 9)
+        ev['channel'][pitched] = ev['channel'][pitched] % 3
+    infos, _ = _oracle_compare(torch, events, songs, abi.make_filter(synth.POPULAR, 0))
+    assert all(int(r['status']) == abi.SONG_OK for r in infos)
+
+
 def test_encode_without_filter_and_with_crop(torch):
     events, songs = synth.synth_corpus(2, seed=5, n_bars=40, n_tracks=8)
     _oracle_compare(torch, events, songs, None)
