@@ -22,9 +22,11 @@
 //   k_grid    persistent CTAs: (slot, bar) tiles built in shared memory (zero-kept buffers, atomicMax
 //             scatter) and written once with TMA bulk stores (cp.async.bulk shared -> global)
 #include <math_constants.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 
 #include "mst_device.cuh"
 #include "mst_sort.cuh"
@@ -527,6 +529,9 @@ __global__ void __launch_bounds__(1024, 1)
 k_offsets(uint32_t n_songs, Workspace ws, MstSongInfo *info, uint64_t arena_floats) {
     __shared__ unsigned long long w64[33];
     __shared__ uint32_t w32[33];
+    __shared__ unsigned long long fill_end;
+    if (threadIdx.x == 0) fill_end = 0;
+    __syncthreads();
     unsigned long long run_floats = 0;
     uint32_t run_bins = 0, run_tiles = 0;
     const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
@@ -575,12 +580,15 @@ k_offsets(uint32_t n_songs, Workspace ws, MstSongInfo *info, uint64_t arena_floa
                 info[song].unpitched_offset = off + pf;
             }
         }
+        if (fits) atomicMax(&fill_end, off + f);     // songs that fit are a prefix of the offset order
         run_floats += chunk_total; run_bins += tb; run_tiles += tt;
     }
+    __syncthreads();
     if (threadIdx.x == 0) {
         ws.tile_prefix[n_songs] = run_tiles;
         ws.totals[0] = run_tiles;
         ws.totals[1] = run_bins;
+        *reinterpret_cast<unsigned long long *>(ws.totals + 2) = fill_end;   // floats [0, fill_end) hold the batch's grids
     }
 }
 
@@ -884,8 +892,13 @@ __device__ __forceinline__ int quantise(int time, int tpb, int tpbar, int *qtime
     return (quants >= 0 && quants < 3) ? c_col3[quants] : -1;
 }
 
+// DIRECT = 1 (the default path): the arena range of the batch has been zero-filled by k_fill, so every quantised note
+// goes straight to its cell with the same max / flag semantics (integer atomicMax on the non-negative f32 bit patterns is
+// np.maximum; order-independent, hence deterministic) and nothing is binned.  DIRECT = 0 bins the cells per (slot, bar)
+// for the shared-memory tile writer k_grid (kept for comparison: MST_GRID_TILES=1).
+template <int DIRECT>
 __global__ void __launch_bounds__(256)
-k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out) {
+k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out, float *__restrict__ arena) {
     __shared__ uint32_t scan_tmp[33];
     __shared__ uint32_t s_count;
     const uint32_t song = blockIdx.x;
@@ -897,12 +910,16 @@ k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
     const int tpb = info->ticks_per_beat, tpbar = info->ticks_per_bar, nb = info->n_beats;
     const int n_out = info->n_bars_out, n_grid = info->n_bars + 1;
     const int tonic = info->tonic, mode = info->mode;
+    const uint64_t p_off = info->pitched_offset, u_off = info->unpitched_offset;
+    const uint32_t Cp = (uint32_t)info->n_pitched;
     uint32_t *bin_count = ws.bin_count + plan.bin_base, *bin_start = ws.bin_start + plan.bin_base;
     uint32_t *bin_fill = ws.bin_fill + plan.bin_base;
     Cell *cells = ws.cells + base;
-    for (uint32_t i = threadIdx.x; i < plan.n_bins; i += blockDim.x) { bin_count[i] = 0; bin_fill[i] = 0; }
-    if (threadIdx.x == 0) s_count = 0;
-    __syncthreads();
+    if (!DIRECT) {
+        for (uint32_t i = threadIdx.x; i < plan.n_bins; i += blockDim.x) { bin_count[i] = 0; bin_fill[i] = 0; }
+        if (threadIdx.x == 0) s_count = 0;
+        __syncthreads();
+    }
     uint32_t scattered = 0;
     for (uint32_t l = 0; l < plan.n_lists; l++) {
         const ListRec L = lists[l];
@@ -932,6 +949,17 @@ k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
             const double duration = __ddiv_rn((double)qdur, (double)tpb);   // :501
             const uint32_t rows = L.pitched ? MST_N_PITCHED_ROWS : MST_N_UNPITCHED_ROWS;
             const uint32_t feats = L.pitched ? MST_N_PITCHED_FEATS : MST_N_UNPITCHED_FEATS;
+            if (DIRECT) {
+                const uint64_t slab = L.pitched
+                    ? p_off + ((uint64_t)L.out_slot * n_out + bar) * nb * MST_PITCHED_BEAT_FLOATS
+                    : u_off + ((uint64_t)(L.out_slot - Cp) * n_out + bar) * nb * MST_UNPITCHED_BEAT_FLOATS;
+                float *cell = arena + slab + (((uint32_t)beat * MST_N_FRACTIONS + col) * rows + row) * feats;
+                const float dur = (float)duration, vel = (float)nt.velocity;       // f64 -> f32 of prepare_input (data.py:136)
+                if (dur > 0.f) atomicMax((int *)cell, __float_as_int(dur));        // np.maximum with 0 (:514)
+                atomicMax((int *)cell + 1, __float_as_int(vel));
+                if (acc < 3) cell[2 + acc] = 1.0f;
+                continue;
+            }
             Cell c;
             c.bin = plan.bin_base + (uint32_t)L.out_slot * n_out + bar;
             c.off_acc = (((uint32_t)beat * MST_N_FRACTIONS + col) * rows + row) * feats | ((uint32_t)acc << 28);
@@ -945,6 +973,7 @@ k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
     // n_notes (informative)
     for (int o = 16; o; o >>= 1) scattered += __shfl_xor_sync(0xffffffffu, scattered, o);
     if (lane_id() == 0 && scattered) atomicAdd((unsigned *)&info->n_notes, scattered);
+    if (DIRECT) return;
     __syncthreads();
     // exclusive scan of the song's bins; bin_start is an absolute index into cells_sorted
     uint32_t running = 0;
@@ -1101,6 +1130,46 @@ k_grid(Workspace ws, float *__restrict__ arena) {
     if (threadIdx.x == 0) bulk_wait<0>();
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_fill: the dense part of qchannel2vchannel / np.stack — 99.7 % of a grid is zeros.  Persistent CTAs stream the batch's
+// arena range [0, fill_end) from a read-only zero tile in shared memory with TMA bulk stores (cp.async.bulk shared ->
+// global, 32 KB each, one issuing thread per CTA, no barrier in the loop); k_cells<1> then drops the notes in.
+// A write-only stream is bounded by the HBM write bandwidth (tools/write_peak_probe.py), not by the copy figure.
+// ------------------------------------------------------------------------------------------------
+constexpr int kFillThreads = 128;
+constexpr uint32_t kFillChunkFloats = 8192;      // 32 KB per bulk store
+
+__global__ void __launch_bounds__(kFillThreads)
+k_fill(Workspace ws, float *__restrict__ arena) {
+    extern __shared__ __align__(128) float zero_tile[];
+    for (uint32_t i = threadIdx.x; i < kFillChunkFloats; i += kFillThreads) zero_tile[i] = 0.f;
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    const unsigned long long total = *reinterpret_cast<const unsigned long long *>(ws.totals + 2);
+    const unsigned long long n_chunks = (total + kFillChunkFloats - 1) / kFillChunkFloats;
+    for (unsigned long long c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        const unsigned long long lo = c * kFillChunkFloats;
+        const uint32_t fl = (uint32_t)min((unsigned long long)kFillChunkFloats, total - lo);
+        bulk_store_s2g(arena + lo, zero_tile, fl * 4u);
+        bulk_commit();
+    }
+    bulk_wait<0>();
+}
+
+// k_fill_flat (the default): plain 16-byte stores, one CTA per 16 KB, no loop; the grid covers the arena and CTAs past
+// fill_end exit.  Measured on the 512-song batch (39 GB): 5.2 ms = 7.5 TB/s alone, against 6.15 ms for the persistent bulk
+// store variant above (MST_FILL_MODE=0) and 5.6-5.9 ms for persistent grid-stride stores at 32-512 CTAs per SM.
+__global__ void __launch_bounds__(256)
+k_fill_flat(Workspace ws, float *__restrict__ arena) {
+    const unsigned long long total4 = *reinterpret_cast<const unsigned long long *>(ws.totals + 2) / 4;
+    float4 *dst = reinterpret_cast<float4 *>(arena);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    const unsigned long long i = (unsigned long long)blockIdx.x * 1024 + threadIdx.x;
+#pragma unroll
+    for (int u = 0; u < 4; u++) if (i + u * 256 < total4) dst[i + u * 256] = z;
+}
+
 }  // namespace
 
 // ================================================================================================
@@ -1145,18 +1214,40 @@ extern "C" size_t mst_encode_workspace_bytes(uint64_t n_events_total, uint32_t n
 
 // optional device-side timing of the two halves of the pipeline (bench.py's roofline numbers)
 static bool g_profile = false;
-static cudaEvent_t g_ev[3] = {nullptr, nullptr, nullptr};
+static cudaEvent_t g_ev[4] = {nullptr, nullptr, nullptr, nullptr};   // pipeline start, fill start, fill end, pipeline end
 extern "C" int mst_profile_enable(int on) {
-    if (on && !g_ev[0]) for (int i = 0; i < 3; i++) MST_CUDA_CHECK(cudaEventCreate(&g_ev[i]));
+    if (on && !g_ev[0]) for (int i = 0; i < 4; i++) MST_CUDA_CHECK(cudaEventCreate(&g_ev[i]));
     g_profile = on != 0;
     return MST_OK;
 }
-// which: 0 = front end (k_sort .. k_cells), 1 = k_grid; valid after the stream has been synchronised
+// which: 0 = the whole pipeline (k_sort .. k_cells), 1 = the grid-writing kernel (k_fill_flat, or k_grid on the tile path);
+// valid after the stream has been synchronised.  The two overlap (side stream), so they do not add up.
 extern "C" float mst_profile_encode_ms(int which) {
     if (!g_ev[0]) return -1.f;
     float ms = -1.f;
-    if (cudaEventElapsedTime(&ms, g_ev[which ? 1 : 0], g_ev[which ? 2 : 1]) != cudaSuccess) { cudaGetLastError(); return -1.f; }
+    if (cudaEventElapsedTime(&ms, g_ev[which ? 1 : 0], g_ev[which ? 2 : 3]) != cudaSuccess) { cudaGetLastError(); return -1.f; }
     return ms;
+}
+
+// high-priority side stream for the latency-bound front-end kernels that run next to the zero fill; fork / join events.  One set per
+// process (one process per GPU); the enqueue sequence is serialised so that callers on several host threads
+// (utils/parallel.py:34-39 consumes iter_inputs off the main thread) cannot interleave the event records.
+static cudaStream_t g_side = nullptr;
+static cudaEvent_t g_fork = nullptr, g_join = nullptr;
+static int g_side_dev = -1;
+static std::mutex g_enqueue_mutex;
+static int side_stream_ready() {
+    int dev = 0;
+    MST_CUDA_CHECK(cudaGetDevice(&dev));
+    if (g_side && dev == g_side_dev) return MST_OK;
+    if (g_side) { cudaStreamDestroy(g_side); cudaEventDestroy(g_fork); cudaEventDestroy(g_join); g_side = nullptr; }
+    int prio_lo = 0, prio_hi = 0;
+    MST_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    MST_CUDA_CHECK(cudaStreamCreateWithPriority(&g_side, cudaStreamNonBlocking, prio_hi));
+    MST_CUDA_CHECK(cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming));
+    MST_CUDA_CHECK(cudaEventCreateWithFlags(&g_join, cudaEventDisableTiming));
+    g_side_dev = dev;
+    return MST_OK;
 }
 
 static int g_num_sms = 0;
@@ -1195,6 +1286,10 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
     if (h_filter) filter = *h_filter; else { memset(&filter, 0, sizeof(filter)); }
     const int sms = num_sms();
 
+    static const bool tiles_path = getenv("MST_GRID_TILES") != nullptr;      // comparison path: shared-memory tile writer
+    static const int fill_mode = getenv("MST_FILL_MODE") ? atoi(getenv("MST_FILL_MODE")) : 2;
+    static const bool overlap = getenv("MST_ENCODE_NO_OVERLAP") == nullptr;
+    std::lock_guard<std::mutex> lock(g_enqueue_mutex);
     if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[0], stream));
     k_sort<<<n_songs, kSortThreads, 0, stream>>>(d_events, d_songs, ws);
     MST_LAUNCH_CHECK("k_sort");
@@ -1206,23 +1301,52 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
     MST_LAUNCH_CHECK("k_info");
     k_offsets<<<1, 1024, 0, stream>>>(n_songs, ws, d_info, arena_floats);
     MST_LAUNCH_CHECK("k_offsets");
-    k_walk<1><<<walk_blocks, 128, 0, stream>>>(d_songs, n_songs, ws, d_info);
-    MST_LAUNCH_CHECK("k_walk<1>");
-    k_pair<<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info);
-    MST_LAUNCH_CHECK("k_pair");
-    k_scale<<<n_songs, kScaleThreads, 0, stream>>>(d_songs, ws, d_info);
-    MST_LAUNCH_CHECK("k_scale");
-    k_cells<<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info);
-    MST_LAUNCH_CHECK("k_cells");
-    const size_t grid_smem = (size_t)(1 + kGridBufs) * kTileFloatsMax * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
-        MST_CUDA_CHECK(cudaFuncSetAttribute(k_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)grid_smem));
-        attr_set = true;
+    // The zero fill needs only k_offsets' result and streams at the HBM write bandwidth; k_walk<1> / k_pair / k_scale are
+    // latency-bound.  They run on a HIGH-PRIORITY side stream so that their CTAs are picked first whenever the fill's
+    // short-lived CTAs retire, and hide behind the fill; k_cells waits for both.
+    const bool fill = !tiles_path && arena_floats != 0;
+    cudaStream_t front = stream;
+    if (fill && overlap) {
+        if (side_stream_ready() != MST_OK) return MST_E_CUDA;
+        MST_CUDA_CHECK(cudaEventRecord(g_fork, stream));
+        MST_CUDA_CHECK(cudaStreamWaitEvent(g_side, g_fork, 0));
+        front = g_side;
     }
-    if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
-    k_grid<<<sms, kGridThreads, grid_smem, stream>>>(ws, d_arena);
-    MST_LAUNCH_CHECK("k_grid");
-    if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
+    k_walk<1><<<walk_blocks, 128, 0, front>>>(d_songs, n_songs, ws, d_info);
+    MST_LAUNCH_CHECK("k_walk<1>");
+    k_pair<<<n_songs, 256, 0, front>>>(d_songs, ws, d_info);
+    MST_LAUNCH_CHECK("k_pair");
+    k_scale<<<n_songs, kScaleThreads, 0, front>>>(d_songs, ws, d_info);
+    MST_LAUNCH_CHECK("k_scale");
+    if (fill) {
+        if (overlap) MST_CUDA_CHECK(cudaEventRecord(g_join, g_side));
+        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
+        if (fill_mode == 0) k_fill<<<sms * 2, kFillThreads, kFillChunkFloats * sizeof(float), stream>>>(ws, d_arena);
+        else k_fill_flat<<<(unsigned)((arena_floats / 4 + 1023) / 1024), 256, 0, stream>>>(ws, d_arena);
+        MST_LAUNCH_CHECK("k_fill");
+        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
+    }
+    if (tiles_path) {
+        k_cells<0><<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info, d_arena);
+        MST_LAUNCH_CHECK("k_cells");
+        const size_t grid_smem = (size_t)(1 + kGridBufs) * kTileFloatsMax * sizeof(float);
+        static bool attr_set = false;
+        if (!attr_set) {
+            MST_CUDA_CHECK(cudaFuncSetAttribute(k_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)grid_smem));
+            attr_set = true;
+        }
+        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
+        k_grid<<<sms, kGridThreads, grid_smem, stream>>>(ws, d_arena);
+        MST_LAUNCH_CHECK("k_grid");
+        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
+    } else {
+        if (fill && overlap) MST_CUDA_CHECK(cudaStreamWaitEvent(stream, g_join, 0));
+        k_cells<1><<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info, d_arena);
+        MST_LAUNCH_CHECK("k_cells");
+    }
+    if (g_profile) {
+        if (!fill && !tiles_path) { MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream)); MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream)); }
+        MST_CUDA_CHECK(cudaEventRecord(g_ev[3], stream));
+    }
     return MST_OK;
 }
