@@ -621,6 +621,7 @@ def main():
         'peak_source': peak_src + '; copy bandwidth (read + write bytes) - a write-only stream can exceed it: torch '
                                   'fill_ of 8 GiB measures 7535 GB/s on this part (tools/write_peak_probe.py)',
         'algorithmic_bytes_per_launch': g_bytes, 'ms_per_launch': g_ms,
+        'frac_of_write_only_peak': achieved / 7535.0, 'write_only_peak_source': 'profiles/r1_write_peak_probe.txt',
         'share_of_step': g_ms / whole_ms,
         'pipeline': {'whole_ms': whole_ms, 'not_hidden_behind_the_fill_ms': whole_ms - g_ms,
                      'note': 'the zero fill runs on a side stream next to k_walk<1> / k_pair / k_scale; k_sort, k_walk<0>, '
