@@ -148,9 +148,9 @@ int         mst_abi_version(void);
 const char *mst_last_error(void);
 int         mst_device_count(void);   /* 0 when no GPU is visible */
 
-/* Optional device-side timing (CUDA events on the caller's stream) of the encode pipeline's two
- * halves: which = 0 front end (sort .. binning), 1 = the grid-writing kernel.  Read after a
- * stream synchronise.  Used by bench.py for the roofline of the dominant kernel. */
+/* Optional device-side timing (CUDA events) of the encode pipeline: which = 0 the whole pipeline
+ * (sort .. note scatter), 1 = the grid-writing kernel (the zero fill), which overlaps part of it.
+ * Read after a stream synchronise.  Used by bench.py for the roofline of the dominant kernel. */
 int   mst_profile_enable(int on);
 float mst_profile_encode_ms(int which);
 

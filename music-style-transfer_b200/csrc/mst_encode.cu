@@ -10,17 +10,19 @@
 //   prepare_input        style/data.py:130-143 (bar crop + f32 cast)
 //
 // Pipeline (one launch each, everything stays in HBM):
-//   k_sort    per-song CTA: stable LSD radix sort of (class, tick) -> merged order, grouped per channel
-//   k_walk<0> warp per (song, channel): program / CC7 state scan, per-instrument message counts
-//   k_info    warp per song: song info (tempo histogram, signatures, bars), channel-list table, filter,
-//             output slots and sizes
-//   k_offsets one CTA: prefix sums of grid floats / bins / tiles over the batch, arena check
-//   k_walk<1> same scan again, now writing NoteMessage records into per-list storage
-//   k_pair    warp per list: note pairing (ballot/match within a 32-message strip, open-note table across)
-//   k_scale   per-song CTA: key histogram in reference summation order + 24-candidate scale choice
-//   k_cells   per-song CTA: f64 dual-grid quantisation, scale-aware rows, binning per (slot, bar)
-//   k_grid    persistent CTAs: (slot, bar) tiles built in shared memory (zero-kept buffers, atomicMax
-//             scatter) and written once with TMA bulk stores (cp.async.bulk shared -> global)
+//   k_sort      per-song CTA: stable partition by class + sortedness check (full stable LSD radix sort of
+//               (class, tick) only for songs whose tracks share a channel) -> merged order, grouped per channel
+//   k_walk<0>   warp per (song, channel): program / CC7 state scan, per-instrument message counts
+//   k_info      warp per song: song info (tempo histogram, signatures, bars), channel-list table, filter,
+//               output slots and sizes
+//   k_offsets   one CTA: prefix sums of grid floats over the batch, arena check, end of the written range
+//   k_fill_flat zero fill of the batch's arena range at the HBM write bandwidth (caller's stream)   } concurrent
+//   k_walk<1>   same scan again, now writing NoteMessage records into per-list storage              } (high-priority
+//   k_pair      warp per list: note pairing (match within a 32-message strip, open-note table across) } side stream)
+//   k_scale     per-song CTA: key histogram in reference summation order + 24-candidate scale choice  }
+//   k_cells<1>  per-song CTA: f64 dual-grid quantisation, scale-aware rows, note scatter (global atomicMax)
+// Comparison path (MST_GRID_TILES=1): k_cells<0> bins the cells per (slot, bar) and k_grid (persistent CTAs) builds
+// (slot, bar) tiles in shared memory and writes them once with TMA bulk stores (cp.async.bulk shared -> global).
 #include <math_constants.h>
 #include <stdlib.h>
 #include <string.h>
@@ -925,8 +927,11 @@ k_cells(const MstSongIn *__restrict__ songs, Workspace ws, MstSongInfo *info_out
         const ListRec L = lists[l];
         if (L.out_slot < 0) continue;
         const Note *notes = ws.notes + base + L.note_offset;
+        Note nxt;                                                    // the next note is fetched while this one is quantised
+        if (threadIdx.x < L.n_notes) nxt = notes[threadIdx.x];
         for (uint32_t j = threadIdx.x; j < L.n_notes; j += blockDim.x) {
-            const Note nt = notes[j];
+            const Note nt = nxt;
+            if (j + blockDim.x < L.n_notes) nxt = notes[j + blockDim.x];
             int row, acc = 1;
             if (L.pitched) {
                 int octave = nt.note_id / 12 - 1;                       // note_id2key_octave (:309-317)
@@ -1233,18 +1238,19 @@ extern "C" float mst_profile_encode_ms(int which) {
 // process (one process per GPU); the enqueue sequence is serialised so that callers on several host threads
 // (utils/parallel.py:34-39 consumes iter_inputs off the main thread) cannot interleave the event records.
 static cudaStream_t g_side = nullptr;
-static cudaEvent_t g_fork = nullptr, g_join = nullptr;
+static cudaEvent_t g_fork = nullptr, g_offs = nullptr, g_join = nullptr;
 static int g_side_dev = -1;
 static std::mutex g_enqueue_mutex;
 static int side_stream_ready() {
     int dev = 0;
     MST_CUDA_CHECK(cudaGetDevice(&dev));
     if (g_side && dev == g_side_dev) return MST_OK;
-    if (g_side) { cudaStreamDestroy(g_side); cudaEventDestroy(g_fork); cudaEventDestroy(g_join); g_side = nullptr; }
+    if (g_side) { cudaStreamDestroy(g_side); cudaEventDestroy(g_fork); cudaEventDestroy(g_offs); cudaEventDestroy(g_join); g_side = nullptr; }
     int prio_lo = 0, prio_hi = 0;
     MST_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     MST_CUDA_CHECK(cudaStreamCreateWithPriority(&g_side, cudaStreamNonBlocking, prio_hi));
     MST_CUDA_CHECK(cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming));
+    MST_CUDA_CHECK(cudaEventCreateWithFlags(&g_offs, cudaEventDisableTiming));
     MST_CUDA_CHECK(cudaEventCreateWithFlags(&g_join, cudaEventDisableTiming));
     g_side_dev = dev;
     return MST_OK;
@@ -1291,26 +1297,40 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
     static const bool overlap = getenv("MST_ENCODE_NO_OVERLAP") == nullptr;
     std::lock_guard<std::mutex> lock(g_enqueue_mutex);
     if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[0], stream));
-    k_sort<<<n_songs, kSortThreads, 0, stream>>>(d_events, d_songs, ws);
-    MST_LAUNCH_CHECK("k_sort");
-    const uint32_t walk_blocks = (uint32_t)std::min<uint64_t>(((uint64_t)n_songs * 16u + 3) / 4, (uint64_t)sms * 16);
-    k_walk<0><<<walk_blocks, 128, 0, stream>>>(d_songs, n_songs, ws, d_info);
-    MST_LAUNCH_CHECK("k_walk<0>");
-    const uint32_t info_blocks = (uint32_t)std::min<uint64_t>(((uint64_t)n_songs + 3) / 4, (uint64_t)sms * 16);
-    k_info<<<info_blocks, 128, 0, stream>>>(d_songs, n_songs, ws, filter, d_info);
-    MST_LAUNCH_CHECK("k_info");
-    k_offsets<<<1, 1024, 0, stream>>>(n_songs, ws, d_info, arena_floats);
-    MST_LAUNCH_CHECK("k_offsets");
-    // The zero fill needs only k_offsets' result and streams at the HBM write bandwidth; k_walk<1> / k_pair / k_scale are
-    // latency-bound.  They run on a HIGH-PRIORITY side stream so that their CTAs are picked first whenever the fill's
-    // short-lived CTAs retire, and hide behind the fill; k_cells waits for both.
+    // The zero fill needs only k_offsets' result and streams at the HBM write bandwidth; every other kernel but the final
+    // note scatter is latency-bound.  Those run on a HIGH-PRIORITY side stream, so that their CTAs are picked first whenever
+    // a fill's short-lived CTAs retire: k_walk<1> / k_pair / k_scale hide behind this batch's fill, and when the caller
+    // alternates two streams (bench.py, iter_inputs' prefetch) the next batch's k_sort .. k_offsets hide behind it too.
+    // The fill and k_cells stay on the caller's stream; k_cells waits for both.
     const bool fill = !tiles_path && arena_floats != 0;
+    const bool side = fill && overlap;
     cudaStream_t front = stream;
-    if (fill && overlap) {
+    if (side) {
         if (side_stream_ready() != MST_OK) return MST_E_CUDA;
         MST_CUDA_CHECK(cudaEventRecord(g_fork, stream));
         MST_CUDA_CHECK(cudaStreamWaitEvent(g_side, g_fork, 0));
         front = g_side;
+    }
+    k_sort<<<n_songs, kSortThreads, 0, front>>>(d_events, d_songs, ws);
+    MST_LAUNCH_CHECK("k_sort");
+    const uint32_t walk_blocks = (uint32_t)std::min<uint64_t>(((uint64_t)n_songs * 16u + 3) / 4, (uint64_t)sms * 16);
+    k_walk<0><<<walk_blocks, 128, 0, front>>>(d_songs, n_songs, ws, d_info);
+    MST_LAUNCH_CHECK("k_walk<0>");
+    const uint32_t info_blocks = (uint32_t)std::min<uint64_t>(((uint64_t)n_songs + 3) / 4, (uint64_t)sms * 16);
+    k_info<<<info_blocks, 128, 0, front>>>(d_songs, n_songs, ws, filter, d_info);
+    MST_LAUNCH_CHECK("k_info");
+    k_offsets<<<1, 1024, 0, front>>>(n_songs, ws, d_info, arena_floats);
+    MST_LAUNCH_CHECK("k_offsets");
+    if (fill) {
+        if (side) {
+            MST_CUDA_CHECK(cudaEventRecord(g_offs, g_side));
+            MST_CUDA_CHECK(cudaStreamWaitEvent(stream, g_offs, 0));
+        }
+        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
+        if (fill_mode == 0) k_fill<<<sms * 2, kFillThreads, kFillChunkFloats * sizeof(float), stream>>>(ws, d_arena);
+        else k_fill_flat<<<(unsigned)((arena_floats / 4 + 1023) / 1024), 256, 0, stream>>>(ws, d_arena);
+        MST_LAUNCH_CHECK("k_fill");
+        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
     }
     k_walk<1><<<walk_blocks, 128, 0, front>>>(d_songs, n_songs, ws, d_info);
     MST_LAUNCH_CHECK("k_walk<1>");
@@ -1318,14 +1338,7 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
     MST_LAUNCH_CHECK("k_pair");
     k_scale<<<n_songs, kScaleThreads, 0, front>>>(d_songs, ws, d_info);
     MST_LAUNCH_CHECK("k_scale");
-    if (fill) {
-        if (overlap) MST_CUDA_CHECK(cudaEventRecord(g_join, g_side));
-        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[1], stream));
-        if (fill_mode == 0) k_fill<<<sms * 2, kFillThreads, kFillChunkFloats * sizeof(float), stream>>>(ws, d_arena);
-        else k_fill_flat<<<(unsigned)((arena_floats / 4 + 1023) / 1024), 256, 0, stream>>>(ws, d_arena);
-        MST_LAUNCH_CHECK("k_fill");
-        if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
-    }
+    if (side) MST_CUDA_CHECK(cudaEventRecord(g_join, g_side));
     if (tiles_path) {
         k_cells<0><<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info, d_arena);
         MST_LAUNCH_CHECK("k_cells");
@@ -1340,7 +1353,7 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
         MST_LAUNCH_CHECK("k_grid");
         if (g_profile) MST_CUDA_CHECK(cudaEventRecord(g_ev[2], stream));
     } else {
-        if (fill && overlap) MST_CUDA_CHECK(cudaStreamWaitEvent(stream, g_join, 0));
+        if (side) MST_CUDA_CHECK(cudaStreamWaitEvent(stream, g_join, 0));
         k_cells<1><<<n_songs, 256, 0, stream>>>(d_songs, ws, d_info, d_arena);
         MST_LAUNCH_CHECK("k_cells");
     }
