@@ -341,7 +341,10 @@ def training_e2e_from_events(args, world, rank, torch, dist, t, sh, N, losses, b
     filt = abi.make_filter(synth.POPULAR, 100, crop_channel_bars=C * B)
     # candidate songs: C pitched tracks + drums over B bars; keep those the encoder turns into exactly (C, B) + drums
     # (tracks that drew the same program are merged by merge_nchannels, data.py:103-114)
-    ev, sg = synth.synth_corpus(2 * N + 8, seed=4321 + 17 * rank, n_bars=B, n_tracks=C + 1)
+    ev, sg = synth.synth_corpus(N + 8, seed=4321 + 17 * rank, n_bars=B, n_tracks=C + 1)
+    ev = ev.copy()
+    pc = ev['kind'] == abi.EV_PROGRAM_CHANGE              # one distinct program per pitched track: C channels after merging
+    ev['d1'][pc] = np.array(sorted(synth.POPULAR), dtype=np.uint8)[(ev['track'][pc].astype(np.int64) - 1) % len(synth.POPULAR)]
     per_song = synth.split_songs(ev, sg)
     cand = lib.DeviceBatch(ev, sg)
     cand.encode(filt, None)
