@@ -542,7 +542,13 @@ def main():
         raise SystemExit('bench.py needs a CUDA device: the B200 path has no CPU fallback')
     torch.cuda.set_device(local_rank)
     if world > 1:
-        os.environ['NCCL_DEBUG'] = os.environ.get('MST_NCCL_DEBUG', 'WARN')   # keep NCCL's banner off stdout: ONE JSON line
+        # stdout carries ONE JSON line: NCCL prints its version banner there at any NCCL_DEBUG level, so the variable is
+        # dropped unless MST_NCCL_DEBUG asks for a level, and then the log goes to stderr
+        if os.environ.get('MST_NCCL_DEBUG'):
+            os.environ['NCCL_DEBUG'] = os.environ['MST_NCCL_DEBUG']
+            os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
+        else:
+            os.environ.pop('NCCL_DEBUG', None)
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     L = lib.require_gpu()
 
