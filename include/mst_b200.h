@@ -166,7 +166,9 @@ int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent *h_events, 
 /* Replaces read_midi (midi_conversion.py:216-232), iter_inputs' filter (data.py:53-58),
  * get_input (data.py:66-100) incl. ChannelConverter.channel2nchannel / nchannel2vchannel
  * (:371-456,490-516), get_keys_dist (:340) + get_scale (scales.py:214), and prepare_input's
- * crop + f32 cast (data.py:130-143) for a whole batch of songs. */
+ * crop + f32 cast (data.py:130-143) for a whole batch of songs.
+ * d_arena must be 16-byte aligned (MST_E_INVALID otherwise); the grids of the songs that fit are
+ * packed from its start, song after song, and that range is the only part of it that is written. */
 size_t mst_encode_workspace_bytes(uint64_t n_events_total, uint32_t n_songs, uint64_t arena_floats);
 
 int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_events_total,

@@ -1277,6 +1277,10 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
         return MST_E_INVALID;
     }
     if (n_songs == 0) return MST_OK;
+    if (reinterpret_cast<uintptr_t>(d_arena) & 15u) {
+        mst_set_error("mst_encode_batch_device: the arena must be 16-byte aligned");
+        return MST_E_INVALID;
+    }
     if (n_events_total >= 0xFFFFFFFFull) {
         mst_set_error("mst_encode_batch_device: at most 2^32-1 events per batch");
         return MST_E_INVALID;
