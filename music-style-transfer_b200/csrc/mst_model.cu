@@ -402,6 +402,13 @@ struct Launcher {
             pack.j[i] = jobs[i];
             max_blocks = std::max(max_blocks, (jobs[i].S + G - 1) / G);
         }
+        if (G == 1 && H == 64) {
+            // one long sequence per CTA: W_hh rows in registers (mst_model_kernels2.cuh)
+            dim3 grid(std::min(max_blocks, std::max(1, 148 * 4 / n_jobs)), n_jobs);
+            if (backward) k_lstm_bwd_r64<<<grid, 256, 0, st>>>(pack); else k_lstm_fwd_r64<<<grid, 256, 0, st>>>(pack);
+            check();
+            return;
+        }
         const size_t smem = lstm_smem(H, G, w_smem);
         const int threads = std::max(32, (4 * H + 31) / 32 * 32);
         // the kernels loop over the sequence groups: enough CTAs to fill every SM, W_hh staged once per CTA

@@ -249,6 +249,117 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Bars-axis recurrences (style/model.py:69,120: one long sequence per sample, H = 64): one sequence per CTA and the
+// step latency is everything.  Thread j keeps its row of W_hh in 64 REGISTERS (k_lstm_fwd streams it from shared memory:
+// 64 loads per thread and step, the shared-memory pipe was the bound), the state is read with 16-byte broadcasts.
+// Same partial-sum assignment and order as the one-sequence branch of k_lstm_fwd / k_lstm_bwd: bit-identical results.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_lstm_fwd_r64(LstmJobs jobs) {
+    const LstmArgs &a = jobs.j[blockIdx.y];
+    constexpr int H = 64, H4 = 256;
+    __shared__ __align__(16) float h_s[H];
+    __shared__ float c_s[H];
+    __shared__ float g_s[H4];
+    const int j = threadIdx.x;
+    float wr[H];
+#pragma unroll
+    for (int k = 0; k < H; k++) wr[k] = a.w[k * H4 + j];            // W_hh^T (H, 4H): column j
+    const bool is_tanh = (j >= 2 * H) && (j < 3 * H);
+    for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
+        if (j < H) { h_s[j] = 0.f; c_s[j] = 0.f; }
+        __syncthreads();
+        float xnext = a.xproj[((long long)s * a.T + (a.reverse ? a.T - 1 : 0)) * H4 + j];
+        for (int step = 0; step < a.T; step++) {
+            const int t = a.reverse ? a.T - 1 - step : step;
+            float a0 = xnext, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            if (step + 1 < a.T) xnext = a.xproj[((long long)s * a.T + (a.reverse ? t - 1 : t + 1)) * H4 + j];
+#pragma unroll
+            for (int k = 0; k < H; k += 4) {
+                const float4 hv = *reinterpret_cast<const float4 *>(h_s + k);
+                a0 = fmaf(wr[k], hv.x, a0); a1 = fmaf(wr[k + 1], hv.y, a1);
+                a2 = fmaf(wr[k + 2], hv.z, a2); a3 = fmaf(wr[k + 3], hv.w, a3);
+            }
+            const float acc = (a0 + a1) + (a2 + a3);
+            const float v = is_tanh ? tanhf(acc) : sigmoid_fast(acc);
+            const long long row = (long long)s * a.T + t;
+            g_s[j] = v;
+            a.gates[row * H4 + j] = v;
+            __syncthreads();
+            if (j < H) {
+                a.hprev[row * H + j] = h_s[j];
+                const float c = g_s[H + j] * c_s[j] + g_s[j] * g_s[2 * H + j];
+                const float h = g_s[3 * H + j] * tanhf(c);
+                c_s[j] = c;
+                h_s[j] = h;
+                a.cells[row * H + j] = c;
+                a.out[row * a.out_ld + a.out_off + j] = h;
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_lstm_bwd_r64(LstmJobs jobs) {
+    const LstmArgs &a = jobs.j[blockIdx.y];
+    constexpr int H = 64, H4 = 256;
+    __shared__ float dh_s[H], dc_s[H];
+    __shared__ __align__(16) float dg_s[H4];
+    __shared__ float part_s[4 * H];
+    const int j = threadIdx.x;
+    const int part = j / H, k = j - part * H;
+    float wr[H];                                                     // W_hh (4H, H): rows part * 64 .., column k
+#pragma unroll
+    for (int r = 0; r < H; r++) wr[r] = a.w[(part * H + r) * H + k];
+    for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
+        if (j < H) { dh_s[j] = 0.f; dc_s[j] = 0.f; }
+        __syncthreads();
+        for (int step = a.T - 1; step >= 0; step--) {
+            const int t = a.reverse ? a.T - 1 - step : step;
+            const int t_prev = a.reverse ? t + 1 : t - 1;
+            if (j < H) {
+                const long long row = (long long)s * a.T + t;
+                const float *gs = a.gates + row * H4;
+                const float gi = gs[j], gf = gs[H + j], gg = gs[2 * H + j], go = gs[3 * H + j];
+                const float c = a.cells[row * H + j];
+                const float c_prev = step > 0 ? a.cells[((long long)s * a.T + t_prev) * H + j] : 0.f;
+                const float tc = tanhf(c);
+                const float dh = dh_s[j] + (a.dout ? a.dout[row * a.out_ld + a.out_off + j] : 0.f);
+                const float dc = dc_s[j] + dh * go * (1.f - tc * tc);
+                const float d_i = dc * gg * gi * (1.f - gi);
+                const float d_f = dc * c_prev * gf * (1.f - gf);
+                const float d_g = dc * gi * (1.f - gg * gg);
+                const float d_o = dh * tc * go * (1.f - go);
+                dc_s[j] = dc * gf;
+                float *dgo = a.dgates + row * H4;
+                dgo[j] = d_i; dgo[H + j] = d_f; dgo[2 * H + j] = d_g; dgo[3 * H + j] = d_o;
+                dg_s[j] = d_i; dg_s[H + j] = d_f; dg_s[2 * H + j] = d_g; dg_s[3 * H + j] = d_o;
+            }
+            __syncthreads();
+            {   // dh_{step-1}[k] = sum_r W_hh[r][k] dgates[r]: a quarter of the rows per thread, partials through shared memory
+                const float *ds = dg_s + part * H;
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                for (int r = 0; r < H; r += 4) {
+                    const float4 dv = *reinterpret_cast<const float4 *>(ds + r);
+                    a0 = fmaf(wr[r], dv.x, a0); a1 = fmaf(wr[r + 1], dv.y, a1);
+                    a2 = fmaf(wr[r + 2], dv.z, a2); a3 = fmaf(wr[r + 3], dv.w, a3);
+                }
+                part_s[part * H + k] = (a0 + a1) + (a2 + a3);
+            }
+            __syncthreads();
+            if (j < H) {
+                float v = part_s[j];
+                for (int q = 1; q < 4; q++) v += part_s[q * H + j];
+                dh_s[j] = v;
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // combine (style/model.py:796-815): out[n, m] = sum_k x[n,k,m] w[n,k] / sum_k w[n,k],  w = sqrt(1 + sum_m x^2).
 // x is addressed as x[n * n_stride + k * k_stride + m].
 // ------------------------------------------------------------------------------------------------
