@@ -387,12 +387,23 @@ struct Launcher {
         if (!w_smem && n_jobs == 1 && H % kClSize == 0 && H * kClFwdParts <= 1024 && jobs[0].S <= 148 &&
             std::max(lstm_cl_fwd_smem(H), lstm_cl_bwd_smem(H)) <= 227 * 1024) {
             const int grid = (jobs[0].S + kClG - 1) / kClG * kClSize;
+            const bool regs = H == 192;       // StyleEncoder.bars_lstm: 48 / 96 weights per thread fit the register file
             if (backward) {
-                cudaFuncSetAttribute(k_lstm_bwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_bwd_smem(H));
-                k_lstm_bwd_cl<<<grid, H / kClSize * kClBwdParts, lstm_cl_bwd_smem(H), st>>>(jobs[0]);
+                if (regs) {
+                    cudaFuncSetAttribute(k_lstm_bwd_cl<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_bwd_smem(H));
+                    k_lstm_bwd_cl<96><<<grid, H / kClSize * kClBwdParts, lstm_cl_bwd_smem(H), st>>>(jobs[0]);
+                } else {
+                    cudaFuncSetAttribute(k_lstm_bwd_cl<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_bwd_smem(H));
+                    k_lstm_bwd_cl<0><<<grid, H / kClSize * kClBwdParts, lstm_cl_bwd_smem(H), st>>>(jobs[0]);
+                }
             } else {
-                cudaFuncSetAttribute(k_lstm_fwd_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_fwd_smem(H));
-                k_lstm_fwd_cl<<<grid, H * kClFwdParts, lstm_cl_fwd_smem(H), st>>>(jobs[0]);
+                if (regs) {
+                    cudaFuncSetAttribute(k_lstm_fwd_cl<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_fwd_smem(H));
+                    k_lstm_fwd_cl<48><<<grid, H * kClFwdParts, lstm_cl_fwd_smem(H), st>>>(jobs[0]);
+                } else {
+                    cudaFuncSetAttribute(k_lstm_fwd_cl<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lstm_cl_fwd_smem(H));
+                    k_lstm_fwd_cl<0><<<grid, H * kClFwdParts, lstm_cl_fwd_smem(H), st>>>(jobs[0]);
+                }
             }
             check();
             return;

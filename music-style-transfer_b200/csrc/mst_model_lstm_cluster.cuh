@@ -26,7 +26,11 @@ __host__ __device__ inline size_t lstm_cl_bwd_smem(int H) {
     return sizeof(float) * ((size_t)4 * H * HQ + 2 * kClG * 4 * H + (size_t)kClBwdParts * kClG * HQ + 2 * kClG * HQ);
 }
 
-__global__ void __cluster_dims__(kClSize, 1, 1)
+// KR > 0 (H = 192: KR = 48 forward, 96 backward): the thread's weights live in KR REGISTERS instead of the shared-memory
+// slice (the shared-memory pipe, not the cluster barrier, was the larger part of a step) and the state / gate-gradient
+// vectors are read with 16-byte broadcasts; same partial sums in the same order.  KR = 0 keeps the slice in shared memory.
+template <int KR>
+__global__ void __cluster_dims__(kClSize, 1, 1) __launch_bounds__(KR ? 768 : 1024)
 k_lstm_fwd_cl(LstmArgs a) {
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
@@ -42,12 +46,18 @@ k_lstm_fwd_cl(LstmArgs a) {
     const int ng = min(kClG, a.S - s0);
     // local column -> global gate column
     auto gcol = [&](int col) { const int gate = col / HQ, u = col - gate * HQ; return gate * H + rank * HQ + u; };
-    for (int i = j; i < H * LC; i += blockDim.x) { const int k = i / LC, col = i - k * LC; w_s[i] = a.w[(long long)k * H4 + gcol(col)]; }
+    if (KR == 0) for (int i = j; i < H * LC; i += blockDim.x) { const int k = i / LC, col = i - k * LC; w_s[i] = a.w[(long long)k * H4 + gcol(col)]; }
     for (int i = j; i < 2 * kClG * H; i += blockDim.x) h_full[i] = 0.f;
     for (int i = j; i < kClG * HQ; i += blockDim.x) c_loc[i] = 0.f;
     cluster.sync();
     const int col = j % LC, part = j / LC;
     const int k_lo = H * part / kClFwdParts, k_hi = H * (part + 1) / kClFwdParts;
+    float wr[KR ? KR : 1];
+    if (KR) {
+        const int gc = gcol(col);
+#pragma unroll
+        for (int i = 0; i < KR; i++) wr[i] = a.w[(long long)(k_lo + i) * H4 + gc];
+    }
     // thread j < G * LC also owns the activation of (g, col): its input projection is fetched one step ahead
     const int ag = j / LC, acol = j - ag * LC;
     const bool act_thread = j < kClG * LC && ag < ng;
@@ -62,6 +72,16 @@ k_lstm_fwd_cl(LstmArgs a) {
         {
             const float *h0 = h_full + (cur * kClG + 0) * H, *h1 = h_full + (cur * kClG + 1) * H;
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+            if (KR) {
+#pragma unroll
+                for (int i = 0; i < KR; i += 4) {
+                    const float4 x0 = *reinterpret_cast<const float4 *>(h0 + k_lo + i), x1 = *reinterpret_cast<const float4 *>(h1 + k_lo + i);
+                    a0 = fmaf(wr[i], x0.x, a0); b0 = fmaf(wr[i], x1.x, b0);
+                    a1 = fmaf(wr[i + 1], x0.y, a1); b1 = fmaf(wr[i + 1], x1.y, b1);
+                    a0 = fmaf(wr[i + 2], x0.z, a0); b0 = fmaf(wr[i + 2], x1.z, b0);
+                    a1 = fmaf(wr[i + 3], x0.w, a1); b1 = fmaf(wr[i + 3], x1.w, b1);
+                }
+            } else {
             int k = k_lo;
             for (; k + 2 <= k_hi; k += 2) {
                 const float w0 = w_s[k * LC + col], w1 = w_s[(k + 1) * LC + col];
@@ -69,6 +89,7 @@ k_lstm_fwd_cl(LstmArgs a) {
                 a1 = fmaf(w1, h0[k + 1], a1); b1 = fmaf(w1, h1[k + 1], b1);
             }
             for (; k < k_hi; k++) { const float w0 = w_s[k * LC + col]; a0 = fmaf(w0, h0[k], a0); b0 = fmaf(w0, h1[k], b0); }
+            }
             part_s[(part * kClG + 0) * LC + col] = a0 + a1;
             part_s[(part * kClG + 1) * LC + col] = b0 + b1;
         }
@@ -107,7 +128,8 @@ k_lstm_fwd_cl(LstmArgs a) {
     }
 }
 
-__global__ void __cluster_dims__(kClSize, 1, 1)
+template <int KR>
+__global__ void __cluster_dims__(kClSize, 1, 1) __launch_bounds__(KR ? 384 : 1024)
 k_lstm_bwd_cl(LstmArgs a) {
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
@@ -121,12 +143,17 @@ k_lstm_bwd_cl(LstmArgs a) {
     const int j = threadIdx.x;
     const int s0 = (blockIdx.x / kClSize) * kClG;
     const int ng = min(kClG, a.S - s0);
-    for (int i = j; i < H4 * HQ; i += blockDim.x) { const int r = i / HQ, u = i - r * HQ; w_s[i] = a.w[(long long)r * H + rank * HQ + u]; }
+    if (KR == 0) for (int i = j; i < H4 * HQ; i += blockDim.x) { const int r = i / HQ, u = i - r * HQ; w_s[i] = a.w[(long long)r * H + rank * HQ + u]; }
     for (int i = j; i < 2 * kClG * H4; i += blockDim.x) dg_full[i] = 0.f;
     for (int i = j; i < kClG * HQ; i += blockDim.x) { dh_loc[i] = 0.f; dc_loc[i] = 0.f; }
     cluster.sync();
     const int ku = j % HQ, part = j / HQ;
     const int r_lo = H4 * part / kClBwdParts, r_hi = H4 * (part + 1) / kClBwdParts;
+    float wr[KR ? KR : 1];
+    if (KR) {
+#pragma unroll
+        for (int i = 0; i < KR; i++) wr[i] = a.w[(long long)(r_lo + i) * H + rank * HQ + ku];
+    }
     int cur = 0;
     for (int step = a.T - 1; step >= 0; step--) {
         const int t = a.reverse ? a.T - 1 - step : step;
@@ -161,6 +188,16 @@ k_lstm_bwd_cl(LstmArgs a) {
         {   // dh_{step-1}[own units] = W_hh[:, own units]^T . dgates
             const float *d0 = dg_full + (cur * kClG + 0) * H4, *d1 = dg_full + (cur * kClG + 1) * H4;
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+            if (KR) {
+#pragma unroll
+                for (int i = 0; i < KR; i += 4) {
+                    const float4 x0 = *reinterpret_cast<const float4 *>(d0 + r_lo + i), x1 = *reinterpret_cast<const float4 *>(d1 + r_lo + i);
+                    a0 = fmaf(wr[i], x0.x, a0); b0 = fmaf(wr[i], x1.x, b0);
+                    a1 = fmaf(wr[i + 1], x0.y, a1); b1 = fmaf(wr[i + 1], x1.y, b1);
+                    a0 = fmaf(wr[i + 2], x0.z, a0); b0 = fmaf(wr[i + 2], x1.z, b0);
+                    a1 = fmaf(wr[i + 3], x0.w, a1); b1 = fmaf(wr[i + 3], x1.w, b1);
+                }
+            } else {
             int r = r_lo;
             for (; r + 2 <= r_hi; r += 2) {
                 const float w0 = w_s[r * HQ + ku], w1 = w_s[(r + 1) * HQ + ku];
@@ -168,6 +205,7 @@ k_lstm_bwd_cl(LstmArgs a) {
                 a1 = fmaf(w1, d0[r + 1], a1); b1 = fmaf(w1, d1[r + 1], b1);
             }
             for (; r < r_hi; r++) { const float w0 = w_s[r * HQ + ku]; a0 = fmaf(w0, d0[r], a0); b0 = fmaf(w0, d1[r], b0); }
+            }
             part_s[(part * kClG + 0) * HQ + ku] = a0 + a1;
             part_s[(part * kClG + 1) * HQ + ku] = b0 + b1;
         }
