@@ -42,7 +42,9 @@ __global__ void k_lstm_fwd(LstmJobs jobs) {
     const int j = threadIdx.x;
     if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
     const float *w = a.w_smem ? w_s : a.w;
-    // persistent over the sequence groups: W_hh is staged once per CTA
+    // persistent over the sequence groups: W_hh is staged once per CTA.  (Keeping the thread's W_hh row in registers, as
+    // k_lstm_fwd_r64 and the backward kernel below do, measured 11 % SLOWER here: 126 registers, the eight sequences' packed
+    // accumulators and the row compete for the register file.)
     for (int s0 = blockIdx.x * G; s0 < a.S; s0 += gridDim.x * G) {
     const int ng = min(G, a.S - s0);
     for (int i = j; i < G * H; i += blockDim.x) { h_s[i] = 0.f; c_s[i] = 0.f; }
@@ -138,6 +140,11 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
     const int j = threadIdx.x;
     if (a.w_smem) for (int i = j; i < H * H4; i += blockDim.x) w_s[i] = a.w[i];
     const float *w = a.w_smem ? w_s : a.w;
+    float wr[64];                     // G > 1, H = 64, 256 threads: rows 64 (j / 64) .. + 63 of W_hh, column j % 64
+    if (H == 64 && G > 1 && blockDim.x == 256) {
+#pragma unroll
+        for (int i = 0; i < 64; i++) wr[i] = a.w[((j >> 6) * 64 + i) * H + (j & 63)];
+    }
     for (int s0 = blockIdx.x * G; s0 < a.S; s0 += gridDim.x * G) {          // persistent over the sequence groups
     const int ng = min(G, a.S - s0);
     for (int i = j; i < G * H; i += blockDim.x) { dh_s[i] = 0.f; dc_s[i] = 0.f; }
@@ -182,6 +189,16 @@ __global__ void k_lstm_bwd(LstmJobs jobs) {
             if (part < qparts) {
                 const int r_lo = (int)((long long)H4 * part / qparts), r_hi = (int)((long long)H4 * (part + 1) / qparts);
                 f32x2 ac2[4] = {pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f)};
+                if (H == 64 && qparts == 4) {
+#pragma unroll
+                    for (int i = 0; i < 64; i++) {
+                        const f32x2 ww = pk2(wr[i], wr[i]);
+                        const ulonglong2 d0 = *reinterpret_cast<const ulonglong2 *>(dg_s + (r_lo + i) * kLstmG);
+                        const ulonglong2 d1 = *reinterpret_cast<const ulonglong2 *>(dg_s + (r_lo + i) * kLstmG + 4);
+                        ac2[0] = fma2(ww, d0.x, ac2[0]); ac2[1] = fma2(ww, d0.y, ac2[1]);
+                        ac2[2] = fma2(ww, d1.x, ac2[2]); ac2[3] = fma2(ww, d1.y, ac2[3]);
+                    }
+                } else
 #pragma unroll 4
                 for (int r = r_lo; r < r_hi; r++) {
                     const float wv = w[r * H + k];
