@@ -413,6 +413,13 @@ struct Launcher {
             pack.j[i] = jobs[i];
             max_blocks = std::max(max_blocks, (jobs[i].S + G - 1) / G);
         }
+        if (G == 1 && H == 8 && n_jobs == 1) {
+            // one narrow sequence per warp: shuffles instead of shared memory and barriers (mst_model_kernels2.cuh)
+            const int blocks = std::min(jobs[0].S, 148 * 16);
+            if (backward) k_lstm_bwd_w8<<<blocks, 32, 0, st>>>(jobs[0]); else k_lstm_fwd_w8<<<blocks, 32, 0, st>>>(jobs[0]);
+            check();
+            return;
+        }
         if (G == 1 && H == 64) {
             // one long sequence per CTA: W_hh rows in registers (mst_model_kernels2.cuh)
             dim3 grid(std::min(max_blocks, std::max(1, 148 * 4 / n_jobs)), n_jobs);

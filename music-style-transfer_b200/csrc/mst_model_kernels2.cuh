@@ -377,6 +377,97 @@ k_lstm_bwd_r64(LstmJobs jobs) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Narrow recurrences (SongInfoModel.bars_lstm, style/model.py:468: H = 8, one sequence of n_bars steps per sample):
+// ONE WARP per sequence, lane j = gate row j (4H = 32), weights in 8 registers, the state and the gates move by
+// shuffles: no shared memory and no barrier inside a step; the next step's global operands are fetched one step ahead.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32)
+k_lstm_fwd_w8(LstmArgs a) {
+    constexpr int H = 8, H4 = 32;
+    const int j = threadIdx.x, u = j & 7, gate = j >> 3;
+    float wr[H];
+#pragma unroll
+    for (int k = 0; k < H; k++) wr[k] = a.w[k * H4 + j];            // W_hh^T (H, 4H): column j
+    for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
+        float h = 0.f, c = 0.f;                                      // lanes 0..7: unit u
+        float xnext = a.xproj[((long long)s * a.T + (a.reverse ? a.T - 1 : 0)) * H4 + j];
+        for (int step = 0; step < a.T; step++) {
+            const int t = a.reverse ? a.T - 1 - step : step;
+            float acc = xnext;
+            if (step + 1 < a.T) xnext = a.xproj[((long long)s * a.T + (a.reverse ? t - 1 : t + 1)) * H4 + j];
+#pragma unroll
+            for (int k = 0; k < H; k++) acc = fmaf(wr[k], __shfl_sync(0xffffffffu, h, k), acc);
+            const float v = gate == 2 ? tanhf(acc) : sigmoid_fast(acc);
+            const long long row = (long long)s * a.T + t;
+            a.gates[row * H4 + j] = v;
+            const float gi = __shfl_sync(0xffffffffu, v, u), gf = __shfl_sync(0xffffffffu, v, 8 + u);
+            const float gg = __shfl_sync(0xffffffffu, v, 16 + u), go = __shfl_sync(0xffffffffu, v, 24 + u);
+            if (j < H) {
+                a.hprev[row * H + j] = h;
+                c = gf * c + gi * gg;
+                h = go * tanhf(c);
+                a.cells[row * H + j] = c;
+                a.out[row * a.out_ld + a.out_off + j] = h;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(32)
+k_lstm_bwd_w8(LstmArgs a) {
+    constexpr int H = 8, H4 = 32;
+    const int j = threadIdx.x, u = j & 7, part = j >> 3;
+    float wr[H];                                                     // W_hh (4H, H): rows part * 8 .., column u
+#pragma unroll
+    for (int i = 0; i < H; i++) wr[i] = a.w[(part * H + i) * H + u];
+    for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
+        float dh_c = 0.f, dc_c = 0.f;                                // carried gradients, lanes 0..7
+        // operands of the step, lanes 0..7 (unit u); fetched one step ahead
+        auto fetch = [&](int step, float (&g4)[4], float &cc, float &cp, float &dout) {
+            const int t = a.reverse ? a.T - 1 - step : step;
+            const int t_prev = a.reverse ? t + 1 : t - 1;
+            const long long row = (long long)s * a.T + t;
+            const float *gs = a.gates + row * H4;
+            g4[0] = gs[u]; g4[1] = gs[H + u]; g4[2] = gs[2 * H + u]; g4[3] = gs[3 * H + u];
+            cc = a.cells[row * H + u];
+            cp = step > 0 ? a.cells[((long long)s * a.T + t_prev) * H + u] : 0.f;
+            dout = a.dout ? a.dout[row * a.out_ld + a.out_off + u] : 0.f;
+        };
+        float g4[4] = {0.f, 0.f, 0.f, 0.f}, cc = 0.f, cp = 0.f, dout = 0.f;
+        if (j < H) fetch(a.T - 1, g4, cc, cp, dout);
+        for (int step = a.T - 1; step >= 0; step--) {
+            const int t = a.reverse ? a.T - 1 - step : step;
+            const long long row = (long long)s * a.T + t;
+            const float gi = g4[0], gf = g4[1], gg = g4[2], go = g4[3], c = cc, c_prev = cp, dout_t = dout;
+            if (j < H && step > 0) fetch(step - 1, g4, cc, cp, dout);
+            float d4[4] = {0.f, 0.f, 0.f, 0.f};
+            if (j < H) {
+                const float tc = tanhf(c);
+                const float dh = dh_c + dout_t;
+                const float dc = dc_c + dh * go * (1.f - tc * tc);
+                d4[0] = dc * gg * gi * (1.f - gi);
+                d4[1] = dc * c_prev * gf * (1.f - gf);
+                d4[2] = dc * gi * (1.f - gg * gg);
+                d4[3] = dh * tc * go * (1.f - go);
+                dc_c = dc * gf;
+            }
+            // lane r = gate * 8 + unit takes dgates[r] from lane `unit`
+            const float e0 = __shfl_sync(0xffffffffu, d4[0], u), e1 = __shfl_sync(0xffffffffu, d4[1], u);
+            const float e2 = __shfl_sync(0xffffffffu, d4[2], u), e3 = __shfl_sync(0xffffffffu, d4[3], u);
+            const float dg = part == 0 ? e0 : (part == 1 ? e1 : (part == 2 ? e2 : e3));
+            a.dgates[row * H4 + j] = dg;
+            // dh_{step-1}[u] = sum_r W_hh[r][u] dgates[r]: lane (part, u) sums rows part * 8 .., then the four parts
+            float acc = 0.f;
+#pragma unroll
+            for (int i = 0; i < H; i++) acc = fmaf(wr[i], __shfl_sync(0xffffffffu, dg, part * H + i), acc);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 8);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+            dh_c = acc;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // combine (style/model.py:796-815): out[n, m] = sum_k x[n,k,m] w[n,k] / sum_k w[n,k],  w = sqrt(1 + sum_m x^2).
 // x is addressed as x[n * n_stride + k * k_stride + m].
 // ------------------------------------------------------------------------------------------------
