@@ -286,33 +286,43 @@ k_lstm_fwd_r64(LstmJobs jobs) {
     for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
         if (j < H) { h_s[j] = 0.f; c_s[j] = 0.f; }
         __syncthreads();
-        float xnext = a.xproj[((long long)s * a.T + (a.reverse ? a.T - 1 : 0)) * H4 + j];
-        for (int step = 0; step < a.T; step++) {
-            const int t = a.reverse ? a.T - 1 - step : step;
-            float a0 = xnext, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-            if (step + 1 < a.T) xnext = a.xproj[((long long)s * a.T + (a.reverse ? t - 1 : t + 1)) * H4 + j];
+        // the input projection is fetched FOUR steps ahead (a step is shorter than the L2 latency): four registers, the
+        // step loop unrolled by four so that each is addressed statically
+        auto x_at = [&](int step) { return a.xproj[((long long)s * a.T + (a.reverse ? a.T - 1 - step : step)) * H4 + j]; };
+        float xr[4];
 #pragma unroll
-            for (int k = 0; k < H; k += 4) {
-                const float4 hv = *reinterpret_cast<const float4 *>(h_s + k);
-                a0 = fmaf(wr[k], hv.x, a0); a1 = fmaf(wr[k + 1], hv.y, a1);
-                a2 = fmaf(wr[k + 2], hv.z, a2); a3 = fmaf(wr[k + 3], hv.w, a3);
+        for (int d = 0; d < 4; d++) xr[d] = d < a.T ? x_at(d) : 0.f;
+        for (int step0 = 0; step0 < a.T; step0 += 4) {
+#pragma unroll
+            for (int d = 0; d < 4; d++) {
+                const int step = step0 + d;
+                if (step >= a.T) break;
+                const int t = a.reverse ? a.T - 1 - step : step;
+                float a0 = xr[d], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                if (step + 4 < a.T) xr[d] = x_at(step + 4);
+#pragma unroll
+                for (int k = 0; k < H; k += 4) {
+                    const float4 hv = *reinterpret_cast<const float4 *>(h_s + k);
+                    a0 = fmaf(wr[k], hv.x, a0); a1 = fmaf(wr[k + 1], hv.y, a1);
+                    a2 = fmaf(wr[k + 2], hv.z, a2); a3 = fmaf(wr[k + 3], hv.w, a3);
+                }
+                const float acc = (a0 + a1) + (a2 + a3);
+                const float v = is_tanh ? tanhf(acc) : sigmoid_fast(acc);
+                const long long row = (long long)s * a.T + t;
+                g_s[j] = v;
+                a.gates[row * H4 + j] = v;
+                __syncthreads();
+                if (j < H) {
+                    a.hprev[row * H + j] = h_s[j];
+                    const float c = g_s[H + j] * c_s[j] + g_s[j] * g_s[2 * H + j];
+                    const float h = g_s[3 * H + j] * tanhf(c);
+                    c_s[j] = c;
+                    h_s[j] = h;
+                    a.cells[row * H + j] = c;
+                    a.out[row * a.out_ld + a.out_off + j] = h;
+                }
+                __syncthreads();
             }
-            const float acc = (a0 + a1) + (a2 + a3);
-            const float v = is_tanh ? tanhf(acc) : sigmoid_fast(acc);
-            const long long row = (long long)s * a.T + t;
-            g_s[j] = v;
-            a.gates[row * H4 + j] = v;
-            __syncthreads();
-            if (j < H) {
-                a.hprev[row * H + j] = h_s[j];
-                const float c = g_s[H + j] * c_s[j] + g_s[j] * g_s[2 * H + j];
-                const float h = g_s[3 * H + j] * tanhf(c);
-                c_s[j] = c;
-                h_s[j] = h;
-                a.cells[row * H + j] = c;
-                a.out[row * a.out_ld + a.out_off + j] = h;
-            }
-            __syncthreads();
         }
     }
 }
@@ -390,24 +400,32 @@ k_lstm_fwd_w8(LstmArgs a) {
     for (int k = 0; k < H; k++) wr[k] = a.w[k * H4 + j];            // W_hh^T (H, 4H): column j
     for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
         float h = 0.f, c = 0.f;                                      // lanes 0..7: unit u
-        float xnext = a.xproj[((long long)s * a.T + (a.reverse ? a.T - 1 : 0)) * H4 + j];
-        for (int step = 0; step < a.T; step++) {
-            const int t = a.reverse ? a.T - 1 - step : step;
-            float acc = xnext;
-            if (step + 1 < a.T) xnext = a.xproj[((long long)s * a.T + (a.reverse ? t - 1 : t + 1)) * H4 + j];
+        auto x_at = [&](int step) { return a.xproj[((long long)s * a.T + (a.reverse ? a.T - 1 - step : step)) * H4 + j]; };
+        float xr[4];                                                 // input projections, fetched four steps ahead
 #pragma unroll
-            for (int k = 0; k < H; k++) acc = fmaf(wr[k], __shfl_sync(0xffffffffu, h, k), acc);
-            const float v = gate == 2 ? tanhf(acc) : sigmoid_fast(acc);
-            const long long row = (long long)s * a.T + t;
-            a.gates[row * H4 + j] = v;
-            const float gi = __shfl_sync(0xffffffffu, v, u), gf = __shfl_sync(0xffffffffu, v, 8 + u);
-            const float gg = __shfl_sync(0xffffffffu, v, 16 + u), go = __shfl_sync(0xffffffffu, v, 24 + u);
-            if (j < H) {
-                a.hprev[row * H + j] = h;
-                c = gf * c + gi * gg;
-                h = go * tanhf(c);
-                a.cells[row * H + j] = c;
-                a.out[row * a.out_ld + a.out_off + j] = h;
+        for (int d = 0; d < 4; d++) xr[d] = d < a.T ? x_at(d) : 0.f;
+        for (int step0 = 0; step0 < a.T; step0 += 4) {
+#pragma unroll
+            for (int d = 0; d < 4; d++) {
+                const int step = step0 + d;
+                if (step >= a.T) break;
+                const int t = a.reverse ? a.T - 1 - step : step;
+                float acc = xr[d];
+                if (step + 4 < a.T) xr[d] = x_at(step + 4);
+#pragma unroll
+                for (int k = 0; k < H; k++) acc = fmaf(wr[k], __shfl_sync(0xffffffffu, h, k), acc);
+                const float v = gate == 2 ? tanhf(acc) : sigmoid_fast(acc);
+                const long long row = (long long)s * a.T + t;
+                a.gates[row * H4 + j] = v;
+                const float gi = __shfl_sync(0xffffffffu, v, u), gf = __shfl_sync(0xffffffffu, v, 8 + u);
+                const float gg = __shfl_sync(0xffffffffu, v, 16 + u), go = __shfl_sync(0xffffffffu, v, 24 + u);
+                if (j < H) {
+                    a.hprev[row * H + j] = h;
+                    c = gf * c + gi * gg;
+                    h = go * tanhf(c);
+                    a.cells[row * H + j] = c;
+                    a.out[row * a.out_ld + a.out_off + j] = h;
+                }
             }
         }
     }
