@@ -50,13 +50,19 @@ __constant__ int8_t d_abs_intervals[2][7] = {{0, 2, 4, 5, 7, 9, 11}, {0, 2, 3, 5
 __constant__ int8_t d_frac_num[10] = {0, 1, 1, 1, 3, 1, 5, 2, 3, 7};    // sorted fractions, midi_conversion.py:358-362
 __constant__ int8_t d_frac_den[10] = {1, 8, 4, 3, 8, 2, 8, 3, 4, 8};
 
+// a song table entry the kernels can index safely (the Python wrapper guards this too; a C caller may not)
+__device__ __forceinline__ bool song_valid(const MstDecodeSong &d) {
+    return d.n_pitched >= 0 && d.n_pitched <= MST_MAX_DECODE_CHANNELS && d.n_bars > 0 && d.n_beats > 0 &&
+           d.ticks_per_beat > 0 && d.tempo > 0 && d.mode >= 0 && d.mode <= 1;
+}
 __device__ __forceinline__ uint32_t song_chunks(const MstDecodeSong &d) {
+    if (!song_valid(d)) return 0u;          // flagged MST_DECODE_BAD_VALUE by k_dec_plan, decodes nothing
     return (uint32_t)(d.n_pitched + (d.has_unpitched ? 1 : 0)) * (uint32_t)d.n_bars;
 }
 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024, 1)
-k_dec_plan(const MstDecodeSong *__restrict__ songs, uint32_t n_songs, DecWorkspace ws) {
+k_dec_plan(const MstDecodeSong *__restrict__ songs, uint32_t n_songs, DecWorkspace ws, uint32_t n_chunks) {
     __shared__ uint32_t tmp[33];
     uint32_t running = 0;
     for (uint32_t c0 = 0; c0 < n_songs; c0 += blockDim.x) {
@@ -64,10 +70,20 @@ k_dec_plan(const MstDecodeSong *__restrict__ songs, uint32_t n_songs, DecWorkspa
         const uint32_t v = s < n_songs ? song_chunks(songs[s]) : 0u;
         uint32_t tot;
         const uint32_t ex = block_exclusive_scan(v, tmp, &tot);
-        if (s < n_songs) { ws.chunk_prefix[s] = running + ex; ws.song_status[s] = MST_DECODE_OK; }
+        if (s < n_songs) {
+            ws.chunk_prefix[s] = running + ex;
+            ws.song_status[s] = song_valid(songs[s]) ? MST_DECODE_OK : MST_DECODE_BAD_VALUE;
+        }
         running += tot;
     }
-    if (threadIdx.x == 0) ws.chunk_prefix[n_songs] = running;
+    __syncthreads();
+    if (running != n_chunks) {
+        // the caller's chunk count (which sized the workspace) disagrees with the song table: decode nothing and say so
+        for (uint32_t s = threadIdx.x; s <= n_songs; s += blockDim.x) {
+            ws.chunk_prefix[s] = 0;
+            if (s < n_songs) ws.song_status[s] = MST_DECODE_CAPACITY;
+        }
+    } else if (threadIdx.x == 0) ws.chunk_prefix[n_songs] = running;
 }
 
 // chunk -> (song, channel, bar) and the chunk's float base / geometry
@@ -118,6 +134,7 @@ k_dec_scan(float *__restrict__ grids, const MstDecodeSong *__restrict__ songs, u
            uint32_t n_chunks) {
     const unsigned lane = lane_id();
     const float thr_v = 0.01f;
+    n_chunks = min(n_chunks, ws.chunk_prefix[n_songs]);       // 0 when k_dec_plan rejected the table
     for (uint32_t chunk = blockIdx.x * kScanWarps + (threadIdx.x >> 5); chunk < n_chunks; chunk += gridDim.x * kScanWarps) {
         const ChunkGeom g = chunk_geom(songs, n_songs, ws.chunk_prefix, chunk);
         const bool write_back = songs[g.song].write_back != 0;
@@ -211,6 +228,7 @@ k_dec_songs(const MstDecodeSong *__restrict__ songs, uint32_t n_songs, DecWorksp
             const double scale = __ddiv_rn(__dmul_rn((double)songs[s].tempo, 1e-6), (double)songs[s].ticks_per_beat);
             r.max_delta = (int32_t)rint(__ddiv_rn(1.0, scale));
             r.status = v == 0 ? MST_DECODE_NO_MESSAGES : (off + v > msg_capacity ? MST_DECODE_CAPACITY : MST_DECODE_OK);
+            if (ws.song_status[s] != MST_DECODE_OK) r.status = ws.song_status[s];     // rejected by k_dec_plan
             results[s] = r;
         }
         running += tot;
@@ -263,6 +281,7 @@ k_dec_emit(const float *__restrict__ grids, const MstDecodeSong *__restrict__ so
            const MstDecodeResult *__restrict__ results, uint32_t n_chunks) {
     const unsigned lane = lane_id();
     const float thr_v = 0.01f;
+    n_chunks = min(n_chunks, ws.chunk_prefix[n_songs]);       // 0 when k_dec_plan rejected the table
     for (uint32_t chunk = blockIdx.x * kScanWarps + (threadIdx.x >> 5); chunk < n_chunks; chunk += gridDim.x * kScanWarps) {
         const uint32_t count = ws.chunk_count[chunk];
         if (count == 0) continue;
@@ -389,7 +408,7 @@ extern "C" int mst_decode_batch_device(float *d_grids, const MstDecodeSong *d_so
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const uint32_t nch = (uint32_t)n_chunks;
     const uint32_t chunk_blocks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((n_chunks + kScanWarps - 1) / kScanWarps, (uint64_t)sms * 8));
-    k_dec_plan<<<1, 1024, 0, stream>>>(d_songs, n_songs, ws);
+    k_dec_plan<<<1, 1024, 0, stream>>>(d_songs, n_songs, ws, nch);
     MST_LAUNCH_CHECK("k_dec_plan");
     k_dec_scan<<<chunk_blocks, kScanWarps * 32, 0, stream>>>(d_grids, d_songs, n_songs, ws, nch);
     MST_LAUNCH_CHECK("k_dec_scan");

@@ -270,8 +270,13 @@ struct Launcher {
     }
     template <int BN, int AM, int BMD, int NS>
     void gemm_t5_launch(const GemmArgs &g, dim3 grid) {
-        static bool attr_set = false;
-        if (!attr_set) { cudaFuncSetAttribute(k_gemm_t5<BN, AM, BMD, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN, NS>()); attr_set = true; }
+        static bool attr_set[64] = {};            // per device: the attribute belongs to the device's copy of the function
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            cudaFuncSetAttribute(k_gemm_t5<BN, AM, BMD, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t5_smem_bytes<BN, NS>());
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
         k_gemm_t5<BN, AM, BMD, NS><<<grid, kT5Block, t5_smem_bytes<BN, NS>(), st>>>(g);
     }
     template <int BN, int NS>

@@ -152,6 +152,10 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb;
     Bwd w{L, c, ar};
     w.tmpA = ar.take(Rf * 32 + Rb * 120); w.tmpB = ar.take(Rf * 32 + Rb * 120);
+    // the tail kernels read the small weights from the constant banks: reload them from THESE parameters (another
+    // forward / predict_apply with other parameters may have run since the forward pass of this step)
+    load_me_constants(L, c);
+    load_psa_constants(L, c);
 
     // ---------------- get_total_loss (model.py:935-997) + its derivative
     // NOTE the positional quirk of train-model.py:115-122 is resolved by the Python caller: here "mode" is the

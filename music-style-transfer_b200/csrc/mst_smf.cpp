@@ -40,18 +40,20 @@ struct Reader {
         if (pos >= n) { eof = true; return 0; }
         return p[pos++];
     }
+    // mido's read_variable_int takes any number of 7-bit groups; values beyond 2^56 saturate here (they can only
+    // describe a payload longer than any file or a tick beyond MST_MAX_TICK, both handled by the callers)
     uint64_t varint() {
         uint64_t v = 0;
         while (true) {
             int b = byte();
             if (eof) return 0;
-            v = (v << 7) | (uint64_t)(b & 0x7F);
+            v = v >= (1ull << 56) ? (1ull << 62) : ((v << 7) | (uint64_t)(b & 0x7F));
             if (b < 0x80) return v;
         }
     }
-    bool skip(size_t k) {
-        if (pos + k > n) { eof = true; pos = n; return false; }
-        pos += k;
+    bool skip(uint64_t k) {
+        if (k > (uint64_t)(n - pos)) { eof = true; pos = n; return false; }   // no wrap-around for huge k
+        pos += (size_t)k;
         return true;
     }
 };
@@ -99,7 +101,7 @@ extern "C" int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent 
         while (r.pos - start != size) {
             const uint64_t delta = r.varint();
             if (r.eof) return -(100 + kFailEof);
-            tick += delta;
+            tick = (delta > (1ull << 62) - tick) ? (1ull << 62) : tick + delta;   // saturate: beyond MST_MAX_TICK anyway
             int status = r.byte();
             if (r.eof) return -(100 + kFailEof);
             int peek = -1;
@@ -115,7 +117,7 @@ extern "C" int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent 
                 const uint64_t len = r.varint();
                 if (r.eof) return -(100 + kFailEof);
                 const size_t dpos = r.pos;
-                if (!r.skip((size_t)len)) return -(100 + kFailEof);
+                if (!r.skip(len)) return -(100 + kFailEof);
                 const uint8_t *d = r.p + dpos;
                 switch (type) {
                     case 0x51:
@@ -147,7 +149,7 @@ extern "C" int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent 
                 const uint64_t len = r.varint();
                 if (r.eof) return -(100 + kFailEof);
                 const size_t dpos = r.pos;
-                if (!r.skip((size_t)len)) return -(100 + kFailEof);
+                if (!r.skip(len)) return -(100 + kFailEof);
                 size_t a = dpos, b = dpos + (size_t)len;
                 if (b > a && r.p[a] == 0xF0) a++;
                 if (b > a && r.p[b - 1] == 0xF7) b--;

@@ -84,9 +84,9 @@ def iter_inputs(files, instruments, min_n_messages=100, shuffle=False, looped=Fa
     """Yields (filename, (info, pitched, instruments_features, instruments, unpitched)) like data.py:51-63."""
     def file_stream():
         order = files[:]
+        if shuffle:
+            np.random.shuffle(order)       # once: the reference shuffles a copy, then loops that permutation (data.py:35-41)
         while True:
-            if shuffle:
-                np.random.shuffle(order)
             yield from order
             if not looped:
                 return

@@ -244,7 +244,7 @@ class StyleTransferModel(nn.Module):
     # ---- flat parameter buffer -------------------------------------------------------------------------------
     def _flatten(self):
         """Move every parameter into the library's flat layout (once; idempotent)."""
-        if self._flat is not None and self._flat.is_cuda:
+        if self._flat is not None and self._flat.is_cuda and self._params_in_flat():
             return
         if not torch.cuda.is_available():
             raise RuntimeError('StyleTransferModel needs a CUDA device: the B200 path has no CPU fallback')
@@ -259,6 +259,13 @@ class StyleTransferModel(nn.Module):
         self._flat = flat
         self._flat_grads = torch.zeros_like(flat)
         self._anchor = torch.zeros(1, device='cuda', requires_grad=True)
+
+    def _params_in_flat(self):
+        """True while every parameter still aliases the flat buffer (a Module._apply such as .cpu() / .cuda() / .half()
+        reallocates them: the kernels must not keep reading the stale buffer while the optimiser updates new tensors)."""
+        lo = self._flat.data_ptr()
+        hi = lo + self._flat.numel() * 4
+        return all(p.is_cuda and p.dtype == torch.float32 and lo <= p.data_ptr() < hi for p in self.parameters())
 
     def _attach_grads(self):
         """Parameters' .grad = views of the flat gradient buffer.  optimizer.zero_grad() (set_to_none) drops them:
@@ -278,6 +285,13 @@ class StyleTransferModel(nn.Module):
         state = self.__dict__.copy()
         state['_workspaces'] = {}
         return state
+
+    def __setstate__(self, state):
+        # a torch.save(model) pickle of the REFERENCE carries none of the private attributes: default them, the first
+        # forward then moves the parameters into the flat buffer
+        self.__dict__.update(state)
+        for k, v in (('_flat', None), ('_flat_grads', None), ('_workspaces', {}), ('_anchor', None)):
+            self.__dict__.setdefault(k, v)
 
     def _workspace(self, C, B, nb, drums, training):
         key = (C, B, nb, bool(drums), bool(training))

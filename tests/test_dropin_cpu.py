@@ -32,6 +32,7 @@ SURFACE = {
     'style.utils.misc': ['iter_all_files', 'make_dirs', 'dict_map', 'ProgressBar'],
     'style.utils.data': ['save_to_csv', 'assert_dir'],
     'style.utils.parallel': ['iter_parallel'],
+    'style.utils.pytorch': ['LSTM', 'Distributed', 'squash_dims', 'cat_with_broadcast', 'safe_sqrt', 'get_mean'],
 }
 
 SIGNATURES = {
@@ -165,3 +166,18 @@ def test_model_needs_the_gpu_library():
     model = build_model()
     with pytest.raises((MstError, RuntimeError, AssertionError)):
         model(torch.tensor([[1., 0.]]), torch.tensor([120.]), torch.zeros(1, 1, 1, 4, 10, 56, 5), torch.zeros(1, 1, 51), None)
+
+
+def test_utils_pytorch_helpers_and_pickle_names():
+    """style.utils.pytorch exists because reference torch.save(model) pickles name LSTM / Distributed by that path."""
+    import torch
+    from style.utils import pytorch as up
+    from style import model as m
+    assert up.LSTM is m.LSTM and up.Distributed is m.Distributed
+    x = torch.arange(2 * 3 * 4 * 5, dtype=torch.float32).view(2, 3, 4, 5)
+    assert up.squash_dims(x, 1, 3).shape == (2, 12, 5) and up.squash_dims(x, -2).shape == (2, 3, 20)
+    a, b = torch.ones(2, 1, 3), torch.zeros(1, 4, 5)
+    assert up.cat_with_broadcast([a, b], -1).shape == (2, 4, 8)
+    t = [torch.tensor(3.0), torch.tensor(4.0)]
+    assert abs(float(up.get_mean(t, mean_type='quadratic')) - (12.5 ** .5)) < 1e-6
+    assert float(up.get_mean([torch.tensor(0.0)], mean_type='quadratic')) == 0.0

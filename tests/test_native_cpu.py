@@ -148,3 +148,18 @@ def test_smf_write_matches_reference_saved_bytes(L):
             assert lib.smf_write(d, msgs, int(res['eot_delta'])) == bytes(s['decoded_smf']), s['name']
             n += 1
     assert n >= 40
+
+
+def test_smf_parse_hostile_lengths_terminate(L):
+    """A meta / sysex / delta varint of any width must end in the EOF load failure mido reports (EOFError ->
+    load_midi_from_file returns None), never in a wrapped position that re-reads the same event for ever."""
+    head = b'MThd' + (6).to_bytes(4, 'big') + b'\x00\x01\x00\x01\x01\xe0' + b'MTrk' + (0x7FFFFFFF).to_bytes(4, 'big')
+    huge = b'\xff' * 9 + b'\x73'                               # 2^64 - 13 as a 10-group varint
+    cases = [
+        head + b'\x00\xff\x01' + huge + b'abc',                # meta text with a wrapping length
+        head + b'\x00\xf0' + huge + b'\x01\x02\xf7',           # sysex with a wrapping length
+        head + huge + b'\x90\x40\x40',                         # delta time wider than 64 bits
+        head + b'\x00\xff\x51' + b'\xff\xff\xff\xff\x7f' + b'\x07\xa1\x20',   # 5-byte length beyond the file
+    ]
+    for data in cases:
+        assert lib.smf_parse(data) is None
