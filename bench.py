@@ -205,22 +205,20 @@ def algorithmic_bytes_per_sample(C, B, nb, drums):
     return 4 * 4 * nb * 10 * (280 * C + (94 if drums else 0)) * B
 
 
-def run_training(args, world, rank, torch, dist, sh=None, N=None):
+def run_training(args, world, rank, torch, dist, sh=None, N=None, precision='bf16', e2e=True):
     """Training leg (BASELINE.json configs[3], or configs[4] with sh=LONG_SHAPE): samples/s over all ranks,
-    device-timed, max over ranks."""
-    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
-    import model_oracle as mo            # synthetic sample generator + seed-108 weights (data, not compute)
-    from mst_native import trainer as tr
+    device-timed, max over ranks.  precision: 'bf16' = the mode configs[3] names (bf16 dense layers: tcgen05 kind::f16
+    GEMMs + PitchedStyleApplier tail), 'fp32' = the fp32-accurate 3xTF32 mode."""
+    from mst_native import synth, trainer as tr   # workload generators live in the product package (no oracle/ import here)
     N = N or args.train_batch
     sh = sh or TRAIN_SHAPE
-    distinct = [mo.synthetic_sample(seed=7 + 100 * rank + i, **sh) for i in range(min(N, 4))]
+    distinct = [synth.synthetic_sample(seed=7 + 100 * rank + i, **sh) for i in range(min(N, 4))]
     pick = lambda k: torch.cat([distinct[i % len(distinct)][k] for i in range(N)]).contiguous()
     host = {k: pick(k).pin_memory() for k in ('pitched', 'unpitched', 'feats', 'mode', 'bpm')}
-    host['it'] = torch.cat([mo.used_instruments(distinct[i % len(distinct)]['feats'], distinct[0]['unpitched'])
-                            for i in range(N)]).pin_memory()
+    host['it'] = pick('used').pin_memory()
     host['bt'] = torch.full((N,), 120.).pin_memory()
     dev = {k: v.cuda() for k, v in host.items()}
-    t = tr.Trainer(mo.make_state_dict(108))
+    t = tr.Trainer(synth.make_state_dict(108), precision=precision)
     losses = torch.empty(N, 16, device='cuda')
     h_losses = torch.empty(N, 16).pin_memory()
 
@@ -250,6 +248,20 @@ def run_training(args, world, rank, torch, dist, sh=None, N=None):
     launches = t.launches
     loss0 = float(losses[0, 0])
 
+    peak, peak_src = measured_peak_hbm()
+    alg = algorithmic_bytes_per_sample(**sh)
+    base = {
+        'metric': 'training samples/sec', 'value': value, 'unit': 'samples/s', 'ms_per_step': s_per_step * 1e3,
+        'steps': args.train_steps, 'config': training_config(N, world, sh), 'dtype': 'bf16 operands, f32 accumulate' if precision == 'bf16' else 'f32 (3xTF32)',
+        'loss_total_sample0': loss0, 'gpu_launches_per_step': launches,
+        'roofline': {'kernel': 'whole training step (all kernels)', 'bound': 'hbm',
+                     'achieved': alg * N / s_per_step / 1e9, 'peak': peak, 'unit': 'GB/s',
+                     'frac': alg * N / s_per_step / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
+                     'algorithmic_bytes_per_sample': alg}}
+    if not e2e:
+        del t, dev
+        torch.cuda.empty_cache()
+        return base
     # e2e: pinned host inputs -> H2D -> step -> D2H of the loss leaves, every step.  Two device slots: the H2D of batch
     # i + 1 runs on a copy stream while batch i trains (what a pin_memory DataLoader with one batch of prefetch does);
     # the loss leaves of every step are read back and consumed on the host one step later.
@@ -304,26 +316,101 @@ def run_training(args, world, rank, torch, dist, sh=None, N=None):
     del slots, dev
     torch.cuda.empty_cache()
     e2e_events = training_e2e_from_events(args, world, rank, torch, dist, t, sh, N, losses, barrier)
-    peak, peak_src = measured_peak_hbm()
-    alg = algorithmic_bytes_per_sample(**sh)
-    out = {
-        'metric': 'training samples/sec', 'value': value, 'unit': 'samples/s', 'ms_per_step': s_per_step * 1e3,
-        'steps': args.train_steps, 'config': training_config(N, world, sh), 'dtype': 'f32',
-        'loss_total_sample0': loss0, 'gpu_launches_per_step': launches,
-        'roofline': {'kernel': 'whole training step (all kernels)', 'bound': 'hbm',
-                     'achieved': alg * N / s_per_step / 1e9, 'peak': peak, 'unit': 'GB/s',
-                     'frac': alg * N / s_per_step / 1e9 / peak, 'traffic': None, 'peak_source': peak_src,
-                     'algorithmic_bytes_per_sample': alg},
+    out = dict(base)
+    out.update({
         'e2e': e2e_events,
         'e2e_dense_grids': {'value': N * world * args.train_steps / float(e2e_s.item()), 'unit': 'samples/s',
                             'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': int(h_losses.numel() * 4),
                             'note': 'the same step fed with dense f32 grids from pinned host memory (what the reference '
                                     'uploads, data.py:144-149): two device slots, H2D of batch i+1 overlaps the step of '
                                     'batch i; PCIe-bound'},
-    }
+    })
     del t
     torch.cuda.empty_cache()
     return out
+
+
+def run_training_n1(args, torch):
+    """N = 1: the batch the reference and the shipped train-model.py actually run (one song per iteration, an optimizer
+    step every iter_size = 2 iterations, train-model.py:97-154), through the drop-in call pattern
+        model(...) -> get_total_loss(...) -> loss.backward() -> optimizer.step()
+    with one CUDA graph per entry point and shape, and through the C-ABI Trainer (one graph per iteration)."""
+    from mst_native import synth, trainer as tr
+    from style import model as m
+    sh = TRAIN_SHAPE
+    samples = [synth.synthetic_sample(seed=7 + i, **sh) for i in range(2)]
+    host = [{k: v.pin_memory() for k, v in s.items() if torch.is_tensor(v)} for s in samples]
+    dev = [{k: v.cuda() for k, v in h.items()} for h in host]
+    model = synth.build_model(108)
+    opt = torch.optim.Adam(model.parameters(), lr=.01)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=200, gamma=.9)
+    opt.zero_grad()
+
+    def iteration(d, i):
+        (ip, mp, bp), pp, up = model(d['mode'], d['bpm'], d['pitched'], d['feats'], d['unpitched'])
+        losses = m.get_total_loss(ip, d['used'], bp, 120, mp, d['mode'], pp, d['pitched'], up, d['unpitched'], normalize=True)
+        losses['total'].backward()
+        vals = [float(x) for x in (losses['total'], losses['channels_loss']['total'], losses['song_info_loss']['total'])]
+        if i % 2 == 1:
+            opt.step(); opt.zero_grad(); sched.step()
+        return vals[0]
+
+    K = max(4, 2 * args.train_steps)
+    for i in range(6):
+        loss0 = iteration(dev[i & 1], i)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(K):
+        iteration(dev[i & 1], i)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms_dropin = ev0.elapsed_time(ev1) / K
+    # e2e: the sample's tensors come from pinned host memory every iteration (what prepare_input's .to(device) does)
+    slots = [{k: torch.empty_like(v) for k, v in dev[0].items()} for _ in range(2)]
+    t0 = time.perf_counter()
+    for i in range(K):
+        for k, v in host[i & 1].items():
+            slots[i & 1][k].copy_(v, non_blocking=True)
+        iteration(slots[i & 1], i)
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / K
+    h2d = int(sum(v.numel() * v.element_size() for v in host[0].values()))
+    del model, opt, slots
+    torch.cuda.empty_cache()
+    # the same iteration through the C-ABI Trainer: ONE graph replay (forward + loss + backward) + fused Adam every 2nd
+    out = {}
+    for graph in (True, False):
+        t = tr.Trainer(synth.make_state_dict(108), graph=graph, precision='fp32')
+        losses = torch.empty(1, 16, device='cuda')
+
+        def tstep(i):
+            d = dev[i & 1]
+            t.accumulate(d['pitched'], d['unpitched'], d['feats'], d['mode'], d['bpm'], d['used'], torch.full((1,), 120., device='cuda'), losses)
+            if i % 2 == 1:
+                t.optimizer_step()
+        for i in range(6):
+            tstep(i)
+        torch.cuda.synchronize()
+        ev0.record()
+        for i in range(K):
+            tstep(i)
+        ev1.record()
+        torch.cuda.synchronize()
+        out['graph' if graph else 'launches'] = ev0.elapsed_time(ev1) / K
+        n_launches = t.launches
+        del t
+        torch.cuda.empty_cache()
+    return {
+        'metric': 'training iterations/sec at N = 1', 'value': 1e3 / out['graph'], 'unit': 'samples/s',
+        'ms_per_iteration': out['graph'], 'ms_per_iteration_without_graph': out['launches'], 'kernels_per_iteration': n_launches,
+        'dropin': {'ms_per_iteration': ms_dropin, 'value': 1e3 / ms_dropin, 'unit': 'samples/s',
+                   'note': 'style.model drop-in: model() + get_total_loss() + loss.backward() + torch.optim.Adam.step(); graphs per '
+                           'entry point; ONE device->host copy of the loss leaves per iteration', 'loss_total': loss0},
+        'e2e': {'value': 1.0 / e2e_s, 'unit': 'samples/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 64,
+                'note': 'drop-in iteration with the sample uploaded from pinned host memory every iteration'},
+        'config': training_config(1, 1), 'dtype': 'f32 (3xTF32)',
+    }
 
 
 def training_e2e_from_events(args, world, rank, torch, dist, t, sh, N, losses, barrier):
@@ -448,35 +535,75 @@ def training_e2e_from_events(args, world, rank, torch, dist, t, sh, N, losses, b
     return out
 
 
-def cpu_training_baseline(threads, steps=2):
-    """The reference's training iteration on the host cores: torch-CPU autograd over the model oracle (the plain-torch
-    restatement of style/model.py, pinned to it) + torch.optim.Adam, one sample of TRAIN_SHAPE per iteration."""
-    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+def cpu_training_baseline_here(threads, warmup=3, steps=10):
+    """Runs INSIDE the --cpu-train-baseline child process: the reference's own training iteration on the host cores.
+    baseline/_ref holds the unmodified reference (oracle/install_reference.py); its `style.model` + `style.utils.pytorch`
+    need torch alone, so StyleTransferModel / get_total_loss / backward / torch.optim.Adam are the reference's code
+    (`kind: "reference"`).  When baseline/_ref is absent the plain-torch oracle restatement is timed instead (`"port"`)."""
     import torch
-    import model_oracle as mo
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import model_oracle as mo            # sample generator (and the fallback model)
     torch.set_num_threads(threads)
     s = mo.synthetic_sample(seed=7, **TRAIN_SHAPE)
-    sd = {k: v.clone().requires_grad_(True) for k, v in mo.make_state_dict(108).items()}
-    opt = torch.optim.Adam(list(sd.values()), lr=0.01)
+    used = mo.used_instruments(s['feats'], s['unpitched'])
+    ref_root = os.path.join(ROOT, 'baseline', '_ref')
+    kind = 'port'
+    if os.path.exists(os.path.join(ref_root, 'style', 'model.py')):
+        sys.path.insert(0, ref_root)
+        import style.model as m
+        assert os.path.abspath(m.__file__).startswith(os.path.abspath(ref_root)), m.__file__
+        kind = 'reference'
+        torch.manual_seed(108)       # train-model.py:52-85: construction order fixes the weights
+        isz, nin = 51, 41            # style.data.instrument_size / n_instruments (style.data itself needs mido)
+        pce = m.PitchedChannelsEncoder(64, 128, isz); uce = m.UnpitchedChannelsEncoder(64, 128)
+        pre = m.PitchedRhythmEncoder(32, 64, 128, isz); ure = m.UnpitchedRhythmEncoder(32, 64, 128)
+        se = m.StyleEncoder(256, 128, isz); me = m.MelodyEncoder(8, 64, 128, isz)
+        sim = m.SongInfoModel(8, 256, 32, nin); psa = m.PitchedStyleApplier(256, 8, 32, isz); usa = m.UnpitchedStyleApplier(256, 32)
+        model = m.StyleTransferModel(pce, uce, se, me, pre, ure, sim, psa, usa)
+        opt = torch.optim.Adam(model.parameters(), lr=0.01)
 
-    def it():
-        losses, _ = mo.training_losses(sd, s['mode'], s['bpm'], s['pitched'], s['feats'], s['unpitched'], s['bpm_target'])
-        losses['total'].sum().backward()
-        opt.step(); opt.zero_grad()
+        def it():
+            (ip, mp, bp), pp, up = model(s['mode'], s['bpm'], s['pitched'], s['feats'], s['unpitched'])
+            losses = m.get_total_loss(ip, used, bp, 120, mp, s['mode'], pp, s['pitched'], up, s['unpitched'], normalize=True)
+            losses['total'].backward()
+            opt.step(); opt.zero_grad()
+            return float(losses['total'])
+    else:
+        sd = {k: v.clone().requires_grad_(True) for k, v in mo.make_state_dict(108).items()}
+        opt = torch.optim.Adam(list(sd.values()), lr=0.01)
 
-    it()
+        def it():
+            losses, _ = mo.training_losses(sd, s['mode'], s['bpm'], s['pitched'], s['feats'], s['unpitched'], s['bpm_target'])
+            losses['total'].sum().backward()
+            opt.step(); opt.zero_grad()
+            return float(losses['total'])
+    for _ in range(warmup):
+        loss0 = it()
     t0 = time.perf_counter()
     for _ in range(steps):
         it()
     dt = (time.perf_counter() - t0) / steps
-    return {'value': 1.0 / dt, 'unit': 'samples/s', 'cores': threads, 'kind': 'port',
-            'sample': f'{steps} iterations of one C=4 x B=200 sample (fwd + loss + bwd + Adam), torch CPU, {threads} threads'}
+    return {'value': 1.0 / dt, 'unit': 'samples/s', 'cores': threads, 'kind': kind, 'ms_per_iteration': dt * 1e3,
+            'loss_first_iteration': loss0,
+            'sample': f'{warmup} warm-up + {steps} timed iterations of one C=4 x B=200 sample (fwd + get_total_loss + bwd + Adam), '
+                      f'torch {torch.__version__} CPU, {threads} threads'
+                      + ('; the unmodified reference style/model.py from baseline/_ref' if kind == 'reference' else '; oracle/model_oracle.py')}
+
+
+def cpu_training_baseline(threads, warmup=3, steps=10):
+    """The CPU arm of the training metric, in a child process (the reference package and the drop-in are both `style`)."""
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), '--cpu-train-baseline', str(threads), str(warmup), str(steps)],
+                       capture_output=True, text=True, timeout=900)
+    for line in reversed(r.stdout.strip().splitlines()):
+        if line.startswith('{'):
+            return json.loads(line)
+    return {'value': None, 'unit': 'samples/s', 'cores': threads, 'kind': 'unavailable', 'sample': (r.stderr or r.stdout)[-300:]}
 
 
 def run_reference(args):
-    """CPU arm: the oracle port (oracle/mst_oracle.c, pthreads over all host cores).  The reference
-    itself is pure Python and cannot travel to the GPU box (its dependencies are not in the image);
-    the C port is a strictly faster restatement of the same algorithm."""
+    """CPU arm.  Codec: the oracle port (oracle/mst_oracle.c, pthreads over all host cores) - the reference's codec is
+    pure Python on top of mido, which is neither in the image nor in the wheelhouse, and the C port is a strictly faster
+    restatement of the same algorithm.  Training: the unmodified reference model from baseline/_ref."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
@@ -484,33 +611,51 @@ def run_reference(args):
     import oracle_lib
     from mst_native import abi, synth
     cores = os.cpu_count() or 1
+    # a step = a bounded sample of the configs[2] workload: `sample` songs (same generator, same filter), a DIFFERENT
+    # slice of the corpus every step
     sample = max(cores * 2, 32)
-    events, songs = synth.synth_corpus(sample, seed=1234)
+    n_steps = args.warmup + args.steps
+    events, songs = synth.synth_corpus(sample * min(n_steps, 4), seed=1234)
+    per = synth.split_songs(events, songs)
+    from mst_native import lib as _l
+    slices = []
+    for k in range(min(n_steps, 4)):
+        slices.append(_l.make_songs(per[k * sample:(k + 1) * sample], [int(t) for t in songs['ticks_per_beat'][k * sample:(k + 1) * sample]]))
     filt = abi.make_filter(synth.POPULAR, 100)
-    for _ in range(args.warmup):
-        oracle_lib.encode_batch(events, songs, filt, cores)
+    for i in range(args.warmup):
+        oracle_lib.encode_batch(*slices[i % len(slices)], filt, cores)
     t0 = time.perf_counter()
     bars = 0
-    for _ in range(args.steps):
-        infos, _ = oracle_lib.encode_batch(events, songs, filt, cores)
+    for i in range(args.steps):
+        infos, _ = oracle_lib.encode_batch(*slices[(args.warmup + i) % len(slices)], filt, cores)
         bars += int(infos['n_bars_out'][infos['status'] == 0].sum())
     dt = time.perf_counter() - t0
     value = bars / dt
     cfg = workload_config(args)
-    training = cpu_training_baseline(cores, steps=2)
+    cfg.update({'songs_per_step': sample, 'distinct_songs_in_pool': sample * len(slices), 'corpus_files_equivalent': sample * args.steps,
+                'streams': f'{cores} host threads', 'l2_policy': 'n/a (host)',
+                'note': 'the CPU arm encodes a bounded sample per step (songs_per_step above), not the 512 songs of the GPU arm'})
+    training = cpu_training_baseline(cores)
     training['config'] = training_config(1, 1)
     print(json.dumps({
-        'impl': 'reference', 'training': training, 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64 quantise -> f32 grid',
         'data': 'synthetic', 'config': cfg,
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                         'sample': f'{sample} songs of the corpus per step, {args.steps} steps'},
+                         'sample': f'{sample} songs of the corpus per step, {args.steps} steps, {len(slices)} distinct slices'},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'training': training,
+        'summary': {'encode_song_bars_per_s': value, 'train_sps': training.get('value'), 'train_kind': training.get('kind'),
+                    'cores': cores},
     }))
 
 
 def main():
+    if len(sys.argv) >= 2 and sys.argv[1] == '--cpu-train-baseline':
+        threads, warmup, steps = (int(x) for x in (sys.argv[2:5] + ['3', '10'])[:3]) if len(sys.argv) > 2 else (os.cpu_count() or 1, 3, 10)
+        print(json.dumps(cpu_training_baseline_here(threads, warmup, steps)))
+        return
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)
@@ -543,13 +688,12 @@ def main():
         raise SystemExit('bench.py needs a CUDA device: the B200 path has no CPU fallback')
     torch.cuda.set_device(local_rank)
     if world > 1:
-        # stdout carries ONE JSON line: NCCL prints its version banner there at any NCCL_DEBUG level, so the variable is
-        # dropped unless MST_NCCL_DEBUG asks for a level, and then the log goes to stderr
+        # stdout carries ONE JSON line; NCCL prints its banner / INFO lines to stdout unless NCCL_DEBUG_FILE names a file
         if os.environ.get('MST_NCCL_DEBUG'):
             os.environ['NCCL_DEBUG'] = os.environ['MST_NCCL_DEBUG']
+        if os.environ.get('NCCL_DEBUG'):
+            # keep what the environment asked for, but route the log (banner included) away from stdout
             os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
-        else:
-            os.environ.pop('NCCL_DEBUG', None)
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     L = lib.require_gpu()
 
@@ -719,13 +863,16 @@ def main():
     # ---- decode leg over the grids of batch 0 (round trip of the encoder's output)
     decode = run_decode(args, world, rank, torch, dist, L, lib, abi, batches[0], filt, arena)
     # ---- training leg (configs[3]); frees the encode buffers first
-    training = training_long = None
+    training = training_long = training_fp32 = training_n1 = None
     if not args.no_train:
         del arena, arenas, slots, batches, h_events, h_songs
         torch.cuda.empty_cache()
-        training = run_training(args, world, rank, torch, dist)
+        training = run_training(args, world, rank, torch, dist, precision='bf16')           # configs[3] as named: bf16 dense layers
+        training_fp32 = run_training(args, world, rank, torch, dist, precision='fp32', e2e=False)
         if not args.no_long:
-            training_long = run_training(args, world, rank, torch, dist, sh=LONG_SHAPE, N=args.long_batch)
+            training_long = run_training(args, world, rank, torch, dist, sh=LONG_SHAPE, N=args.long_batch, precision='bf16')
+        if world == 1:
+            training_n1 = run_training_n1(args, torch)
         t_load1 = time.time()
     clocks = sampler.stop(t_load0, t_load1) if sampler else None
 
@@ -743,7 +890,7 @@ def main():
                         'cores': 1, 'kind': 'port',
                         'sample': f'first {sample} songs of batch 0 (same generator, same filter), one pass'}
         if training is not None:
-            training['cpu_baseline'] = cpu_training_baseline(min(os.cpu_count() or 1, 32), steps=2)
+            training['cpu_baseline'] = cpu_training_baseline(min(os.cpu_count() or 1, 32))
 
     if rank == 0:
         print(json.dumps({
@@ -756,7 +903,23 @@ def main():
             'gpu_launches': KERNELS_PER_STEP * args.steps +
             (training['gpu_launches_per_step'] * args.train_steps if training else 0) +
             (training_long['gpu_launches_per_step'] * args.train_steps if training_long else 0),
-            'decode': decode, 'training': training, 'training_long': training_long,
+            'decode': decode, 'training': training, 'training_fp32': training_fp32, 'training_long': training_long,
+            'training_n1': training_n1,
+            # compact digest, LAST so that a truncated stdout tail still carries the training half of the metric
+            'summary': {
+                'encode_song_bars_per_s': value, 'encode_e2e': e2e_value, 'encode_frac': roofline['frac'],
+                'decode_frac': decode['roofline']['frac'],
+                'train_sps': training['value'] if training else None,
+                'train_e2e_sps': training['e2e']['value'] if training else None,
+                'train_ms': training['ms_per_step'] if training else None,
+                'train_frac': training['roofline']['frac'] if training else None,
+                'train_dtype': 'bf16' if training else None,
+                'train_fp32_sps': training_fp32['value'] if training_fp32 else None,
+                'long_sps': training_long['value'] if training_long else None,
+                'n1_ms': training_n1['ms_per_iteration'] if training_n1 else None,
+                'n1_dropin_ms': training_n1['dropin']['ms_per_iteration'] if training_n1 else None,
+                'train_cpu_sps': (training.get('cpu_baseline') or {}).get('value') if training else None,
+                'n_gpus': world},
         }))
     if world > 1:
         dist.destroy_process_group()

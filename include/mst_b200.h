@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define MST_ABI_VERSION 1
+#define MST_ABI_VERSION 2
 
 /* ---------------------------------------------------------------- errors */
 #define MST_OK                0
@@ -279,12 +279,19 @@ int64_t mst_smf_write(const MstDecodeSong *song, const MstOutMsg *h_msgs, uint32
  * (style/model.py:751-793) with its nine sub-modules, get_total_loss (:935-997), loss.backward() and
  * torch.optim.Adam.step (train-model.py:113-154) for a batch of N independent batch-1 samples of one shape.
  * Parameters live in ONE flat fp32 buffer; mst_model_param_* describe its layout by state-dict name. */
+/* arithmetic of the dense contractions (conv / linear / LSTM input projections of style/model.py:36-724) */
+#define MST_PRECISION_FP32 0   /* fp32-accurate: tcgen05 kind::tf32 with the 3-term split (1e-5 / 1e-4 parity with torch fp32) */
+#define MST_PRECISION_BF16 1   /* BASELINE.json configs[3] "bf16 dense layers": bf16 operands, fp32 accumulation in TMEM
+                                  (tcgen05 kind::f16), for the row-space GEMMs and the per-note PitchedStyleApplier tail;
+                                  tolerance 1e-3 on losses / 2e-2 on gradients */
+
 typedef struct MstModelShape {
     int32_t n_samples;      /* N independent samples (the reference runs N = 1) */
     int32_t n_channels;     /* C pitched channels */
     int32_t n_bars;         /* B */
     int32_t n_beats;        /* beats per bar (time-signature numerator) */
     int32_t has_unpitched;  /* drums grid present */
+    int32_t precision;      /* MST_PRECISION_* */
 } MstModelShape;
 
 typedef struct MstModelOutputs {   /* device pointers into the workspace, valid until it is reused */
@@ -385,7 +392,8 @@ int mst_adam_step(float *d_params, float *d_grads, float *d_m, float *d_v, long 
  * nn.Linear / Distributed(Linear) forward (model.py:23-33), input-gradient and weight-gradient product.
  * act: 0 none, 1 LeakyReLU(.01).  accumulate: 0 store, 1 +=, 2 atomic +=.  split_k > 1 splits K over CTAs (atomic).
  * kernel: 0 = the library's own choice, 1 = fp32 SIMT tiles, 2 = mma.sync TF32 (3-term split: fp32-accurate),
- * 3 = tcgen05.mma kind::tf32 with the accumulator in TMEM (same 3-term split). */
+ * 3 = tcgen05.mma kind::tf32 with the accumulator in TMEM (same 3-term split), 4 = tcgen05.mma kind::f16 with bf16
+ * operands (the MST_PRECISION_BF16 mode: NOT fp32-accurate). */
 int mst_model_gemm(const float *d_A, long long a_si, long long a_sk, const float *d_B, long long b_sk, long long b_sj,
                    float *d_C, long long c_si, int M, int N, int K, const float *d_bias, int act, int accumulate,
                    int split_k, int kernel, void *stream);

@@ -15,6 +15,8 @@
 #include "mst_model_sparse.cuh"
 #include "mst_model_gemm_tc.cuh"
 #include "mst_model_gemm_t5.cuh"
+#include "mst_model_gemm_b16.cuh"
+#include "mst_model_psa_tc.cuh"
 #include "mst_model_lstm_cluster.cuh"
 #include "mst_model_tails_bwd.cuh"
 #include "mst_model_me.cuh"
@@ -245,6 +247,7 @@ struct Launcher {
     cudaStream_t st;
     int launches = 0;
     bool dry = false;             // planning pass: carve the arena, launch nothing
+    bool bf16 = false;            // bf16 dense mode (MstModelShape.precision = MST_PRECISION_BF16)
     cudaError_t err = cudaSuccess;
     void check() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && err == cudaSuccess) err = e; launches++; }
 
@@ -287,6 +290,27 @@ struct Launcher {
         else if (am == 1) { if (bm == 0) gemm_t5_launch<BN, 1, 0, NS>(g, grid); else gemm_t5_launch<BN, 1, 2, NS>(g, grid); }
         else { if (bm == 0) gemm_t5_launch<BN, 2, 0, NS>(g, grid); else gemm_t5_launch<BN, 2, 2, NS>(g, grid); }
     }
+    // bf16 dense mode (mst_model_gemm_b16.cuh): same tiling, bf16 operands, one MMA per k-step
+    template <int BN, int AM, int BMD>
+    void gemm_b16_launch(const GemmArgs &g, dim3 grid) {
+        static bool attr_set[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            cudaFuncSetAttribute(k_gemm_b16<BN, AM, BMD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b16_smem_bytes<BN>());
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
+        k_gemm_b16<BN, AM, BMD><<<grid, kT5Block, b16_smem_bytes<BN>(), st>>>(g);
+    }
+    template <int BN>
+    void gemm_b16(const GemmArgs &g, int split_k) {
+        dim3 grid((g.N + BN - 1) / BN, (g.M + kT5BM - 1) / kT5BM, split_k);
+        const int am = t5_mode(g.A, g.a_si, g.a_sk);
+        const int bm = t5_mode(g.B, g.b_sj, g.b_sk) == 0 ? 0 : 2;
+        if (am == 0) { if (bm == 0) gemm_b16_launch<BN, 0, 0>(g, grid); else gemm_b16_launch<BN, 0, 2>(g, grid); }
+        else if (am == 1) { if (bm == 0) gemm_b16_launch<BN, 1, 0>(g, grid); else gemm_b16_launch<BN, 1, 2>(g, grid); }
+        else { if (bm == 0) gemm_b16_launch<BN, 2, 0>(g, grid); else gemm_b16_launch<BN, 2, 2>(g, grid); }
+    }
     template <int BN>
     void gemm_t5(const GemmArgs &g, int split_k) {
         dim3 grid((g.N + BN - 1) / BN, (g.M + kT5BM - 1) / kT5BM, split_k);
@@ -314,6 +338,8 @@ struct Launcher {
                 case 5: k_gemm_smallk<20><<<blocks, threads, 0, st>>>(g); break;
                 default: k_gemm_smallk<24><<<blocks, threads, 0, st>>>(g); break;
             }
+        } else if (kernel == 4 || (kernel == 0 && bf16 && use_tc(M, N, K) && K >= 24)) {
+            if (N <= 16) gemm_b16<16>(g, split_k); else if (N <= 32) gemm_b16<32>(g, split_k); else gemm_b16<64>(g, split_k);
         } else if (kernel == 3 || (kernel == 0 && use_tc(M, N, K) && K >= 24)) {
             if (N <= 16) gemm_t5<16>(g, split_k); else if (N <= 32) gemm_t5<32>(g, split_k); else gemm_t5<64>(g, split_k);
         } else if (kernel == 2 || (kernel == 0 && use_tc(M, N, K))) {
@@ -814,9 +840,15 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
         load_psa_constants(L, c);
         k_psa_zci<<<grid_for((long long)NC * 450), 256, 0, L.st>>>(PRM(c, psa_oct_b), c.psa_zi, c.psa_zs, c.psa_zci, N, C); L.check();
         PsaArgs2 a{c.psa_zr, c.psa_zci, c.melody, c.psa_out, N, C, B, T};
-        const size_t smem = sizeof(PsaWarpSmem) * kPsaWarps;
-        cudaFuncSetAttribute(k_psa_fwd3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_psa_fwd3<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
+        if (L.bf16 && !L.dry) {
+            // bf16 dense mode: the 5 x 50 contraction per note row as tcgen05 tiles (mst_model_psa_tc.cuh)
+            cudaFuncSetAttribute(k_psa_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPtcSmem);
+            k_psa_fwd_tc<<<(int)std::min<long long>(Rbf, 148 * 4), kPtcThreads, kPtcSmem, L.st>>>(a); L.check();
+        } else if (!L.dry) {
+            const size_t smem = sizeof(PsaWarpSmem) * kPsaWarps;
+            cudaFuncSetAttribute(k_psa_fwd3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            k_psa_fwd3<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
+        }
     }
     if (unpitched) {
         // ---------------- UnpitchedStyleApplier (model.py:703-724)
@@ -883,7 +915,7 @@ extern "C" int mst_model_forward(const float *d_params, const MstModelShape *sha
     int rc = setup_ctx(c, shape, d_workspace, workspace_bytes, training != 0, false);
     if (rc) return rc;
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params;
-    Launcher L; L.st = (cudaStream_t)stream;
+    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
     forward_extract(L, c);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);
@@ -915,7 +947,7 @@ extern "C" int mst_model_train_step(const float *d_params, float *d_grads, const
     Arena ar{(char *)d_workspace, 0, false};
     plan_forward(c, ar);
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
-    Launcher L; L.st = (cudaStream_t)stream;
+    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
     forward_extract(L, c);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);
@@ -939,7 +971,7 @@ extern "C" int mst_model_predict_apply(const float *d_params, const MstModelShap
     if (rc) return rc;
     c.F = d_features; c.prm = d_params;
     c.style = (float *)d_style; c.melody = (float *)d_melody; c.rhythm = d_rhythm;   // read only on this path
-    Launcher L; L.st = (cudaStream_t)stream;
+    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
     prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
     prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
     forward_song_info(L, c);
@@ -969,7 +1001,7 @@ extern "C" int mst_model_backward(const float *d_params, float *d_grads, const M
     plan_forward(c, ar);
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
     c.bars = c.U ? c.bars_c : c.pce_bars; c.rhythm = c.U ? c.rh_c : c.pre_out;     // as forward_extract left them
-    Launcher L; L.st = (cudaStream_t)stream;
+    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
     TrainIn ti{d_instruments_target, d_bpm_target, normalize, d_losses};
     backward(L, c, ar, ti);
     if (L.err != cudaSuccess) { mst_set_error("mst_model_backward: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
@@ -1012,7 +1044,7 @@ extern "C" int mst_adam_step(float *d_params, float *d_grads, float *d_m, float 
 extern "C" int mst_model_gemm(const float *d_A, long long a_si, long long a_sk, const float *d_B, long long b_sk, long long b_sj,
                               float *d_C, long long c_si, int M, int N, int K, const float *d_bias, int act, int accumulate,
                               int split_k, int kernel, void *stream) {
-    if (!d_A || !d_B || !d_C || M <= 0 || N <= 0 || K <= 0 || split_k < 1 || kernel < 0 || kernel > 3) {
+    if (!d_A || !d_B || !d_C || M <= 0 || N <= 0 || K <= 0 || split_k < 1 || kernel < 0 || kernel > 4) {
         mst_set_error("mst_model_gemm: bad argument");
         return MST_E_INVALID;
     }

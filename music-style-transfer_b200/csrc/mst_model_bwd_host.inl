@@ -172,7 +172,18 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     float *d_melody = w.A(Rbf * 448);
     {
         float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
-        if (!L.dry) {
+        const bool tc_tail = L.bf16 && ptc_bwd_smem(C) <= 72 * 1024;     // bf16 dense mode: tcgen05 tiles (mst_model_psa_tc.cuh)
+        if (!L.dry && tc_tail) {
+            PsaBwdTcArgs a{};
+            a.Zr = c.psa_zr; a.Zci = c.psa_zci; a.pred = c.psa_out; a.target = c.P; a.coef = lb.coef_p;
+            a.dZr = dZr; a.dZi = dZi; a.dps = d_melody; a.dps_stride = 448; a.gWl = GRD(c, psa_lin_w);
+            a.N = N; a.C = C; a.B = B; a.T = T;
+            a.ctas_per_n = (int)std::max<long long>(1, std::min<long long>((148 * 3 + N - 1) / N, (long long)B * T * 10));
+            const size_t smem = ptc_bwd_smem(C);
+            cudaFuncSetAttribute(k_psa_bwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            k_psa_bwd_tc<<<N * a.ctas_per_n, kPtcThreads, smem, L.st>>>(a); L.check();
+        }
+        if (!L.dry && !tc_tail) {
             // the per-note channel sums of the pre-sigmoid gradient travel through the (not yet written) dmelody buffer
             PsaBwdArgs3 a{};
             a.Zr = c.psa_zr; a.Zci = c.psa_zci; a.melody = c.melody; a.target = c.P; a.coef = lb.coef_p;
@@ -188,6 +199,8 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             a.warps = warps;
             cudaFuncSetAttribute(k_psa_bwd3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             k_psa_bwd3<<<N * a.ctas_per_n, warps * 32, smem, L.st>>>(a); L.check();
+        }
+        if (!L.dry) {
             PsaMelBwdArgs m{};
             m.melody = c.melody; m.dps = d_melody; m.dps_stride = 448; m.dmelody = d_melody;
             m.gWm = GRD(c, psa_ml_w); m.gbm = GRD(c, psa_ml_b); m.gWl = GRD(c, psa_lin_w); m.gbl = GRD(c, psa_lin_b);

@@ -1,7 +1,8 @@
 """numpy mirrors of the structs in include/mst_b200.h (kept in lock-step; tests check sizeof)."""
 import numpy as np
 
-MST_ABI_VERSION = 1
+MST_ABI_VERSION = 2
+PRECISION_FP32, PRECISION_BF16 = 0, 1
 MST_MAX_TICK = 10_000_000
 
 # event kinds

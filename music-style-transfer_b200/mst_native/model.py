@@ -11,7 +11,20 @@ from . import lib as _lib
 
 class ModelShape(ctypes.Structure):
     _fields_ = [('n_samples', ctypes.c_int32), ('n_channels', ctypes.c_int32), ('n_bars', ctypes.c_int32),
-                ('n_beats', ctypes.c_int32), ('has_unpitched', ctypes.c_int32)]
+                ('n_beats', ctypes.c_int32), ('has_unpitched', ctypes.c_int32), ('precision', ctypes.c_int32)]
+
+
+def precision_id(precision):
+    """'fp32' / 'bf16' / None (= the MST_PRECISION environment variable, default fp32) -> MST_PRECISION_*."""
+    import os
+    if precision is None:
+        precision = os.environ.get('MST_PRECISION', 'fp32')
+    if precision in (0, 1):
+        return int(precision)
+    try:
+        return {'fp32': 0, 'f32': 0, 'bf16': 1}[str(precision).lower()]
+    except KeyError:
+        raise ValueError(f'unknown precision {precision!r}: fp32 or bf16')
 
 
 class ModelOutputs(ctypes.Structure):
@@ -43,6 +56,7 @@ LOSS_LEAVES = {
     'song_info_loss/mode_loss': 13, 'song_info_loss/bpm_loss': 14}
 
 _ready = False
+_loss_bufs = {}
 
 
 def _L():
@@ -122,15 +136,51 @@ def unflatten(flat, like_sd):
 class Workspace:
     """Activation arena for one batch shape (reused across steps)."""
 
-    def __init__(self, N, C, B, nb, has_unpitched, training=False, device=None):
+    def __init__(self, N, C, B, nb, has_unpitched, training=False, device=None, precision=None, graph=False):
         import torch
         _lib.require_gpu()
-        self.shape = ModelShape(int(N), int(C), int(B), int(nb), int(bool(has_unpitched)))
+        self.shape = ModelShape(int(N), int(C), int(B), int(nb), int(bool(has_unpitched)), precision_id(precision))
         self.training = bool(training)
         self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
         self.bytes = _L().mst_model_workspace_bytes(ctypes.byref(self.shape), int(self.training))
         self.buf = torch.empty(self.bytes, dtype=torch.uint8, device=self.device)
         self.launches = 0
+        # CUDA graphs (one per entry point, captured on first use when graph=True): a step is ~200-425 short launches, at
+        # N = 1 (the reference's own batch, train-model.py:97-154) half of the step time is launch overhead
+        self.graph = bool(graph)
+        self._graphs = {}          # entry name -> (torch.cuda.CUDAGraph, result, n_launches)
+        self._uses = {}
+        self._static = {}          # fixed-address copies of the inputs the captured kernels read
+
+    def _stage(self, name, t):
+        """Copy `t` into this workspace's fixed-address input buffer `name` (graphs bake addresses in)."""
+        import torch
+        if t is None:
+            return None
+        buf = self._static.get(name)
+        if buf is None or buf.shape != t.shape:
+            buf = self._static[name] = torch.empty_like(t, dtype=torch.float32, device=self.device).contiguous()
+        if buf.data_ptr() != t.data_ptr():
+            buf.copy_(t, non_blocking=True)
+        return buf
+
+    def _run(self, name, fn):
+        """Run `fn(stream)` eagerly the first time (its launches execute), capture it once, replay afterwards."""
+        import torch
+        if not self.graph:
+            return fn(torch.cuda.current_stream(self.device))
+        hit = self._graphs.get(name)
+        if hit is None:
+            uses = self._uses[name] = self._uses.get(name, 0) + 1
+            if uses < 2:                                           # a shape seen once is not worth a capture
+                return fn(torch.cuda.current_stream(self.device))
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                result = fn(torch.cuda.current_stream(self.device))    # recorded, not executed
+            hit = self._graphs[name] = (g, result, self.launches)
+        g, result, self.launches = hit
+        g.replay()
+        return result
 
     def _view(self, ptr, shape):
         import torch
@@ -150,21 +200,26 @@ class Workspace:
         assert tuple(feats.shape) == (N, C, 51) and tuple(mode.shape) == (N, 2) and tuple(bpm.shape) == (N,)
         if s.has_unpitched:
             assert unpitched is not None and unpitched.numel() == N * B * nb * 10 * 47 * 2 and unpitched.is_contiguous()
-        outs = ModelOutputs()
-        nl = ctypes.c_int(0)
-        st = torch.cuda.current_stream(self.device) if stream is None else stream
-        _lib.check(_L().mst_model_forward(
-            flat_params.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
-            unpitched.data_ptr() if s.has_unpitched else None, feats.contiguous().data_ptr(),
-            mode.contiguous().data_ptr(), bpm.contiguous().data_ptr(), ctypes.byref(outs), self.buf.data_ptr(),
-            self.bytes, int(self.training), st.cuda_stream, ctypes.byref(nl)))
-        self.launches = nl.value
-        return dict(
-            instruments=self._view(outs.instruments, (N, 41)), mode=self._view(outs.mode, (N, 2)),
-            bpm=self._view(outs.bpm, (N,)), pitched=self._view(outs.pitched, (N, C, B, nb, 10, 56, 5)),
-            unpitched=self._view(outs.unpitched, (N, 1, B, nb, 10, 47, 2)) if s.has_unpitched else None,
-            style=self._view(outs.style, (N, 256)), melody=self._view(outs.melody, (N, B, nb, 10, 56, 8)),
-            rhythm=self._view(outs.rhythm, (N, B, nb, 10, 32)))
+        feats, mode, bpm = feats.contiguous(), mode.contiguous(), bpm.contiguous()
+        if self.graph and stream is None:
+            pitched, unpitched = self._stage('pitched', pitched), self._stage('unpitched', unpitched if s.has_unpitched else None)
+            feats, mode, bpm = self._stage('feats', feats), self._stage('mode', mode), self._stage('bpm', bpm)
+            self._static['params_ptr'] = flat_params.data_ptr()
+
+        self.last_inputs = (mode, bpm, pitched, feats, unpitched)      # what the kernels read (staged copies under a graph)
+
+        def call(st):
+            outs = ModelOutputs()
+            nl = ctypes.c_int(0)
+            _lib.check(_L().mst_model_forward(
+                flat_params.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
+                unpitched.data_ptr() if s.has_unpitched else None, feats.data_ptr(), mode.data_ptr(), bpm.data_ptr(),
+                ctypes.byref(outs), self.buf.data_ptr(), self.bytes, int(self.training), st.cuda_stream, ctypes.byref(nl)))
+            self.launches = nl.value
+            return self._outs(outs)
+        if stream is not None:
+            return call(stream)
+        return self._run(f'forward@{flat_params.data_ptr()}', call)
 
     def _outs(self, outs):
         s = self.shape
@@ -211,17 +266,32 @@ class Workspace:
             assert unpitched is not None and unpitched.numel() == N * B * nb * 10 * 47 * 2 and unpitched.is_contiguous()
         if losses is None:
             losses = torch.empty(N, N_LOSS_LEAVES, dtype=torch.float32, device=self.device)
-        outs = ModelOutputs()
-        nl = ctypes.c_int(0)
-        st = torch.cuda.current_stream(self.device) if stream is None else stream
-        _lib.check(_L().mst_model_train_step(
-            flat_params.data_ptr(), flat_grads.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
-            unpitched.data_ptr() if s.has_unpitched else None, feats.contiguous().data_ptr(),
-            mode.contiguous().data_ptr(), bpm.contiguous().data_ptr(), instruments_target.contiguous().data_ptr(),
-            bpm_target.contiguous().data_ptr(), int(bool(normalize)), losses.data_ptr(), ctypes.byref(outs),
-            self.buf.data_ptr(), self.bytes, st.cuda_stream, ctypes.byref(nl)))
-        self.launches = nl.value
-        return losses, self._outs(outs)
+        feats, mode, bpm = feats.contiguous(), mode.contiguous(), bpm.contiguous()
+        it, bt = instruments_target.contiguous(), bpm_target.contiguous()
+        use_graph = self.graph and stream is None
+        out_losses = losses
+        if use_graph:
+            pitched, unpitched = self._stage('pitched', pitched), self._stage('unpitched', unpitched if s.has_unpitched else None)
+            feats, mode, bpm = self._stage('feats', feats), self._stage('mode', mode), self._stage('bpm', bpm)
+            it, bt = self._stage('it', it), self._stage('bt', bt)
+            losses = self._static.setdefault('losses', torch.empty(N, N_LOSS_LEAVES, dtype=torch.float32, device=self.device))
+
+        def call(st):
+            outs = ModelOutputs()
+            nl = ctypes.c_int(0)
+            _lib.check(_L().mst_model_train_step(
+                flat_params.data_ptr(), flat_grads.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
+                unpitched.data_ptr() if s.has_unpitched else None, feats.data_ptr(), mode.data_ptr(), bpm.data_ptr(),
+                it.data_ptr(), bt.data_ptr(), int(bool(normalize)), losses.data_ptr(), ctypes.byref(outs),
+                self.buf.data_ptr(), self.bytes, st.cuda_stream, ctypes.byref(nl)))
+            self.launches = nl.value
+            return self._outs(outs)
+        if not use_graph:
+            return losses, call(torch.cuda.current_stream(self.device) if stream is None else stream)
+        outs = self._run(f'train_step@{flat_params.data_ptr()},{flat_grads.data_ptr()},{int(bool(normalize))}', call)
+        if out_losses.data_ptr() != losses.data_ptr():
+            out_losses.copy_(losses, non_blocking=True)
+        return out_losses, outs
 
 
 def backward_from_forward(ws, flat_params, flat_grads, pitched, unpitched, feats, mode, bpm, instruments_target, bpm_target,
@@ -232,15 +302,32 @@ def backward_from_forward(ws, flat_params, flat_grads, pitched, unpitched, feats
     s = ws.shape
     if losses is None:
         losses = torch.empty(s.n_samples, N_LOSS_LEAVES, dtype=torch.float32, device=ws.device)
-    nl = ctypes.c_int(0)
-    st = torch.cuda.current_stream(ws.device) if stream is None else stream
-    _lib.check(_L().mst_model_backward(
-        flat_params.data_ptr(), flat_grads.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
-        unpitched.data_ptr() if s.has_unpitched else None, feats.data_ptr(), mode.data_ptr(), bpm.data_ptr(),
-        instruments_target.data_ptr(), bpm_target.data_ptr(), int(bool(normalize)), losses.data_ptr(), ws.buf.data_ptr(),
-        ws.bytes, st.cuda_stream, ctypes.byref(nl)))
-    ws.launches += nl.value
-    return losses
+    it, bt = instruments_target.contiguous(), bpm_target.contiguous()
+    use_graph = ws.graph and stream is None
+    out_losses = losses
+    if use_graph:
+        # the forward of this step staged its inputs at fixed addresses; targets and the leaf buffer get theirs here
+        pitched, unpitched = ws._stage('pitched', pitched), ws._stage('unpitched', unpitched if s.has_unpitched else None)
+        feats, mode, bpm = ws._stage('feats', feats), ws._stage('mode', mode), ws._stage('bpm', bpm)
+        it, bt = ws._stage('it', it), ws._stage('bt', bt)
+        losses = ws._static.setdefault('bwd_losses', torch.empty(s.n_samples, N_LOSS_LEAVES, dtype=torch.float32, device=ws.device))
+
+    def call(st):
+        nl = ctypes.c_int(0)
+        _lib.check(_L().mst_model_backward(
+            flat_params.data_ptr(), flat_grads.data_ptr(), ctypes.byref(s), pitched.data_ptr(),
+            unpitched.data_ptr() if s.has_unpitched else None, feats.data_ptr(), mode.data_ptr(), bpm.data_ptr(),
+            it.data_ptr(), bt.data_ptr(), int(bool(normalize)), losses.data_ptr(), ws.buf.data_ptr(),
+            ws.bytes, st.cuda_stream, ctypes.byref(nl)))
+        ws.launches = nl.value
+        return None
+    if not use_graph:
+        call(torch.cuda.current_stream(ws.device) if stream is None else stream)
+        return losses
+    ws._run(f'backward@{flat_params.data_ptr()},{flat_grads.data_ptr()},{int(bool(normalize))}', call)
+    if out_losses.data_ptr() != losses.data_ptr():
+        out_losses.copy_(losses, non_blocking=True)
+    return out_losses
 
 
 def total_loss(pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits, instruments_target,
@@ -249,13 +336,16 @@ def total_loss(pitched_pred, pitched_target, unpitched_pred, unpitched_target, i
     import torch
     _lib.require_gpu()
     N, C, B, nb = pitched_pred.shape[:4]
-    shape = ModelShape(int(N), int(C), int(B), int(nb), int(unpitched_pred is not None))
+    shape = ModelShape(int(N), int(C), int(B), int(nb), int(unpitched_pred is not None), 0)
     f = lambda t: None if t is None else t.contiguous().float()
     keep = [f(t) for t in (pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits,
                            instruments_target, mode_logits, mode_target, bpm_pred, bpm_target)]
     li = LossIn(*[None if t is None else t.data_ptr() for t in keep], int(bool(normalize)), 0)
     wsb = _L().mst_model_loss_workspace_bytes(ctypes.byref(shape))
-    ws = torch.empty(wsb, dtype=torch.uint8, device=pitched_pred.device)
+    key = (int(N), str(pitched_pred.device))
+    if key not in _loss_bufs:
+        _loss_bufs[key] = torch.empty(wsb, dtype=torch.uint8, device=pitched_pred.device)
+    ws = _loss_bufs[key]
     out = torch.empty(int(N), N_LOSS_LEAVES, dtype=torch.float32, device=pitched_pred.device)
     _lib.check(_L().mst_model_loss(ctypes.byref(shape), ctypes.byref(li), out.data_ptr(), ws.data_ptr(), wsb,
                                    torch.cuda.current_stream(pitched_pred.device).cuda_stream))

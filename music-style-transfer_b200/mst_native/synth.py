@@ -105,3 +105,56 @@ def synth_corpus(n_songs, seed=1234, tpb=480, n_bars=128, n_tracks=16, notes_per
 def split_songs(events, songs):
     """-> list of per-song event arrays (views)."""
     return [events[int(s['event_offset']):int(s['event_offset']) + int(s['n_events'])] for s in songs]
+
+
+# ---------------------------------------------------------------------------------- training workload (SURVEY.md 8(d) config 4 / 5)
+def build_model(seed=108):
+    """The network train-model.py:52-85 creates: torch.manual_seed(seed), then the nine sub-modules in the script's
+    construction order (it fixes the RNG stream, hence the weights), through the drop-in `style.model` classes."""
+    import torch
+    from style import model as m, data as d
+    torch.manual_seed(seed)
+    pce = m.PitchedChannelsEncoder(64, 128, d.instrument_size)
+    uce = m.UnpitchedChannelsEncoder(64, 128)
+    pre = m.PitchedRhythmEncoder(32, 64, 128, d.instrument_size)
+    ure = m.UnpitchedRhythmEncoder(32, 64, 128)
+    se = m.StyleEncoder(256, 128, d.instrument_size)
+    me = m.MelodyEncoder(8, 64, 128, d.instrument_size)
+    sim = m.SongInfoModel(8, 256, 32, d.n_instruments)
+    psa = m.PitchedStyleApplier(256, 8, 32, d.instrument_size)
+    usa = m.UnpitchedStyleApplier(256, 32)
+    return m.StyleTransferModel(pce, uce, se, me, pre, ure, sim, psa, usa)
+
+
+def make_state_dict(seed=108):
+    """state_dict (CPU tensors, reference names) of build_model(seed)."""
+    return {k: v.detach().clone() for k, v in build_model(seed).state_dict().items()}
+
+
+def synthetic_sample(seed, C=4, B=200, nb=4, drums=True, density=0.003):
+    """One synthetic training sample (CPU tensors with a leading batch dim of 1): Bernoulli(density) occupancy, velocity
+    U(0,1], duration U(0,4], one-hot accidentals; instruments = the first C sorted popular programs; mode major; bpm 120."""
+    import torch
+    from style import data as d
+    g = torch.Generator().manual_seed(seed)
+    p = torch.zeros(1, C, B, nb, 10, 56, 5)
+    occ = torch.rand(p.shape[:-1], generator=g) < density
+    n = int(occ.sum())
+    vals = torch.zeros(n, 5)
+    vals[:, 0] = torch.rand(n, generator=g) * 4 + 1e-3
+    vals[:, 1] = torch.rand(n, generator=g) * 0.999 + 1e-3
+    vals[torch.arange(n), 2 + torch.randint(0, 3, (n,), generator=g)] = 1.0
+    p[occ] = vals
+    u = None
+    if drums:
+        u = torch.zeros(1, 1, B, nb, 10, 47, 2)
+        occ = torch.rand(u.shape[:-1], generator=g) < density
+        n = int(occ.sum())
+        uv = torch.zeros(n, 2)
+        uv[:, 0] = torch.rand(n, generator=g) * 4 + 1e-3
+        uv[:, 1] = torch.rand(n, generator=g) * 0.999 + 1e-3
+        u[occ] = uv
+    feats = torch.as_tensor(d.encode_instruments(sorted(POPULAR)[:C]), dtype=torch.float32).unsqueeze(0)
+    used = d.get_used_instruments(feats, u)
+    return dict(mode=torch.tensor([[1., 0.]]), bpm=torch.tensor([120.]), pitched=p, feats=feats, unpitched=u, bpm_target=120,
+                used=used)

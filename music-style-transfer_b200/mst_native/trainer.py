@@ -45,7 +45,7 @@ def allreduce_sum_(flat, group=None):
 class Trainer:
     """Flat-buffer trainer: params / grads / Adam m, v as single fp32 CUDA tensors in the library's layout."""
 
-    def __init__(self, state_dict, lr=0.01, step_size=200, gamma=0.9, betas=(0.9, 0.999), eps=1e-8, device=None):
+    def __init__(self, state_dict, lr=0.01, step_size=200, gamma=0.9, betas=(0.9, 0.999), eps=1e-8, device=None, precision=None, graph=False):
         import torch
         from . import model as mm
         self.mm = mm
@@ -55,6 +55,8 @@ class Trainer:
         self.m = torch.zeros_like(self.params)
         self.v = torch.zeros_like(self.params)
         self.base_lr, self.step_size, self.gamma, self.betas, self.eps = lr, step_size, gamma, betas, eps
+        self.precision = mm.precision_id(precision)     # 'fp32' | 'bf16' (BASELINE configs[3]: bf16 dense layers)
+        self.graph = bool(graph)                        # replay one CUDA graph per batch shape instead of ~425 launches
         self.optimizer_steps = 0
         self._ws = {}
         self.launches = 0
@@ -62,7 +64,8 @@ class Trainer:
     def workspace(self, N, C, B, nb, drums):
         key = (N, C, B, nb, bool(drums))
         if key not in self._ws:
-            self._ws[key] = self.mm.Workspace(N, C, B, nb, drums, training=True, device=self.device)
+            self._ws[key] = self.mm.Workspace(N, C, B, nb, drums, training=True, device=self.device, precision=self.precision,
+                                              graph=self.graph)
         return self._ws[key]
 
     def accumulate(self, pitched, unpitched, feats, mode, bpm, instruments_target, bpm_target, losses=None):

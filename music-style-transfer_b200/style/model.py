@@ -15,6 +15,7 @@ forward = mst_model_forward (activations kept in the workspace); get_total_loss 
 specialised for them); sub-modules cannot be called on their own.
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -191,8 +192,8 @@ class UnpitchedStyleApplier(_Part):
 class _ForwardContext:
     """What one model(...) call leaves behind for get_total_loss / backward: the workspace and its inputs."""
 
-    def __init__(self, model, ws, inputs):
-        self.model, self.ws, self.inputs = model, ws, inputs
+    def __init__(self, model, ws, inputs, src_ptr=0):
+        self.model, self.ws, self.inputs, self.src_ptr = model, ws, inputs, src_ptr
 
 
 class _TotalLoss(torch.autograd.Function):
@@ -202,7 +203,7 @@ class _TotalLoss(torch.autograd.Function):
     @staticmethod
     def forward(ctx, anchor, handle):
         ctx.handle = handle
-        return handle['leaves'][0, 0].clone()
+        return handle['host'][0, :1].clone()          # shape (1,) like the reference's total (bpm_loss keeps its batch dim)
 
     @staticmethod
     def backward(ctx, grad_out):
@@ -295,9 +296,16 @@ class StyleTransferModel(nn.Module):
 
     def _workspace(self, C, B, nb, drums, training):
         key = (C, B, nb, bool(drums), bool(training))
-        if key not in self._workspaces:
-            self._workspaces.clear()                    # one shape at a time: songs differ in length
-            self._workspaces[key] = _mm.Workspace(1, C, B, nb, drums, training=training)
+        if key in self._workspaces:
+            self._workspaces[key] = self._workspaces.pop(key)       # most recently used last
+        else:
+            # songs differ in length, but train-model.py:101 crops to 800 // C bars, so a few shapes recur: keep the last few
+            # (their activation arenas and captured graphs) instead of one
+            keep = int(os.environ.get('MST_WORKSPACE_CACHE', 4))
+            while len(self._workspaces) >= max(1, keep):
+                self._workspaces.pop(next(iter(self._workspaces)))
+            # one CUDA graph per entry point and shape (MST_NO_GRAPH=1 launches kernel by kernel); MST_PRECISION picks the mode
+            self._workspaces[key] = _mm.Workspace(1, C, B, nb, drums, training=training, graph=not os.environ.get('MST_NO_GRAPH'))
         return self._workspaces[key]
 
     @staticmethod
@@ -313,7 +321,7 @@ class StyleTransferModel(nn.Module):
         _, C, B, nb = pitched.shape[:4]
         ws = self._workspace(C, B, nb, unpitched is not None, training)
         out = ws.forward(self._flat, pitched, unpitched, feats, mode, bpm)
-        return out, _ForwardContext(self, ws, inputs)
+        return out, _ForwardContext(self, ws, ws.last_inputs, pitched.data_ptr())
 
     def extract_style(self, mode, bpm, pitched_channels, instruments_features, unpitched_channels=None):
         out, _ = self._run_forward(mode, bpm, pitched_channels, instruments_features, unpitched_channels, False)
@@ -385,13 +393,16 @@ def get_total_loss(instruments_pred, instruments_target, mode_pred, mode_target,
                             unpitched_target if use_u else None, instruments_pred.detach(), instruments_target,
                             mode_in.detach(), mode_t, bpm_in.detach().reshape(-1), bpm_t, normalize=normalize)
     fc = getattr(pitched_pred, '_mst_forward', None)
-    row = leaves[0]
+    # ONE device -> host copy of the (N, 16) leaf buffer: every leaf of the returned dict is a host scalar, so the
+    # reference's `float(x)` per leaf (train-model.py:129, ~15 device syncs there) costs nothing more
+    host = leaves.cpu()
+    row = host[0]
     get = lambda k: row[_LEAVES[k]]
-    total = row[0]
+    total = row[:1]
     if fc is not None and fc.ws.training and torch.is_grad_enabled():
-        same = fc.inputs[2].data_ptr() == pitched_target.data_ptr() or torch.equal(fc.inputs[2], pitched_target)
+        same = fc.src_ptr == pitched_target.data_ptr() or torch.equal(fc.inputs[2], pitched_target)
         if same and (fc.inputs[4] is not None) == use_u:
-            handle = dict(fc=fc, leaves=leaves, instruments_target=instruments_target.detach().float().contiguous(),
+            handle = dict(fc=fc, leaves=leaves, host=host, instruments_target=instruments_target.detach().float().contiguous(),
                           bpm_target=bpm_t, normalize=bool(normalize))
             total = _TotalLoss.apply(fc.model._anchor, handle)
     out_p = dict(total=get('channels_loss/pitched/total'), notes_loss=get('channels_loss/pitched/notes_loss'),

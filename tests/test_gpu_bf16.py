@@ -1,0 +1,154 @@
+"""GPU tests of the bf16 dense mode (BASELINE.json configs[3]: "bf16 dense layers"; MstModelShape.precision =
+MST_PRECISION_BF16): tcgen05 kind::f16 GEMMs with bf16 operands / fp32 accumulation (kernel selector 4) and the
+PitchedStyleApplier tail as tcgen05 tiles.
+
+Tolerances of the mode: GEMM error below 8e-3 of the row scale sum|a||b| (two bf16
+roundings of 2^-9 per product), loss leaves 1e-3 relative, parameter gradients 2e-2 measured as ||g - g_ref|| / ||g_ref||
+against the fp32 torch oracle.  The fp32 mode keeps its own (2e-5 / 2e-4) tests unchanged."""
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+
+pytestmark = pytest.mark.gpu
+OUT = os.path.join(gu.ROOT, 'gpurun_out')
+
+BF16_LOSS_RTOL = 1e-3
+BF16_GRAD_RTOL = 2e-2
+
+
+@pytest.fixture(scope='module')
+def torch():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail('GPU tests need a CUDA device (no CPU fallback exists)')
+    return torch
+
+
+CASES = [  # (M, N, K, layout, split_k, bias, act, accumulate)
+    (1000, 450, 32, 'linear', 1, True, 1, 0),
+    (4099, 17, 450, 'dx', 1, False, 0, 0),
+    (450, 32, 20011, 'dw', 37, False, 0, 2),
+    (129, 64, 57, 'linear', 1, True, 0, 1),
+    (300, 33, 100, 'at', 1, False, 0, 0),
+    (96, 512, 128, 'linear', 1, True, 1, 0),
+    (2048, 256, 192, 'dx', 1, False, 0, 1),
+    (3200, 64, 456, 'linear', 1, False, 0, 0),
+    (700, 16, 64, 'linear', 1, True, 1, 0),
+]
+
+
+@pytest.mark.parametrize('case', CASES)
+def test_bf16_gemm_matches_float64(torch, case):
+    from mst_native import model as mm
+    M, N, K, layout, split, use_bias, act, accumulate = case
+    gen = torch.Generator(device='cuda').manual_seed(M * 31 + N * 7 + K)
+    r = lambda *s: torch.randn(*s, device='cuda', generator=gen)
+    pad = 3
+    if layout == 'linear':
+        X, W = r(M, K + pad), r(N, K + pad)
+        A, a_si, a_sk, B, b_sk, b_sj = X, K + pad, 1, W, 1, K + pad
+        A64, B64 = X[:, :K].double(), W[:, :K].double().t()
+    elif layout == 'dx':
+        dY, W = r(M, K + pad), r(K, N + pad)
+        A, a_si, a_sk, B, b_sk, b_sj = dY, K + pad, 1, W, N + pad, 1
+        A64, B64 = dY[:, :K].double(), W[:, :N].double()
+    elif layout == 'dw':
+        dY, X = r(K, M + pad), r(K, N + pad)
+        A, a_si, a_sk, B, b_sk, b_sj = dY, 1, M + pad, X, N + pad, 1
+        A64, B64 = dY[:, :M].double().t(), X[:, :N].double()
+    else:
+        At, W = r(K, M + pad), r(N, K + pad)
+        A, a_si, a_sk, B, b_sk, b_sj = At, 1, M + pad, W, 1, K + pad
+        A64, B64 = At[:, :M].double().t(), W[:, :K].double().t()
+    bias = r(N + 1)[1:] if use_bias else None
+    C = r(M, N + pad)
+    C0 = C.clone()
+    mm.gemm(A, a_si, a_sk, B, b_sk, b_sj, C, N + pad, M, N, K, bias=bias, act=act, accumulate=accumulate, split_k=split, kernel=4)
+    want = A64 @ B64
+    if use_bias:
+        want = want + bias.double()
+    if act:
+        want = torch.where(want > 0, want, 0.01 * want)
+    if accumulate:
+        want = want + C0[:, :N].double()
+    scale = (A64.abs() @ B64.abs()) + 1.0
+    err = ((C[:, :N].double() - want).abs() / scale).max().item()
+    assert err < 8e-3, (case, err)
+    assert err > 1e-7 or K < 4, 'suspiciously exact: the bf16 path did not run'
+    assert torch.equal(C[:, N:], C0[:, N:])
+
+
+def _sample_batch(torch, case, n, seed0=21):
+    import model_oracle as mo
+    samples = [mo.synthetic_sample(seed=seed0 + i, **case) for i in range(n)]
+    cat = lambda k: torch.cat([s[k] for s in samples]).cuda().contiguous()
+    u = torch.cat([s['unpitched'] for s in samples]).cuda().contiguous() if samples[0]['unpitched'] is not None else None
+    it = torch.cat([mo.used_instruments(s['feats'], s['unpitched']) for s in samples]).cuda()
+    bt = torch.tensor([float(s['bpm_target']) for s in samples], device='cuda')
+    return samples, (cat('pitched'), u, cat('feats'), cat('mode'), cat('bpm'), it, bt)
+
+
+FWD_CASES = [dict(C=2, B=3, nb=4, drums=True, density=0.02), dict(C=3, B=5, nb=3, drums=False, density=0.01),
+             dict(C=1, B=4, nb=4, drums=True, density=0.02), dict(C=5, B=2, nb=2, drums=False, density=0.02)]
+
+
+@pytest.mark.parametrize('case', FWD_CASES)
+def test_bf16_forward_close_to_fp32_forward(torch, case):
+    """The same parameters and inputs through both modes: every output of mst_model_forward agrees to bf16 accuracy (the
+    PitchedStyleApplier tail runs as tcgen05 tiles in the bf16 mode, as FP32 SIMT in the fp32 mode)."""
+    import model_oracle as mo
+    from mst_native import model as mm
+    flat = mm.flatten_state_dict(mo.make_state_dict(108))
+    _, (p, u, f, m, b, _, _) = _sample_batch(torch, case, 2)
+    outs = {}
+    for prec in ('fp32', 'bf16'):
+        ws = mm.Workspace(2, case['C'], case['B'], case['nb'], case['drums'], training=False, precision=prec)
+        o = ws.forward(flat, p, u, f, m, b)
+        outs[prec] = {k: v.clone() for k, v in o.items() if v is not None}
+    torch.cuda.synchronize()
+    for k, ref in outs['fp32'].items():
+        got = outs['bf16'][k]
+        assert torch.isfinite(got).all(), k
+        err = float((got - ref).abs().max())
+        tol = 3e-2 * max(1.0, float(ref.abs().max()))
+        assert err < tol, (k, err, tol)
+    assert not torch.equal(outs['bf16']['pitched'], outs['fp32']['pitched']), 'the bf16 mode produced the fp32 bits: not engaged'
+
+
+TRAIN_CASES = [dict(C=2, B=4, nb=4, drums=True, density=0.02), dict(C=3, B=6, nb=4, drums=False, density=0.01),
+               dict(C=4, B=12, nb=4, drums=True, density=0.003)]
+
+
+@pytest.mark.parametrize('case', TRAIN_CASES)
+def test_bf16_train_step_within_mode_tolerance(torch, case):
+    import model_oracle as mo
+    from mst_native import model as mm
+    from test_gpu_train import oracle_step, flat_losses  # noqa: F401
+    sd = mo.make_state_dict(108)
+    flat = mm.flatten_state_dict(sd)
+    samples, (p, u, f, m, b, it, bt) = _sample_batch(torch, case, 2, seed0=5)
+    ws = mm.Workspace(2, case['C'], case['B'], case['nb'], case['drums'], training=True, precision='bf16')
+    grads = torch.zeros_like(flat)
+    losses, _ = ws.train_step(flat, grads, p, u, f, m, b, it, bt, normalize=True)
+    torch.cuda.synchronize()
+    leaves, ref_grads = oracle_step(torch, sd, samples)
+    got = losses.cpu().numpy()
+    report = []
+    for i, row in enumerate(leaves):
+        for k, idx in mm.LOSS_LEAVES.items():
+            if k in row:
+                err = abs(got[i, idx] - row[k]) / max(abs(row[k]), 1e-6)
+                assert err < BF16_LOSS_RTOL, (i, k, got[i, idx], row[k])
+    worst = (0.0, '')
+    for name, off, numel in mm.param_table():
+        g = grads[off:off + numel].cpu()
+        r = ref_grads[name].reshape(-1)
+        err = float((g - r).norm() / (r.norm() + 1e-12))
+        worst = max(worst, (err, name))
+        assert err < BF16_GRAD_RTOL or float(r.norm()) < 1e-7, (name, err)
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, 'bf16_train_parity.txt'), 'a') as fh:
+        fh.write(f'{case}: worst gradient rel-norm error {worst[0]:.3e} ({worst[1]}), total loss {got[0, 0]:.6f} vs {leaves[0]["total"]:.6f}\n')

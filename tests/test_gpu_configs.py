@@ -1,0 +1,200 @@
+"""GPU parity on BASELINE.json configs[0] and configs[1] AS WRITTEN, on the bundled example files
+(tests/golden/bundled_inputs.npz = the raw bytes of the reference's examples, tests/golden/config0.npz / config1.npz =
+what the UNMODIFIED reference produced for them in the build container, oracle/gen_golden_configs.py).
+
+configs[0]: one epoch of train-model.py's loop over `examples/drums - midi/*.mid` (2 iterations, one Adam step, seed 108):
+    loss leaves <= 2e-5 relative, parameters after the step <= 1e-4 on their norms.
+configs[1]: style_transfer.transfer_style for the four `examples/style transfer - midi/<Song>/` folders with seed-108
+    weights: `original/*.mid` byte-identical; apply_style's choices (instruments, mode, tempo) identical; files decoded
+    from PREDICTED grids compared message by message on every 16th bar and by per-(channel, bar) digests on the rest,
+    mismatch fraction asserted < 1e-4 and written to gpurun_out/ (copied to profiles/)."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import golden_util as gu
+from test_dropin_cpu import build_model
+
+pytestmark = pytest.mark.gpu
+OUT = os.path.join(gu.ROOT, 'gpurun_out')
+
+
+@pytest.fixture(scope='module')
+def torch():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail('GPU tests need a CUDA device (no CPU fallback exists)')
+    return torch
+
+
+def write_bundled(tmp, prefix):
+    z = np.load(os.path.join(gu.GOLDEN_DIR, 'bundled_inputs.npz'))
+    paths = []
+    for i, name in enumerate(str(n) for n in z['names']):
+        if name.startswith(prefix):
+            p = os.path.join(str(tmp), name[len(prefix):])
+            os.makedirs(os.path.dirname(p), exist_ok=True)
+            with open(p, 'wb') as f:
+                f.write(bytes(z[f'file{i:02d}']))
+            paths.append(p)
+    return paths
+
+
+def test_config0_drums_epoch_matches_reference(torch, tmp_path):
+    import math
+    from style import data as d, model as m
+    G = np.load(os.path.join(gu.GOLDEN_DIR, 'config0.npz'))
+    files = sorted(write_bundled(tmp_path, 'drums/'))
+    assert [os.path.basename(f) for f in files] == [str(x) for x in G['files']]
+    model = build_model()
+    optimizer = torch.optim.Adam(model.parameters(), lr=.01)
+    scheduler = torch.optim.lr_scheduler.StepLR(optimizer, step_size=200, gamma=.9)
+    names = [str(n) for n in G['loss_names']]
+    report = []
+    optimizer.zero_grad()
+    for iteration, input in enumerate(d.iter_inputs(files, d.included_instruments, shuffle=False, looped=False)):
+        filename, (info, pitched_channels, instruments_features, instruments, unpitched_channels) = input
+        max_n_bars = 800 // pitched_channels.shape[0]
+        mode, bpm, pitched_channels, instruments_features, unpitched_channels = d.prepare_input(input, max_n_bars)
+        if unpitched_channels is not None and unpitched_channels.sum() == 0:
+            unpitched_channels = None
+        assert list(pitched_channels.shape[1:4]) + [int(unpitched_channels is not None), int(info['bpm'])] == list(G['shapes'][iteration])
+        used = d.get_used_instruments(instruments_features, unpitched_channels)
+        (ip, mp, bp), pp, up = model(mode, bpm, pitched_channels, instruments_features, unpitched_channels)
+        losses = m.get_total_loss(ip, used, bp, info['bpm'], mp, mode, pp, pitched_channels, up, unpitched_channels,
+                                  normalize=True)
+        loss = losses['total']
+        assert not math.isnan(loss)
+        loss.backward()
+        row = {}
+
+        def walk(prefix, x):
+            if isinstance(x, dict):
+                for k, v in x.items():
+                    walk(prefix + [k], v)
+            else:
+                row['/'.join(prefix)] = float('nan') if x is None else float(x)
+        walk([], losses)
+        worst = 0.0
+        for j, k in enumerate(names):
+            w, g = float(G['losses'][iteration, j]), row.get(k, float('nan'))
+            if np.isnan(w):
+                assert np.isnan(g), (iteration, k)
+                continue
+            err = abs(g - w) / max(abs(w), 1e-6)
+            worst = max(worst, err)
+            assert err < 2e-5, (iteration, k, g, w)
+        report.append(f'iteration {iteration} ({os.path.basename(filename)}): total {row["total"]:.7f} '
+                      f'(reference {float(G["losses"][iteration, names.index("total")]):.7f}), worst leaf rel err {worst:.2e}')
+        if (iteration + 1) % 2 == 0:
+            sd = model.state_dict()
+            pn = [str(n) for n in G['param_names']]
+            gn = np.array([float(dict(model.named_parameters())[k].grad.double().norm()) for k in pn])
+            rel_g = np.abs(gn - G['grad_norms']) / np.maximum(G['grad_norms'], 1e-9)
+            report.append(f'accumulated gradient norms: worst rel err {rel_g.max():.2e} ({pn[int(rel_g.argmax())]})')
+            assert rel_g.max() < 2e-4, report[-1]
+            optimizer.step()
+            optimizer.zero_grad()
+            scheduler.step()
+    assert iteration == 1
+    sd = model.state_dict()
+    norms = np.array([float(sd[k].double().norm()) for k in pn])
+    rel = np.abs(norms - G['param_norms']) / np.maximum(G['param_norms'], 1e-9)
+    report.append(f'parameters after the Adam step: worst norm rel err {rel.max():.2e} ({pn[int(rel.argmax())]})')
+    heads = np.stack([np.pad(sd[k].cpu().numpy().ravel()[:8], (0, max(0, 8 - sd[k].numel()))) for k in pn])
+    flipped = int((np.abs(heads - G['param_heads']) > 1e-5).sum())
+    report.append(f'parameter heads: {flipped} of {heads.size} values differ by more than 1e-5 (first Adam step moves every '
+                  f'weight by lr * sign(g): a differing value is a gradient element whose sign is inside the fp32 noise)')
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, 'config0_parity.txt'), 'w') as f:
+        f.write('\n'.join(report) + '\n')
+    assert rel.max() < 1e-4, report[-2]
+    assert flipped <= heads.size // 100, report[-1]
+
+
+def _rows_from_smf(data):
+    from mst_native import abi, lib
+    events, tpb = lib.smf_parse(bytes(data))
+    notes = events[(events['kind'] == abi.EV_NOTE_ON) | (events['kind'] == abi.EV_NOTE_OFF)]
+    rows = np.stack([notes['tick'].astype(np.int64), (notes['kind'] == abi.EV_NOTE_ON).astype(np.int64),
+                     notes['channel'].astype(np.int64), notes['d1'].astype(np.int64), notes['d2'].astype(np.int64)], 1)
+    rows[rows[:, 1] == 0, 4] = 0 * rows[rows[:, 1] == 0, 4]          # note_off velocity is written as 0
+    return rows.astype(np.int32), tpb
+
+
+def _digest(rows, tpbar):
+    bars = rows[:, 0] // tpbar
+    key = rows[:, 2].astype(np.int64) * (1 << 20) + bars
+    order = np.argsort(key, kind='stable')
+    rows_s, key_s = rows[order], key[order]
+    uniq, start, count = np.unique(key_s, return_index=True, return_counts=True)
+    dig = np.zeros(len(uniq), dtype=np.uint64)
+    for i, (s, c) in enumerate(zip(start, count)):
+        dig[i] = np.frombuffer(hashlib.sha256(np.ascontiguousarray(rows_s[s:s + c]).tobytes()).digest()[:8], dtype=np.uint64)[0]
+    return uniq, count.astype(np.int32), dig
+
+
+@pytest.mark.parametrize('folder_index', [0, 1, 2, 3])
+def test_config1_transfer_style_matches_reference(torch, tmp_path, folder_index):
+    path = os.path.join(gu.GOLDEN_DIR, 'config1.npz')
+    if not os.path.exists(path):
+        pytest.fail('tests/golden/config1.npz is missing: run oracle/gen_golden_configs.py --config1')
+    from style import style_transfer as st
+    G = np.load(path)
+    folder = str(G['folders'][folder_index])
+    files = write_bundled(tmp_path / 'in', f'transfer/{folder}/')
+    comp = [p for p in files if os.path.basename(p).startswith(folder)]
+    assert len(comp) == 1
+    styles = sorted(p for p in files if p != comp[0])
+    out = tmp_path / 'out'
+    model = build_model()
+    decisions = {}
+    orig_save = st.save
+
+    def save_spy(cc, pitched, unpitched, instruments, save_path):
+        from style.scales import major_mode, key_names
+        decisions[os.path.relpath(save_path, str(out))] = [int(cc.info['scale']['mode'] is major_mode), int(cc.info['tempo']),
+                                                            int(unpitched is not None), key_names.index(cc.info['scale']['key'])] + [int(i) for i in instruments]
+        return orig_save(cc, pitched, unpitched, instruments, save_path)
+    st.save = save_spy
+    try:
+        st.transfer_style(model, comp[0], styles, str(out))
+    finally:
+        st.save = orig_save
+    names = [str(n) for n in G[f'{folder_index}/names']]
+    got_names = sorted(os.path.relpath(os.path.join(r, f), out) for r, _, fs in os.walk(out) for f in fs)
+    assert got_names == names
+    every = int(G['sample_every'])
+    report = [f'folder {folder}']
+    for i, n in enumerate(names):
+        pre = f'{folder_index}/{i:02d}/'
+        data = open(out / n, 'rb').read()
+        assert decisions[n] == [int(x) for x in G[pre + 'decision']], (n, decisions[n], list(G[pre + 'decision']))
+        same_bytes = hashlib.sha256(data).digest() == bytes(G[pre + 'sha256'])
+        if '/original/' in '/' + n:
+            assert same_bytes, n                              # encode -> decode -> SMF writer: byte-identical
+            report.append(f'  {n}: byte-identical ({len(data)} bytes)')
+            continue
+        rows, _ = _rows_from_smf(data)
+        tpbar = int(G[pre + 'ticks_per_bar'])
+        want_n = int(G[pre + 'n_messages'])
+        keys, counts, digs = _digest(rows, tpbar)
+        wk, wc, wd = G[pre + 'chunk_keys'], G[pre + 'chunk_counts'], G[pre + 'chunk_digests']
+        want = {int(k): (int(c), int(d)) for k, c, d in zip(wk, wc, wd)}
+        got = {int(k): (int(c), int(d)) for k, c, d in zip(keys, counts, digs)}
+        bad_chunks = sum(1 for k in set(want) | set(got) if want.get(k) != got.get(k))
+        sample = rows[(rows[:, 0] // tpbar) % every == 0]
+        ws = G[pre + 'sample_rows']
+        a = set(map(tuple, sample.tolist()))
+        b = set(map(tuple, ws.tolist()))
+        differing = len(a - b) + len(b - a)
+        frac = differing / max(1, len(b))
+        report.append(f'  {n}: bytes identical={same_bytes}, messages {len(rows)} vs {want_n}, sampled bars (every {every}th): '
+                      f'{differing} of {len(b)} messages differ ({frac:.2e}); (channel, bar) digests differing: {bad_chunks} of {len(want)}')
+        assert abs(len(rows) - want_n) <= 1e-4 * want_n + 2, report[-1]
+        assert frac < 1e-4, report[-1]
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, f'config1_parity_{folder_index}.txt'), 'w') as f:
+        f.write('\n'.join(report) + '\n')
