@@ -257,7 +257,10 @@ typedef struct MstDecodeResult {
     int32_t  max_delta;          /* second2tick(1, ticks_per_beat, tempo) */
 } MstDecodeResult;
 
-/* n_chunks = sum over songs of (n_pitched + has_unpitched) * n_bars (the caller built the song table).
+/* n_chunks >= sum over songs of (n_pitched + has_unpitched) * n_bars: an upper bound is enough (it sizes the workspace;
+ * mst_transfer_select decides n_pitched / has_unpitched on the device).  A song table that needs MORE chunks than
+ * n_chunks, or an entry with n_pitched > MST_MAX_DECODE_CHANNELS / non-positive bars, beats, ticks or tempo, is
+ * reported per song (MST_DECODE_CAPACITY / MST_DECODE_BAD_VALUE), never indexed.
  * d_grids is written only when a song asks for write_back. */
 size_t mst_decode_workspace_bytes(uint32_t n_songs, uint64_t n_chunks, uint64_t msg_capacity);
 
@@ -273,6 +276,29 @@ int mst_decode_batch_device(float *d_grids,
  * MST_E_CAPACITY (needed size in *n_needed). */
 int64_t mst_smf_write(const MstDecodeSong *song, const MstOutMsg *h_msgs, uint32_t n_messages,
                       int32_t eot_delta, uint8_t *out, size_t capacity, size_t *n_needed);
+
+/* ---------------------------------------------------------------- style transfer glue (style/style_transfer.py) */
+/* apply_style's host decisions (style/style_transfer.py:101-122), made on the device for a batch of S styles so that a
+ * "composition x S styles" transfer needs no host round trip between the song-info heads and the finished messages:
+ *   instruments = argsort(-logits)[:n] (+1 when the single pick is percussion, :106-108), percussion removed (:109-110),
+ *   mapped through the one-hot encoder's sorted categories (:112-116); mode = argmax of the two logits (:118-121);
+ *   tempo = bpm2tempo(round(bpm)) with Python's half-to-even round (:103).
+ * Outputs: d_features (S, max_channels, 51) = encode_instruments of the chosen programs (zero rows beyond n_pitched),
+ * d_choice[s], and d_songs[s] (in/out): n_pitched, has_unpitched, mode, tempo, channel_id (0..15 without 9, :78-80) and
+ * instrument_id are filled in, every other field (offsets, bars, ticks, tonic, ...) is the caller's. */
+typedef struct MstTransferChoice {
+    int32_t n_pitched;         /* instruments chosen, percussion removed */
+    int32_t has_unpitched;     /* percussion was among the picks */
+    int32_t mode;              /* 0 major, 1 minor */
+    int32_t tempo;             /* microseconds per beat */
+    int16_t instruments[MST_MAX_DECODE_CHANNELS];   /* programs, descending logit; -1 beyond n_pitched */
+} MstTransferChoice;
+
+int mst_transfer_select(const float *d_instruments_logits /* (S,41) */, const float *d_mode_logits /* (S,2) */,
+                        const float *d_bpm /* (S) */, const int32_t *d_n_instruments /* (S) */, uint32_t n_styles,
+                        const int16_t *h_programs /* [40] sorted included programs */,
+                        const int16_t *h_groups /* [40] group one-hot index of each */, int32_t max_channels,
+                        float *d_features, MstDecodeSong *d_songs, MstTransferChoice *d_choice, void *stream);
 
 /* ---------------------------------------------------------------- model (style/model.py) */
 /* Replaces StyleTransferModel.forward / extract_style / predict_song_info / apply_style
@@ -357,6 +383,13 @@ int mst_model_train_step(const float *d_params, float *d_grads, const MstModelSh
 int mst_model_predict_apply(const float *d_params, const MstModelShape *shape, const float *d_style, const float *d_melody,
                             const float *d_rhythm, const float *d_features, MstModelOutputs *outputs,
                             void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches);
+
+/* predict_song_info alone (SongInfoModel, style/model.py:513-562,775-777): the three heads from style (N,256) and rhythm
+ * (N,B,nb,10,32); shape->n_channels is ignored by the computation (the workspace is the forward workspace of the shape).
+ * Fills outputs->instruments, mode, bpm.  With mst_transfer_select and mst_model_predict_apply this is the device-side
+ * apply_style of style_transfer.py:101-131. */
+int mst_model_song_info(const float *d_params, const MstModelShape *shape, const float *d_style, const float *d_rhythm,
+                        MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches);
 
 /* get_total_loss + loss.backward() on the workspace a preceding mst_model_forward(..., training = 1) call filled for the
  * SAME shape, inputs and parameters (the reference's call pattern: model(...), get_total_loss(...), loss.backward(),

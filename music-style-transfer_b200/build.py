@@ -25,6 +25,7 @@ UNITS = [
     ('mst_encode.cu', ['-fmad=false']),
     ('mst_decode.cu', ['-fmad=false']),
     ('mst_model.cu', []),
+    ('mst_transfer.cu', []),
     ('mst_smf.cpp', []),
 ]
 

@@ -77,8 +77,8 @@ k_dec_plan(const MstDecodeSong *__restrict__ songs, uint32_t n_songs, DecWorkspa
         running += tot;
     }
     __syncthreads();
-    if (running != n_chunks) {
-        // the caller's chunk count (which sized the workspace) disagrees with the song table: decode nothing and say so
+    if (running > n_chunks) {
+        // the song table needs more chunks than the caller's count (which sized the workspace): decode nothing and say so
         for (uint32_t s = threadIdx.x; s <= n_songs; s += blockDim.x) {
             ws.chunk_prefix[s] = 0;
             if (s < n_songs) ws.song_status[s] = MST_DECODE_CAPACITY;

@@ -248,6 +248,16 @@ struct Launcher {
     int launches = 0;
     bool dry = false;             // planning pass: carve the arena, launch nothing
     bool bf16 = false;            // bf16 dense mode (MstModelShape.precision = MST_PRECISION_BF16)
+    // development knobs: attribute the mode's error / time to its two halves
+    // MST_BF16_MASK: which GEMM classes take the bf16 kernel (1 linear forward, 2 input gradient, 4 weight gradient,
+    // 8 LSTM input projection, 16 LSTM backward products); default all
+    int gemm_cls = 1;
+    bool bf16_gemm() const {
+        static const bool off = getenv("MST_BF16_NO_GEMM") != nullptr;
+        static const int mask = getenv("MST_BF16_MASK") ? atoi(getenv("MST_BF16_MASK")) : 31;
+        return bf16 && !off && (mask & gemm_cls) != 0;
+    }
+    bool bf16_tails() const { static const bool off = getenv("MST_BF16_NO_TAILS") != nullptr; return bf16 && !off; }
     cudaError_t err = cudaSuccess;
     void check() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && err == cudaSuccess) err = e; launches++; }
 
@@ -338,7 +348,7 @@ struct Launcher {
                 case 5: k_gemm_smallk<20><<<blocks, threads, 0, st>>>(g); break;
                 default: k_gemm_smallk<24><<<blocks, threads, 0, st>>>(g); break;
             }
-        } else if (kernel == 4 || (kernel == 0 && bf16 && use_tc(M, N, K) && K >= 24)) {
+        } else if (kernel == 4 || (kernel == 0 && bf16_gemm() && use_tc(M, N, K) && K >= 24)) {
             if (N <= 16) gemm_b16<16>(g, split_k); else if (N <= 32) gemm_b16<32>(g, split_k); else gemm_b16<64>(g, split_k);
         } else if (kernel == 3 || (kernel == 0 && use_tc(M, N, K) && K >= 24)) {
             if (N <= 16) gemm_t5<16>(g, split_k); else if (N <= 32) gemm_t5<32>(g, split_k); else gemm_t5<64>(g, split_k);
@@ -358,11 +368,17 @@ struct Launcher {
     // Y[M,N] = act(X[M,K]·W[N,K]^T + bias)      (nn.Linear); W row stride ldw (column block of a wider weight)
     void linear(const float *X, long long ldx, const float *W, long long ldw, const float *bias, float *Y, long long ldy,
                 int M, int N, int K, int act, int accumulate = 0) {
+        const int keep = gemm_cls;
+        if (gemm_cls != 8) gemm_cls = 1;
         gemm(X, ldx, 1, W, 1, ldw, Y, ldy, M, N, K, bias, act, accumulate);
+        gemm_cls = keep;
     }
     // dX[M,K] (+)= dY[M,N]·W[N,K]
     void linear_dx(const float *dY, long long ldy, const float *W, long long ldw, float *dX, long long ldx, int M, int N, int K, int accumulate) {
+        const int keep = gemm_cls;
+        if (gemm_cls != 16) gemm_cls = 2;
         gemm(dY, ldy, 1, W, ldw, 1, dX, ldx, M, K, N, nullptr, 0, accumulate);
+        gemm_cls = keep;
     }
     // dW[N,K] += dY[M,N]^T·X[M,K]   (atomic accumulate, K-dimension of the GEMM = M rows, split over CTAs)
     void linear_dw(const float *dY, long long ldy, const float *X, long long ldx, float *dW, long long ldw, int M, int N, int K) {
@@ -371,7 +387,10 @@ struct Launcher {
         const int tm = tc ? kTcBM : kGemmTile, tn = tc ? (K <= 16 ? 16 : (K <= 32 ? 32 : 64)) : kGemmTile;
         const int tiles = ((N + tm - 1) / tm) * ((K + tn - 1) / tn);
         const int split = std::max(1, std::min(std::min(512, M / 128), (2 * 148 + tiles - 1) / tiles));
+        const int keep = gemm_cls;
+        if (gemm_cls != 16) gemm_cls = 4;
         gemm(dY, 1, ldy, X, ldx, 1, dW, ldw, N, K, M, nullptr, 0, 2, split);
+        gemm_cls = keep;
     }
     void colsum(const float *in, float *out, long long rows, int cols, float *out2 = nullptr) {
         if (dry || rows <= 0) return;
@@ -632,7 +651,9 @@ void prep_weights(Launcher &L, Ctx &c) {
 
 // input projection of one LSTM direction for all time steps + the recurrence's arguments
 LstmArgs lstm_project(Launcher &L, const Ctx &c, LstmBuf &lb, const float *X, ParamId wih, float *out, long long out_ld, int out_off, int reverse) {
+    L.gemm_cls = 8;
     L.linear(X, lb.I, PRM(c, wih), lb.I, lb.bias_sum, lb.xproj, 4 * lb.H, lb.S * lb.T, 4 * lb.H, lb.I, 0);
+    L.gemm_cls = 1;
     LstmArgs a{};
     a.xproj = lb.xproj; a.w = lb.wt; a.out = out; a.out_ld = out_ld; a.out_off = out_off;
     a.gates = lb.gates; a.cells = lb.cells; a.hprev = lb.hprev; a.S = lb.S; a.T = lb.T; a.H = lb.H; a.reverse = reverse;
@@ -641,7 +662,9 @@ LstmArgs lstm_project(Launcher &L, const Ctx &c, LstmBuf &lb, const float *X, Pa
 
 // run one LSTM direction: xproj = X·W_ih^T + (b_ih + b_hh), then the recurrence
 void lstm_forward(Launcher &L, const Ctx &c, LstmBuf &lb, const float *X, ParamId wih, float *out, long long out_ld, int out_off, int reverse) {
+    L.gemm_cls = 8;
     L.linear(X, lb.I, PRM(c, wih), lb.I, lb.bias_sum, lb.xproj, 4 * lb.H, lb.S * lb.T, 4 * lb.H, lb.I, 0);
+    L.gemm_cls = 1;
     LstmArgs a{};
     a.xproj = lb.xproj; a.w = lb.wt; a.out = out; a.out_ld = out_ld; a.out_off = out_off;
     a.gates = lb.gates; a.cells = lb.cells; a.hprev = lb.hprev; a.S = lb.S; a.T = lb.T; a.H = lb.H; a.reverse = reverse;
@@ -840,7 +863,7 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
         load_psa_constants(L, c);
         k_psa_zci<<<grid_for((long long)NC * 450), 256, 0, L.st>>>(PRM(c, psa_oct_b), c.psa_zi, c.psa_zs, c.psa_zci, N, C); L.check();
         PsaArgs2 a{c.psa_zr, c.psa_zci, c.melody, c.psa_out, N, C, B, T};
-        if (L.bf16 && !L.dry) {
+        if (L.bf16_tails() && !L.dry) {
             // bf16 dense mode: the 5 x 50 contraction per note row as tcgen05 tiles (mst_model_psa_tc.cuh)
             cudaFuncSetAttribute(k_psa_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPtcSmem);
             k_psa_fwd_tc<<<(int)std::min<long long>(Rbf, 148 * 4), kPtcThreads, kPtcSmem, L.st>>>(a); L.check();
@@ -978,6 +1001,29 @@ extern "C" int mst_model_predict_apply(const float *d_params, const MstModelShap
     forward_apply(L, c, c.U != 0);
     if (L.err != cudaSuccess) { mst_set_error("mst_model_predict_apply: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     fill_outputs(c, outputs);
+    if (n_launches) *n_launches = L.launches;
+    return MST_OK;
+}
+
+extern "C" int mst_model_song_info(const float *d_params, const MstModelShape *shape, const float *d_style, const float *d_rhythm,
+                                   MstModelOutputs *outputs, void *d_workspace, size_t workspace_bytes, void *stream, int *n_launches) {
+    if (!d_params || !shape || !d_style || !d_rhythm || !outputs || !d_workspace) {
+        mst_set_error("mst_model_song_info: null pointer argument");
+        return MST_E_INVALID;
+    }
+    Ctx c;
+    int rc = setup_ctx(c, shape, d_workspace, workspace_bytes, false, false);
+    if (rc) return rc;
+    c.prm = d_params;
+    c.style = (float *)d_style; c.rhythm = d_rhythm;                                   // read only on this path
+    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
+    prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
+    prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
+    forward_song_info(L, c);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_song_info: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    memset(outputs, 0, sizeof(*outputs));
+    outputs->instruments = c.sim_instr; outputs->mode = c.sim_mode; outputs->bpm = c.sim_bpm;
+    outputs->style = c.style; outputs->rhythm = (float *)c.rhythm;
     if (n_launches) *n_launches = L.launches;
     return MST_OK;
 }

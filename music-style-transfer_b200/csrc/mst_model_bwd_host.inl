@@ -92,10 +92,12 @@ struct Bwd {
     }
     void lstm_bwd_grads(LstmBuf &lb, const float *X, ParamId wih, ParamId whh, ParamId bih, ParamId bhh, float *dX, int acc_dx) {
         const int rows = lb.S * lb.T, H4 = 4 * lb.H;
+        L.gemm_cls = 16;
         L.linear_dw(lb.dgates, H4, X, lb.I, GRD(c, wih), lb.I, rows, H4, lb.I);
         L.linear_dw(lb.dgates, H4, lb.hprev, lb.H, GRD(c, whh), lb.H, rows, H4, lb.H);
         L.colsum(lb.dgates, GRD(c, bih), rows, H4, GRD(c, bhh));      // b_ih and b_hh see the same gradient
         if (dX) L.linear_dx(lb.dgates, H4, PRM(c, wih), lb.I, dX, lb.I, rows, H4, lb.I, acc_dx);
+        L.gemm_cls = 1;
     }
     void lstm_bwd(LstmBuf &lb, const float *dout, long long out_ld, int out_off, int reverse, const float *X,
                   ParamId wih, ParamId whh, ParamId bih, ParamId bhh, float *dX, int acc_dx) {
@@ -172,7 +174,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     float *d_melody = w.A(Rbf * 448);
     {
         float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
-        const bool tc_tail = L.bf16 && ptc_bwd_smem(C) <= 72 * 1024;     // bf16 dense mode: tcgen05 tiles (mst_model_psa_tc.cuh)
+        const bool tc_tail = L.bf16_tails() && ptc_bwd_smem(C) <= 72 * 1024;     // bf16 dense mode: tcgen05 tiles (mst_model_psa_tc.cuh)
         if (!L.dry && tc_tail) {
             PsaBwdTcArgs a{};
             a.Zr = c.psa_zr; a.Zci = c.psa_zci; a.pred = c.psa_out; a.target = c.P; a.coef = lb.coef_p;

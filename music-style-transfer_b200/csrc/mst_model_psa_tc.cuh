@@ -141,9 +141,24 @@ k_psa_fwd_tc(PsaArgs2 a) {
         __syncwarp();
     };
 
+    // the (n, c) rows of Zci a tile adds to the unit's Zr row come from L2: fetched into registers ONE TILE AHEAD so that
+    // their latency hides behind the current tile (task i of this thread = column pair q = tid + 128 i of the pair's 2 x 225)
+    float2 zc[4];
+    auto fetch_zci = [&](int nn, int c0n) {
+        const int nchn = min(2, a.C - c0n);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int q = tid + i * kPtcThreads;
+            if (q < 225 * nchn) {
+                const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
+                zc[i] = __ldg(reinterpret_cast<const float2 *>(a.Zci + ((long long)nn * a.C + c0n + ch) * 450 + 2 * qq));
+            }
+        }
+    };
     long long it = 0;
     int sb = 0;
     prefetch(blockIdx.x, 0);
+    if ((long long)blockIdx.x < units) fetch_zci((int)(blockIdx.x / per_n), 0);
     for (long long u = blockIdx.x; u < units; u += gridDim.x, sb ^= 1) {
         const int n = (int)(u / per_n);
         const long long btf = u - (long long)n * per_n;
@@ -155,13 +170,18 @@ k_psa_fwd_tc(PsaArgs2 a) {
         for (int c0 = 0; c0 < a.C; c0 += 2, it++) {
             const int nch = min(2, a.C - c0), ib = (int)(it & 1);
             // ---- S1: od rows of the pair (bf16), and once per unit the melody branch
-            for (int q = tid; q < 225 * nch; q += kPtcThreads) {
-                const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
-                const float2 z = *reinterpret_cast<const float2 *>(zr + 2 * qq);
-                const float2 zc = __ldg(reinterpret_cast<const float2 *>(a.Zci + ((long long)n * a.C + c0 + ch) * 450 + 2 * qq));
-                const int j = qq / 15, kk = (qq - j * 15) * 2;
-                *reinterpret_cast<uint32_t *>(smem + kPtcOffOd + ch * kPtcOdCh + j * 80 + kk * 2) = pack_bf16(leaky(z.x + zc.x), leaky(z.y + zc.y));
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int q = tid + i * kPtcThreads;
+                if (q < 225 * nch) {
+                    const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
+                    const float2 z = *reinterpret_cast<const float2 *>(zr + 2 * qq);
+                    const int j = qq / 15, kk = (qq - j * 15) * 2;
+                    *reinterpret_cast<uint32_t *>(smem + kPtcOffOd + ch * kPtcOdCh + j * 80 + kk * 2) = pack_bf16(leaky(z.x + zc[i].x), leaky(z.y + zc[i].y));
+                }
             }
+            if (c0 + 2 < a.C) fetch_zci(n, c0 + 2);
+            else if (u + gridDim.x < units) fetch_zci((int)((u + gridDim.x) / per_n), 0);
             if (c0 == 0 && r_valid) {
                 const float4 m0 = *reinterpret_cast<const float4 *>(mel + r_note * 8), m1 = *reinterpret_cast<const float4 *>(mel + r_note * 8 + 4);
                 const float mv[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
@@ -250,8 +270,8 @@ constexpr uint32_t kPbS = kPbG + 2 * 2048;                   // S: 4 k-groups x 
 constexpr uint32_t kPbW = kPbS + 4 * 2048;                   // Wl^T: 4 k-groups x 256 B
 constexpr uint32_t kPbOd = kPbW + 4 * 256;                   // od bf16 [2][15][40]
 constexpr uint32_t kPbZr = kPbOd + 2 * kPtcOdCh;             // 2 x zr[452]
-constexpr uint32_t kPbStage = kPbZr + 2 * 1808;              // per warp: pred[160] + target[160] floats
-constexpr uint32_t kPbDzr = kPbStage + 4 * 1280;             // dzr accumulator [450] (+2 pad)
+constexpr uint32_t kPbStage = kPbZr + 2 * 1808;              // 2 buffers x 4 warps x (pred[160] + target[160] floats)
+constexpr uint32_t kPbDzr = kPbStage + 2 * 4 * 1280;             // dzr accumulator [450] (+2 pad)
 constexpr uint32_t kPbDps = kPbDzr + 1808;                   // dps accumulator [280]
 constexpr uint32_t kPbDzi = kPbDps + 1120;                   // dzi accumulators [C][450]
 __host__ __device__ constexpr uint32_t ptc_bwd_smem(int C) { return kPbDzi + (uint32_t)C * 1800; }
@@ -346,30 +366,15 @@ k_psa_bwd_tc(PsaBwdTcArgs a) {
     unsigned char *az_row = smem + kPbAz + (uint32_t)(tid >> 3) * kPbAzRG + (uint32_t)(tid & 7) * 16;
     unsigned char *g_row = smem + kPbG + (uint32_t)(tid >> 3) * 128 + (uint32_t)(tid & 7) * 16;
     unsigned char *s_row = smem + kPbS + (uint32_t)(tid >> 3) * 128 + (uint32_t)(tid & 7) * 16;
-    float *st_pred = reinterpret_cast<float *>(smem + kPbStage) + warp * 320, *st_tgt = st_pred + 160;
+    float *st_pred = reinterpret_cast<float *>(smem + kPbStage) + warp * 320, *st_tgt = st_pred + 160;      // buffer b: + b * 1280 floats
 
-    auto prefetch_zr = [&](long long btf, int sb) {
+    // everything tile t + 1 needs from global memory travels in ONE cp.async group issued at the start of tile t: its
+    // prediction / target rows (per-warp staging, 16-byte coalesced) and, when it opens a new unit, that unit's Zr row
+    auto prefetch_tile = [&](long long btf, int c0, int buf, int zbuf) {
         if (btf < b_hi) {
-            const float *zg = a.Zr + ((long long)n * per_n + btf) * 450;
-            float *zs = reinterpret_cast<float *>(smem + kPbZr + sb * 1808);
-            for (int i = tid; i < 225; i += kPtcThreads) cp_async8(zs + i * 2, zg + i * 2);
-        }
-        asm volatile("cp.async.commit_group;");
-    };
-
-    uint32_t tile = 0;                       // tiles issued so far by this CTA: barrier phase = tile & 1
-    int sb = 0;
-    prefetch_zr(b_lo, 0);
-    for (long long btf = b_lo; btf < b_hi; btf++, sb ^= 1) {
-        const long long u = (long long)n * per_n + btf;
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        __syncthreads();                                        // this unit's Zr row is visible to every thread
-        const float *zr = reinterpret_cast<const float *>(smem + kPbZr + sb * 1808);
-        for (int c0 = 0; c0 < C; c0 += 2, tile++) {
             const int nch = min(2, C - c0);
-            const uint32_t ph = tile & 1;
             const long long base0 = (((long long)n * C + c0) * per_n + btf) * 280, base1 = (((long long)n * C + c0 + 1) * per_n + btf) * 280;
-            // ---- the tile's prediction / target rows -> per-warp staging (16-byte coalesced)
+            float *sp = st_pred + buf * 1280, *stg = st_tgt + buf * 1280;
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int q = lane + 32 * h;
@@ -377,24 +382,60 @@ k_psa_bwd_tc(PsaBwdTcArgs a) {
                     const int f = 160 * warp + 4 * q, ch = f >= 280 ? 1 : 0;
                     if (f < 560 && ch < nch) {
                         const long long g = (ch ? base1 : base0) + (f - 280 * ch);
-                        cp_async16(st_pred + 4 * q, a.pred + g);
-                        cp_async16(st_tgt + 4 * q, a.target + g);
+                        cp_async16(sp + 4 * q, a.pred + g);
+                        cp_async16(stg + 4 * q, a.target + g);
                     }
                 }
             }
-            asm volatile("cp.async.commit_group;");
-            if (c0 == 0) prefetch_zr(btf + 1, sb ^ 1);          // a NEWER group than the tile's rows: it may stay in flight below
-            // ---- P1: od rows of the pair (bf16)
-            for (int q = tid; q < 225 * nch; q += kPtcThreads) {
-                const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
-                const float2 z = *reinterpret_cast<const float2 *>(zr + 2 * qq);
-                const float2 zc = __ldg(reinterpret_cast<const float2 *>(a.Zci + ((long long)n * C + c0 + ch) * 450 + 2 * qq));
-                const int j = qq / 15, kk = (qq - j * 15) * 2;
-                *reinterpret_cast<uint32_t *>(smem + kPbOd + ch * kPtcOdCh + j * 80 + kk * 2) = pack_bf16(leaky(z.x + zc.x), leaky(z.y + zc.y));
+            if (c0 == 0) {
+                const float *zg = a.Zr + ((long long)n * per_n + btf) * 450;
+                float *zs = reinterpret_cast<float *>(smem + kPbZr + zbuf * 1808);
+                for (int i = tid; i < 225; i += kPtcThreads) cp_async8(zs + i * 2, zg + i * 2);     // Zr rows are 1800 bytes: 8-byte aligned
             }
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+    float2 zc[4];
+    auto fetch_zci = [&](int c0n) {
+        const int nchn = min(2, C - c0n);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int q = tid + i * kPtcThreads;
+            if (q < 225 * nchn) {
+                const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
+                zc[i] = __ldg(reinterpret_cast<const float2 *>(a.Zci + ((long long)n * C + c0n + ch) * 450 + 2 * qq));
+            }
+        }
+    };
+
+    uint32_t tile = 0;                       // tiles issued so far by this CTA: barrier phase = tile & 1
+    int sb = 0;
+    prefetch_tile(b_lo, 0, 0, 0);
+    fetch_zci(0);
+    for (long long btf = b_lo; btf < b_hi; btf++, sb ^= 1) {
+        const long long u = (long long)n * per_n + btf;
+        const float *zr = reinterpret_cast<const float *>(smem + kPbZr + sb * 1808);
+        for (int c0 = 0; c0 < C; c0 += 2, tile++) {
+            const int nch = min(2, C - c0);
+            const uint32_t ph = tile & 1;
+            const int tb = (int)(tile & 1);
+            if (c0 + 2 < C) prefetch_tile(btf, c0 + 2, tb ^ 1, sb); else prefetch_tile(btf + 1, 0, tb ^ 1, sb ^ 1);
+            const float *sp = st_pred + tb * 1280, *stg = st_tgt + tb * 1280;
+            asm volatile("cp.async.wait_group 1;" ::: "memory");    // everything but the group just issued: this tile's rows (and Zr row) landed
+            __syncthreads();
+            // ---- P1: od rows of the pair (bf16)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int q = tid + i * kPtcThreads;
+                if (q < 225 * nch) {
+                    const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
+                    const float2 z = *reinterpret_cast<const float2 *>(zr + 2 * qq);
+                    const int j = qq / 15, kk = (qq - j * 15) * 2;
+                    *reinterpret_cast<uint32_t *>(smem + kPbOd + ch * kPtcOdCh + j * 80 + kk * 2) = pack_bf16(leaky(z.x + zc[i].x), leaky(z.y + zc[i].y));
+                }
+            }
+            if (c0 + 2 < C) fetch_zci(c0 + 2); else fetch_zci(0);
             if (tile > 0) mbar_wait(bar3, (tile - 1) & 1);       // the weight-gradient MMAs of the previous tile have read Az and G
-            if (c0 == 0) asm volatile("cp.async.wait_group 1;" ::: "memory");   // all but the newest group (the next unit's Zr row)
-            else asm volatile("cp.async.wait_group 0;" ::: "memory");
             __syncthreads();
             // ---- P2: loss gradient of the row, its z row; G and Az chunks
             uint4 zreg[4];
@@ -402,7 +443,7 @@ k_psa_bwd_tc(PsaBwdTcArgs a) {
             if (active) {
                 float y[5], t[5], dpre[5];
 #pragma unroll
-                for (int e = 0; e < 5; e++) { y[e] = st_pred[lane * 5 + e]; t[e] = st_tgt[lane * 5 + e]; }
+                for (int e = 0; e < 5; e++) { y[e] = sp[lane * 5 + e]; t[e] = stg[lane * 5 + e]; }
                 loss_cell_grad<5>(y, t, cf, dpre);
                 *reinterpret_cast<uint4 *>(g_row) = make_uint4(pack_bf16(dpre[0], dpre[1]), pack_bf16(dpre[2], dpre[3]), pack_bf16(dpre[4], 0.f), 0u);
 #pragma unroll

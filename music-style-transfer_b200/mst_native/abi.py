@@ -128,3 +128,8 @@ def make_filter(included=None, min_n_messages=100, crop_channel_bars=0):
         f['included'] = inc
     f['crop_channel_bars'] = crop_channel_bars
     return f
+
+
+TRANSFER_CHOICE_DTYPE = np.dtype([('n_pitched', '<i4'), ('has_unpitched', '<i4'), ('mode', '<i4'), ('tempo', '<i4'),
+                                  ('instruments', '<i2', (MAX_DECODE_CHANNELS,))])
+assert TRANSFER_CHOICE_DTYPE.itemsize == 80

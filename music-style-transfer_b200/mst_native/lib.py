@@ -22,9 +22,9 @@ EXPORTS = [
     'mst_smf_parse',
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
     'mst_encode_host_workspace_bytes', 'mst_encode_batch_host', 'mst_encode_batch_host_async',
-    'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write',
+    'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write', 'mst_transfer_select',
     'mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
-    'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply', 'mst_model_backward', 'mst_model_loss_workspace_bytes',
+    'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply', 'mst_model_song_info', 'mst_model_backward', 'mst_model_loss_workspace_bytes',
     'mst_model_loss', 'mst_adam_step', 'mst_model_gemm',
 ]
 
@@ -77,6 +77,10 @@ def load():
     L.mst_smf_write.restype = ctypes.c_int64
     L.mst_smf_write.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int32, ctypes.c_void_p,
                                 ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t)]
+    L.mst_transfer_select.restype = ctypes.c_int
+    L.mst_transfer_select.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
+                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p,
+                                      ctypes.c_void_p, ctypes.c_void_p]
     if L.mst_abi_version() != abi.MST_ABI_VERSION:
         raise MstError('libmst_b200.so ABI version mismatch: rebuild')
     _lib = L
@@ -252,3 +256,26 @@ def smf_write(dsong, msgs, eot_delta):
     if n < 0:
         raise MstError(f'mst_smf_write failed ({n})')
     return out[:n].tobytes()
+
+
+# ---------------------------------------------------------------------------------- style transfer glue
+def transfer_select(instr_logits, mode_logits, bpm, n_instruments, programs, groups, max_channels, d_songs, stream=None):
+    """apply_style's host decisions on the device (mst_transfer_select).  instr_logits (S,41), mode_logits (S,2), bpm (S):
+    float32 CUDA tensors; n_instruments: list of ints; programs / groups: the 40 sorted included programs and the group
+    one-hot index of each; d_songs: uint8 CUDA tensor holding S MstDecodeSong records (updated in place).
+    Returns (features (S, max_channels, 51) float32 CUDA, choices uint8 CUDA tensor of S MstTransferChoice records)."""
+    import torch
+    L = require_gpu()
+    S = int(instr_logits.shape[0])
+    dev = instr_logits.device
+    n_dev = torch.tensor([int(x) for x in n_instruments], dtype=torch.int32, device=dev)
+    feats = torch.empty(S, int(max_channels), 51, dtype=torch.float32, device=dev)
+    choice = torch.empty(S * abi.TRANSFER_CHOICE_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    prog = np.ascontiguousarray(programs, dtype=np.int16)
+    grp = np.ascontiguousarray(groups, dtype=np.int16)
+    assert len(prog) == 40 and len(grp) == 40
+    s = torch.cuda.current_stream(dev) if stream is None else stream
+    check(L.mst_transfer_select(instr_logits.contiguous().data_ptr(), mode_logits.contiguous().data_ptr(), bpm.contiguous().data_ptr(),
+                                n_dev.data_ptr(), S, _np_ptr(prog), _np_ptr(grp), int(max_channels), feats.data_ptr(),
+                                d_songs.data_ptr(), choice.data_ptr(), s.cuda_stream))
+    return feats, choice

@@ -41,7 +41,7 @@ class LossIn(ctypes.Structure):
 
 EXPORTS = ['mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
            'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply',
-           'mst_model_backward',
+           'mst_model_song_info', 'mst_model_backward',
            'mst_model_loss_workspace_bytes',
            'mst_model_loss', 'mst_adam_step', 'mst_model_gemm']
 
@@ -82,6 +82,9 @@ def _L():
                                      ctypes.c_size_t, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
         L.mst_model_predict_apply.restype = ctypes.c_int
         L.mst_model_predict_apply.argtypes = [ctypes.c_void_p, ctypes.POINTER(ModelShape)] + [ctypes.c_void_p] * 4 + [
+            ctypes.POINTER(ModelOutputs), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        L.mst_model_song_info.restype = ctypes.c_int
+        L.mst_model_song_info.argtypes = [ctypes.c_void_p, ctypes.POINTER(ModelShape)] + [ctypes.c_void_p] * 2 + [
             ctypes.POINTER(ModelOutputs), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
         L.mst_model_backward.restype = ctypes.c_int
         L.mst_model_backward.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ModelShape)] + \
@@ -250,6 +253,23 @@ class Workspace:
             instruments=self._view(outs.instruments, (N, 41)), mode=self._view(outs.mode, (N, 2)),
             bpm=self._view(outs.bpm, (N,)), pitched=self._view(outs.pitched, (N, C, B, nb, 10, 56, 5)),
             unpitched=self._view(outs.unpitched, (N, 1, B, nb, 10, 47, 2)) if s.has_unpitched else None)
+
+    def song_info(self, flat_params, style, rhythm, stream=None):
+        """predict_song_info from given style (N,256) / rhythm (N,B,nb,10,32): dict of workspace views instruments (N,41),
+        mode (N,2), bpm (N)."""
+        import torch
+        s = self.shape
+        N, B, nb = s.n_samples, s.n_bars, s.n_beats
+        assert tuple(style.shape) == (N, 256) and tuple(rhythm.shape) == (N, B, nb, 10, 32)
+        outs = ModelOutputs()
+        nl = ctypes.c_int(0)
+        st = torch.cuda.current_stream(self.device) if stream is None else stream
+        _lib.check(_L().mst_model_song_info(flat_params.data_ptr(), ctypes.byref(s), style.contiguous().data_ptr(),
+                                            rhythm.contiguous().data_ptr(), ctypes.byref(outs), self.buf.data_ptr(), self.bytes,
+                                            st.cuda_stream, ctypes.byref(nl)))
+        self.launches = nl.value
+        return dict(instruments=self._view(outs.instruments, (N, 41)), mode=self._view(outs.mode, (N, 2)),
+                    bpm=self._view(outs.bpm, (N,)))
 
     def train_step(self, flat_params, flat_grads, pitched, unpitched, feats, mode, bpm, instruments_target,
                    bpm_target, losses=None, normalize=True, stream=None):

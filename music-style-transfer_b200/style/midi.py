@@ -89,5 +89,45 @@ class DecodedMidi:
 
 
 def create_midi(info, *instruments, max_delta_time=math.inf):
-    raise NotImplementedError('create_midi is fused into the GPU decode: use style.style_transfer.decode_midi, which '
-                              'returns the finished file (ordering, int velocities, delta clip: mst_decode_batch_device)')
+    """create_midi (midi.py:120-168) on Python message lists: `instruments` are channel dicts {'channel_id', 'instrument_id',
+    'messages': [objects with .type ('note_on' | 'note_off'), .note, .time (absolute ticks), .velocity]}.  Host logic of the
+    reference restated on numpy (int velocities, stable sort by time, end_of_track, delta times with the max_delta_time clip);
+    the bytes come from the native SMF writer.  Returns a DecodedMidi (`.save(path)` like mido.MidiFile).
+    The fused GPU path (style_transfer.decode_midi) does the same on the device for whole grids."""
+    import numpy as np
+    from mst_native import abi
+    tpb, tempo = int(info['ticks_per_beat']), int(info['tempo'])
+    clip = None
+    if math.isfinite(max_delta_time):
+        clip = int(round(max_delta_time / (tempo * 1e-6 / tpb)))          # mido.second2tick, then int() (:121-123)
+    if len(instruments) > abi.MAX_DECODE_CHANNELS:
+        raise ValueError(f'at most {abi.MAX_DECODE_CHANNELS} channels per file')
+    rows = []
+    for idx, instrument in enumerate(instruments):
+        ch = int(instrument['channel_id'])
+        if not 0 <= ch <= 15:
+            raise ValueError('channel must be in range 0..15')
+        for msg in instrument['messages']:
+            velocity = int(msg.velocity * max_velocity)                    # np.float32 * int stays f32 under numpy >= 2 (:147)
+            assert velocity <= 127, (velocity, msg.velocity)
+            if not (0 <= int(msg.note) <= 127 and velocity >= 0):
+                raise ValueError('data byte must be in range 0..127')     # what mido.Message raises
+            rows.append((int(msg.time), 1 if msg.type == 'note_on' else 0, ch, int(msg.note), velocity))
+    rows.sort(key=lambda r: r[0])                                          # sorted(messages, key=time): stable (:157)
+    duration = info.get('duration', (rows[-1][0] + info['ticks_per_bar']) if rows else None)
+    if duration is None:
+        raise IndexError('list index out of range')                       # messages[-1] on an empty list (:158)
+    out = np.zeros(len(rows), dtype=abi.OUT_MSG_DTYPE)
+    time = 0
+    for i, (t, on, ch, note, vel) in enumerate(rows):
+        delta = t - time if clip is None else min(t - time, clip)
+        time = t
+        out[i] = (t, max(0, delta), on, ch, note, vel if on else vel)
+    eot = int(duration) - time if clip is None else min(int(duration) - time, clip)
+    ts = info['time_signature']
+    rec = dict(ticks_per_beat=tpb, ticks_per_bar=int(info.get('ticks_per_bar', tpb * ts['numerator'])), tempo=tempo, tonic=0, mode=0,
+               numerator=int(ts['numerator']), denominator_log2=int(ts['denominator']).bit_length() - 1, n_beats=int(ts['numerator']))
+    song = abi.make_decode_song(rec, len(instruments), False, 1, channel_ids=[int(i['channel_id']) for i in instruments],
+                                instrument_ids=[max(0, int(i.get('instrument_id', 0))) for i in instruments], write_back=False)
+    data = _lib.smf_write(song, out, max(0, eot))
+    return DecodedMidi(out, data, tpb)

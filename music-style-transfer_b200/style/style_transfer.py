@@ -1,7 +1,9 @@
 """style/style_transfer.py of the reference (style_transfer.py:22-158): encode two songs, swap the style vector,
-predict instruments / mode / bpm, decode and save.  Encode, the model and decode run on the GPU; decode_midi hands
-the model's device tensor straight to the decode kernels (no .cpu().numpy() of the grid) and returns the finished
-file produced by the native SMF writer."""
+predict instruments / mode / bpm, decode and save.  Everything between the MIDI bytes and the finished files runs on
+the GPU: the encoder, the network, apply_style's own decisions (which instruments, which mode, which tempo:
+mst_transfer_select) and the decoder; `transfer_style` renders the composition in ALL requested styles as one batched
+device pass with a single read-back of the finished messages.  decode_midi hands a device tensor
+straight to the decode kernels (no .cpu().numpy() of the grid) and returns the file the native SMF writer produced."""
 import os
 
 import numpy as np
@@ -14,12 +16,13 @@ from style.data import (
     prepare_input,
     percussion_id,
     instruments_one_hot_encoder,
+    groups_one_hot_encoder,
     encode_instruments,
 )
-from style.midi import load_midi_from_file, DecodedMidi
+from style.midi import load_midi_from_file, program2group, DecodedMidi
 from style.midi_conversion import ChannelConverter, read_midi
 from style.model import device
-from style.scales import major_mode, minor_mode
+from style.scales import major_mode, minor_mode, MODES
 from style.utils.misc import make_dirs
 
 
@@ -29,6 +32,9 @@ def bpm2tempo(bpm):
 
 
 def transfer_style(model, composition_path, style_paths, output_path):
+    """style_transfer.py:22-54.  Writes original/<song>.mid for the composition and every style, `<composition>
+    (reconstructed).mid` and `<composition> (<style> style).mid` per style: the same files in the same places; the
+    renderings are produced together by apply_styles()."""
     composition_name = os.path.splitext(os.path.basename(composition_path))[0]
     composition_input = get_model_input(composition_path)
     (_, (composition_info, composition_pitched_channels, _, composition_instruments,
@@ -43,8 +49,8 @@ def transfer_style(model, composition_path, style_paths, output_path):
     save(
         composition_cc, composition_pitched_channels, composition_unpitched_channels,
         composition_instruments, os.path.join(output_path, f'original/{composition_name}.mid'))
-    apply_style(model, composition_info, style_, melody, rhythm, len(composition_instruments),
-                os.path.join(output_path, f'{composition_name} (reconstructed).mid'))
+    jobs = [(composition_info, style_, len(composition_instruments),
+             os.path.join(output_path, f'{composition_name} (reconstructed).mid'))]
     for style_path in style_paths:
         style_name = os.path.splitext(os.path.basename(style_path))[0]
         style_input = get_model_input(style_path)
@@ -56,9 +62,9 @@ def transfer_style(model, composition_path, style_paths, output_path):
         save(style_cc, style_pitched_channels, style_unpitched_channels, style_instruments,
              os.path.join(output_path, f'original/{style_name}.mid'))
         info = combine_info(style_info=style_info, melody_info=composition_info)
-
-        apply_style(model, info, style, melody, rhythm, len(style_instruments),
-                    os.path.join(output_path, f'{composition_name} ({style_name} style).mid'))
+        jobs.append((info, style, len(style_instruments),
+                     os.path.join(output_path, f'{composition_name} ({style_name} style).mid')))
+    apply_styles(model, jobs, melody, rhythm)
 
 
 def get_model_input(path):
@@ -106,39 +112,96 @@ def save(cc, pitched_channels, unpitched_channels, instruments, save_path):
     mid.save(save_path)
 
 
+# the one-hot encoders' category tables as the select kernel takes them: sorted included programs, and for each the
+# index of its group among the sorted group names (style/data.py:23-27)
+_PROGRAMS = [int(p) for p in instruments_one_hot_encoder.categories_[0]]
+_GROUPS = [list(groups_one_hot_encoder.categories_[0]).index(program2group[p]) for p in _PROGRAMS]
+
+
+def apply_styles(model, jobs, melody, rhythm):
+    """Device-side apply_style (style_transfer.py:101-131) for a batch: jobs = [(info, style (1,256), n_instruments,
+    save_path)], all rendered on the composition's melody / rhythm.
+
+      1. predict_song_info for all S styles at once (mst_model_song_info, N = S);
+      2. mst_transfer_select: top-k instruments with the percussion special case, mode arg-max, bpm2tempo(round(bpm)),
+         the instrument one-hot features and the decode-table entries - on the device, nothing is read back;
+      3. model.apply_style per style into one grid buffer (mst_model_predict_apply; the number of channels a style
+         renders is known up front: n_instruments, of which the kernel's choice may drop the percussion slot);
+      4. one mst_decode_batch_device over all S renderings, ONE device->host copy of results + messages + choices;
+      5. the native SMF writer per file.
+    Like the reference, every job's info dict gets info['tempo'] and info['scale']['mode'] of the prediction."""
+    from mst_native import model as _mm
+    S = len(jobs)
+    if S == 0:
+        return
+    model._flatten()
+    f = lambda t: t.detach().to('cuda', torch.float32).contiguous()
+    melody, rhythm = f(melody), f(rhythm)
+    _, B, nb = rhythm.shape[:3]
+    styles = torch.cat([f(j[1]).reshape(1, 256) for j in jobs])
+    n_inst = [int(j[2]) for j in jobs]
+    with torch.no_grad():
+        # 1. the three heads, all styles at once (the composition's rhythm is shared)
+        ws = _mm.Workspace(S, 1, B, nb, False, training=False)
+        heads = ws.song_info(model._flat, styles, rhythm.expand(S, *rhythm.shape[1:]).contiguous())
+        # 2. the decisions, on the device.  A style renders at most n (+1 for the lone-percussion case) channels; the
+        # decode table's grid offsets are fixed by that bound, so no decision has to come back to the host first
+        max_c = [max(1, n) for n in n_inst]
+        pitched_floats = [c * B * nb * abi.PITCHED_BEAT_FLOATS for c in max_c]
+        unpitched_floats = B * nb * abi.UNPITCHED_BEAT_FLOATS
+        offsets, total = [], 0
+        for pf in pitched_floats:
+            offsets.append(total)
+            total += pf + unpitched_floats
+        recs = []
+        for (info, _, _, _), c, off, pf in zip(jobs, max_c, offsets, pitched_floats):
+            cc = ChannelConverter(info)
+            rec = cc.decode_song_record(c, True, B, nb, [i for i in range(16) if i != 9][:c], [0] * min(c, 15), write_back=False)
+            rec['pitched_offset'], rec['unpitched_offset'] = off, off + pf
+            recs.append(rec)
+        dsongs = np.array(recs, dtype=abi.DECODE_SONG_DTYPE)
+        d_songs = torch.from_numpy(dsongs.view(np.uint8).reshape(-1)).cuda()
+        feats, d_choice = _lib.transfer_select(heads['instruments'], heads['mode'], heads['bpm'], n_inst, _PROGRAMS, _GROUPS,
+                                                max(max_c), d_songs)
+        # 3. the renderings, one per style, into one grid buffer
+        grids = torch.empty(total, dtype=torch.float32, device='cuda')
+        for s, (c, off, pf) in enumerate(zip(max_c, offsets, pitched_floats)):
+            wa = model._workspace(c, B, nb, True, False)
+            out = wa.predict_apply(model._flat, styles[s:s + 1], melody, rhythm, feats[s:s + 1, :c].contiguous())
+            grids[off:off + pf].copy_(out['pitched'].reshape(-1))
+            grids[off + pf:off + pf + unpitched_floats].copy_(out['unpitched'].reshape(-1))
+        # 4. decode everything; the chunk count is an upper bound (the kernel's choices may drop channels)
+        n_chunks = sum((min(c, 15) + 1) * B for c in max_c)
+        cap = 2 * sum((min(c, 15) * 56 + 47) * B * nb * 10 for c in max_c) + 1024
+        L = _lib.require_gpu()
+        d_res = torch.empty(S * abi.DECODE_RESULT_DTYPE.itemsize, dtype=torch.uint8, device='cuda')
+        d_msgs = torch.empty(cap * abi.OUT_MSG_DTYPE.itemsize, dtype=torch.uint8, device='cuda')
+        wsb = L.mst_decode_workspace_bytes(S, n_chunks, cap)
+        dws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
+        _lib.check(L.mst_decode_batch_device(grids.data_ptr(), d_songs.data_ptr(), S, n_chunks, d_msgs.data_ptr(), cap, d_res.data_ptr(),
+                                             dws.data_ptr(), wsb, torch.cuda.current_stream().cuda_stream))
+        # the single host round trip of the whole transfer
+        res = d_res.cpu().numpy().view(abi.DECODE_RESULT_DTYPE)
+        songs_out = d_songs.cpu().numpy().view(abi.DECODE_SONG_DTYPE)
+        choices = d_choice.cpu().numpy().view(abi.TRANSFER_CHOICE_DTYPE)
+        n_used = int(res['msg_offset'][-1]) + int(res['n_messages'][-1]) if int(res['status'][-1]) == abi.DECODE_OK else cap
+        msgs = d_msgs[:min(cap, n_used) * abi.OUT_MSG_DTYPE.itemsize].cpu().numpy().view(abi.OUT_MSG_DTYPE)
+    # 5. files + the reference's side effects on the info dicts
+    for s, (info, _, _, save_path) in enumerate(jobs):
+        info['tempo'] = int(choices[s]['tempo'])
+        info['scale']['mode'] = MODES[int(choices[s]['mode'])]
+        r = res[s]
+        _raise_for_decode_status(int(r['status']))
+        m = msgs[int(r['msg_offset']):int(r['msg_offset']) + int(r['n_messages'])]
+        data = _lib.smf_write(songs_out[s], m, int(r['eot_delta']))
+        make_dirs(os.path.dirname(save_path))
+        DecodedMidi(m.copy(), data, int(songs_out[s]['ticks_per_beat'])).save(save_path)
+    return choices
+
+
 def apply_style(model, info, style, melody, rhythm, n_instruments, save_path):
-    with torch.no_grad():
-        instruments_pred, mode, bpm = model.predict_song_info(style, rhythm)
-    info['tempo'] = bpm2tempo(round(float(bpm)))
-
-    instruments_pred = instruments_pred.detach().cpu().numpy()
-    instruments = np.argsort(-instruments_pred[0])[:n_instruments]
-    if len(instruments) == 1 and instruments[0] == [percussion_id]:
-        instruments = np.argsort(-instruments_pred[0])[:n_instruments+1]
-    unpitched = percussion_id in instruments
-    instruments = [instrument for instrument in instruments if instrument != percussion_id]
-
-    instruments_encoded = np.zeros([len(instruments), len(included_instruments)])
-    for i, instrument in enumerate(instruments):
-        instruments_encoded[i, instrument] = 1
-    instruments = instruments_one_hot_encoder.inverse_transform(instruments_encoded)
-    instruments = [int(x[0]) for x in instruments]
-
-    if mode[0].argmax() == 0:
-        mode = major_mode
-    else:
-        mode = minor_mode
-    info['scale']['mode'] = mode
-
-    cc = ChannelConverter(info)
-    instruments_features = encode_instruments(instruments)
-    instruments_features = torch.tensor(
-        instruments_features, dtype=torch.float).to(device).unsqueeze(0)
-    with torch.no_grad():
-        pitched_pred, unpitched_pred = model.apply_style(
-            style, melody, rhythm, instruments_features, unpitched)
-
-    save(cc, pitched_pred, unpitched_pred, instruments, save_path)
+    """style_transfer.py:101-131 for one style: the batch of one of apply_styles()."""
+    apply_styles(model, [(info, style, n_instruments, save_path)], melody, rhythm)
 
 
 def combine_info(style_info, melody_info):
@@ -150,6 +213,15 @@ def combine_info(style_info, melody_info):
         'tempo': style_info['tempo'],
     }
     return info
+
+
+def _raise_for_decode_status(status):
+    if status == abi.DECODE_NO_MESSAGES:
+        raise IndexError('list index out of range')               # messages[-1] in create_midi (midi.py:158)
+    if status == abi.DECODE_VELOCITY:
+        raise AssertionError('velocity out of range')             # the assert at midi.py:148
+    if status != abi.DECODE_OK:
+        raise ValueError(f'cannot decode grid (status {status})')
 
 
 def decode_midi(channel_converter, channels_info, pitched_channels, unpitched_channel_info=None,
@@ -177,13 +249,7 @@ def decode_midi(channel_converter, channels_info, pitched_channels, unpitched_ch
     dsongs = np.array([rec], dtype=abi.DECODE_SONG_DTYPE)
     res, msgs = _lib.decode_batch(grids, dsongs)
     r = res[0]
-    status = int(r['status'])
-    if status == abi.DECODE_NO_MESSAGES:
-        raise IndexError('list index out of range')               # messages[-1] in create_midi (midi.py:158)
-    if status == abi.DECODE_VELOCITY:
-        raise AssertionError('velocity out of range')             # the assert at midi.py:148
-    if status != abi.DECODE_OK:
-        raise ValueError(f'cannot decode grid (status {status})')
+    _raise_for_decode_status(int(r['status']))
     if not contiguous_in_place:                                    # hard_output's in-place gate on the caller's tensors
         pitched.copy_(grids[:p.numel()].view_as(pitched))
         if has_u:

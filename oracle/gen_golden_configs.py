@@ -212,7 +212,45 @@ def run_config1():
     print(path, os.path.getsize(path) // 1024, 'KiB')
 
 
+def run_create_midi():
+    """tests/golden/create_midi.npz: the reference's create_midi (style/midi.py:120-168) on seeded random message lists
+    (three channels incl. channel 9, np.float32 velocities, negative durations, long gaps) for two max_delta_time values:
+    the message arrays and the bytes mid.save() wrote."""
+    ref = ref_harness.load()
+    NM = ref.midi_conversion.NoteMessage
+    rng = np.random.default_rng(3)
+    flat = {}
+    info = {'ticks_per_beat': 480, 'tempo': 434783, 'time_signature': {'numerator': 3, 'denominator': 4}, 'ticks_per_bar': 1440}
+    cases = [(1, {}), (0.25, {'duration': 400000}), (2, {})]
+    for ci, (mdt, extra) in enumerate(cases):
+        chans = []
+        for ch, prog in ((0, 25), (9, -1), (3, 48)):
+            msgs, t = [], 0
+            for _ in range(150):
+                t += int(rng.integers(0, 3000))
+                msgs.append(NM('note_on', int(rng.integers(0, 128)), t, np.float32(rng.random())))
+                msgs.append(NM('note_off', int(rng.integers(0, 128)), t + int(rng.integers(-50, 900)), 0))
+            chans.append({'channel_id': ch, 'instrument_id': prog, 'messages': sorted(msgs, key=lambda m: m.time)})
+        mid = ref.midi.create_midi(dict(info, **extra), *chans, max_delta_time=mdt)
+        with tempfile.NamedTemporaryFile(suffix='.mid') as f:
+            mid.save(f.name)
+            flat[f'{ci}/bytes'] = np.frombuffer(open(f.name, 'rb').read(), dtype=np.uint8)
+        flat[f'{ci}/max_delta_time'] = np.float64(mdt)
+        flat[f'{ci}/duration'] = np.int64(extra.get('duration', -1))
+        for k, c in enumerate(chans):
+            flat[f'{ci}/{k}/channel'] = np.array([c['channel_id'], c['instrument_id']], dtype=np.int64)
+            flat[f'{ci}/{k}/msgs'] = np.array([(m.type == 'note_on', m.note, m.time) for m in c['messages']], dtype=np.int64)
+            flat[f'{ci}/{k}/velocity'] = np.array([m.velocity for m in c['messages']], dtype=np.float32)
+    flat['n_cases'] = np.int64(len(cases))
+    path = os.path.join(GOLDEN, 'create_midi.npz')
+    np.savez_compressed(path, **flat)
+    print(path, os.path.getsize(path) // 1024, 'KiB')
+
+
 if __name__ == '__main__':
+    if '--create-midi' in sys.argv:
+        run_create_midi()
+        sys.exit(0)
     todo = sys.argv[1:] or ['--inputs', '--config0', '--config1']
     if '--inputs' in todo:
         write_inputs()

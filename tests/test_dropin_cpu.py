@@ -181,3 +181,27 @@ def test_utils_pytorch_helpers_and_pickle_names():
     t = [torch.tensor(3.0), torch.tensor(4.0)]
     assert abs(float(up.get_mean(t, mean_type='quadratic')) - (12.5 ** .5)) < 1e-6
     assert float(up.get_mean([torch.tensor(0.0)], mean_type='quadratic')) == 0.0
+
+
+def test_create_midi_matches_reference_bytes():
+    """style.midi.create_midi on Python message lists (host logic + native SMF writer) against the bytes the reference's
+    create_midi + mid.save() produced for the same lists (tests/golden/create_midi.npz, oracle/gen_golden_configs.py)."""
+    from style.midi import create_midi
+    G = np.load(os.path.join(gu.GOLDEN_DIR, 'create_midi.npz'))
+
+    class Msg:
+        def __init__(self, on, note, time, velocity):
+            self.type, self.note, self.time, self.velocity = ('note_on' if on else 'note_off'), int(note), int(time), velocity
+
+    info = {'ticks_per_beat': 480, 'tempo': 434783, 'time_signature': {'numerator': 3, 'denominator': 4}, 'ticks_per_bar': 1440}
+    for ci in range(int(G['n_cases'])):
+        i2 = dict(info)
+        if int(G[f'{ci}/duration']) >= 0:
+            i2['duration'] = int(G[f'{ci}/duration'])
+        chans = []
+        for k in range(3):
+            ch, prog = (int(x) for x in G[f'{ci}/{k}/channel'])
+            msgs = [Msg(on, note, t, np.float32(v) if on else 0) for (on, note, t), v in zip(G[f'{ci}/{k}/msgs'], G[f'{ci}/{k}/velocity'])]
+            chans.append({'channel_id': ch, 'instrument_id': prog, 'messages': msgs})
+        got = create_midi(i2, *chans, max_delta_time=float(G[f'{ci}/max_delta_time']))
+        assert got.data == bytes(G[f'{ci}/bytes']), ci
