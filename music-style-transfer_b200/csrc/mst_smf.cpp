@@ -261,3 +261,144 @@ extern "C" int64_t mst_smf_write(const MstDecodeSong *song, const MstOutMsg *msg
     if (!out || w.n > capacity) return MST_E_CAPACITY;
     return (int64_t)w.n;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Batch loader: replaces the per-file `load_midi_from_file` (style/midi.py:104-108) + the one-thread prefetcher
+// (style/utils/parallel.py:34-51) in front of the encoder.  A pool of C++ threads reads and parses the files straight
+// into the caller's (page-locked) MstEvent / MstSongIn buffers, so that mst_encode_batch_host_async can start its H2D
+// copy from them without another pass over the data.
+// ------------------------------------------------------------------------------------------------
+#include <stdio.h>
+
+#include <atomic>
+#include <thread>
+
+extern "C" int mst_smf_load_batch(const char *const *paths, uint32_t n_files, int32_t n_threads, MstEvent *h_events,
+                                  uint64_t capacity, MstSongIn *h_songs, int32_t *h_status, uint64_t *n_events_total) {
+    if (!paths || !h_songs || !h_status || !n_events_total || (!h_events && capacity)) return MST_E_INVALID;
+    *n_events_total = 0;
+    if (n_files == 0) return MST_OK;
+    unsigned nt = n_threads > 0 ? (unsigned)n_threads : std::thread::hardware_concurrency();
+    if (nt == 0) nt = 1;
+    if (nt > n_files) nt = n_files;
+    std::vector<std::vector<MstEvent>> parsed(n_files);
+    std::vector<int32_t> tpb(n_files, 0);
+    std::atomic<uint32_t> next(0);
+    auto parse_worker = [&]() {
+        std::vector<uint8_t> bytes;
+        for (;;) {
+            const uint32_t i = next.fetch_add(1);
+            if (i >= n_files) return;
+            h_status[i] = -1;                                   // unreadable file (OSError in the reference)
+            FILE *f = paths[i] ? fopen(paths[i], "rb") : nullptr;
+            if (!f) continue;
+            fseek(f, 0, SEEK_END);
+            const long size = ftell(f);
+            fseek(f, 0, SEEK_SET);
+            if (size < 0) { fclose(f); continue; }
+            bytes.resize((size_t)size);
+            const size_t got = size ? fread(bytes.data(), 1, (size_t)size, f) : 0;
+            fclose(f);
+            if (got != (size_t)size) continue;
+            std::vector<MstEvent> &ev = parsed[i];
+            ev.resize((size_t)size / 2 + 1);                    // an event takes at least two bytes (delta + data byte)
+            int32_t division = 0, n_tracks = 0;
+            size_t need = 0;
+            const int64_t n = mst_smf_parse(bytes.data(), bytes.size(), ev.data(), ev.size(), &division, &n_tracks, &need);
+            if (n < 0) { ev.clear(); h_status[i] = (int32_t)n; continue; }   // -(100 + reason): mido would raise, the reference gets None
+            ev.resize((size_t)n);
+            tpb[i] = division;
+            h_status[i] = 0;
+        }
+    };
+    {
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nt; t++) pool.emplace_back(parse_worker);
+        parse_worker();
+        for (auto &t : pool) t.join();
+    }
+    uint64_t total = 0;
+    for (uint32_t i = 0; i < n_files; i++) {
+        h_songs[i].event_offset = total;
+        h_songs[i].n_events = (uint32_t)parsed[i].size();
+        h_songs[i].ticks_per_beat = tpb[i];
+        total += parsed[i].size();
+    }
+    *n_events_total = total;
+    if (total > capacity) return MST_E_CAPACITY;
+    next = 0;
+    auto copy_worker = [&]() {
+        for (;;) {
+            const uint32_t i = next.fetch_add(1);
+            if (i >= n_files) return;
+            if (!parsed[i].empty()) memcpy(h_events + h_songs[i].event_offset, parsed[i].data(), parsed[i].size() * sizeof(MstEvent));
+        }
+    };
+    {
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nt; t++) pool.emplace_back(copy_worker);
+        copy_worker();
+        for (auto &t : pool) t.join();
+    }
+    return MST_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// General SMF serialiser of an MstEvent array (track-major, absolute ticks): the inverse of mst_smf_parse for the event
+// kinds the encoder consumes.  Used to put synthetic corpora on disk as real .mid files (bench.py's file-fed legs, tests).
+// ------------------------------------------------------------------------------------------------
+extern "C" int64_t mst_smf_write_events(const MstEvent *events, uint64_t n_events, int32_t ticks_per_beat, uint8_t *out,
+                                        size_t capacity, size_t *n_needed) {
+    if (!events && n_events) return MST_E_INVALID;
+    Writer w{out, capacity, 0};
+    uint32_t n_tracks = 0;
+    for (uint64_t i = 0; i < n_events; i++) if (events[i].track + 1u > n_tracks) n_tracks = events[i].track + 1u;
+    if (n_tracks == 0) n_tracks = 1;
+    const char hdr[8] = {'M', 'T', 'h', 'd', 0, 0, 0, 6};
+    for (int i = 0; i < 8; i++) w.put((uint8_t)hdr[i]);
+    w.put(0); w.put(1);
+    w.put((uint8_t)(n_tracks >> 8)); w.put((uint8_t)n_tracks);
+    w.put((uint8_t)((ticks_per_beat >> 8) & 0xFF)); w.put((uint8_t)(ticks_per_beat & 0xFF));
+    uint64_t i = 0;
+    for (uint32_t t = 0; t < n_tracks; t++) {
+        const char trk[4] = {'M', 'T', 'r', 'k'};
+        for (int k = 0; k < 4; k++) w.put((uint8_t)trk[k]);
+        const size_t len_pos = w.n;
+        for (int k = 0; k < 4; k++) w.put(0);
+        const size_t start = w.n;
+        uint32_t prev = 0;
+        int running = -1;
+        for (; i < n_events && events[i].track == t; i++) {
+            const MstEvent &e = events[i];
+            w.varint(e.tick >= prev ? e.tick - prev : 0);
+            prev = e.tick >= prev ? e.tick : prev;
+            if (e.kind <= MST_EV_PITCHWHEEL) {
+                const int status = ((e.kind + 8) << 4) | (e.channel & 0x0F);
+                if (status != running) w.put((uint8_t)status);
+                running = status;
+                w.put(e.d1 & 0x7F);
+                if (e.kind != MST_EV_PROGRAM_CHANGE && e.kind != MST_EV_AFTERTOUCH) w.put(e.d2 & 0x7F);
+            } else {
+                running = -1;                                    // a meta event cancels running status in a file
+                w.put(0xFF);
+                switch (e.kind) {
+                    case MST_EV_SET_TEMPO: w.put(0x51); w.put(3); w.put((uint8_t)(e.aux >> 16)); w.put((uint8_t)(e.aux >> 8)); w.put((uint8_t)e.aux); break;
+                    case MST_EV_TIME_SIGNATURE: w.put(0x58); w.put(4); w.put(e.d1); w.put(e.d2); w.put(24); w.put(8); break;
+                    case MST_EV_KEY_SIGNATURE: w.put(0x59); w.put(2); w.put((uint8_t)(int8_t)((int)(e.aux / 2) - 7)); w.put((uint8_t)(e.aux & 1)); break;
+                    case MST_EV_CHANNEL_PREFIX: w.put(0x20); w.put(1); w.put(e.channel); break;
+                    case MST_EV_UNKNOWN: w.put(0x09); w.put(0); break;   // device_name: a type outside known_messages
+                    default: w.put(0x01); w.put(0); break;               // an ignored meta (empty text)
+                }
+            }
+        }
+        w.put(0); w.put(0xFF); w.put(0x2F); w.put(0);
+        const size_t len = w.n - start;
+        if (out && w.n <= capacity) {
+            out[len_pos] = (uint8_t)(len >> 24); out[len_pos + 1] = (uint8_t)(len >> 16);
+            out[len_pos + 2] = (uint8_t)(len >> 8); out[len_pos + 3] = (uint8_t)len;
+        }
+    }
+    if (n_needed) *n_needed = w.n;
+    if (!out || w.n > capacity) return MST_E_CAPACITY;
+    return (int64_t)w.n;
+}

@@ -19,9 +19,10 @@ _lib = None
 EXPORTS = [
     'mst_abi_version', 'mst_last_error', 'mst_device_count',
     'mst_profile_enable', 'mst_profile_encode_ms',
-    'mst_smf_parse',
+    'mst_smf_parse', 'mst_smf_load_batch', 'mst_smf_write_events',
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
     'mst_encode_host_workspace_bytes', 'mst_encode_batch_host', 'mst_encode_batch_host_async',
+    'mst_events_pack', 'mst_encode_packed_workspace_bytes', 'mst_encode_batch_packed_async',
     'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write', 'mst_transfer_select',
     'mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
     'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply', 'mst_model_song_info', 'mst_model_backward', 'mst_model_loss_workspace_bytes',
@@ -52,6 +53,12 @@ def load():
     L.mst_smf_parse.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
                                 ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
                                 ctypes.POINTER(ctypes.c_size_t)]
+    L.mst_smf_load_batch.restype = ctypes.c_int
+    L.mst_smf_load_batch.argtypes = [ctypes.POINTER(ctypes.c_char_p), ctypes.c_uint32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_uint64,
+                                     ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64)]
+    L.mst_smf_write_events.restype = ctypes.c_int64
+    L.mst_smf_write_events.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int32, ctypes.c_void_p, ctypes.c_size_t,
+                                       ctypes.POINTER(ctypes.c_size_t)]
     for name in ('mst_encode_workspace_bytes', 'mst_encode_host_workspace_bytes'):
         f = getattr(L, name)
         f.restype = ctypes.c_size_t
@@ -68,6 +75,12 @@ def load():
     L.mst_encode_batch_host_async.argtypes = [
         ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
         ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    L.mst_events_pack.restype = None
+    L.mst_events_pack.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
+    L.mst_encode_packed_workspace_bytes.restype = ctypes.c_size_t
+    L.mst_encode_packed_workspace_bytes.argtypes = [ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint64]
+    L.mst_encode_batch_packed_async.restype = ctypes.c_int
+    L.mst_encode_batch_packed_async.argtypes = L.mst_encode_batch_host_async.argtypes
     L.mst_decode_workspace_bytes.restype = ctypes.c_size_t
     L.mst_decode_workspace_bytes.argtypes = [ctypes.c_uint32, ctypes.c_uint64, ctypes.c_uint64]
     L.mst_decode_batch_device.restype = ctypes.c_int
@@ -118,6 +131,49 @@ def smf_parse(data):
     if n < 0:
         return None
     return out[:n].copy(), int(tpb.value)
+
+
+def smf_load_batch(paths, events_out, songs_out=None, status_out=None, n_threads=0):
+    """Parse `paths` on a C++ thread pool into `events_out` (ndarray[EVENT_DTYPE], ideally a view of page-locked memory).
+    Returns (n_events_total, songs ndarray[SONG_IN_DTYPE], status int32 ndarray) or raises MstError(capacity) carrying the
+    needed record count in `.needed`.  The GIL is released for the duration of the call."""
+    L = load()
+    n = len(paths)
+    songs = np.zeros(n, dtype=abi.SONG_IN_DTYPE) if songs_out is None else songs_out[:n]
+    status = np.zeros(n, dtype=np.int32) if status_out is None else status_out[:n]
+    arr = (ctypes.c_char_p * max(n, 1))(*[os.fsencode(p) for p in paths])
+    total = ctypes.c_uint64(0)
+    rc = L.mst_smf_load_batch(arr, n, int(n_threads), _np_ptr(events_out), len(events_out), _np_ptr(songs), _np_ptr(status),
+                              ctypes.byref(total))
+    if rc == -3:
+        e = MstError(f'event buffer too small: {total.value} records needed')
+        e.needed = int(total.value)
+        raise e
+    check(rc)
+    return int(total.value), songs, status
+
+
+def events_pack(events, out=None):
+    """MstEvent records -> the 8-byte wire format (uint64 ndarray; `out` may be a view of page-locked memory)."""
+    L = load()
+    events = np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE)
+    if out is None:
+        out = np.empty(len(events), dtype=np.uint64)
+    L.mst_events_pack(_np_ptr(events), len(events), _np_ptr(out))
+    return out
+
+
+def smf_write_events(events, ticks_per_beat):
+    """MstEvent records (track-major, absolute ticks) -> Standard MIDI File bytes (mst_smf_write_events)."""
+    L = load()
+    events = np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE)
+    cap = 64 + 16 * (int(events['track'].max()) + 2 if len(events) else 2) + 8 * len(events)
+    out = np.empty(cap, dtype=np.uint8)
+    need = ctypes.c_size_t(0)
+    n = L.mst_smf_write_events(_np_ptr(events), len(events), int(ticks_per_beat), _np_ptr(out), cap, ctypes.byref(need))
+    if n < 0:
+        raise MstError(f'mst_smf_write_events failed ({n})')
+    return out[:n].tobytes()
 
 
 # ---------------------------------------------------------------------------------- batches

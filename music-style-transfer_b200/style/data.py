@@ -81,37 +81,29 @@ def _input_from_record(r, arena):
 
 
 def iter_inputs(files, instruments, min_n_messages=100, shuffle=False, looped=False, encode_batch=16):
-    """Yields (filename, (info, pitched, instruments_features, instruments, unpitched)) like data.py:51-63."""
-    def file_stream():
-        order = files[:]
-        if shuffle:
-            np.random.shuffle(order)       # once: the reference shuffles a copy, then loops that permutation (data.py:35-41)
+    """Yields (filename, (info, pitched, instruments_features, instruments, unpitched)) like data.py:51-63.
+
+    The files go through mst_native.pipeline.EventPipeline: a C++ thread pool parses `encode_batch` files at a time into
+    page-locked buffers while the GPU encodes the previous batch (the job of the reference's prefetch thread,
+    utils/parallel.py:34-51, and of its per-file Python encoder).  Order and skip rules are the reference's: unreadable
+    files, MidiFormatError rejects and songs without a pitched channel are skipped (data.py:42-47,57)."""
+    from mst_native.pipeline import EventPipeline
+    order = list(files)
+    if shuffle:
+        np.random.shuffle(order)       # once: the reference shuffles a copy, then loops that permutation (data.py:35-41)
+    pipe = EventPipeline(abi.make_filter(instruments, min_n_messages), batch_files=encode_batch)
+    try:
         while True:
-            yield from order
+            for f, r, arena in pipe.run(order):
+                if int(r['status']) != abi.SONG_OK:
+                    continue
+                info, pitched, feats, ins, unpitched = _input_from_record(r, arena)
+                # the arena slot is rewritten two batches later: the caller gets its own copy of the grids
+                yield f, (info, pitched.clone(), feats, ins, None if unpitched is None else unpitched.clone())
             if not looped:
                 return
-
-    pending = []
-    stream = file_stream()
-    done = False
-    while not done:
-        while len(pending) < encode_batch:
-            try:
-                f = next(stream)
-            except StopIteration:
-                done = True
-                break
-            mid = load_midi_from_file(f)
-            if mid is not None:
-                pending.append((f, mid))
-        if not pending:
-            break
-        infos, arena = _encode_many([(m.events, m.ticks_per_beat) for _, m in pending], instruments, min_n_messages)
-        for (f, _), r in zip(pending, infos):
-            if int(r['status']) != abi.SONG_OK:        # MidiFormatError / no pitched channel: skip (data.py:47,57)
-                continue
-            yield f, _input_from_record(r, arena)
-        pending = []
+    finally:
+        pipe.close()
 
 
 def get_input(channels, info):

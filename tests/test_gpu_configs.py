@@ -154,19 +154,29 @@ def test_config1_transfer_style_matches_reference(torch, tmp_path, folder_index)
     styles = sorted(p for p in files if p != comp[0])
     out = tmp_path / 'out'
     model = build_model()
+    # apply_style's decisions: for the original/ files save() sees them (as in the reference); the renderings are decided
+    # on the device by mst_transfer_select and come back from apply_styles()
     decisions = {}
-    orig_save = st.save
+    orig_save, orig_apply = st.save, st.apply_styles
+    from style.scales import major_mode, key_names
 
     def save_spy(cc, pitched, unpitched, instruments, save_path):
-        from style.scales import major_mode, key_names
         decisions[os.path.relpath(save_path, str(out))] = [int(cc.info['scale']['mode'] is major_mode), int(cc.info['tempo']),
                                                             int(unpitched is not None), key_names.index(cc.info['scale']['key'])] + [int(i) for i in instruments]
         return orig_save(cc, pitched, unpitched, instruments, save_path)
-    st.save = save_spy
+
+    def apply_spy(model_, jobs, melody, rhythm):
+        choices = orig_apply(model_, jobs, melody, rhythm)
+        for (info, _, _, save_path), c in zip(jobs, choices):
+            decisions[os.path.relpath(save_path, str(out))] = [1 - int(c['mode']), int(c['tempo']), int(c['has_unpitched']),
+                                                                key_names.index(info['scale']['key'])] + [int(i) for i in c['instruments'][:int(c['n_pitched'])]]
+            assert info['tempo'] == int(c['tempo']) and (info['scale']['mode'] is major_mode) == (int(c['mode']) == 0)   # the reference's side effects
+        return choices
+    st.save, st.apply_styles = save_spy, apply_spy
     try:
         st.transfer_style(model, comp[0], styles, str(out))
     finally:
-        st.save = orig_save
+        st.save, st.apply_styles = orig_save, orig_apply
     names = [str(n) for n in G[f'{folder_index}/names']]
     got_names = sorted(os.path.relpath(os.path.join(r, f), out) for r, _, fs in os.walk(out) for f in fs)
     assert got_names == names

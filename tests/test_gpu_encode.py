@@ -226,3 +226,37 @@ def test_host_async_entry_point_two_slots(torch):
             sl['job'] = i
     for sl in slots:
         drain(sl)
+
+
+def test_packed_event_entry_point_equals_the_16_byte_path(torch):
+    """mst_events_pack + mst_encode_batch_packed_async (8-byte wire records, widened on the device): infos and grids are
+    bit-identical to the MstEvent path, including songs with set_tempo / key_signature (their aux travels in other bytes),
+    every bundled golden song and a file written by the pipeline's loader."""
+    L = lib.load()
+    filt = abi.make_filter(synth.POPULAR, 0)
+    events, songs = synth.synth_corpus(4, seed=31, n_bars=10, n_tracks=6)
+    per = synth.split_songs(events, songs)
+    tpbs = [int(t) for t in songs['ticks_per_beat']]
+    for s in gu.load_songs('codec_bundled')[:6] + gu.load_songs('codec_synth'):
+        per.append(s['events'])
+        tpbs.append(int(s['ticks_per_beat']))
+    ev, sg = lib.make_songs(per, tpbs)
+    assert (ev['kind'] == abi.EV_SET_TEMPO).any()
+    infos, arena = lib.encode_songs(per, tpbs, filt)
+    packed = lib.events_pack(ev)
+    n = arena.numel()
+    wsb = L.mst_encode_packed_workspace_bytes(len(ev), len(sg), n)
+    ws = torch.empty(wsb, dtype=torch.uint8, device='cuda')
+    d_arena = torch.full((n,), -1.0, dtype=torch.float32, device='cuda')
+    h_packed = torch.from_numpy(packed.view(np.uint8).copy()).pin_memory()
+    h_songs = torch.from_numpy(sg.view(np.uint8).reshape(-1).copy()).pin_memory()
+    h_info = torch.zeros(len(sg) * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    st = torch.cuda.Stream()
+    lib.check(L.mst_encode_batch_packed_async(h_packed.data_ptr(), len(ev), h_songs.data_ptr(), len(sg), filt.reshape(1).ctypes.data,
+                                              h_info.data_ptr(), d_arena.data_ptr(), n, ws.data_ptr(), wsb, st.cuda_stream))
+    st.synchronize()
+    got = h_info.numpy().view(abi.SONG_INFO_DTYPE)
+    for k in ('status', 'n_pitched', 'n_unpitched', 'n_bars_out', 'pitched_offset', 'unpitched_offset', 'tonic', 'mode', 'tempo', 'bpm',
+              'key_signature', 'duration', 'n_notes'):
+        np.testing.assert_array_equal(got[k], infos[k], err_msg=k)
+    assert torch.equal(d_arena, arena)
