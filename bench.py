@@ -152,14 +152,33 @@ def run_decode(args, world, rank, torch, dist, L, lib, abi, batch, filt, arena):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     s_per_step = float(ms.item()) / 1e3 / args.steps
-    # e2e: results + messages read back to pinned host memory every step (the grids come from the model on device)
+    # e2e: results + messages read back to pinned host memory every step (the grids come from the model on device).  Two
+    # slots (stream + device / host result buffers + workspace): the D2H of step i overlaps the kernels of step i + 1, the
+    # host consumes step i - 1's results while step i runs
+    slots = [dict(stream=torch.cuda.Stream(), d_res=d_res, d_msgs=d_msgs, ws=ws, h_res=h_res, h_msgs=h_msgs),
+             dict(stream=torch.cuda.Stream(), d_res=torch.empty_like(d_res), d_msgs=torch.empty_like(d_msgs), ws=torch.empty_like(ws),
+                  h_res=torch.empty_like(h_res).pin_memory(), h_msgs=torch.empty_like(h_msgs).pin_memory())]
+    seen = [0]
+
+    def e2e_step(i):
+        sl = slots[i & 1]
+        with torch.cuda.stream(sl['stream']):
+            lib.check(L.mst_decode_batch_device(arena.data_ptr(), d_songs.data_ptr(), S, n_chunks, sl['d_msgs'].data_ptr(), cap,
+                                                sl['d_res'].data_ptr(), sl['ws'].data_ptr(), wsb, sl['stream'].cuda_stream))
+            sl['h_res'].copy_(sl['d_res'], non_blocking=True)
+            sl['h_msgs'].copy_(sl['d_msgs'], non_blocking=True)
+        if i > 0:
+            prev = slots[(i - 1) & 1]
+            prev['stream'].synchronize()
+            seen[0] += int(prev['h_res'].numpy().view(abi.DECODE_RESULT_DTYPE)['n_messages'].astype(np.int64).sum())
+
+    torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-        h_res.copy_(d_res, non_blocking=True)
-        h_msgs.copy_(d_msgs, non_blocking=True)
-        torch.cuda.synchronize()
+    for i in range(args.steps):
+        e2e_step(i)
+    slots[(args.steps - 1) & 1]['stream'].synchronize()
     e2e_s = (time.perf_counter() - t0) / args.steps
+    assert seen[0] == n_msgs * (args.steps - 1), 'decode e2e: message counts changed between steps'
     peak, peak_src = measured_peak_hbm()
     alg = grid_bytes + 12.0 * n_msgs
     return {

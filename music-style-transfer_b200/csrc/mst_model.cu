@@ -251,7 +251,9 @@ struct Launcher {
     bool bf16 = false;            // bf16 dense mode (MstModelShape.precision = MST_PRECISION_BF16)
     // development knobs: attribute the mode's error / time to its two halves
     // MST_BF16_MASK: which GEMM classes take the bf16 kernel (1 linear forward, 2 input gradient, 4 weight gradient,
-    // 8 LSTM input projection, 16 LSTM backward products).  Default 23: everything but the LSTM input projections - their
+    // 8 LSTM input projection, 16 LSTM backward products, 32 the input gradient towards the conv features: the conv weight
+    // gradient behind it is a near-cancelling sum over a few thousand occupied cells (|g| 1e-5 of the step's largest), where
+    // bf16 rounding of dY shows as 2-8 % of its norm; that GEMM is bound by its 456-wide output write in either mode).  Default 23: everything but the LSTM input projections - their
     // inputs carry the raw bpm / un-normalised features, and a 2^-9 rounding of those moves the gates of a 200-800 step
     // recurrence enough to push gradients 8 % off the fp32 oracle (tools/bf16_diag.py), against <= 1 % for all other classes
     int gemm_cls = 1;
@@ -410,7 +412,7 @@ struct Launcher {
     // dX[M,K] (+)= dY[M,N]·W[N,K]
     void linear_dx(const float *dY, long long ldy, const float *W, long long ldw, float *dX, long long ldx, int M, int N, int K, int accumulate) {
         const int keep = gemm_cls;
-        if (gemm_cls != 16) gemm_cls = 2;
+        if (gemm_cls != 16 && gemm_cls != 32) gemm_cls = 2;
         gemm(dY, ldy, 1, W, ldw, 1, dX, ldx, M, K, N, nullptr, 0, accumulate);
         gemm_cls = keep;
     }

@@ -402,7 +402,9 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         float *gWp = w.Z(64 * 514), *d_conv = w.A(Rb * 456), *gT = w.Z(700 * 57);
         L.linear_dw(d_x, 64, c.pce_conv, 456, gWp, 514, (int)Rb, 64, 456);
         if (!L.dry) { k_permute_cols<<<grid_for(64 * 514), 256, 0, L.st>>>(gWp, GRD(c, pce_lin_w), 64, 514, 1, 1, 1); L.check(); }
+        L.gemm_cls = 32;
         L.linear_dx(d_x, 64, c.wpcelin_p, 514, d_conv, 456, (int)Rb, 64, 456, 0);
+        L.gemm_cls = 1;
         L.act_grad(d_conv, c.pce_conv, d_conv, Rb * 456);
         L.colsum(d_conv, GRD(c, pce_conv_b), Rb * 8, 57);
         // gT[k][o] = sum over occupied cells of p[feat] * d_conv[row][oct][o]  (k = f * 70 + tap * 5 + feat)

