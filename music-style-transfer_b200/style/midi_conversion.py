@@ -101,10 +101,13 @@ class ChannelConverter:
         raise NotImplementedError('per-note conversion is fused into the batched kernels: use style.data.get_input / '
                                   'style.style_transfer.decode_midi')
 
-    channel2nchannel = nchannel2vchannel = vchannel2channel = vchannel2qchannel = qchannel2channel = _unsupported
+    channel2nchannel = nchannel2kchannel = kchannel2qchannel = qchannel2vchannel = nchannel2vchannel = _unsupported
+    vchannel2channel = vchannel2qchannel = qchannel2channel = _unsupported
 
 
 def get_keys_dist(info, nchannel):
     raise NotImplementedError('the key histogram is computed inside the encoder (k_scale); see MstSongInfo.keys_dist')
 
 
+def get_notes_dist(info, nchannel):
+    raise NotImplementedError('per-note statistics need the reference\'s Note lists, which the CUDA codec never builds')
