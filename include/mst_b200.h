@@ -440,6 +440,19 @@ size_t mst_model_loss_workspace_bytes(const MstModelShape *shape);
 int mst_model_loss(const MstModelShape *shape, const MstLossIn *in, float *d_losses, void *d_workspace,
                    size_t workspace_bytes, void *stream);
 
+/* mst_model_loss for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, results and
+ * error codes as mst_model_loss minus the workspace: the kernels' scratch (per-sample partial sums) is a file-scope
+ * `static __device__` array of MST_LOSS_NOALLOC_MAX_SAMPLES * 1024 + 4096 bytes (266 240 B) that every GPU loading the library
+ * holds until exit; its device address is resolved once per device (cudaGetSymbolAddress with that device current).
+ * Neither this call nor anything below it calls cudaMalloc / cudaFree or an allocating library routine.
+ * shape->n_samples outside 1..MST_LOSS_NOALLOC_MAX_SAMPLES returns MST_E_CAPACITY (use mst_model_loss then).
+ * All calls on a device share the one array (it keeps the previous call's contents; each call clears the sums it
+ * accumulates into, on `stream`): calls whose kernels may overlap on the GPU (different streams without an ordering
+ * between them) race on it and must be serialised by the caller. */
+#define MST_LOSS_NOALLOC_MAX_SAMPLES 256
+int mst_model_loss_noalloc(const MstModelShape *shape, const MstLossIn *in, float *d_losses, void *stream);
+
 /* torch.optim.Adam.step (train-model.py:89,152; defaults betas (.9,.999), eps 1e-8, no weight decay) on the flat
  * buffers, `step` = 1-based optimizer step count (bias correction), lr already scheduled by the caller
  * (StepLR(200, .9), :90,154).  grad_scale multiplies the gradient first (1 = the reference's summed gradients);

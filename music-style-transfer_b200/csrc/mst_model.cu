@@ -10,6 +10,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "mst_model_sparse.cuh"
@@ -1119,6 +1120,72 @@ extern "C" int mst_model_loss(const MstModelShape *shape, const MstLossIn *in, f
                in->pitched_pred, in->pitched_target, in->unpitched_pred, in->unpitched_target, in->instruments_logits,
                in->instruments_target, in->mode_logits, in->mode_target, in->bpm_pred, in->bpm_target, in->normalize, d_losses, false);
     if (L.err != cudaSuccess) { mst_set_error("mst_model_loss: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
+    return MST_OK;
+}
+
+// ---- mst_model_loss without any allocation by anybody: the scratch of the loss kernels (per-sample partial sums) lives in a
+// file-scope device array that every GPU loading the library holds until exit.  No counterpart in the reference; added
+// for callers that cannot allocate (graph capture, serving loops).
+constexpr size_t kLossNoAllocBytes = (size_t)MST_LOSS_NOALLOC_MAX_SAMPLES * 1024 + 4096;
+static __device__ __align__(256) unsigned char g_loss_noalloc_scratch[kLossNoAllocBytes];
+
+// The array's name is a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress, asked once per
+// device with that device current.
+static int loss_noalloc_scratch(void **out) {
+    static void *ptr[64] = {};
+    static std::mutex mu;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { mst_set_error("mst_model_loss_noalloc: cudaGetDevice: %s", cudaGetErrorString(e)); return MST_E_CUDA; }
+    if (dev < 0 || dev >= 64) { mst_set_error("mst_model_loss_noalloc: device ordinal %d out of range", dev); return MST_E_INVALID; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_loss_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            mst_set_error("mst_model_loss_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return MST_E_CUDA;
+        }
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return MST_OK;
+}
+
+extern "C" int mst_model_loss_noalloc(const MstModelShape *shape, const MstLossIn *in, float *d_losses, void *stream) {
+    if (!shape || !in || !d_losses || !in->pitched_pred || !in->pitched_target || !in->instruments_logits ||
+        !in->instruments_target || !in->mode_logits || !in->mode_target || !in->bpm_pred || !in->bpm_target) {
+        mst_set_error("mst_model_loss_noalloc: null pointer argument");
+        return MST_E_INVALID;
+    }
+    if (shape->n_samples < 1 || shape->n_samples > MST_LOSS_NOALLOC_MAX_SAMPLES) {
+        mst_set_error("mst_model_loss_noalloc: n_samples = %d is outside 1..%d (MST_LOSS_NOALLOC_MAX_SAMPLES: the static scratch holds "
+                      "%zu bytes); use mst_model_loss with a caller workspace for larger batches", shape->n_samples,
+                      MST_LOSS_NOALLOC_MAX_SAMPLES, kLossNoAllocBytes);
+        return MST_E_CAPACITY;
+    }
+    if (mst_device_count() <= 0) { mst_set_error("mst_model_loss_noalloc: no CUDA device"); return MST_E_NO_DEVICE; }
+    void *scratch = nullptr;
+    const int rc = loss_noalloc_scratch(&scratch);
+    if (rc != MST_OK) return rc;
+    const int N = shape->n_samples, U = (in->unpitched_pred && in->unpitched_target) ? 1 : 0;
+    const long long cells_p = (long long)shape->n_channels * shape->n_bars * shape->n_beats * 560, cells_u = (long long)shape->n_bars * shape->n_beats * 470;
+    {   // planning pass: what run_losses carves must fit the static array
+        Arena plan{nullptr, 0, true};
+        Launcher P; P.dry = true;
+        run_losses(P, plan, N, U, cells_p, cells_u, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, false);
+        if (plan.off > kLossNoAllocBytes) {
+            mst_set_error("mst_model_loss_noalloc: internal: scratch carve %zu > %zu", plan.off, kLossNoAllocBytes);
+            return MST_E_CAPACITY;
+        }
+    }
+    Arena ar{(char *)scratch, 0, false};
+    Launcher L; L.st = (cudaStream_t)stream;
+    // run_losses clears the partial sums it accumulates into (the array keeps the previous call's contents)
+    run_losses(L, ar, N, U, cells_p, cells_u,
+               in->pitched_pred, in->pitched_target, in->unpitched_pred, in->unpitched_target, in->instruments_logits,
+               in->instruments_target, in->mode_logits, in->mode_target, in->bpm_pred, in->bpm_target, in->normalize, d_losses, false);
+    if (L.err != cudaSuccess) { mst_set_error("mst_model_loss_noalloc: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     return MST_OK;
 }
 

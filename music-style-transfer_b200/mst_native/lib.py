@@ -26,7 +26,7 @@ EXPORTS = [
     'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write', 'mst_transfer_select',
     'mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
     'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply', 'mst_model_song_info', 'mst_model_backward', 'mst_model_loss_workspace_bytes',
-    'mst_model_loss', 'mst_adam_step', 'mst_model_gemm',
+    'mst_model_loss', 'mst_model_loss_noalloc', 'mst_adam_step', 'mst_model_gemm',
 ]
 
 

@@ -43,7 +43,7 @@ EXPORTS = ['mst_model_param_count', 'mst_model_param_name', 'mst_model_param_num
            'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply',
            'mst_model_song_info', 'mst_model_backward',
            'mst_model_loss_workspace_bytes',
-           'mst_model_loss', 'mst_adam_step', 'mst_model_gemm']
+           'mst_model_loss', 'mst_model_loss_noalloc', 'mst_adam_step', 'mst_model_gemm']
 
 N_LOSS_LEAVES = 16
 # index of every leaf of get_total_loss's nested dict in the (N, 16) loss buffer (include/mst_b200.h MST_LOSS_*)
@@ -95,6 +95,8 @@ def _L():
         L.mst_model_loss.restype = ctypes.c_int
         L.mst_model_loss.argtypes = [ctypes.POINTER(ModelShape), ctypes.POINTER(LossIn), ctypes.c_void_p, ctypes.c_void_p,
                                      ctypes.c_size_t, ctypes.c_void_p]
+        L.mst_model_loss_noalloc.restype = ctypes.c_int
+        L.mst_model_loss_noalloc.argtypes = [ctypes.POINTER(ModelShape), ctypes.POINTER(LossIn), ctypes.c_void_p, ctypes.c_void_p]
         L.mst_adam_step.restype = ctypes.c_int
         L.mst_adam_step.argtypes = [ctypes.c_void_p] * 4 + [ctypes.c_longlong, ctypes.c_int] + [ctypes.c_float] * 5 + [
             ctypes.c_int, ctypes.c_void_p]
@@ -369,6 +371,32 @@ def total_loss(pitched_pred, pitched_target, unpitched_pred, unpitched_target, i
     out = torch.empty(int(N), N_LOSS_LEAVES, dtype=torch.float32, device=pitched_pred.device)
     _lib.check(_L().mst_model_loss(ctypes.byref(shape), ctypes.byref(li), out.data_ptr(), ws.data_ptr(), wsb,
                                    torch.cuda.current_stream(pitched_pred.device).cuda_stream))
+    return out
+
+
+LOSS_NOALLOC_MAX_SAMPLES = 256          # MST_LOSS_NOALLOC_MAX_SAMPLES
+
+
+def total_loss_noalloc(out, pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits,
+                       instruments_target, mode_logits, mode_target, bpm_pred, bpm_target, normalize=False, stream=None):
+    """`total_loss` through mst_model_loss_noalloc: nothing is allocated on the device, by the library or by this wrapper (the
+    kernels' scratch is a static device array inside the library, at most LOSS_NOALLOC_MAX_SAMPLES samples).  Every tensor,
+    including the (N, 16) float32 output `out`, is the caller's and must already be contiguous float32 on one device; calls
+    share the scratch, so issue them on one stream (or order them).  No counterpart in the reference."""
+    import torch
+    _lib.require_gpu()
+    tensors = (pitched_pred, pitched_target, unpitched_pred, unpitched_target, instruments_logits, instruments_target,
+               mode_logits, mode_target, bpm_pred, bpm_target)
+    for t in tensors + (out,):
+        if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise ValueError('total_loss_noalloc takes contiguous float32 CUDA tensors (it does not copy or cast)')
+    N, C, B, nb = pitched_pred.shape[:4]
+    if tuple(out.shape) != (int(N), N_LOSS_LEAVES):
+        raise ValueError(f'out must be ({int(N)}, {N_LOSS_LEAVES})')
+    shape = ModelShape(int(N), int(C), int(B), int(nb), int(unpitched_pred is not None), 0)
+    li = LossIn(*[None if t is None else t.data_ptr() for t in tensors], int(bool(normalize)), 0)
+    st = torch.cuda.current_stream(out.device) if stream is None else stream
+    _lib.check(_L().mst_model_loss_noalloc(ctypes.byref(shape), ctypes.byref(li), out.data_ptr(), st.cuda_stream))
     return out
 
 
