@@ -932,7 +932,11 @@ def main():
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
     barrier()
     t_load1 = time.time()
+    e2e_per_rank = [float(e2e_s.item())]
     if world > 1:
+        each = [torch.zeros_like(e2e_s) for _ in range(world)]
+        dist.all_gather(each, e2e_s)
+        e2e_per_rank = [float(t.item()) for t in each]
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_total = torch.tensor([float(e2e_bars[0])], dtype=torch.float64, device='cuda')
     if world > 1:
@@ -941,6 +945,8 @@ def main():
     e2e = {'value': e2e_value, 'unit': UNIT,
            'h2d_bytes_per_step': int(statistics.mean(n_ev) * 8 + args.batch * 16),
            'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
+           'ms_per_step_per_rank': [round(t / args.steps * 1e3, 3) for t in e2e_per_rank],
+           'h2d_GBps_per_rank': [round((statistics.mean(n_ev) * 8 + args.batch * 16) * args.steps / t / 1e9, 2) for t in e2e_per_rank],
            'note': 'mst_encode_batch_packed_async (8-byte event records) on three rotating slots (H2D of batch i+1, i+2 overlaps the kernels of '
                    'batch i); grids stay in HBM for the training consumer (SURVEY.md 8(b)); infos are read back and '
                    'consumed every step'}

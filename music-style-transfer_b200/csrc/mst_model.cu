@@ -245,8 +245,41 @@ inline int grid_for(long long n, int threads = 256, int cap = 148 * 16) {
     return (int)std::max<long long>(1, std::min<long long>(b, cap));
 }
 
+// Side streams of one caller stream.  Independent branches of the model (the two channel encoders, the rhythm / melody / style
+// encoders, the two style appliers and their backward passes) run on them concurrently: the sequential recurrences keep a
+// handful of SMs busy for hundreds of microseconds, and at N = 1 every kernel is that small.  Branches are forked from and
+// joined back to the caller's stream with events, so at return all work is ordered on the caller's stream as before, and a
+// CUDA graph capture of the call records the branches as parallel graph nodes.  One set per (device, caller stream): two
+// callers on different streams never share side streams (a capture on one must not swallow the other's launches).
+// MST_MODEL_STREAMS=0 keeps everything on the caller's stream.
+constexpr int kSideStreams = 3, kSideEvents = 32;
+constexpr int kBranchLeaf = 2;       // weight-gradient GEMMs and bias column sums of the backward pass: nothing downstream reads them
+struct StreamSet {
+    cudaStream_t s[kSideStreams];
+    cudaEvent_t ev[kSideEvents];
+    int next_ev = 0;
+};
+static StreamSet *stream_set_for(cudaStream_t main_st, cudaError_t *err) {
+    static std::mutex mu;
+    static std::vector<std::pair<std::pair<int, cudaStream_t>, StreamSet *>> sets;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { *err = e; return nullptr; }
+    std::lock_guard<std::mutex> lock(mu);
+    for (auto &kv : sets) if (kv.first.first == dev && kv.first.second == main_st) return kv.second;
+    StreamSet *ss = new StreamSet();
+    for (int i = 0; i < kSideStreams && e == cudaSuccess; i++) e = cudaStreamCreateWithFlags(&ss->s[i], cudaStreamNonBlocking);
+    for (int i = 0; i < kSideEvents && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&ss->ev[i], cudaEventDisableTiming);
+    if (e != cudaSuccess) { *err = e; delete ss; return nullptr; }
+    sets.push_back({{dev, main_st}, ss});
+    return ss;
+}
+
 struct Launcher {
-    cudaStream_t st;
+    cudaStream_t st;              // the stream launches go to: the caller's, or a side stream between on(k) and on(-1)
+    cudaStream_t main_st = nullptr;
+    StreamSet *ss = nullptr;      // null: no concurrency, every branch runs on the caller's stream in program order
+    unsigned forked = 0;          // side streams that hold work not yet joined into the caller's stream
     int launches = 0;
     bool dry = false;             // planning pass: carve the arena, launch nothing
     bool bf16 = false;            // bf16 dense mode (MstModelShape.precision = MST_PRECISION_BF16)
@@ -269,6 +302,41 @@ struct Launcher {
     bool psa_fwd_tc() const { return bf16 && getenv("MST_PSA_FWD_TC") != nullptr; }
     bool psa_bwd_tc() const { return bf16 && getenv("MST_PSA_BWD_TC") != nullptr; }
     cudaError_t err = cudaSuccess;
+    // ---- branches.  begin(stream): call once per entry point.  wait(k, on): branch k continues only after everything queued
+    // so far on branch `on` (-1 = the caller's stream).  on(k): the launches that follow go to branch k.  join_all(): the
+    // caller's stream waits for every branch (every entry point ends with it; a capture would fail on unjoined work).
+    void begin(void *stream) {
+        st = main_st = (cudaStream_t)stream;
+        static const bool off = getenv("MST_MODEL_STREAMS") && atoi(getenv("MST_MODEL_STREAMS")) == 0;
+        if (!dry && !off) ss = stream_set_for(main_st, &err);
+    }
+    cudaStream_t stream_of(int k) const { return k < 0 ? main_st : ss->s[k]; }
+    void wait(int k, int on_k) {
+        if (!ss || dry || k == on_k) return;
+        if (on_k >= 0 && !(forked & (1u << on_k))) return;      // nothing pending there (and, under capture, not part of it)
+        cudaEvent_t ev = ss->ev[ss->next_ev];
+        ss->next_ev = (ss->next_ev + 1) % kSideEvents;
+        cudaError_t e = cudaEventRecord(ev, stream_of(on_k));
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(stream_of(k), ev, 0);
+        if (e != cudaSuccess && err == cudaSuccess) err = e;
+        if (k >= 0) forked |= 1u << k;
+        if (k < 0 && on_k >= 0) forked &= ~(1u << on_k);
+    }
+    int cur = -1;                 // the branch launches currently go to
+    void on(int k) { if (ss && !dry) { st = stream_of(k); cur = k; } }
+    // run f's launches on the leaf branch, after what is queued on the current one (the gradient they read is ready there)
+    template <class F> void leaf(F f) {
+        if (!ss || dry) { f(); return; }
+        const int back = cur;
+        wait(kBranchLeaf, back); on(kBranchLeaf);
+        f();
+        on(back);
+    }
+    void join_all() {
+        if (!ss || dry) return;
+        on(-1);
+        for (int k = 0; k < kSideStreams; k++) if (forked & (1u << k)) wait(-1, k);
+    }
     void check() { cudaError_t e = cudaGetLastError(); if (e != cudaSuccess && err == cudaSuccess) err = e; launches++; }
 
     // C[M,N] (op)= act(A·B + bias) with explicit strides
@@ -669,20 +737,23 @@ void prep_lstm(Launcher &L, const Ctx &c, LstmBuf &lb, ParamId whh, ParamId bih,
     k_transpose<<<grid_for(4 * lb.H * lb.H), 256, 0, L.st>>>(PRM(c, whh), lb.wt, 4 * lb.H, lb.H); L.check();
 }
 
-void prep_weights(Launcher &L, Ctx &c) {
+// weight preparation, split by the branch that needs it first (forward_extract)
+void prep_weights_main(Launcher &L, Ctx &c) {
     k_permute_cols<<<grid_for(57 * 700), 256, 0, L.st>>>(PRM(c, pce_conv_w), c.wconv_p, 57, 700, 0, 0, 0); L.check();
     k_permute_cols<<<grid_for(64 * 514), 256, 0, L.st>>>(PRM(c, pce_lin_w), c.wpcelin_p, 64, 514, 1, 0, 0); L.check();
     k_transpose<<<grid_for(57 * 700), 256, 0, L.st>>>(c.wconv_p, c.wconv_t, 57, 700); L.check();
     k_transpose<<<grid_for(16 * 280), 256, 0, L.st>>>(PRM(c, pre_ch_w), c.wprech_t, 16, 280); L.check();
+}
+void prep_weights_uce(Launcher &L, Ctx &c) {
+    k_permute_cols<<<grid_for(64 * 940), 256, 0, L.st>>>(PRM(c, uce_lin_w), c.wucelin_p, 64, 940, 2, 0, 0); L.check();
+    prep_lstm(L, c, c.uce_bl, uce_bl_whh, uce_bl_bih, uce_bl_bhh);
+    prep_lstm(L, c, c.uce_brf, uce_br_whh, uce_br_bih, uce_br_bhh);
+    prep_lstm(L, c, c.uce_brr, uce_br_whh_r, uce_br_bih_r, uce_br_bhh_r);
+}
+void prep_weights_lstm(Launcher &L, Ctx &c) {
     prep_lstm(L, c, c.pce_bl, pce_bl_whh, pce_bl_bih, pce_bl_bhh);
     prep_lstm(L, c, c.pce_brf, pce_br_whh, pce_br_bih, pce_br_bhh);
     prep_lstm(L, c, c.pce_brr, pce_br_whh_r, pce_br_bih_r, pce_br_bhh_r);
-    if (c.U) {
-        k_permute_cols<<<grid_for(64 * 940), 256, 0, L.st>>>(PRM(c, uce_lin_w), c.wucelin_p, 64, 940, 2, 0, 0); L.check();
-        prep_lstm(L, c, c.uce_bl, uce_bl_whh, uce_bl_bih, uce_bl_bhh);
-        prep_lstm(L, c, c.uce_brf, uce_br_whh, uce_br_bih, uce_br_bhh);
-        prep_lstm(L, c, c.uce_brr, uce_br_whh_r, uce_br_bih_r, uce_br_bhh_r);
-    }
     prep_lstm(L, c, c.se_l, se_lstm_whh, se_lstm_bih, se_lstm_bhh);
     prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
     prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
@@ -745,7 +816,27 @@ MeArgs2 me_args(const Ctx &c) {
 void forward_extract(Launcher &L, Ctx &c) {
     const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
     const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb;
-    prep_weights(L, c);
+    // Branches (Launcher::wait / on): 1 = the LSTM weight preparations, needed by the caller's stream at its first recurrence;
+    // 0 = the UnpitchedChannelsEncoder up to its bars input (model.py:128-138), independent of the pitched chain.  Both start
+    // after whatever the caller queued before this call (the previous optimiser step).
+    LstmArgs bar_jobs[4];
+    int n_bar_jobs = 2;
+    L.wait(1, -1); L.on(1);
+    prep_weights_lstm(L, c);
+    if (c.U) {
+        L.wait(0, -1); L.on(0);
+        prep_weights_uce(L, c);
+        L.linear(c.Ug, 940, c.wucelin_p, 940, PRM(c, uce_lin_b), c.uce_lin, 64, (int)(Nb * T), 64, 940, 1);
+        lstm_forward(L, c, c.uce_bl, c.uce_lin, uce_bl_wih, c.uce_beats, 64, 0, 0);
+        L.take_last(c.uce_beats, c.uce_last, Nb, T, 64);
+        { CombineArgs a{}; a.x = c.uce_last; a.M = (long long)B * 64; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
+          a.ss = c.uce_ss; a.out = c.uce_bars_in; L.combine_fwd(a); }
+        bar_jobs[2] = lstm_project(L, c, c.uce_brf, c.uce_bars_in, uce_br_wih, c.uce_bars, 128, 0, 0);
+        bar_jobs[3] = lstm_project(L, c, c.uce_brr, c.uce_bars_in, uce_br_wih_r, c.uce_bars, 128, 64, 1);
+        n_bar_jobs = 4;
+    }
+    L.on(-1);
+    prep_weights_main(L, c);
     // ---------------- occupied cells of the piano roll, CSR by beat row (mst_model_sparse.cuh)
     {
         const int g = (int)std::min<long long>((Rb + 7) / 8, 148 * 8);
@@ -766,28 +857,21 @@ void forward_extract(Launcher &L, Ctx &c) {
         L.linear(c.pce_conv, 456, c.wpcelin_p, 514, nullptr, c.pce_zc, 64, (int)Rb, 64, 456, 0);
     }
     bcast_fwd(L, Dims5{N, C, B, T, 1}, 64, PRM(c, pce_lin_b), c.pce_x, 1, {{c.pce_zc, M_N | M_C | M_B | M_T}, {c.pce_zi, M_N | M_C}});
+    L.wait(-1, 1);                                   // LSTM weights ready
     lstm_forward(L, c, c.pce_bl, c.pce_x, pce_bl_wih, c.pce_beats, 64, 0, 0);
     L.take_last(c.pce_beats, c.pce_last, (long long)NC * B, T, 64);
     { CombineArgs a{}; a.x = c.pce_last; a.n_stride = (long long)C * B * 64; a.k_stride = (long long)B * 64; a.N = N; a.K = C; a.M = (long long)B * 64;
       a.ss = c.pce_ss; a.out = c.pce_bars_in; L.combine_fwd(a); }
     // the bar-axis BiLSTMs of both channel encoders are independent serial recurrences: one joint launch
-    {
-        LstmArgs jobs[4];
-        int nj = 0;
-        jobs[nj++] = lstm_project(L, c, c.pce_brf, c.pce_bars_in, pce_br_wih, c.pce_bars, 128, 0, 0);
-        jobs[nj++] = lstm_project(L, c, c.pce_brr, c.pce_bars_in, pce_br_wih_r, c.pce_bars, 128, 64, 1);
-        if (c.U) {
-            // ---------------- UnpitchedChannelsEncoder up to its bars input (model.py:128-138)
-            L.linear(c.Ug, 940, c.wucelin_p, 940, PRM(c, uce_lin_b), c.uce_lin, 64, (int)(Nb * T), 64, 940, 1);
-            lstm_forward(L, c, c.uce_bl, c.uce_lin, uce_bl_wih, c.uce_beats, 64, 0, 0);
-            L.take_last(c.uce_beats, c.uce_last, Nb, T, 64);
-            { CombineArgs a{}; a.x = c.uce_last; a.M = (long long)B * 64; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
-              a.ss = c.uce_ss; a.out = c.uce_bars_in; L.combine_fwd(a); }
-            jobs[nj++] = lstm_project(L, c, c.uce_brf, c.uce_bars_in, uce_br_wih, c.uce_bars, 128, 0, 0);
-            jobs[nj++] = lstm_project(L, c, c.uce_brr, c.uce_bars_in, uce_br_wih_r, c.uce_bars, 128, 64, 1);
-        }
-        L.lstm_multi(jobs, nj, false);
-    }
+    bar_jobs[0] = lstm_project(L, c, c.pce_brf, c.pce_bars_in, pce_br_wih, c.pce_bars, 128, 0, 0);
+    bar_jobs[1] = lstm_project(L, c, c.pce_brr, c.pce_bars_in, pce_br_wih_r, c.pce_bars, 128, 64, 1);
+    L.wait(-1, 0);                                   // the unpitched encoder's bars input
+    L.lstm_multi(bar_jobs, n_bar_jobs, false);
+    // From here three independent branches: 0 = both rhythm encoders and their combine (then the SongInfoModel recurrences,
+    // forward_song_info), 1 = MelodyEncoder, caller's stream = combine of the bars + StyleEncoder (its 192-wide recurrence
+    // over the bars is the longest serial kernel of the forward pass).
+    L.wait(0, -1); L.wait(1, -1);
+    L.on(0);
     // ---------------- PitchedRhythmEncoder (model.py:346-381)
     const float *plw = PRM(c, pre_lin_w);
     L.linear(c.pce_beats, 64, PRM(c, pre_bl_w), 64, PRM(c, pre_bl_b), c.pre_a1, 48, (int)Rb, 48, 64, 1);
@@ -823,14 +907,19 @@ void forward_extract(Launcher &L, Ctx &c) {
                   {{c.ure_z[0], M_N | M_B | M_T}, {c.ure_z[1], M_N | M_B}, {c.ure_z[2], M_N | M_B | M_T | M_F}, {c.ure_z[3], M_N}});
         { CombineArgs a{}; a.x = c.ure_x; a.M = (long long)B * T * 320; a.n_stride = a.M; a.k_stride = a.M; a.N = N; a.K = 1;
           a.ss = c.ure_ss; a.out = c.ure_out; L.combine_fwd(a); }
-        // ---------------- combine(pitched, unpitched) for bars and rhythm (model.py:766-767)
-        k_pair_pack<<<grid_for(Nb * 128), 256, 0, L.st>>>(c.pce_bars, c.uce_bars, c.bars_pair, N, (long long)B * 128); L.check();
-        { CombineArgs a{}; a.x = c.bars_pair; a.M = (long long)B * 128; a.n_stride = 2 * a.M; a.k_stride = a.M; a.N = N; a.K = 2;
-          a.ss = c.bars_ss; a.out = c.bars_c; L.combine_fwd(a); }
+        // ---------------- combine(pitched, unpitched) for the rhythm (model.py:767)
         k_pair_pack<<<grid_for(Rbf * 32), 256, 0, L.st>>>(c.pre_out, c.ure_out, c.rh_pair, N, (long long)B * T * 320); L.check();
         { CombineArgs a{}; a.x = c.rh_pair; a.M = (long long)B * T * 320; a.n_stride = 2 * a.M; a.k_stride = a.M; a.N = N; a.K = 2;
           a.ss = c.rh_ss; a.out = c.rh_c; L.combine_fwd(a); }
-        c.bars = c.bars_c; c.rhythm = c.rh_c;
+        c.rhythm = c.rh_c;
+    }
+    L.on(-1);
+    if (c.U) {
+        // ---------------- combine(pitched, unpitched) for the bars (model.py:766)
+        k_pair_pack<<<grid_for(Nb * 128), 256, 0, L.st>>>(c.pce_bars, c.uce_bars, c.bars_pair, N, (long long)B * 128); L.check();
+        { CombineArgs a{}; a.x = c.bars_pair; a.M = (long long)B * 128; a.n_stride = 2 * a.M; a.k_stride = a.M; a.N = N; a.K = 2;
+          a.ss = c.bars_ss; a.out = c.bars_c; L.combine_fwd(a); }
+        c.bars = c.bars_c;
     }
     // ---------------- StyleEncoder (model.py:179-200)
     lstm_forward(L, c, c.se_l, c.bars, se_lstm_wih, c.se_h, 192, 0, 0);
@@ -848,6 +937,7 @@ void forward_extract(Launcher &L, Ctx &c) {
     { CombineArgs a{}; a.x = c.se_x; a.M = 256; a.n_stride = (long long)C * 256; a.k_stride = 256; a.N = N; a.K = C;
       a.ss = c.se_ss; a.out = c.style; L.combine_fwd(a); }
     // ---------------- MelodyEncoder (model.py:252-297); octave+degree weights act as one (120, 112) matrix
+    L.on(1);
     const float *mow = PRM(c, me_oct_w);
     L.linear(c.pce_beats, 64, PRM(c, me_bl_w), 64, PRM(c, me_bl_b), c.me_a1, 36, (int)Rb, 36, 64, 1);
     L.linear(c.pce_bars, 128, PRM(c, me_br_w), 128, PRM(c, me_br_b), c.me_a2, 68, (int)Nb, 68, 128, 1);
@@ -864,14 +954,23 @@ void forward_extract(Launcher &L, Ctx &c) {
         k_me_sumsq2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
         k_me_fwd2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
     }
+    L.on(-1);
+    // returns with branch 0 (rhythm) and branch 1 (melody) still running: forward_song_info / forward_apply wait where they
+    // consume them, the entry points end with join_all()
 }
 
 void forward_song_info(Launcher &L, Ctx &c) {   // SongInfoModel (model.py:513-562)
     const int N = c.N, B = c.B, T = c.T;
+    // the two recurrences read the rhythm only: they follow the rhythm encoders on branch 0 while the caller's stream is still
+    // in the StyleEncoder (standalone use, mst_model_song_info / _predict_apply: the branch starts from the caller's stream)
+    if (!(L.forked & 1u)) L.wait(0, -1);
+    L.on(0);
     lstm_forward(L, c, c.sim_l1, c.rhythm, sim_bl_wih, c.sim_h1, 9, 0, 0);
     L.take_last(c.sim_h1, c.sim_last1, c.Nb, T, 9);
     lstm_forward(L, c, c.sim_l2, c.sim_last1, sim_br_wih, c.sim_h2, 8, 0, 0);
     L.take_last(c.sim_h2, c.sim_rf, N, B, 8);
+    L.on(-1);
+    L.wait(-1, 0);                                   // the heads read the style (caller's stream) and sim_rf (branch 0)
     auto head = [&](ParamId sw, ParamId sb, int ks, float *sa, ParamId rw, ParamId rb, int kr, float *ra, ParamId fw, ParamId fb, int nout, float *out) {
         L.linear(c.style, 256, PRM(c, sw), 256, PRM(c, sb), sa, ks, N, ks, 256, 1);
         L.linear(c.sim_rf, 8, PRM(c, rw), 8, PRM(c, rb), ra, kr, N, kr, 8, 1);
@@ -897,6 +996,23 @@ void load_psa_constants(Launcher &L, const Ctx &c) {
 void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
     const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C;
     const long long Rbf = c.Rbf;
+    // style, rhythm (branch 0 unless forward_song_info joined it) and melody (branch 1) meet here; the two appliers are
+    // independent of each other: the unpitched one runs on branch 0
+    if (L.forked & 1u) L.wait(-1, 0);
+    if (unpitched) {
+        // ---------------- UnpitchedStyleApplier (model.py:703-724)
+        L.wait(0, -1); L.on(0);
+        const float *nw = PRM(c, usa_nl_w);
+        L.linear(c.style, 256, PRM(c, usa_sl_w), 256, PRM(c, usa_sl_b), c.usa_s650, 650, N, 650, 256, 1);
+        L.linear(c.rhythm, 32, PRM(c, usa_rl_w), 32, PRM(c, usa_rl_b), c.usa_r17, 17, (int)Rbf, 17, 32, 1);
+        L.linear(c.usa_s650, 65, nw + 0, 82, nullptr, c.usa_zs, 376, N * 10, 376, 65, 0);
+        L.linear(c.usa_r17, 17, nw + 65, 82, nullptr, c.usa_zr, 376, (int)Rbf, 376, 17, 0);
+        UsaArgs a{};
+        a.bias = PRM(c, usa_nl_b); a.Wl = PRM(c, usa_lin_w); a.bl = PRM(c, usa_lin_b); a.Zr = c.usa_zr; a.Zs = c.usa_zs;
+        a.H = c.usa_h; a.out = c.usa_out; a.N = N; a.B = B; a.T = T;
+        k_usa_fwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
+        L.on(-1);
+    }
     // ---------------- PitchedStyleApplier (model.py:624-675); octave+degree weights = one (450, 88) matrix
     const float *pow_ = PRM(c, psa_oct_w);
     L.linear(c.style, 256, PRM(c, psa_sl_w), 256, PRM(c, psa_sl_b), c.psa_s66, 66, N, 66, 256, 1);
@@ -908,6 +1024,7 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
     {
         load_psa_constants(L, c);
         k_psa_zci<<<grid_for((long long)NC * 450), 256, 0, L.st>>>(PRM(c, psa_oct_b), c.psa_zi, c.psa_zs, c.psa_zci, N, C); L.check();
+        if (L.forked & 2u) L.wait(-1, 1);            // the melody
         PsaArgs2 a{c.psa_zr, c.psa_zci, c.melody, c.psa_out, N, C, B, T};
         if (L.psa_fwd_tc() && !L.dry) {
             // bf16 dense mode: the 5 x 50 contraction per note row as tcgen05 tiles (mst_model_psa_tc.cuh)
@@ -919,18 +1036,7 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
             k_psa_fwd3<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
         }
     }
-    if (unpitched) {
-        // ---------------- UnpitchedStyleApplier (model.py:703-724)
-        const float *nw = PRM(c, usa_nl_w);
-        L.linear(c.style, 256, PRM(c, usa_sl_w), 256, PRM(c, usa_sl_b), c.usa_s650, 650, N, 650, 256, 1);
-        L.linear(c.rhythm, 32, PRM(c, usa_rl_w), 32, PRM(c, usa_rl_b), c.usa_r17, 17, (int)Rbf, 17, 32, 1);
-        L.linear(c.usa_s650, 65, nw + 0, 82, nullptr, c.usa_zs, 376, N * 10, 376, 65, 0);
-        L.linear(c.usa_r17, 17, nw + 65, 82, nullptr, c.usa_zr, 376, (int)Rbf, 376, 17, 0);
-        UsaArgs a{};
-        a.bias = PRM(c, usa_nl_b); a.Wl = PRM(c, usa_lin_w); a.bl = PRM(c, usa_lin_b); a.Zr = c.usa_zr; a.Zs = c.usa_zs;
-        a.H = c.usa_h; a.out = c.usa_out; a.N = N; a.B = B; a.T = T;
-        k_usa_fwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
-    }
+    if (unpitched) L.wait(-1, 0);
 }
 
 }  // namespace
@@ -984,10 +1090,11 @@ extern "C" int mst_model_forward(const float *d_params, const MstModelShape *sha
     int rc = setup_ctx(c, shape, d_workspace, workspace_bytes, training != 0, false);
     if (rc) return rc;
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params;
-    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
+    Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
     forward_extract(L, c);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);
+    L.join_all();
     if (L.err != cudaSuccess) { mst_set_error("mst_model_forward: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     fill_outputs(c, outputs);
     if (n_launches) *n_launches = L.launches;
@@ -1016,12 +1123,13 @@ extern "C" int mst_model_train_step(const float *d_params, float *d_grads, const
     Arena ar{(char *)d_workspace, 0, false};
     plan_forward(c, ar);
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
-    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
+    Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
     forward_extract(L, c);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);
     TrainIn ti{d_instruments_target, d_bpm_target, normalize, d_losses};
     backward(L, c, ar, ti);
+    L.join_all();
     if (L.err != cudaSuccess) { mst_set_error("mst_model_train_step: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     if (outputs) fill_outputs(c, outputs);
     if (n_launches) *n_launches = L.launches;
@@ -1040,11 +1148,12 @@ extern "C" int mst_model_predict_apply(const float *d_params, const MstModelShap
     if (rc) return rc;
     c.F = d_features; c.prm = d_params;
     c.style = (float *)d_style; c.melody = (float *)d_melody; c.rhythm = d_rhythm;   // read only on this path
-    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
+    Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
     prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
     prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);
+    L.join_all();
     if (L.err != cudaSuccess) { mst_set_error("mst_model_predict_apply: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     fill_outputs(c, outputs);
     if (n_launches) *n_launches = L.launches;
@@ -1062,10 +1171,11 @@ extern "C" int mst_model_song_info(const float *d_params, const MstModelShape *s
     if (rc) return rc;
     c.prm = d_params;
     c.style = (float *)d_style; c.rhythm = d_rhythm;                                   // read only on this path
-    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
+    Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
     prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
     prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
     forward_song_info(L, c);
+    L.join_all();
     if (L.err != cudaSuccess) { mst_set_error("mst_model_song_info: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     memset(outputs, 0, sizeof(*outputs));
     outputs->instruments = c.sim_instr; outputs->mode = c.sim_mode; outputs->bpm = c.sim_bpm;
@@ -1093,9 +1203,10 @@ extern "C" int mst_model_backward(const float *d_params, float *d_grads, const M
     plan_forward(c, ar);
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
     c.bars = c.U ? c.bars_c : c.pce_bars; c.rhythm = c.U ? c.rh_c : c.pre_out;     // as forward_extract left them
-    Launcher L; L.st = (cudaStream_t)stream; L.bf16 = shape->precision == MST_PRECISION_BF16;
+    Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
     TrainIn ti{d_instruments_target, d_bpm_target, normalize, d_losses};
     backward(L, c, ar, ti);
+    L.join_all();
     if (L.err != cudaSuccess) { mst_set_error("mst_model_backward: %s", cudaGetErrorString(L.err)); return MST_E_CUDA; }
     if (n_launches) *n_launches = L.launches;
     return MST_OK;

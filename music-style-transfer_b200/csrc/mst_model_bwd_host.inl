@@ -15,10 +15,24 @@ struct TrainIn {
 
 struct Bwd {
     Launcher &L; Ctx &c; Arena &ar;
+    Arena &zar;                               // region of the buffers that must start at zero (see Z)
     float *tmpA = nullptr, *tmpB = nullptr;   // ping-pong scratch of the staged reductions
 
+    // Buffers that must start at zero come from a region of their own (zar), cleared by ONE launch before the pass starts
+    // instead of one fill per buffer on the critical chain.
     float *A(long long n) { return ar.take(n); }
-    float *Z(long long n) { float *p = ar.take(n); L.fill(p, n, 0.f); return p; }
+    float *Z(long long n) { return zar.take(n); }
+    // weight gradients / bias column sums straight into the flat gradient buffer: leaf work, off the dX chain (Launcher::leaf).
+    // leaf_dw = false where another kernel of the caller's stream accumulates into the same parameter.
+    bool leaf_dw = true;
+    void dw(const float *dY, long long ldy, const float *X, long long ldx, float *gW, long long ldw, int M, int Nout, int K) {
+        if (leaf_dw) L.leaf([&] { L.linear_dw(dY, ldy, X, ldx, gW, ldw, M, Nout, K); });
+        else L.linear_dw(dY, ldy, X, ldx, gW, ldw, M, Nout, K);
+    }
+    void bias_grad(const float *dY, float *gb, long long rows, int cols, float *gb2 = nullptr) {
+        if (leaf_dw) L.leaf([&] { L.colsum(dY, gb, rows, cols, gb2); });
+        else L.colsum(dY, gb, rows, cols, gb2);
+    }
 
     // out[kept rows, cols] += sum over the dropped axes of in[(n,c,b,t,f), cols]; runs of dropped axes are reduced
     // innermost first, each as one split "sum over the middle axis".  `out` must hold valid data (zeros or a gradient).
@@ -67,9 +81,9 @@ struct Bwd {
         if (Yact && bias >= 0) L.act_grad_colsum(dY, Yact, dY, GRD(c, (ParamId)bias), M, Nout);
         else {
             if (Yact) L.act_grad(dY, Yact, dY, (long long)M * Nout);
-            if (bias >= 0) L.colsum(dY, GRD(c, (ParamId)bias), M, Nout);
+            if (bias >= 0) bias_grad(dY, GRD(c, (ParamId)bias), M, Nout);
         }
-        L.linear_dw(dY, Nout, X, ldx, GRD(c, w) + w_col_off, ldw, M, Nout, K);
+        dw(dY, Nout, X, ldx, GRD(c, w) + w_col_off, ldw, M, Nout, K);
         if (dX) L.linear_dx(dY, Nout, PRM(c, w) + w_col_off, ldw, dX, lddx, M, Nout, K, acc_dx);
     }
     // one term of a decomposed "Linear over a broadcast concat": z_s = W[:, off:off+K] a_s, a_s = leaky(X W2^T + b2).
@@ -77,7 +91,7 @@ struct Bwd {
     void branch_bwd(const float *dZ, int rows, int Nout, ParamId W, int col_off, int ldw, const float *a_s, int K,
                     const float *X, long long ldx, int Kin, ParamId w2, ParamId b2, float *dX, long long lddx, int acc_dx) {
         float *d_a = A((long long)rows * K);
-        L.linear_dw(dZ, Nout, a_s, K, GRD(c, W) + col_off, ldw, rows, Nout, K);
+        dw(dZ, Nout, a_s, K, GRD(c, W) + col_off, ldw, rows, Nout, K);
         L.linear_dx(dZ, Nout, PRM(c, W) + col_off, ldw, d_a, K, rows, Nout, K, 0);
         lin_bwd(d_a, a_s, rows, K, X, ldx, Kin, w2, 0, Kin, b2, dX, lddx, acc_dx);
     }
@@ -93,9 +107,9 @@ struct Bwd {
     void lstm_bwd_grads(LstmBuf &lb, const float *X, ParamId wih, ParamId whh, ParamId bih, ParamId bhh, float *dX, int acc_dx) {
         const int rows = lb.S * lb.T, H4 = 4 * lb.H;
         L.gemm_cls = 16;
-        L.linear_dw(lb.dgates, H4, X, lb.I, GRD(c, wih), lb.I, rows, H4, lb.I);
-        L.linear_dw(lb.dgates, H4, lb.hprev, lb.H, GRD(c, whh), lb.H, rows, H4, lb.H);
-        L.colsum(lb.dgates, GRD(c, bih), rows, H4, GRD(c, bhh));      // b_ih and b_hh see the same gradient
+        dw(lb.dgates, H4, X, lb.I, GRD(c, wih), lb.I, rows, H4, lb.I);
+        dw(lb.dgates, H4, lb.hprev, lb.H, GRD(c, whh), lb.H, rows, H4, lb.H);
+        bias_grad(lb.dgates, GRD(c, bih), rows, H4, GRD(c, bhh));      // b_ih and b_hh see the same gradient
         if (dX) L.linear_dx(lb.dgates, H4, PRM(c, wih), lb.I, dX, lb.I, rows, H4, lb.I, acc_dx);
         L.gemm_cls = 1;
     }
@@ -149,10 +163,10 @@ static LossBufs run_losses(Launcher &L, Arena &ar, int N, int U, long long cells
 }
 
 // ---------------------------------------------------------------------------------------------- backward
-static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
+static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const TrainIn &ti) {
     const int N = c.N, C = c.C, B = c.B, T = c.T, NC = N * C, U = c.U;
     const long long Rb = c.Rb, Rf = c.Rf, Rbf = c.Rbf, Nb = c.Nb;
-    Bwd w{L, c, ar};
+    Bwd w{L, c, ar, zar};
     w.tmpA = ar.take(Rf * 32 + Rb * 120); w.tmpB = ar.take(Rf * 32 + Rb * 120);
     // the tail kernels read the small weights from the constant banks: reload them from THESE parameters (another
     // forward / predict_apply with other parameters may have run since the forward pass of this step)
@@ -213,7 +227,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             k_psa_mel_bwd<<<(int)std::min<long long>((Rbf + kPsaMelWarps - 1) / kPsaMelWarps, 148), kPsaMelWarps * 32, msmem, L.st>>>(m); L.check();
         }
         L.reduce_mid(dZi, dZs, N, C, 450, 0);
-        L.colsum(dZs, GRD(c, psa_oct_b), N, 450);
+        w.bias_grad(dZs, GRD(c, psa_oct_b), N, 450);
         w.branch_bwd(dZs, N, 450, psa_oct_w, 0, 88, c.psa_s66, 66, c.style, 256, 256, psa_sl_w, psa_sl_b, d_style, 256, 1);
         w.branch_bwd(dZr, (int)Rbf, 450, psa_oct_w, 66, 88, c.psa_r10, 10, c.rhythm, 32, 32, psa_rl_w, psa_rl_b, d_rhythm, 32, 1);
         w.branch_bwd(dZi, NC, 450, psa_oct_w, 76, 88, c.psa_i12, 12, c.F, 51, 51, psa_il_w, psa_il_b, nullptr, 0, 0);
@@ -228,29 +242,58 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             a.target = c.Ug; a.coef = lb.coef_u; a.dHpre = dH; a.gWl = GRD(c, usa_lin_w); a.gbl = GRD(c, usa_lin_b);
             k_usa_bwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
         }
-        L.colsum(dH, GRD(c, usa_nl_b), Rbf, 376);
+        w.bias_grad(dH, GRD(c, usa_nl_b), Rbf, 376);
         w.reduce_to(dH, Dims5{N, 1, B, T, 10}, 376, M_N | M_F, dZs);
         // style branch: a_s = usa_s650 viewed (N*10, 65); its producer is style_linear 256 -> 650 on N rows
         {
             float *d_a = w.A((long long)N * 650);
-            L.linear_dw(dZs, 376, c.usa_s650, 65, GRD(c, usa_nl_w), 82, N * 10, 376, 65);
+            w.dw(dZs, 376, c.usa_s650, 65, GRD(c, usa_nl_w), 82, N * 10, 376, 65);
             L.linear_dx(dZs, 376, PRM(c, usa_nl_w), 82, d_a, 65, N * 10, 376, 65, 0);
             w.lin_bwd(d_a, c.usa_s650, N, 650, c.style, 256, 256, usa_sl_w, 0, 256, usa_sl_b, d_style, 256, 1);
         }
         w.branch_bwd(dH, (int)Rbf, 376, usa_nl_w, 65, 82, c.usa_r17, 17, c.rhythm, 32, 32, usa_rl_w, usa_rl_b, d_rhythm, 32, 1);
     }
     // ---------------- SongInfoModel (model.py:513-562)
+    float *d_rf = w.Z((long long)N * 8);
     {
-        float *d_rf = w.Z((long long)N * 8);
         auto head = [&](float *dOut, int nout, ParamId sw, ParamId sb, int ks, const float *sa, ParamId rw, ParamId rb, int kr,
                         const float *ra, ParamId fw, ParamId fb) {
-            L.colsum(dOut, GRD(c, fb), N, nout);
+            w.bias_grad(dOut, GRD(c, fb), N, nout);
             w.branch_bwd(dOut, N, nout, fw, 0, ks + kr, sa, ks, c.style, 256, 256, sw, sb, d_style, 256, 1);
             w.branch_bwd(dOut, N, nout, fw, ks, ks + kr, ra, kr, c.sim_rf, 8, 8, rw, rb, d_rf, 8, 1);
         };
         head(lb.d_instr, 41, sim_si_w, sim_si_b, 8, c.sim_si, sim_ri_w, sim_ri_b, 10, c.sim_ri, sim_i_w, sim_i_b);
         head(lb.d_mode, 2, sim_sm_w, sim_sm_b, 2, c.sim_sm, sim_rm_w, sim_rm_b, 2, c.sim_rm, sim_m_w, sim_m_b);
         head(lb.d_bpm_pre, 1, sim_sb_w, sim_sb_b, 2, c.sim_sb, sim_rb_w, sim_rb_b, 2, c.sim_rb, sim_b_w, sim_b_b);
+    }
+    // ---------------- StyleEncoder (model.py:179-200) on branch 0: d_style is complete once the heads above are through, and
+    // the backward of its 192-wide recurrence is the longest serial kernel of the step; the caller's stream meanwhile runs the
+    // SongInfoModel recurrences, the MelodyEncoder and both rhythm encoders.  Branch 0 only WRITES buffers of its own (d_bars,
+    // d_bp, its parameter gradients): what it adds to d_pce_bars / d_uce_bars is applied after the join below.
+    float *d_bars = w.A(Nb * 128), *d_bp = U ? w.A(2 * Nb * 128) : nullptr;
+    L.wait(0, -1); L.on(0);
+    {
+        float *d_x = w.A((long long)NC * 256);
+        w.combine_bwd(c.se_x, (long long)C * 256, 256, C, 256, c.se_ss, c.style, d_style, d_x, 0);
+        L.act_grad(d_x, c.se_x, d_x, (long long)NC * 256);
+        w.bias_grad(d_x, GRD(c, se_lin_b), NC, 256);
+        float *dzn = w.Z((long long)N * 256);
+        w.reduce_to(d_x, Dims5{N, C, 1, 1, 1}, 256, M_N, dzn);
+        float *d_last = w.A((long long)N * 192), *d_h = w.Z(Nb * 192);
+        w.dw(dzn, 256, c.se_last, 192, GRD(c, se_lin_w), 251, N, 256, 192);
+        L.linear_dx(dzn, 256, PRM(c, se_lin_w), 251, d_last, 192, N, 256, 192, 0);
+        w.branch_bwd(d_x, NC, 256, se_lin_w, 192, 251, c.se_a2, 39, c.F, 51, 51, se_il_w, se_il_b, nullptr, 0, 0);
+        w.branch_bwd(dzn, N, 256, se_lin_w, 231, 251, c.se_a3, 13, c.mode, 2, 2, se_ml_w, se_ml_b, nullptr, 0, 0);
+        w.branch_bwd(dzn, N, 256, se_lin_w, 244, 251, c.se_a4, 7, c.bpm, 1, 1, se_bp_w, se_bp_b, nullptr, 0, 0);
+        L.put_last(d_last, d_h, N, B, 192);
+        w.lstm_bwd(c.se_l, d_h, 192, 0, 0, c.bars, se_lstm_wih, se_lstm_whh, se_lstm_bih, se_lstm_bhh, d_bars, 0);
+    }
+    if (U) {
+        const long long Mb = (long long)B * 128;
+        w.combine_bwd(c.bars_pair, 2 * Mb, Mb, 2, Mb, c.bars_ss, c.bars_c, d_bars, d_bp, 0);
+    }
+    L.on(-1);
+    {
         float *d_h2 = w.Z(Nb * 8), *d_last1 = w.A(Nb * 9), *d_h1 = w.Z(Nb * T * 9);
         L.put_last(d_rf, d_h2, N, B, 8);
         w.lstm_bwd(c.sim_l2, d_h2, 8, 0, 0, c.sim_last1, sim_br_wih, sim_br_whh, sim_br_bih, sim_br_bhh, d_last1, 0);
@@ -270,43 +313,22 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         }
         const Dims5 d{N, C, B, T, 1};
         float *dz1 = w.Z(Nb * 120), *dz2 = w.Z((long long)NC * 120);
-        L.colsum(dod, GRD(c, me_oct_b), Rb, 120);
+        w.bias_grad(dod, GRD(c, me_oct_b), Rb, 120);
         w.reduce_to(dod, d, 120, M_N | M_B, dz1);
         w.reduce_to(dod, d, 120, M_N | M_C, dz2);
         w.branch_bwd(dod, (int)Rb, 120, me_oct_w, 0, 112, c.me_a1, 36, c.pce_beats, 64, 64, me_bl_w, me_bl_b, d_pce_beats, 64, 1);
         w.branch_bwd(dz1, (int)Nb, 120, me_oct_w, 36, 112, c.me_a2, 68, c.pce_bars, 128, 128, me_br_w, me_br_b, d_pce_bars, 128, 1);
         w.branch_bwd(dz2, NC, 120, me_oct_w, 104, 112, c.me_a3, 8, c.F, 51, 51, me_il_w, me_il_b, nullptr, 0, 0);
     }
-    // ---------------- StyleEncoder (model.py:179-200)
-    float *d_bars = w.A(Nb * 128);
-    {
-        float *d_x = w.A((long long)NC * 256);
-        w.combine_bwd(c.se_x, (long long)C * 256, 256, C, 256, c.se_ss, c.style, d_style, d_x, 0);
-        L.act_grad(d_x, c.se_x, d_x, (long long)NC * 256);
-        L.colsum(d_x, GRD(c, se_lin_b), NC, 256);
-        float *dzn = w.Z((long long)N * 256);
-        w.reduce_to(d_x, Dims5{N, C, 1, 1, 1}, 256, M_N, dzn);
-        float *d_last = w.A((long long)N * 192), *d_h = w.Z(Nb * 192);
-        L.linear_dw(dzn, 256, c.se_last, 192, GRD(c, se_lin_w), 251, N, 256, 192);
-        L.linear_dx(dzn, 256, PRM(c, se_lin_w), 251, d_last, 192, N, 256, 192, 0);
-        w.branch_bwd(d_x, NC, 256, se_lin_w, 192, 251, c.se_a2, 39, c.F, 51, 51, se_il_w, se_il_b, nullptr, 0, 0);
-        w.branch_bwd(dzn, N, 256, se_lin_w, 231, 251, c.se_a3, 13, c.mode, 2, 2, se_ml_w, se_ml_b, nullptr, 0, 0);
-        w.branch_bwd(dzn, N, 256, se_lin_w, 244, 251, c.se_a4, 7, c.bpm, 1, 1, se_bp_w, se_bp_b, nullptr, 0, 0);
-        L.put_last(d_last, d_h, N, B, 192);
-        w.lstm_bwd(c.se_l, d_h, 192, 0, 0, c.bars, se_lstm_wih, se_lstm_whh, se_lstm_bih, se_lstm_bhh, d_bars, 0);
-    }
-    // ---------------- combine(pitched, unpitched) (model.py:766-767)
+    // ---------------- combine(pitched, unpitched) of the rhythm (model.py:767)
     float *d_pre_out, *d_ure_out = nullptr;
     if (U) {
-        const long long Mb = (long long)B * 128, Mr = (long long)B * T * 320;
-        float *d_bp = w.A(2 * Nb * 128), *d_rp = w.A(2 * Rbf * 32);
+        const long long Mr = (long long)B * T * 320;
+        float *d_rp = w.A(2 * Rbf * 32);
         d_pre_out = w.Z(Rbf * 32); d_ure_out = w.Z(Rbf * 32);
-        w.combine_bwd(c.bars_pair, 2 * Mb, Mb, 2, Mb, c.bars_ss, c.bars_c, d_bars, d_bp, 0);
-        if (!L.dry) { k_pair_unpack_add<<<grid_for(Nb * 128), 256, 0, L.st>>>(d_bp, d_pce_bars, d_uce_bars, N, Mb); L.check(); }
         w.combine_bwd(c.rh_pair, 2 * Mr, Mr, 2, Mr, c.rh_ss, c.rh_c, d_rhythm, d_rp, 0);
         if (!L.dry) { k_pair_unpack_add<<<grid_for(Rbf * 32), 256, 0, L.st>>>(d_rp, d_pre_out, d_ure_out, N, Mr); L.check(); }
     } else {
-        L.axpy(d_pce_bars, d_bars, Nb * 128);
         d_pre_out = d_rhythm;
     }
     if (U) {
@@ -316,7 +338,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             float *d_x = w.A(Rbf * 32);
             w.combine_bwd(c.ure_x, (long long)B * T * 320, (long long)B * T * 320, 1, (long long)B * T * 320, c.ure_ss, c.ure_out, d_ure_out, d_x, 0);
             L.act_grad(d_x, c.ure_x, d_x, Rbf * 32);
-            L.colsum(d_x, GRD(c, ure_lin_b), Rbf, 32);
+            w.bias_grad(d_x, GRD(c, ure_lin_b), Rbf, 32);
             float *dz0 = w.Z(Nb * T * 32), *dz1 = w.Z(Nb * 32), *dz3 = w.Z((long long)N * 32);
             w.reduce_to(d_x, d, 32, M_N | M_B | M_T, dz0);
             w.reduce_to(d_x, d, 32, M_N | M_B, dz1);
@@ -334,7 +356,7 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         float *d_x = w.A(Rf * 32);
         w.combine_bwd(c.pre_x, C * M, M, C, M, c.pre_ss, c.pre_out, d_pre_out, d_x, 0);
         L.act_grad(d_x, c.pre_x, d_x, Rf * 32);
-        L.colsum(d_x, GRD(c, pre_lin_b), Rf, 32);
+        w.bias_grad(d_x, GRD(c, pre_lin_b), Rf, 32);
         float *dz0 = w.Z(Rb * 32), *dz1 = w.Z(Nb * 32), *dz3 = w.Z((long long)NC * 32), *dz4 = w.Z((long long)N * 32);
         w.reduce_to(d_x, d, 32, M_N | M_C | M_B | M_T, dz0);
         w.reduce_to(dz0, Dims5{N, C, B, T, 1}, 32, M_N | M_B, dz1);
@@ -344,10 +366,10 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         w.branch_bwd(dz1, (int)Nb, 32, pre_lin_w, 48, 135, c.pre_a2, 40, c.pce_bars, 128, 128, pre_br_w, pre_br_b, d_pce_bars, 128, 1);
         {   // channels branch: the weight gradient of channels_linear runs over the occupied cells only
             float *d_a = w.A(Rf * 16);
-            L.linear_dw(d_x, 32, c.pre_a3, 16, GRD(c, pre_lin_w) + 88, 135, (int)Rf, 32, 16);
+            w.dw(d_x, 32, c.pre_a3, 16, GRD(c, pre_lin_w) + 88, 135, (int)Rf, 32, 16);
             L.linear_dx(d_x, 32, PRM(c, pre_lin_w) + 88, 135, d_a, 16, (int)Rf, 32, 16, 0);
             L.act_grad(d_a, c.pre_a3, d_a, Rf * 16);
-            L.colsum(d_a, GRD(c, pre_ch_b), Rf, 16);
+            w.bias_grad(d_a, GRD(c, pre_ch_b), Rf, 16);
             if (!L.dry) {
                 k_chlin_sparse_wgrad<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(c.cells_off, c.cells_rec, d_a, GRD(c, pre_ch_w), Rb);
                 L.check();
@@ -356,6 +378,13 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         w.branch_bwd(dz3, NC, 32, pre_lin_w, 104, 135, c.pre_a4, 21, c.F, 51, 51, pre_il_w, pre_il_b, nullptr, 0, 0);
         w.branch_bwd(dz4, N, 32, pre_lin_w, 125, 135, c.pre_a5, 5, c.mode, 2, 2, pre_ml_w, pre_ml_b, nullptr, 0, 0);
         w.branch_bwd(dz4, N, 32, pre_lin_w, 130, 135, c.pre_a6, 5, c.bpm, 1, 1, pre_bp_w, pre_bp_b, nullptr, 0, 0);
+    }
+    // ---------------- join branch 0: the StyleEncoder's gradient w.r.t. the bars reaches the channel encoders (model.py:766)
+    L.wait(-1, 0);
+    if (U) {
+        if (!L.dry) { k_pair_unpack_add<<<grid_for(Nb * 128), 256, 0, L.st>>>(d_bp, d_pce_bars, d_uce_bars, N, (long long)B * 128); L.check(); }
+    } else {
+        L.axpy(d_pce_bars, d_bars, Nb * 128);
     }
     // ---------------- bar-axis BiLSTMs of both channel encoders: their four recurrences are independent -> one launch
     {
@@ -370,7 +399,8 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         L.lstm_multi(jobs, nj, true);
     }
     if (U) {
-        // ---------------- UnpitchedChannelsEncoder (model.py:128-141)
+        // ---------------- UnpitchedChannelsEncoder (model.py:128-141), on branch 0 beside the pitched encoder's backward
+        L.wait(0, -1); L.on(0);
         {
             float *d_in = w.A(Nb * 64), *d_last = w.A(Nb * 64), *d_lin = w.A(Nb * T * 64), *gWp = w.Z(64 * 940);
             w.lstm_bwd_grads(c.uce_brf, c.uce_bars_in, uce_br_wih, uce_br_whh, uce_br_bih, uce_br_bhh, d_in, 0);
@@ -379,10 +409,11 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
             L.put_last(d_last, d_uce_beats, Nb, T, 64);
             w.lstm_bwd(c.uce_bl, d_uce_beats, 64, 0, 0, c.uce_lin, uce_bl_wih, uce_bl_whh, uce_bl_bih, uce_bl_bhh, d_lin, 0);
             L.act_grad(d_lin, c.uce_lin, d_lin, Nb * T * 64);
-            L.colsum(d_lin, GRD(c, uce_lin_b), Nb * T, 64);
+            w.bias_grad(d_lin, GRD(c, uce_lin_b), Nb * T, 64);
             L.linear_dw(d_lin, 64, c.Ug, 940, gWp, 940, (int)(Nb * T), 64, 940);
             if (!L.dry) { k_permute_cols<<<grid_for(64 * 940), 256, 0, L.st>>>(gWp, GRD(c, uce_lin_w), 64, 940, 2, 1, 1); L.check(); }
         }
+        L.on(-1);
     }
     // ---------------- PitchedChannelsEncoder (model.py:77-99)
     {
@@ -393,11 +424,13 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         L.put_last(d_last, d_pce_beats, (long long)NC * B, T, 64);
         w.lstm_bwd(c.pce_bl, d_pce_beats, 64, 0, 0, c.pce_x, pce_bl_wih, pce_bl_whh, pce_bl_bih, pce_bl_bhh, d_x, 0);
         L.act_grad(d_x, c.pce_x, d_x, Rb * 64);
-        L.colsum(d_x, GRD(c, pce_lin_b), Rb, 64);
+        w.bias_grad(d_x, GRD(c, pce_lin_b), Rb, 64);
         // instruments branch (columns 456.. of linear.weight are not permuted)
         float *dzi = w.Z((long long)NC * 64);
         w.reduce_to(d_x, Dims5{N, C, B, T, 1}, 64, M_N | M_C, dzi);
+        w.leaf_dw = false;            // k_permute_cols below adds into every column of pce_lin_w's gradient on this stream
         w.branch_bwd(dzi, NC, 64, pce_lin_w, 456, 514, c.pce_il, 58, c.F, 51, 51, pce_il_w, pce_il_b, nullptr, 0, 0);
+        w.leaf_dw = true;
         // conv branch: z = conv_out (rows, 456) . Wp[:, :456]^T in the permuted column order
         float *gWp = w.Z(64 * 514), *d_conv = w.A(Rb * 456), *gT = w.Z(700 * 57);
         L.linear_dw(d_x, 64, c.pce_conv, 456, gWp, 514, (int)Rb, 64, 456);
@@ -406,13 +439,27 @@ static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
         L.linear_dx(d_x, 64, c.wpcelin_p, 514, d_conv, 456, (int)Rb, 64, 456, 0);
         L.gemm_cls = 1;
         L.act_grad(d_conv, c.pce_conv, d_conv, Rb * 456);
-        L.colsum(d_conv, GRD(c, pce_conv_b), Rb * 8, 57);
+        w.bias_grad(d_conv, GRD(c, pce_conv_b), Rb * 8, 57);
         // gT[k][o] = sum over occupied cells of p[feat] * d_conv[row][oct][o]  (k = f * 70 + tap * 5 + feat)
         if (!L.dry) {
             k_conv_sparse_wgrad<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 8), 256, 0, L.st>>>(c.cells_off, c.cells_rec, d_conv, gT, Rb); L.check();
             k_conv_wgrad_unpack<<<grid_for(57 * 700), 256, 0, L.st>>>(gT, GRD(c, pce_conv_w)); L.check();
         }
     }
+    if (U) L.wait(-1, 0);
+}
+
+static void backward(Launcher &L, Ctx &c, Arena &ar, const TrainIn &ti) {
+    // sizing pass: what the pass carves from the work region and from the zero region, which follows it
+    Launcher P; P.st = nullptr; P.dry = true; P.bf16 = L.bf16;
+    Arena a1{nullptr, ar.off, true}, z1{nullptr, 0, true};
+    TrainIn none{};
+    backward_impl(P, c, a1, z1, none);
+    const size_t z_base = mst_align_up(a1.off, 256);
+    Arena zar{ar.base + z_base, 0, ar.dry};
+    if (!L.dry) L.fill((float *)(ar.base + z_base), (long long)(z1.off / sizeof(float)), 0.f);
+    backward_impl(L, c, ar, zar, ti);
+    ar.off = z_base + z1.off;
 }
 
 static size_t plan_backward(Ctx &c, Arena &ar) {
