@@ -373,24 +373,35 @@ def run_files(args, torch, lib, abi, synth, filt):
         probe.encode(filt, None)
         arena_floats = int(1.1 * sum(lib.grid_floats(r) for r in probe.infos()))
         del probe
-        pipe = EventPipeline(filt, batch_files=batch, slots=3, arena_floats=arena_floats)
+        def timed(wire):
+            pipe = EventPipeline(filt, batch_files=batch, slots=3, arena_floats=arena_floats, wire=wire)
 
-        def one_pass():
-            bars = ok = 0
-            for _, r, _ in pipe.run(paths):
-                if int(r['status']) == 0:
-                    ok += 1
-                    bars += int(r['n_bars_out'])
-            torch.cuda.synchronize()
-            return ok, bars
-        one_pass()                                            # warm-up: page cache, pinned buffers, workspaces
-        t0 = time.perf_counter()
-        ok, bars = one_pass()
-        dt = time.perf_counter() - t0
-        pipe.close()
+            def one_pass():
+                bars = ok = 0
+                for _, r, _ in pipe.run(paths):
+                    if int(r['status']) == 0:
+                        ok += 1
+                        bars += int(r['n_bars_out'])
+                torch.cuda.synchronize()
+                return ok, bars
+            one_pass()                                            # warm-up: page cache, pinned buffers, workspaces
+            t0 = time.perf_counter()
+            ok, bars = one_pass()
+            dt = time.perf_counter() - t0
+            pipe.close()
+            del pipe
+            torch.cuda.empty_cache()
+            return ok, bars, dt
+        ok, bars, dt = timed('smf')
+        ok_e, bars_e, dt_e = timed('events')
+        assert (ok, bars) == (ok_e, bars_e), ((ok, bars), (ok_e, bars_e))
         out = {'metric': 'piano-roll bars/sec encoded from .mid files on disk', 'value': bars / dt, 'unit': UNIT, 'files_per_s': ok / dt,
                'files': n_files, 'files_ok': ok, 'file_bytes': n_bytes, 'batch_files': batch, 'ms_per_file': dt / n_files * 1e3,
-               'note': 'EventPipeline: mst_smf_load_batch (C++ threads) -> pinned buffers -> mst_encode_batch_host_async, three slots'}
+               'note': 'EventPipeline(wire="smf"): mst_files_read_batch (C++ threads) -> pinned file bytes -> mst_encode_batch_smf_async '
+                       '(device-side parse), three slots',
+               'host_parse_path': {'value': bars_e / dt_e, 'unit': UNIT, 'files_per_s': ok_e / dt_e,
+                                   'note': 'EventPipeline(wire="events"): mst_smf_load_batch parses on the host cores, '
+                                           'mst_encode_batch_host_async uploads 16-byte event records'}}
         # CPU arm on the same files: same native parser on all cores + the C oracle port of the encoder
         sys.path.insert(0, os.path.join(ROOT, 'oracle'))
         import oracle_lib
@@ -883,10 +894,23 @@ def main():
     # the host buffers hold the 8-byte wire format of the events (mst_events_pack, done once outside the timed region: it is
     # the form a loader writes); mst_encode_batch_packed_async widens them on the device.  Half the H2D volume of MstEvent
     # records: what matters once several ranks share one host socket
+    # Round 2b: the headline e2e leg uploads the FILES THEMSELVES (Standard MIDI File bytes, 3-4 bytes per event) and parses
+    # them on the device (mst_encode_batch_smf_async); the packed-event leg is measured beside it for comparison.
+    def song_bytes(events, songs):
+        blobs = []
+        for srec in songs:
+            o, k = int(srec['event_offset']), int(srec['n_events'])
+            blobs.append(lib.smf_write_events(events[o:o + k], int(srec['ticks_per_beat'])))
+        return lib.concat_files(blobs)
+    smf = [song_bytes(*h) for h in host_batches]
+    h_bytes = [torch.from_numpy(b).pin_memory() for b, _ in smf]
+    h_files = [torch.from_numpy(f.view(np.uint8).reshape(-1)).pin_memory() for _, f in smf]
+    n_by = [len(b) for b, _ in smf]
     h_events = [torch.from_numpy(lib.events_pack(h[0]).view(np.uint8)).pin_memory() for h in host_batches]
     h_songs = [torch.from_numpy(h[1].view(np.uint8).reshape(-1)).pin_memory() for h in host_batches]
     n_ev = [len(h[0]) for h in host_batches]
-    wsb = max(L.mst_encode_packed_workspace_bytes(n, args.batch, arena.numel()) for n in n_ev)
+    wsb = max(max(L.mst_encode_packed_workspace_bytes(n, args.batch, arena.numel()) for n in n_ev),
+              max(L.mst_encode_smf_workspace_bytes(n, args.batch, arena.numel()) for n in n_by))
     for b in batches:
         b._ws = None   # release the device-path workspaces before allocating the host-path ones
     n_slots = args.e2e_slots
@@ -896,60 +920,75 @@ def main():
                       'ws': torch.empty(wsb, dtype=torch.uint8, device='cuda'),
                       'arena': arenas[k] if k < len(arenas) else torch.empty_like(arena),
                       'info': torch.empty(args.batch * abi.SONG_INFO_DTYPE.itemsize, dtype=torch.uint8).pin_memory()})
-    e2e_bars = [0]
 
-    def e2e_drain(sl):
-        """Wait for the slot's batch and consume its infos (what a caller does before handing the grids on)."""
-        sl['stream'].synchronize()
-        if sl.get('busy'):
-            info = sl['info'].numpy().view(abi.SONG_INFO_DTYPE)
-            ok = info['status'] == 0
-            e2e_bars[0] += int(info['n_bars_out'][ok].sum())
-            sl['busy'] = False
+    def run_e2e(wire):
+        e2e_bars = [0]
 
-    def e2e_step(i):
-        j = i % n_batches
-        sl = slots[i % n_slots]
-        e2e_drain(sl)
-        lib.check(L.mst_encode_batch_packed_async(
-            h_events[j].data_ptr(), n_ev[j], h_songs[j].data_ptr(), args.batch, filt.reshape(1).ctypes.data,
-            sl['info'].data_ptr(), sl['arena'].data_ptr(), sl['arena'].numel(), sl['ws'].data_ptr(), wsb,
-            sl['stream'].cuda_stream))
-        sl['busy'] = True
+        def e2e_drain(sl):
+            """Wait for the slot's batch and consume its infos (what a caller does before handing the grids on)."""
+            sl['stream'].synchronize()
+            if sl.get('busy'):
+                info = sl['info'].numpy().view(abi.SONG_INFO_DTYPE)
+                ok = info['status'] == 0
+                e2e_bars[0] += int(info['n_bars_out'][ok].sum())
+                sl['busy'] = False
 
-    for i in range(2):
-        e2e_step(i)
-    for sl in slots:
-        e2e_drain(sl)
-    e2e_bars[0] = 0
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
-    for sl in slots:
-        e2e_drain(sl)
-    torch.cuda.synchronize()
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
-    barrier()
+        def e2e_step(i):
+            j = i % n_batches
+            sl = slots[i % n_slots]
+            e2e_drain(sl)
+            if wire == 'smf':
+                lib.check(L.mst_encode_batch_smf_async(
+                    h_bytes[j].data_ptr(), n_by[j], h_files[j].data_ptr(), args.batch, filt.reshape(1).ctypes.data,
+                    sl['info'].data_ptr(), sl['arena'].data_ptr(), sl['arena'].numel(), sl['ws'].data_ptr(), wsb,
+                    sl['stream'].cuda_stream))
+            else:
+                lib.check(L.mst_encode_batch_packed_async(
+                    h_events[j].data_ptr(), n_ev[j], h_songs[j].data_ptr(), args.batch, filt.reshape(1).ctypes.data,
+                    sl['info'].data_ptr(), sl['arena'].data_ptr(), sl['arena'].numel(), sl['ws'].data_ptr(), wsb,
+                    sl['stream'].cuda_stream))
+            sl['busy'] = True
+
+        for i in range(3):
+            e2e_step(i)
+        for sl in slots:
+            e2e_drain(sl)
+        warm_bars = e2e_bars[0]
+        e2e_bars[0] = 0
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            e2e_step(i)
+        for sl in slots:
+            e2e_drain(sl)
+        torch.cuda.synchronize()
+        e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+        barrier()
+        e2e_per_rank = [float(e2e_s.item())]
+        if world > 1:
+            each = [torch.zeros_like(e2e_s) for _ in range(world)]
+            dist.all_gather(each, e2e_s)
+            e2e_per_rank = [float(t.item()) for t in each]
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        e2e_total = torch.tensor([float(e2e_bars[0])], dtype=torch.float64, device='cuda')
+        if world > 1:
+            dist.all_reduce(e2e_total, op=dist.ReduceOp.SUM)
+        h2d = (statistics.mean(n_by) + args.batch * 16) if wire == 'smf' else (statistics.mean(n_ev) * 8 + args.batch * 16)
+        assert warm_bars == sum(bars[i % n_batches] for i in range(3)), (wire, warm_bars)      # same songs encoded as on the device path
+        return {'value': float(e2e_total.item()) / float(e2e_s.item()), 'unit': UNIT,
+                'h2d_bytes_per_step': int(h2d),
+                'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
+                'ms_per_step_per_rank': [round(t / args.steps * 1e3, 3) for t in e2e_per_rank],
+                'h2d_GBps_per_rank': [round(h2d * args.steps / t / 1e9, 2) for t in e2e_per_rank]}
+
+    e2e = run_e2e('smf')
+    e2e['bytes_per_event'] = round(statistics.mean(n_by) / statistics.mean(n_ev), 2)
+    e2e['note'] = ('mst_encode_batch_smf_async: the batch\'s Standard MIDI File bytes are uploaded as they are and parsed on the '
+                   'device (thread per track), three rotating slots (H2D of batch i+1, i+2 overlaps the kernels of batch i); grids '
+                   'stay in HBM for the training consumer (SURVEY.md 8(b)); infos are read back and consumed every step')
+    e2e['packed_events'] = run_e2e('events')
+    e2e['packed_events']['note'] = 'the same loop on mst_encode_batch_packed_async (8-byte event records parsed on the host beforehand)'
     t_load1 = time.time()
-    e2e_per_rank = [float(e2e_s.item())]
-    if world > 1:
-        each = [torch.zeros_like(e2e_s) for _ in range(world)]
-        dist.all_gather(each, e2e_s)
-        e2e_per_rank = [float(t.item()) for t in each]
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_total = torch.tensor([float(e2e_bars[0])], dtype=torch.float64, device='cuda')
-    if world > 1:
-        dist.all_reduce(e2e_total, op=dist.ReduceOp.SUM)
-    e2e_value = float(e2e_total.item()) / float(e2e_s.item())
-    e2e = {'value': e2e_value, 'unit': UNIT,
-           'h2d_bytes_per_step': int(statistics.mean(n_ev) * 8 + args.batch * 16),
-           'd2h_bytes_per_step': int(args.batch * abi.SONG_INFO_DTYPE.itemsize),
-           'ms_per_step_per_rank': [round(t / args.steps * 1e3, 3) for t in e2e_per_rank],
-           'h2d_GBps_per_rank': [round((statistics.mean(n_ev) * 8 + args.batch * 16) * args.steps / t / 1e9, 2) for t in e2e_per_rank],
-           'note': 'mst_encode_batch_packed_async (8-byte event records) on three rotating slots (H2D of batch i+1, i+2 overlaps the kernels of '
-                   'batch i); grids stay in HBM for the training consumer (SURVEY.md 8(b)); infos are read back and '
-                   'consumed every step'}
     # ---- decode leg over the grids of batch 0 (round trip of the encoder's output)
     decode = run_decode(args, world, rank, torch, dist, L, lib, abi, batches[0], filt, arena)
     files_leg = None
@@ -1005,7 +1044,7 @@ def main():
             'training_n1': training_n1,
             # compact digest, LAST so that a truncated stdout tail still carries the training half of the metric
             'summary': {
-                'encode_song_bars_per_s': value, 'encode_e2e': e2e_value, 'encode_frac': roofline['frac'],
+                'encode_song_bars_per_s': value, 'encode_e2e': e2e['value'], 'encode_e2e_events8': e2e['packed_events']['value'], 'encode_frac': roofline['frac'],
                 'decode_frac': decode['roofline']['frac'],
                 'files_song_bars_per_s': files_leg['value'] if files_leg else None,
                 'files_cpu_song_bars_per_s': files_leg['cpu_baseline']['value'] if files_leg else None,

@@ -233,6 +233,36 @@ int    mst_encode_batch_packed_async(const MstPackedEvent *h_events, uint64_t n_
                                      uint32_t n_songs, const MstFilter *h_filter, MstSongInfo *h_info, float *d_arena,
                                      uint64_t arena_floats, void *d_workspace, size_t workspace_bytes, void *stream);
 
+/* Raw Standard MIDI File bytes as the wire format of the host path: the files of a batch lie concatenated in one
+ * (page-locked) host buffer, are copied as they are and PARSED ON THE DEVICE (one thread per track chunk), then encoded.
+ * Replaces mido.MidiFile(path) in load_midi_from_file (style/midi.py:104-108) + everything mst_encode_batch_host_async
+ * replaces, for a batch of files: same events and same "load failed" verdicts as mst_smf_parse, reported as
+ * MST_SONG_LOAD_FAILED in the file's MstSongInfo.  A file spends 3 - 4 bytes on an event where MstEvent spends 16 and
+ * MstPackedEvent 8: this is the form that keeps the host -> device copy off the critical path when several GPUs share
+ * one host.  The workspace is sized from the BYTE count (an event takes at least 2 bytes, a track chunk at least 8). */
+typedef struct MstFileIn {
+    uint64_t byte_offset;   /* of the file's first byte in the batch buffer */
+    uint32_t n_bytes;
+    uint32_t reserved;
+} MstFileIn;
+/* Reads the files as they are into one buffer (C++ thread pool, no Python in the loop; stat first, then the reads): file i
+ * starts at h_files[i].byte_offset (16-byte aligned); an unreadable file gets n_bytes = 0 and h_status[i] = -1 (the
+ * device parser then reports MST_SONG_LOAD_FAILED for it).  MST_E_CAPACITY with the needed size in *n_bytes_total when
+ * the buffer is too small. */
+int    mst_files_read_batch(const char *const *paths, uint32_t n_files, int32_t n_threads, uint8_t *h_bytes, uint64_t capacity,
+                            MstFileIn *h_files, int32_t *h_status, uint64_t *n_bytes_total);
+/* The device-side parser alone (synchronous; for callers that want the events): same results as mst_smf_parse per file -
+ * h_songs[i] = (event offset, count, division), h_status[i] != 0 where the load fails, *n_events_total records in h_events
+ * (MST_E_CAPACITY with the needed count when `capacity` is too small). */
+size_t mst_smf_parse_device_workspace_bytes(uint64_t n_bytes_total, uint32_t n_files);
+int    mst_smf_parse_batch_device(const uint8_t *h_bytes, uint64_t n_bytes_total, const MstFileIn *h_files, uint32_t n_files,
+                                  MstEvent *h_events, uint64_t capacity, MstSongIn *h_songs, int32_t *h_status,
+                                  uint64_t *n_events_total, void *d_workspace, size_t workspace_bytes, void *stream);
+size_t mst_encode_smf_workspace_bytes(uint64_t n_bytes_total, uint32_t n_files, uint64_t arena_floats);
+int    mst_encode_batch_smf_async(const uint8_t *h_bytes, uint64_t n_bytes_total, const MstFileIn *h_files, uint32_t n_files,
+                                  const MstFilter *h_filter, MstSongInfo *h_info, float *d_arena, uint64_t arena_floats,
+                                  void *d_workspace, size_t workspace_bytes, void *stream);
+
 /* ---------------------------------------------------------------- decode (grids -> MIDI events) */
 /* Replaces hard_output (style/model.py:818-832), ChannelConverter.vchannel2channel
  * (midi_conversion.py:518-573 = vchannel2qchannel + qchannel2channel), decode_midi

@@ -27,6 +27,7 @@ UNITS = [
     ('mst_model.cu', []),
     ('mst_transfer.cu', []),
     ('mst_smf.cpp', []),
+    ('mst_smf_gpu.cu', []),
 ]
 
 

@@ -27,6 +27,12 @@ void mst_set_error(const char *fmt, ...);
         }                                                                                \
     } while (0)
 
+// mst_encode_batch_device with a hook that enqueues the producers of d_events / d_songs on the front-end stream (internal)
+int mst_encode_batch_device_front(const MstEvent *d_events, uint64_t n_events_total, const MstSongIn *d_songs, uint32_t n_songs,
+                                  const MstFilter *h_filter, MstSongInfo *d_info, float *d_arena, uint64_t arena_floats,
+                                  void *d_workspace, size_t workspace_bytes, void *stream,
+                                  int (*front_hook)(void *ctx, cudaStream_t front), void *hook_ctx);
+
 static inline size_t mst_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---------------------------------------------------------------- device helpers

@@ -1272,6 +1272,18 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
                                        const MstFilter *h_filter, MstSongInfo *d_info,
                                        float *d_arena, uint64_t arena_floats,
                                        void *d_workspace, size_t workspace_bytes, void *stream_) {
+    return mst_encode_batch_device_front(d_events, n_events_total, d_songs, n_songs, h_filter, d_info, d_arena, arena_floats,
+                                         d_workspace, workspace_bytes, stream_, nullptr, nullptr);
+}
+
+// The same with a hook that enqueues producer kernels of d_events / d_songs (the device-side SMF parser) on the stream the
+// front end runs on - the library's high-priority side stream when the fill overlaps - right in front of k_sort.
+int mst_encode_batch_device_front(const MstEvent *d_events, uint64_t n_events_total,
+                                  const MstSongIn *d_songs, uint32_t n_songs,
+                                  const MstFilter *h_filter, MstSongInfo *d_info,
+                                  float *d_arena, uint64_t arena_floats,
+                                  void *d_workspace, size_t workspace_bytes, void *stream_,
+                                  int (*front_hook)(void *ctx, cudaStream_t front), void *hook_ctx) {
     if (!d_songs || !d_info || !d_workspace || (!d_events && n_events_total) || (!d_arena && arena_floats)) {
         mst_set_error("mst_encode_batch_device: null pointer argument");
         return MST_E_INVALID;
@@ -1314,6 +1326,10 @@ extern "C" int mst_encode_batch_device(const MstEvent *d_events, uint64_t n_even
         MST_CUDA_CHECK(cudaEventRecord(g_fork, stream));
         MST_CUDA_CHECK(cudaStreamWaitEvent(g_side, g_fork, 0));
         front = g_side;
+    }
+    if (front_hook) {
+        const int hrc = front_hook(hook_ctx, front);
+        if (hrc != MST_OK) return hrc;
     }
     k_sort<<<n_songs, kSortThreads, 0, front>>>(d_events, d_songs, ws);
     MST_LAUNCH_CHECK("k_sort");

@@ -323,7 +323,7 @@ struct Launcher {
         if (k < 0 && on_k >= 0) forked &= ~(1u << on_k);
     }
     int cur = -1;                 // the branch launches currently go to
-    void on(int k) { if (ss && !dry) { st = stream_of(k); cur = k; } }
+    void on(int k) { if (ss && !dry) { st = stream_of(k); cur = k; if (k >= 0) forked |= 1u << k; } }
     // run f's launches on the leaf branch, after what is queued on the current one (the gradient they read is ready there)
     template <class F> void leaf(F f) {
         if (!ss || dry) { f(); return; }
@@ -640,6 +640,7 @@ struct LstmBuf {
 
 struct Ctx {
     int N, C, B, T, U;
+    bool fused;                     // forward_extract + _song_info + _apply run in one call: pieces move between them (see forward_extract)
     long long Rb, Rf, Rbf, Nb;      // beat rows (n,c,b,t), fraction rows, (n,b,t,f) rows, bar rows (n,b)
     const float *P, *Ug, *F, *mode, *bpm;   // inputs
     const float *prm;               // flat parameters
@@ -823,6 +824,19 @@ void forward_extract(Launcher &L, Ctx &c) {
     int n_bar_jobs = 2;
     L.wait(1, -1); L.on(1);
     prep_weights_lstm(L, c);
+    {   // linears that read only the instrument features / mode / bpm: off the chains that end in the style vector
+        const float *slw = PRM(c, se_lin_w);
+        L.linear(c.F, 51, PRM(c, se_il_w), 51, PRM(c, se_il_b), c.se_a2, 39, NC, 39, 51, 1);
+        L.linear(c.mode, 2, PRM(c, se_ml_w), 2, PRM(c, se_ml_b), c.se_a3, 13, N, 13, 2, 1);
+        L.linear(c.bpm, 1, PRM(c, se_bp_w), 1, PRM(c, se_bp_b), c.se_a4, 7, N, 7, 1, 1);
+        L.linear(c.se_a2, 39, slw + 192, 251, nullptr, c.se_z[1], 256, NC, 256, 39, 0);
+        L.linear(c.se_a3, 13, slw + 231, 251, nullptr, c.se_z[2], 256, N, 256, 13, 0);
+        L.linear(c.se_a4, 7, slw + 244, 251, nullptr, c.se_z[3], 256, N, 256, 7, 0);
+        if (c.fused) {
+            L.linear(c.F, 51, PRM(c, psa_il_w), 51, PRM(c, psa_il_b), c.psa_i12, 12, NC, 12, 51, 1);
+            L.linear(c.psa_i12, 12, PRM(c, psa_oct_w) + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
+        }
+    }
     if (c.U) {
         L.wait(0, -1); L.on(0);
         prep_weights_uce(L, c);
@@ -913,6 +927,15 @@ void forward_extract(Launcher &L, Ctx &c) {
           a.ss = c.rh_ss; a.out = c.rh_c; L.combine_fwd(a); }
         c.rhythm = c.rh_c;
     }
+    if (c.fused) {
+        // the appliers' linears that read only the rhythm follow it on this branch (forward_apply skips them)
+        L.linear(c.rhythm, 32, PRM(c, psa_rl_w), 32, PRM(c, psa_rl_b), c.psa_r10, 10, (int)Rbf, 10, 32, 1);
+        L.linear(c.psa_r10, 10, PRM(c, psa_oct_w) + 66, 88, nullptr, c.psa_zr, 450, (int)Rbf, 450, 10, 0);
+        if (c.U) {
+            L.linear(c.rhythm, 32, PRM(c, usa_rl_w), 32, PRM(c, usa_rl_b), c.usa_r17, 17, (int)Rbf, 17, 32, 1);
+            L.linear(c.usa_r17, 17, PRM(c, usa_nl_w) + 65, 82, nullptr, c.usa_zr, 376, (int)Rbf, 376, 17, 0);
+        }
+    }
     L.on(-1);
     if (c.U) {
         // ---------------- combine(pitched, unpitched) for the bars (model.py:766)
@@ -925,17 +948,14 @@ void forward_extract(Launcher &L, Ctx &c) {
     lstm_forward(L, c, c.se_l, c.bars, se_lstm_wih, c.se_h, 192, 0, 0);
     L.take_last(c.se_h, c.se_last, N, B, 192);
     const float *slw = PRM(c, se_lin_w);
-    L.linear(c.F, 51, PRM(c, se_il_w), 51, PRM(c, se_il_b), c.se_a2, 39, NC, 39, 51, 1);
-    L.linear(c.mode, 2, PRM(c, se_ml_w), 2, PRM(c, se_ml_b), c.se_a3, 13, N, 13, 2, 1);
-    L.linear(c.bpm, 1, PRM(c, se_bp_w), 1, PRM(c, se_bp_b), c.se_a4, 7, N, 7, 1, 1);
-    L.linear(c.se_last, 192, slw + 0, 251, nullptr, c.se_z[0], 256, N, 256, 192, 0);
-    L.linear(c.se_a2, 39, slw + 192, 251, nullptr, c.se_z[1], 256, NC, 256, 39, 0);
-    L.linear(c.se_a3, 13, slw + 231, 251, nullptr, c.se_z[2], 256, N, 256, 13, 0);
-    L.linear(c.se_a4, 7, slw + 244, 251, nullptr, c.se_z[3], 256, N, 256, 7, 0);
+    L.linear(c.se_last, 192, slw + 0, 251, nullptr, c.se_z[0], 256, N, 256, 192, 0);     // se_z[1..3]: branch 1, top of this function
     bcast_fwd(L, Dims5{N, C, 1, 1, 1}, 256, PRM(c, se_lin_b), c.se_x, 1,
               {{c.se_z[0], M_N}, {c.se_z[1], M_N | M_C}, {c.se_z[2], M_N}, {c.se_z[3], M_N}});
     { CombineArgs a{}; a.x = c.se_x; a.M = 256; a.n_stride = (long long)C * 256; a.k_stride = 256; a.N = N; a.K = C;
       a.ss = c.se_ss; a.out = c.style; L.combine_fwd(a); }
+    // fused forward: the caller's stream takes what branch 0 has produced so far (rhythm, psa_zr, usa_zr) - recorded NOW, before
+    // forward_song_info queues the SongInfoModel on that branch, so the PitchedStyleApplier does not wait for it
+    if (c.fused) L.wait(-1, 0);
     // ---------------- MelodyEncoder (model.py:252-297); octave+degree weights act as one (120, 112) matrix
     L.on(1);
     const float *mow = PRM(c, me_oct_w);
@@ -963,14 +983,18 @@ void forward_song_info(Launcher &L, Ctx &c) {   // SongInfoModel (model.py:513-5
     const int N = c.N, B = c.B, T = c.T;
     // the two recurrences read the rhythm only: they follow the rhythm encoders on branch 0 while the caller's stream is still
     // in the StyleEncoder (standalone use, mst_model_song_info / _predict_apply: the branch starts from the caller's stream)
-    if (!(L.forked & 1u)) L.wait(0, -1);
+    if (!c.fused && !(L.forked & 1u)) L.wait(0, -1);   // fused: branch 0 carries the rhythm itself
     L.on(0);
     lstm_forward(L, c, c.sim_l1, c.rhythm, sim_bl_wih, c.sim_h1, 9, 0, 0);
     L.take_last(c.sim_h1, c.sim_last1, c.Nb, T, 9);
     lstm_forward(L, c, c.sim_l2, c.sim_last1, sim_br_wih, c.sim_h2, 8, 0, 0);
     L.take_last(c.sim_h2, c.sim_rf, N, B, 8);
-    L.on(-1);
-    L.wait(-1, 0);                                   // the heads read the style (caller's stream) and sim_rf (branch 0)
+    if (c.fused) {
+        L.wait(0, -1);                               // fused forward: the heads stay on branch 0, after the style (caller's stream)
+    } else {
+        L.on(-1);
+        L.wait(-1, 0);                               // the heads read the style (caller's stream) and sim_rf (branch 0)
+    }
     auto head = [&](ParamId sw, ParamId sb, int ks, float *sa, ParamId rw, ParamId rb, int kr, float *ra, ParamId fw, ParamId fb, int nout, float *out) {
         L.linear(c.style, 256, PRM(c, sw), 256, PRM(c, sb), sa, ks, N, ks, 256, 1);
         L.linear(c.sim_rf, 8, PRM(c, rw), 8, PRM(c, rb), ra, kr, N, kr, 8, 1);
@@ -981,6 +1005,7 @@ void forward_song_info(Launcher &L, Ctx &c) {   // SongInfoModel (model.py:513-5
     head(sim_sm_w, sim_sm_b, 2, c.sim_sm, sim_rm_w, sim_rm_b, 2, c.sim_rm, sim_m_w, sim_m_b, 2, c.sim_mode);
     head(sim_sb_w, sim_sb_b, 2, c.sim_sb, sim_rb_w, sim_rb_b, 2, c.sim_rb, sim_b_w, sim_b_b, 1, c.sim_bpm_pre);
     k_bpm_head<<<(N + 63) / 64, 64, 0, L.st>>>(c.sim_bpm_pre, c.sim_bpm, N); L.check();
+    L.on(-1);
 }
 
 // melody_linear / linear of the PitchedStyleApplier into the constant bank (device -> device, stream ordered)
@@ -998,15 +1023,20 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
     const long long Rbf = c.Rbf;
     // style, rhythm (branch 0 unless forward_song_info joined it) and melody (branch 1) meet here; the two appliers are
     // independent of each other: the unpitched one runs on branch 0
-    if (L.forked & 1u) L.wait(-1, 0);
+    // fused forward: the rhythm-only linears were computed on branch 0 (forward_extract) and the caller's stream has already
+    // taken them; branch 0 now holds the SongInfoModel, which nothing here reads
+    if (!c.fused && (L.forked & 1u)) L.wait(-1, 0);
     if (unpitched) {
         // ---------------- UnpitchedStyleApplier (model.py:703-724)
-        L.wait(0, -1); L.on(0);
+        if (!c.fused) L.wait(0, -1);                 // fused: branch 0 waited for the style before the SongInfoModel heads
+        L.on(0);
         const float *nw = PRM(c, usa_nl_w);
         L.linear(c.style, 256, PRM(c, usa_sl_w), 256, PRM(c, usa_sl_b), c.usa_s650, 650, N, 650, 256, 1);
-        L.linear(c.rhythm, 32, PRM(c, usa_rl_w), 32, PRM(c, usa_rl_b), c.usa_r17, 17, (int)Rbf, 17, 32, 1);
         L.linear(c.usa_s650, 65, nw + 0, 82, nullptr, c.usa_zs, 376, N * 10, 376, 65, 0);
-        L.linear(c.usa_r17, 17, nw + 65, 82, nullptr, c.usa_zr, 376, (int)Rbf, 376, 17, 0);
+        if (!c.fused) {
+            L.linear(c.rhythm, 32, PRM(c, usa_rl_w), 32, PRM(c, usa_rl_b), c.usa_r17, 17, (int)Rbf, 17, 32, 1);
+            L.linear(c.usa_r17, 17, nw + 65, 82, nullptr, c.usa_zr, 376, (int)Rbf, 376, 17, 0);
+        }
         UsaArgs a{};
         a.bias = PRM(c, usa_nl_b); a.Wl = PRM(c, usa_lin_w); a.bl = PRM(c, usa_lin_b); a.Zr = c.usa_zr; a.Zs = c.usa_zs;
         a.H = c.usa_h; a.out = c.usa_out; a.N = N; a.B = B; a.T = T;
@@ -1016,11 +1046,13 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
     // ---------------- PitchedStyleApplier (model.py:624-675); octave+degree weights = one (450, 88) matrix
     const float *pow_ = PRM(c, psa_oct_w);
     L.linear(c.style, 256, PRM(c, psa_sl_w), 256, PRM(c, psa_sl_b), c.psa_s66, 66, N, 66, 256, 1);
-    L.linear(c.rhythm, 32, PRM(c, psa_rl_w), 32, PRM(c, psa_rl_b), c.psa_r10, 10, (int)Rbf, 10, 32, 1);
-    L.linear(c.F, 51, PRM(c, psa_il_w), 51, PRM(c, psa_il_b), c.psa_i12, 12, NC, 12, 51, 1);
     L.linear(c.psa_s66, 66, pow_ + 0, 88, nullptr, c.psa_zs, 450, N, 450, 66, 0);
-    L.linear(c.psa_r10, 10, pow_ + 66, 88, nullptr, c.psa_zr, 450, (int)Rbf, 450, 10, 0);
-    L.linear(c.psa_i12, 12, pow_ + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
+    if (!c.fused) {
+        L.linear(c.rhythm, 32, PRM(c, psa_rl_w), 32, PRM(c, psa_rl_b), c.psa_r10, 10, (int)Rbf, 10, 32, 1);
+        L.linear(c.F, 51, PRM(c, psa_il_w), 51, PRM(c, psa_il_b), c.psa_i12, 12, NC, 12, 51, 1);
+        L.linear(c.psa_r10, 10, pow_ + 66, 88, nullptr, c.psa_zr, 450, (int)Rbf, 450, 10, 0);
+        L.linear(c.psa_i12, 12, pow_ + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
+    }
     {
         load_psa_constants(L, c);
         k_psa_zci<<<grid_for((long long)NC * 450), 256, 0, L.st>>>(PRM(c, psa_oct_b), c.psa_zi, c.psa_zs, c.psa_zci, N, C); L.check();
@@ -1036,7 +1068,7 @@ void forward_apply(Launcher &L, Ctx &c, bool unpitched) {
             k_psa_fwd3<<<(int)std::min<long long>((Rbf + kPsaWarps - 1) / kPsaWarps, 148), kPsaWarps * 32, smem, L.st>>>(a); L.check();
         }
     }
-    if (unpitched) L.wait(-1, 0);
+    if (unpitched || c.fused) L.wait(-1, 0);         // the unpitched applier (and, fused, the SongInfoModel heads)
 }
 
 }  // namespace
@@ -1091,6 +1123,7 @@ extern "C" int mst_model_forward(const float *d_params, const MstModelShape *sha
     if (rc) return rc;
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params;
     Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
+    c.fused = true;
     forward_extract(L, c);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);
@@ -1124,6 +1157,7 @@ extern "C" int mst_model_train_step(const float *d_params, float *d_grads, const
     plan_forward(c, ar);
     c.P = d_pitched; c.Ug = d_unpitched; c.F = d_features; c.mode = d_mode; c.bpm = d_bpm; c.prm = d_params; c.grad = d_grads;
     Launcher L; L.bf16 = shape->precision == MST_PRECISION_BF16; L.begin(stream);
+    c.fused = true;
     forward_extract(L, c);
     forward_song_info(L, c);
     forward_apply(L, c, c.U != 0);

@@ -184,10 +184,48 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
     float *d_pce_beats = w.Z(Rb * 64), *d_pce_bars = w.Z(Nb * 128);
     float *d_uce_beats = U ? w.Z(Nb * T * 64) : nullptr, *d_uce_bars = U ? w.Z(Nb * 128) : nullptr;
 
+    // Branch 0: the unpitched applier's backward and the SongInfoModel heads, beside the pitched applier's tail kernels on the
+    // caller's stream.  Both sides add into d_style / d_rhythm: branch 0 first, the pitched applier after the join below.
+    L.wait(0, -1); L.on(0);
+    // ---------------- UnpitchedStyleApplier (model.py:703-724)
+    if (U) {
+        float *dH = w.A(Rbf * 376), *dZs = w.Z((long long)N * 10 * 376);
+        if (!L.dry) {
+            UsaBwdArgs a{};
+            a.f.bias = PRM(c, usa_nl_b); a.f.Wl = PRM(c, usa_lin_w); a.f.bl = PRM(c, usa_lin_b); a.f.Zr = c.usa_zr; a.f.Zs = c.usa_zs;
+            a.f.H = c.usa_h; a.f.out = nullptr; a.f.N = N; a.f.B = B; a.f.T = T;
+            a.target = c.Ug; a.coef = lb.coef_u; a.dHpre = dH; a.gWl = GRD(c, usa_lin_w); a.gbl = GRD(c, usa_lin_b);
+            k_usa_bwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
+        }
+        w.bias_grad(dH, GRD(c, usa_nl_b), Rbf, 376);
+        w.reduce_to(dH, Dims5{N, 1, B, T, 10}, 376, M_N | M_F, dZs);
+        // style branch: a_s = usa_s650 viewed (N*10, 65); its producer is style_linear 256 -> 650 on N rows
+        {
+            float *d_a = w.A((long long)N * 650);
+            w.dw(dZs, 376, c.usa_s650, 65, GRD(c, usa_nl_w), 82, N * 10, 376, 65);
+            L.linear_dx(dZs, 376, PRM(c, usa_nl_w), 82, d_a, 65, N * 10, 376, 65, 0);
+            w.lin_bwd(d_a, c.usa_s650, N, 650, c.style, 256, 256, usa_sl_w, 0, 256, usa_sl_b, d_style, 256, 1);
+        }
+        w.branch_bwd(dH, (int)Rbf, 376, usa_nl_w, 65, 82, c.usa_r17, 17, c.rhythm, 32, 32, usa_rl_w, usa_rl_b, d_rhythm, 32, 1);
+    }
+    // ---------------- SongInfoModel (model.py:513-562)
+    float *d_rf = w.Z((long long)N * 8);
+    {
+        auto head = [&](float *dOut, int nout, ParamId sw, ParamId sb, int ks, const float *sa, ParamId rw, ParamId rb, int kr,
+                        const float *ra, ParamId fw, ParamId fb) {
+            w.bias_grad(dOut, GRD(c, fb), N, nout);
+            w.branch_bwd(dOut, N, nout, fw, 0, ks + kr, sa, ks, c.style, 256, 256, sw, sb, d_style, 256, 1);
+            w.branch_bwd(dOut, N, nout, fw, ks, ks + kr, ra, kr, c.sim_rf, 8, 8, rw, rb, d_rf, 8, 1);
+        };
+        head(lb.d_instr, 41, sim_si_w, sim_si_b, 8, c.sim_si, sim_ri_w, sim_ri_b, 10, c.sim_ri, sim_i_w, sim_i_b);
+        head(lb.d_mode, 2, sim_sm_w, sim_sm_b, 2, c.sim_sm, sim_rm_w, sim_rm_b, 2, c.sim_rm, sim_m_w, sim_m_b);
+        head(lb.d_bpm_pre, 1, sim_sb_w, sim_sb_b, 2, c.sim_sb, sim_rb_w, sim_rb_b, 2, c.sim_rb, sim_b_w, sim_b_b);
+    }
+    L.on(-1);
     // ---------------- PitchedStyleApplier (model.py:624-675)
     float *d_melody = w.A(Rbf * 448);
+    float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
     {
-        float *dZr = w.A(Rbf * 450), *dZi = w.Z((long long)NC * 450), *dZs = w.A((long long)N * 450);
         // the tcgen05 formulation of this backward (k_psa_bwd_tc, mst_model_psa_tc.cuh): on request only, see Launcher::psa_bwd_tc
         const bool tc_tail = L.psa_bwd_tc() && ptc_bwd_smem(C) <= 72 * 1024;
         if (!L.dry && tc_tail) {
@@ -228,43 +266,40 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
         }
         L.reduce_mid(dZi, dZs, N, C, 450, 0);
         w.bias_grad(dZs, GRD(c, psa_oct_b), N, 450);
+    }
+    // ---------------- MelodyEncoder (model.py:252-297) on branch 1: it needs d_melody only.  What it adds to d_pce_beats / d_pce_bars
+    // lands before the PitchedRhythmEncoder's contributions (the caller's stream joins branch 1 in front of that block); its staged
+    // reductions use a scratch pair of their own.
+    L.wait(1, -1); L.on(1);
+    {
+        float *keepA = w.tmpA, *keepB = w.tmpB;
+        w.tmpA = w.A(Rb * 120); w.tmpB = w.A(Rb * 120);
+        float *stats = w.Z((long long)N * (C + 1)), *dod = w.A(Rb * 120), *dsum = w.A((long long)N * B * T * 448);
+        if (!L.dry) {
+            MeArgs2 a = me_args(c);
+            a.dmelody = d_melody; a.dsum = dsum; a.stats = stats; a.dod = dod;
+            a.gWc = GRD(c, me_ch_w); a.gbc = GRD(c, me_ch_b); a.gWl = GRD(c, me_lin_w); a.gbl = GRD(c, me_lin_b);
+            k_me_bwd_stats2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
+            k_me_bwd2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 4), 256, 0, L.st>>>(a); L.check();
+            k_me_bwd_cells<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 2), 256, 0, L.st>>>(a); L.check();
+        }
+        const Dims5 d{N, C, B, T, 1};
+        float *dz1 = w.Z(Nb * 120), *dz2 = w.Z((long long)NC * 120);
+        w.bias_grad(dod, GRD(c, me_oct_b), Rb, 120);
+        w.reduce_to(dod, d, 120, M_N | M_B, dz1);
+        w.reduce_to(dod, d, 120, M_N | M_C, dz2);
+        w.branch_bwd(dod, (int)Rb, 120, me_oct_w, 0, 112, c.me_a1, 36, c.pce_beats, 64, 64, me_bl_w, me_bl_b, d_pce_beats, 64, 1);
+        w.branch_bwd(dz1, (int)Nb, 120, me_oct_w, 36, 112, c.me_a2, 68, c.pce_bars, 128, 128, me_br_w, me_br_b, d_pce_bars, 128, 1);
+        w.branch_bwd(dz2, NC, 120, me_oct_w, 104, 112, c.me_a3, 8, c.F, 51, 51, me_il_w, me_il_b, nullptr, 0, 0);
+        w.tmpA = keepA; w.tmpB = keepB;
+    }
+    L.on(-1);
+    // the style / rhythm gradients of branch 0 (unpitched applier, SongInfoModel heads) are in: the pitched applier adds its own
+    L.wait(-1, 0);
+    {
         w.branch_bwd(dZs, N, 450, psa_oct_w, 0, 88, c.psa_s66, 66, c.style, 256, 256, psa_sl_w, psa_sl_b, d_style, 256, 1);
         w.branch_bwd(dZr, (int)Rbf, 450, psa_oct_w, 66, 88, c.psa_r10, 10, c.rhythm, 32, 32, psa_rl_w, psa_rl_b, d_rhythm, 32, 1);
         w.branch_bwd(dZi, NC, 450, psa_oct_w, 76, 88, c.psa_i12, 12, c.F, 51, 51, psa_il_w, psa_il_b, nullptr, 0, 0);
-    }
-    // ---------------- UnpitchedStyleApplier (model.py:703-724)
-    if (U) {
-        float *dH = w.A(Rbf * 376), *dZs = w.Z((long long)N * 10 * 376);
-        if (!L.dry) {
-            UsaBwdArgs a{};
-            a.f.bias = PRM(c, usa_nl_b); a.f.Wl = PRM(c, usa_lin_w); a.f.bl = PRM(c, usa_lin_b); a.f.Zr = c.usa_zr; a.f.Zs = c.usa_zs;
-            a.f.H = c.usa_h; a.f.out = nullptr; a.f.N = N; a.f.B = B; a.f.T = T;
-            a.target = c.Ug; a.coef = lb.coef_u; a.dHpre = dH; a.gWl = GRD(c, usa_lin_w); a.gbl = GRD(c, usa_lin_b);
-            k_usa_bwd<<<(int)std::min<long long>((Rbf + kUsaWarps - 1) / kUsaWarps, 148 * 4), kUsaWarps * 32, 0, L.st>>>(a); L.check();
-        }
-        w.bias_grad(dH, GRD(c, usa_nl_b), Rbf, 376);
-        w.reduce_to(dH, Dims5{N, 1, B, T, 10}, 376, M_N | M_F, dZs);
-        // style branch: a_s = usa_s650 viewed (N*10, 65); its producer is style_linear 256 -> 650 on N rows
-        {
-            float *d_a = w.A((long long)N * 650);
-            w.dw(dZs, 376, c.usa_s650, 65, GRD(c, usa_nl_w), 82, N * 10, 376, 65);
-            L.linear_dx(dZs, 376, PRM(c, usa_nl_w), 82, d_a, 65, N * 10, 376, 65, 0);
-            w.lin_bwd(d_a, c.usa_s650, N, 650, c.style, 256, 256, usa_sl_w, 0, 256, usa_sl_b, d_style, 256, 1);
-        }
-        w.branch_bwd(dH, (int)Rbf, 376, usa_nl_w, 65, 82, c.usa_r17, 17, c.rhythm, 32, 32, usa_rl_w, usa_rl_b, d_rhythm, 32, 1);
-    }
-    // ---------------- SongInfoModel (model.py:513-562)
-    float *d_rf = w.Z((long long)N * 8);
-    {
-        auto head = [&](float *dOut, int nout, ParamId sw, ParamId sb, int ks, const float *sa, ParamId rw, ParamId rb, int kr,
-                        const float *ra, ParamId fw, ParamId fb) {
-            w.bias_grad(dOut, GRD(c, fb), N, nout);
-            w.branch_bwd(dOut, N, nout, fw, 0, ks + kr, sa, ks, c.style, 256, 256, sw, sb, d_style, 256, 1);
-            w.branch_bwd(dOut, N, nout, fw, ks, ks + kr, ra, kr, c.sim_rf, 8, 8, rw, rb, d_rf, 8, 1);
-        };
-        head(lb.d_instr, 41, sim_si_w, sim_si_b, 8, c.sim_si, sim_ri_w, sim_ri_b, 10, c.sim_ri, sim_i_w, sim_i_b);
-        head(lb.d_mode, 2, sim_sm_w, sim_sm_b, 2, c.sim_sm, sim_rm_w, sim_rm_b, 2, c.sim_rm, sim_m_w, sim_m_b);
-        head(lb.d_bpm_pre, 1, sim_sb_w, sim_sb_b, 2, c.sim_sb, sim_rb_w, sim_rb_b, 2, c.sim_rb, sim_b_w, sim_b_b);
     }
     // ---------------- StyleEncoder (model.py:179-200) on branch 0: d_style is complete once the heads above are through, and
     // the backward of its 192-wide recurrence is the longest serial kernel of the step; the caller's stream meanwhile runs the
@@ -300,26 +335,6 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
         L.put_last(d_last1, d_h1, Nb, T, 9);
         w.lstm_bwd(c.sim_l1, d_h1, 9, 0, 0, c.rhythm, sim_bl_wih, sim_bl_whh, sim_bl_bih, sim_bl_bhh, d_rhythm, 1);
     }
-    // ---------------- MelodyEncoder (model.py:252-297)
-    {
-        float *stats = w.Z((long long)N * (C + 1)), *dod = w.A(Rb * 120), *dsum = w.A((long long)N * B * T * 448);
-        if (!L.dry) {
-            MeArgs2 a = me_args(c);
-            a.dmelody = d_melody; a.dsum = dsum; a.stats = stats; a.dod = dod;
-            a.gWc = GRD(c, me_ch_w); a.gbc = GRD(c, me_ch_b); a.gWl = GRD(c, me_lin_w); a.gbl = GRD(c, me_lin_b);
-            k_me_bwd_stats2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
-            k_me_bwd2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 4), 256, 0, L.st>>>(a); L.check();
-            k_me_bwd_cells<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 2), 256, 0, L.st>>>(a); L.check();
-        }
-        const Dims5 d{N, C, B, T, 1};
-        float *dz1 = w.Z(Nb * 120), *dz2 = w.Z((long long)NC * 120);
-        w.bias_grad(dod, GRD(c, me_oct_b), Rb, 120);
-        w.reduce_to(dod, d, 120, M_N | M_B, dz1);
-        w.reduce_to(dod, d, 120, M_N | M_C, dz2);
-        w.branch_bwd(dod, (int)Rb, 120, me_oct_w, 0, 112, c.me_a1, 36, c.pce_beats, 64, 64, me_bl_w, me_bl_b, d_pce_beats, 64, 1);
-        w.branch_bwd(dz1, (int)Nb, 120, me_oct_w, 36, 112, c.me_a2, 68, c.pce_bars, 128, 128, me_br_w, me_br_b, d_pce_bars, 128, 1);
-        w.branch_bwd(dz2, NC, 120, me_oct_w, 104, 112, c.me_a3, 8, c.F, 51, 51, me_il_w, me_il_b, nullptr, 0, 0);
-    }
     // ---------------- combine(pitched, unpitched) of the rhythm (model.py:767)
     float *d_pre_out, *d_ure_out = nullptr;
     if (U) {
@@ -349,6 +364,7 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
             w.branch_bwd(dz3, N, 32, ure_lin_w, 104, 109, c.ure_a4, 5, c.bpm, 1, 1, ure_bp_w, ure_bp_b, nullptr, 0, 0);
         }
     }
+    L.wait(-1, 1);                                   // MelodyEncoder's contributions to d_pce_beats / d_pce_bars are in
     // ---------------- PitchedRhythmEncoder (model.py:346-381)
     {
         const Dims5 d{N, C, B, T, 10};

@@ -72,7 +72,15 @@ k_lstm_fwd_cl(LstmArgs a) {
         {
             const float *h0 = h_full + (cur * kClG + 0) * H, *h1 = h_full + (cur * kClG + 1) * H;
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
-            if (KR) {
+            if (KR && ng == 1) {
+                // one sequence in the cluster (N = 1, the reference's batch size): half the loads and FMAs per step
+#pragma unroll
+                for (int i = 0; i < KR; i += 4) {
+                    const float4 x0 = *reinterpret_cast<const float4 *>(h0 + k_lo + i);
+                    a0 = fmaf(wr[i], x0.x, a0); a1 = fmaf(wr[i + 1], x0.y, a1);
+                    a0 = fmaf(wr[i + 2], x0.z, a0); a1 = fmaf(wr[i + 3], x0.w, a1);
+                }
+            } else if (KR) {
 #pragma unroll
                 for (int i = 0; i < KR; i += 4) {
                     const float4 x0 = *reinterpret_cast<const float4 *>(h0 + k_lo + i), x1 = *reinterpret_cast<const float4 *>(h1 + k_lo + i);
@@ -94,6 +102,7 @@ k_lstm_fwd_cl(LstmArgs a) {
             part_s[(part * kClG + 1) * LC + col] = b0 + b1;
         }
         __syncthreads();
+        float act_v = 0.f;
         if (act_thread) {
             float v = xcur;
 #pragma unroll
@@ -101,29 +110,39 @@ k_lstm_fwd_cl(LstmArgs a) {
             const int gate = acol / HQ;
             v = gate == 2 ? tanhf(v) : sigmoidf(v);
             g_loc[ag * LC + acol] = v;
-            a.gates[((long long)(s0 + ag) * a.T + t) * H4 + a_gc] = v;
+            act_v = v;
         }
         __syncthreads();
-        if (j < kClG * HQ) {
+        // the new h goes to every CTA of the cluster first and the barrier is ARRIVED at right after it; the saved tensors are
+        // written to global memory between arrive and wait, so the barrier's release does not have to wait for those stores
+        const bool cell_thread = j < kClG * HQ && j / HQ < ng;
+        float sv_hprev = 0.f, sv_c = 0.f, sv_h = 0.f;
+        if (cell_thread) {
             const int g = j / HQ, u = j - g * HQ;
-            if (g < ng) {
-                const int unit = rank * HQ + u;
-                const float *gs = g_loc + g * LC;
-                const long long row = (long long)(s0 + g) * a.T + t;
-                a.hprev[row * H + unit] = h_full[(cur * kClG + g) * H + unit];
-                const float c = gs[HQ + u] * c_loc[j] + gs[u] * gs[2 * HQ + u];
-                const float h = gs[3 * HQ + u] * tanhf(c);
-                c_loc[j] = c;
-                a.cells[row * H + unit] = c;
-                a.out[row * a.out_ld + a.out_off + unit] = h;
+            const int unit = rank * HQ + u;
+            const float *gs = g_loc + g * LC;
+            sv_hprev = h_full[(cur * kClG + g) * H + unit];
+            const float c = gs[HQ + u] * c_loc[j] + gs[u] * gs[2 * HQ + u];
+            const float h = gs[3 * HQ + u] * tanhf(c);
+            c_loc[j] = c;
+            sv_c = c; sv_h = h;
 #pragma unroll
-                for (int rr = 0; rr < kClSize; rr++) {
-                    float *remote = cluster.map_shared_rank(h_full, rr);
-                    remote[((cur ^ 1) * kClG + g) * H + unit] = h;
-                }
+            for (int rr = 0; rr < kClSize; rr++) {
+                float *remote = cluster.map_shared_rank(h_full, rr);
+                remote[((cur ^ 1) * kClG + g) * H + unit] = h;
             }
         }
-        cluster.sync();
+        cluster.barrier_arrive();
+        if (act_thread) a.gates[((long long)(s0 + ag) * a.T + t) * H4 + a_gc] = act_v;
+        if (cell_thread) {
+            const int g = j / HQ, u = j - g * HQ;
+            const int unit = rank * HQ + u;
+            const long long row = (long long)(s0 + g) * a.T + t;
+            a.hprev[row * H + unit] = sv_hprev;
+            a.cells[row * H + unit] = sv_c;
+            a.out[row * a.out_ld + a.out_off + unit] = sv_h;
+        }
+        cluster.barrier_wait();
         cur ^= 1;
     }
 }
@@ -155,40 +174,66 @@ k_lstm_bwd_cl(LstmArgs a) {
         for (int i = 0; i < KR; i++) wr[i] = a.w[(long long)(r_lo + i) * H + rank * HQ + ku];
     }
     int cur = 0;
-    for (int step = a.T - 1; step >= 0; step--) {
+    // cell threads: the saved tensors of a step (4 gates, cell, previous cell, upstream gradient) do not depend on the
+    // recurrence - they are loaded one step ahead, so that their L2 latency is off the per-step critical path
+    const bool cell_thread = j < kClG * HQ && j / HQ < ng;
+    const int cg_ = j / HQ, cu_ = j - cg_ * HQ, cunit = rank * HQ + cu_;
+    float n_gi = 0.f, n_gf = 0.f, n_gg = 0.f, n_go = 0.f, n_c = 0.f, n_cprev = 0.f, n_dout = 0.f;
+    auto fetch = [&](int step) {
         const int t = a.reverse ? a.T - 1 - step : step;
         const int t_prev = a.reverse ? t + 1 : t - 1;
+        const long long row = (long long)(s0 + cg_) * a.T + t;
+        const float *gs = a.gates + row * H4;
+        n_gi = gs[cunit]; n_gf = gs[H + cunit]; n_gg = gs[2 * H + cunit]; n_go = gs[3 * H + cunit];
+        n_c = a.cells[row * H + cunit];
+        n_cprev = step > 0 ? a.cells[((long long)(s0 + cg_) * a.T + t_prev) * H + cunit] : 0.f;
+        n_dout = a.dout ? a.dout[row * a.out_ld + a.out_off + cunit] : 0.f;
+    };
+    if (cell_thread && a.T > 0) fetch(a.T - 1);
+    for (int step = a.T - 1; step >= 0; step--) {
+        const int t = a.reverse ? a.T - 1 - step : step;
+        float sv_i = 0.f, sv_f = 0.f, sv_g = 0.f, sv_o = 0.f;
         if (j < kClG * HQ) {
             const int g = j / HQ, u = j - g * HQ;
             if (g < ng) {
                 const int unit = rank * HQ + u;
-                const long long row = (long long)(s0 + g) * a.T + t;
-                const float *gs = a.gates + row * H4;
-                const float gi = gs[unit], gf = gs[H + unit], gg = gs[2 * H + unit], go = gs[3 * H + unit];
-                const float c = a.cells[row * H + unit];
-                const float c_prev = step > 0 ? a.cells[((long long)(s0 + g) * a.T + t_prev) * H + unit] : 0.f;
+                const float gi = n_gi, gf = n_gf, gg = n_gg, go = n_go, c = n_c, c_prev = n_cprev, dout_v = n_dout;
                 const float tc = tanhf(c);
-                const float dh = dh_loc[j] + (a.dout ? a.dout[row * a.out_ld + a.out_off + unit] : 0.f);
+                const float dh = dh_loc[j] + dout_v;
                 const float dc = dc_loc[j] + dh * go * (1.f - tc * tc);
                 const float d_i = dc * gg * gi * (1.f - gi);
                 const float d_f = dc * c_prev * gf * (1.f - gf);
                 const float d_g = dc * gi * (1.f - gg * gg);
                 const float d_o = dh * tc * go * (1.f - go);
                 dc_loc[j] = dc * gf;
-                float *dgo = a.dgates + row * H4;
-                dgo[unit] = d_i; dgo[H + unit] = d_f; dgo[2 * H + unit] = d_g; dgo[3 * H + unit] = d_o;
 #pragma unroll
                 for (int rr = 0; rr < kClSize; rr++) {
                     float *remote = cluster.map_shared_rank(dg_full, rr) + (cur * kClG + g) * H4;
                     remote[unit] = d_i; remote[H + unit] = d_f; remote[2 * H + unit] = d_g; remote[3 * H + unit] = d_o;
                 }
+                sv_i = d_i; sv_f = d_f; sv_g = d_g; sv_o = d_o;
             }
         }
-        cluster.sync();
+        // arrive right after the distributed-shared-memory stores; the global stores of the gate gradients and the loads of the
+        // next step's saved tensors go between arrive and wait (the barrier's release need not wait for them)
+        cluster.barrier_arrive();
+        if (cell_thread) {
+            float *dgo = a.dgates + ((long long)(s0 + cg_) * a.T + t) * H4;
+            dgo[cunit] = sv_i; dgo[H + cunit] = sv_f; dgo[2 * H + cunit] = sv_g; dgo[3 * H + cunit] = sv_o;
+            if (step > 0) fetch(step - 1);                // consumed at the top of the next step
+        }
+        cluster.barrier_wait();
         {   // dh_{step-1}[own units] = W_hh[:, own units]^T . dgates
             const float *d0 = dg_full + (cur * kClG + 0) * H4, *d1 = dg_full + (cur * kClG + 1) * H4;
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
-            if (KR) {
+            if (KR && ng == 1) {
+#pragma unroll
+                for (int i = 0; i < KR; i += 4) {
+                    const float4 x0 = *reinterpret_cast<const float4 *>(d0 + r_lo + i);
+                    a0 = fmaf(wr[i], x0.x, a0); a1 = fmaf(wr[i + 1], x0.y, a1);
+                    a0 = fmaf(wr[i + 2], x0.z, a0); a1 = fmaf(wr[i + 3], x0.w, a1);
+                }
+            } else if (KR) {
 #pragma unroll
                 for (int i = 0; i < KR; i += 4) {
                     const float4 x0 = *reinterpret_cast<const float4 *>(d0 + r_lo + i), x1 = *reinterpret_cast<const float4 *>(d1 + r_lo + i);

@@ -402,3 +402,52 @@ extern "C" int64_t mst_smf_write_events(const MstEvent *events, uint64_t n_event
     if (!out || w.n > capacity) return MST_E_CAPACITY;
     return (int64_t)w.n;
 }
+
+// ------------------------------------------------------------------------------------------------
+// mst_files_read_batch: the files of a batch, read as they are into one (page-locked) buffer for the device-side parser
+// (mst_encode_batch_smf_async).  Sizes first (stat), then the reads on a thread pool; an unreadable file gets n_bytes = 0
+// and status -1 (OSError in the reference's load_midi_from_file -> the file is skipped; here the device parser reports
+// MST_SONG_LOAD_FAILED for a 0-byte file).  Files start on 16-byte boundaries.
+// ------------------------------------------------------------------------------------------------
+extern "C" int mst_files_read_batch(const char *const *paths, uint32_t n_files, int32_t n_threads, uint8_t *h_bytes,
+                                    uint64_t capacity, MstFileIn *h_files, int32_t *h_status, uint64_t *n_bytes_total) {
+    if (!paths || !h_files || !h_status || !n_bytes_total || (!h_bytes && capacity)) return MST_E_INVALID;
+    *n_bytes_total = 0;
+    if (n_files == 0) return MST_OK;
+    uint64_t total = 0;
+    for (uint32_t i = 0; i < n_files; i++) {
+        h_status[i] = -1;
+        h_files[i].byte_offset = total; h_files[i].n_bytes = 0; h_files[i].reserved = 0;
+        FILE *f = paths[i] ? fopen(paths[i], "rb") : nullptr;
+        if (!f) continue;
+        long size = -1;
+        if (fseek(f, 0, SEEK_END) == 0) size = ftell(f);
+        fclose(f);
+        if (size < 0 || (uint64_t)size >= 0xFFFFFFFFull) continue;
+        h_files[i].n_bytes = (uint32_t)size;
+        h_status[i] = 0;
+        total += ((uint64_t)size + 15) & ~15ull;
+    }
+    *n_bytes_total = total;
+    if (total > capacity) return MST_E_CAPACITY;
+    unsigned nt = n_threads > 0 ? (unsigned)n_threads : std::thread::hardware_concurrency();
+    if (nt == 0) nt = 1;
+    if (nt > n_files) nt = n_files;
+    std::atomic<uint32_t> next(0);
+    auto worker = [&]() {
+        for (;;) {
+            const uint32_t i = next.fetch_add(1);
+            if (i >= n_files) return;
+            if (h_status[i] != 0 || h_files[i].n_bytes == 0) continue;
+            FILE *f = fopen(paths[i], "rb");
+            size_t got = 0;
+            if (f) { got = fread(h_bytes + h_files[i].byte_offset, 1, h_files[i].n_bytes, f); fclose(f); }
+            if (got != h_files[i].n_bytes) { h_files[i].n_bytes = 0; h_status[i] = -1; }   // changed under us: treated as unreadable
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < nt; t++) pool.emplace_back(worker);
+    worker();
+    for (auto &t : pool) t.join();
+    return MST_OK;
+}

@@ -47,6 +47,7 @@ EVENT_DTYPE = np.dtype([
 assert EVENT_DTYPE.itemsize == 16
 
 SONG_IN_DTYPE = np.dtype([('event_offset', '<u8'), ('n_events', '<u4'), ('ticks_per_beat', '<i4')])
+FILE_IN_DTYPE = np.dtype([('byte_offset', '<u8'), ('n_bytes', '<u4'), ('reserved', '<u4')])      # MstFileIn
 assert SONG_IN_DTYPE.itemsize == 16
 
 FILTER_DTYPE = np.dtype([

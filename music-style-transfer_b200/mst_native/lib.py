@@ -23,6 +23,8 @@ EXPORTS = [
     'mst_encode_workspace_bytes', 'mst_encode_batch_device',
     'mst_encode_host_workspace_bytes', 'mst_encode_batch_host', 'mst_encode_batch_host_async',
     'mst_events_pack', 'mst_encode_packed_workspace_bytes', 'mst_encode_batch_packed_async',
+    'mst_files_read_batch', 'mst_smf_parse_device_workspace_bytes', 'mst_smf_parse_batch_device',
+    'mst_encode_smf_workspace_bytes', 'mst_encode_batch_smf_async',
     'mst_decode_workspace_bytes', 'mst_decode_batch_device', 'mst_smf_write', 'mst_transfer_select',
     'mst_model_param_count', 'mst_model_param_name', 'mst_model_param_numel', 'mst_model_param_offset',
     'mst_model_workspace_bytes', 'mst_model_forward', 'mst_model_train_step', 'mst_model_predict_apply', 'mst_model_song_info', 'mst_model_backward', 'mst_model_loss_workspace_bytes',
@@ -81,6 +83,21 @@ def load():
     L.mst_encode_packed_workspace_bytes.argtypes = [ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint64]
     L.mst_encode_batch_packed_async.restype = ctypes.c_int
     L.mst_encode_batch_packed_async.argtypes = L.mst_encode_batch_host_async.argtypes
+    L.mst_files_read_batch.restype = ctypes.c_int
+    L.mst_files_read_batch.argtypes = [ctypes.POINTER(ctypes.c_char_p), ctypes.c_uint32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_uint64,
+                                       ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64)]
+    L.mst_smf_parse_device_workspace_bytes.restype = ctypes.c_size_t
+    L.mst_smf_parse_device_workspace_bytes.argtypes = [ctypes.c_uint64, ctypes.c_uint32]
+    L.mst_smf_parse_batch_device.restype = ctypes.c_int
+    L.mst_smf_parse_batch_device.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p,
+                                             ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64),
+                                             ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    L.mst_encode_smf_workspace_bytes.restype = ctypes.c_size_t
+    L.mst_encode_smf_workspace_bytes.argtypes = [ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint64]
+    L.mst_encode_batch_smf_async.restype = ctypes.c_int
+    L.mst_encode_batch_smf_async.argtypes = [
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+        ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
     L.mst_decode_workspace_bytes.restype = ctypes.c_size_t
     L.mst_decode_workspace_bytes.argtypes = [ctypes.c_uint32, ctypes.c_uint64, ctypes.c_uint64]
     L.mst_decode_batch_device.restype = ctypes.c_int
@@ -151,6 +168,92 @@ def smf_load_batch(paths, events_out, songs_out=None, status_out=None, n_threads
         raise e
     check(rc)
     return int(total.value), songs, status
+
+
+def files_read_batch(paths, bytes_out, files_out=None, status_out=None, n_threads=0):
+    """Read `paths` as they are into `bytes_out` (uint8 ndarray, ideally a view of page-locked memory) on a C++ thread pool.
+    Returns (n_bytes_total, files ndarray[FILE_IN_DTYPE], status int32 ndarray) or raises MstError carrying `.needed`."""
+    L = load()
+    n = len(paths)
+    files = np.zeros(n, dtype=abi.FILE_IN_DTYPE) if files_out is None else files_out[:n]
+    status = np.zeros(n, dtype=np.int32) if status_out is None else status_out[:n]
+    arr = (ctypes.c_char_p * max(n, 1))(*[os.fsencode(p) for p in paths])
+    total = ctypes.c_uint64(0)
+    rc = L.mst_files_read_batch(arr, n, int(n_threads), _np_ptr(bytes_out), len(bytes_out), _np_ptr(files), _np_ptr(status),
+                                ctypes.byref(total))
+    if rc == -3:
+        e = MstError(f'byte buffer too small: {total.value} bytes needed')
+        e.needed = int(total.value)
+        raise e
+    check(rc)
+    return int(total.value), files, status
+
+
+def concat_files(blobs):
+    """[bytes, ...] -> (uint8 ndarray of the files on 16-byte boundaries, files ndarray[FILE_IN_DTYPE]): the batch buffer of
+    mst_encode_batch_smf_async for files already in memory."""
+    files = np.zeros(len(blobs), dtype=abi.FILE_IN_DTYPE)
+    off = 0
+    for i, b in enumerate(blobs):
+        files[i]['byte_offset'], files[i]['n_bytes'] = off, len(b)
+        off += (len(b) + 15) & ~15
+    buf = np.zeros(max(off, 1), dtype=np.uint8)
+    for i, b in enumerate(blobs):
+        o = int(files[i]['byte_offset'])
+        buf[o:o + len(b)] = np.frombuffer(bytes(b), dtype=np.uint8)
+    return buf, files
+
+
+def smf_parse_device(blobs):
+    """Parse files given as raw bytes ON THE DEVICE (mst_smf_parse_batch_device).  Returns [(events, ticks_per_beat) or None]
+    per file, exactly what smf_parse returns for each."""
+    import torch
+    L = require_gpu()
+    buf, files = concat_files(blobs)
+    n = len(blobs)
+    ws = torch.empty(L.mst_smf_parse_device_workspace_bytes(len(buf), n), dtype=torch.uint8, device='cuda')
+    events = np.empty(len(buf) // 2 + 1, dtype=abi.EVENT_DTYPE)
+    songs = np.zeros(n, dtype=abi.SONG_IN_DTYPE)
+    status = np.zeros(n, dtype=np.int32)
+    total = ctypes.c_uint64(0)
+    check(L.mst_smf_parse_batch_device(_np_ptr(buf), len(buf), _np_ptr(files), n, _np_ptr(events), len(events), _np_ptr(songs),
+                                       _np_ptr(status), ctypes.byref(total), ws.data_ptr(), ws.numel(),
+                                       torch.cuda.current_stream().cuda_stream))
+    out = []
+    for i in range(n):
+        if status[i] != 0:
+            out.append(None)
+        else:
+            o, c = int(songs[i]['event_offset']), int(songs[i]['n_events'])
+            out.append((events[o:o + c].copy(), int(songs[i]['ticks_per_beat'])))
+    return out
+
+
+def encode_smf(blobs, filt=None, arena_floats=None):
+    """Encode files given as raw SMF bytes through mst_encode_batch_smf_async (device-side parse).  Synchronous convenience
+    wrapper for tests and small jobs: returns (infos ndarray[SONG_INFO_DTYPE], arena CUDA tensor)."""
+    import torch
+    L = require_gpu()
+    buf, files = concat_files(blobs)
+    n = len(blobs)
+    if filt is None:
+        filt = abi.make_filter(None, 0, 0)
+    filt = np.ascontiguousarray(filt).reshape(1)
+    infos = np.zeros(n, dtype=abi.SONG_INFO_DTYPE)
+    if arena_floats is None:
+        # planning pass (no arena) for the sizes, then the real pass
+        ws0 = torch.empty(L.mst_encode_smf_workspace_bytes(len(buf), n, 0), dtype=torch.uint8, device='cuda')
+        check(L.mst_encode_batch_smf_async(_np_ptr(buf), len(buf), _np_ptr(files), n, _np_ptr(filt), _np_ptr(infos), None, 0,
+                                           ws0.data_ptr(), ws0.numel(), torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        arena_floats = max(1, sum(grid_floats(r) for r in infos if r['status'] in (abi.SONG_OK, abi.SONG_ARENA_FULL)))
+        del ws0
+    arena = torch.empty(int(arena_floats), dtype=torch.float32, device='cuda')
+    ws = torch.empty(L.mst_encode_smf_workspace_bytes(len(buf), n, arena.numel()), dtype=torch.uint8, device='cuda')
+    check(L.mst_encode_batch_smf_async(_np_ptr(buf), len(buf), _np_ptr(files), n, _np_ptr(filt), _np_ptr(infos), arena.data_ptr(),
+                                       arena.numel(), ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    return infos, arena
 
 
 def events_pack(events, out=None):

@@ -205,3 +205,37 @@ def test_create_midi_matches_reference_bytes():
             chans.append({'channel_id': ch, 'instrument_id': prog, 'messages': msgs})
         got = create_midi(i2, *chans, max_delta_time=float(G[f'{ci}/max_delta_time']))
         assert got.data == bytes(G[f'{ci}/bytes']), ci
+
+
+@pytest.mark.refcheck
+def test_train_script_is_the_reference_script_modulo_documented_lines():
+    """music-style-transfer_b200/train-model.py claims to be the reference's script (same hyper-parameters, same loop): the
+    only differences allowed are the docstring, the flatten_dict import / call (third-party package not needed) and the two
+    environment overrides of data_path / n_iterations.  Needs /root/reference (build container only)."""
+    import difflib
+    ref_path = '/root/reference/train-model.py'
+    if not os.path.exists(ref_path):
+        pytest.skip('/root/reference is not present on this machine')
+    here = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'music-style-transfer_b200', 'train-model.py')
+    ref = [l.rstrip() for l in open(ref_path).read().splitlines()]
+    ours = [l.rstrip() for l in open(here).read().splitlines()]
+    removed, added = [], []
+    for l in difflib.ndiff(ref, ours):
+        if l.startswith('- '):
+            removed.append(l[2:].strip())
+        elif l.startswith('+ '):
+            added.append(l[2:].strip())
+    assert removed == [
+        'from flatten_dict import flatten as flatten_dict',
+        'from style.utils.data import save_to_csv, assert_dir',
+        "data_path = 'data/Lakh MIDI Dataset/clean_midi/'",
+        'n_iterations = 5000',
+        "losses = flatten_dict(losses, reducer='underscore')",
+    ], removed
+    code_added = [l for l in added if l and not l.startswith('"""') and 'drop-in package' not in l and 'third-party' not in l]
+    assert code_added == [
+        'from style.utils.data import save_to_csv, assert_dir, flatten_dict',
+        "data_path = os.environ.get('MST_DATA_PATH', 'data/Lakh MIDI Dataset/clean_midi/')",
+        "n_iterations = int(os.environ.get('MST_N_ITERATIONS', 5000))",
+        'losses = flatten_dict(losses)',
+    ], code_added

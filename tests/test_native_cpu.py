@@ -163,3 +163,34 @@ def test_smf_parse_hostile_lengths_terminate(L):
     ]
     for data in cases:
         assert lib.smf_parse(data) is None
+
+
+def test_files_read_batch_reads_files_as_they_are(tmp_path):
+    """mst_files_read_batch: raw bytes on 16-byte boundaries, unreadable files as 0 bytes + status -1, capacity error with
+    the needed size."""
+    import numpy as np
+    from mst_native import lib
+    blobs = [bytes(range(200)) * 3, b'MThd', b'', bytes(17)]
+    paths = []
+    for i, b in enumerate(blobs):
+        p = tmp_path / f'f{i}.bin'
+        p.write_bytes(b)
+        paths.append(str(p))
+    paths.insert(2, str(tmp_path / 'missing.mid'))
+    blobs.insert(2, None)
+    buf = np.full(4096, 0xEE, dtype=np.uint8)
+    total, files, status = lib.files_read_batch(paths, buf, n_threads=3)
+    assert list(status) == [0, 0, -1, 0, 0]
+    end = 0
+    for i, b in enumerate(blobs):
+        o, n = int(files[i]['byte_offset']), int(files[i]['n_bytes'])
+        assert o % 16 == 0 and o >= end
+        if b is None:
+            assert n == 0
+            continue
+        assert n == len(b) and buf[o:o + n].tobytes() == b
+        end = o + n
+    assert total >= end and total % 16 == 0
+    with pytest.raises(lib.MstError) as e:
+        lib.files_read_batch(paths, np.zeros(64, dtype=np.uint8))
+    assert e.value.needed == total
