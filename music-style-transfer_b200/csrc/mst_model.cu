@@ -252,7 +252,8 @@ inline int grid_for(long long n, int threads = 256, int cap = 148 * 16) {
 // CUDA graph capture of the call records the branches as parallel graph nodes.  One set per (device, caller stream): two
 // callers on different streams never share side streams (a capture on one must not swallow the other's launches).
 // MST_MODEL_STREAMS=0 keeps everything on the caller's stream.
-constexpr int kSideStreams = 3, kSideEvents = 32;
+constexpr int kSideStreams = 4, kSideEvents = 32;
+constexpr int kBranchSim = 3;        // backward of the SongInfoModel recurrences (beside the pitched applier and the StyleEncoder)
 constexpr int kBranchLeaf = 2;       // weight-gradient GEMMs and bias column sums of the backward pass: nothing downstream reads them
 struct StreamSet {
     cudaStream_t s[kSideStreams];

@@ -144,16 +144,19 @@ static LossBufs run_losses(Launcher &L, Arena &ar, int N, int U, long long cells
     if (L.dry) return b;
     L.fill((float *)b.sums_p, (long long)N * kLossSums * 2, 0.f);
     if (U) L.fill((float *)b.sums_u, (long long)N * kLossSums * 2, 0.f);
+    if (U) {                                         // the unpitched sums on branch 0, beside the pitched ones
+        L.wait(0, -1); L.on(0);
+        LossSumsArgs a{pred_u, tgt_u, cells_u, b.sums_u};
+        dim3 g((unsigned)std::max<long long>(1, std::min<long long>((cells_u + 8191) / 8192, 148 * 4)), N);
+        k_loss_sums<2><<<g, 256, 0, L.st>>>(a); L.check();
+        L.on(-1);
+    }
     {
         LossSumsArgs a{pred_p, tgt_p, cells_p, b.sums_p};
         dim3 g((unsigned)std::max<long long>(1, std::min<long long>((cells_p + 8191) / 8192, 148 * 4)), N);
         k_loss_sums<5><<<g, 256, 0, L.st>>>(a); L.check();
     }
-    if (U) {
-        LossSumsArgs a{pred_u, tgt_u, cells_u, b.sums_u};
-        dim3 g((unsigned)std::max<long long>(1, std::min<long long>((cells_u + 8191) / 8192, 148 * 4)), N);
-        k_loss_sums<2><<<g, 256, 0, L.st>>>(a); L.check();
-    }
+    if (U) L.wait(-1, 0);
     LossTreeArgs t{};
     t.sums_p = b.sums_p; t.sums_u = b.sums_u; t.instr = instr; t.instr_target = instr_t; t.mode = mode; t.mode_target = mode_t;
     t.bpm = bpm; t.bpm_target = bpm_t; t.leaves = leaves; t.coef_p = b.coef_p; t.coef_u = b.coef_u;
@@ -220,6 +223,17 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
         head(lb.d_instr, 41, sim_si_w, sim_si_b, 8, c.sim_si, sim_ri_w, sim_ri_b, 10, c.sim_ri, sim_i_w, sim_i_b);
         head(lb.d_mode, 2, sim_sm_w, sim_sm_b, 2, c.sim_sm, sim_rm_w, sim_rm_b, 2, c.sim_rm, sim_m_w, sim_m_b);
         head(lb.d_bpm_pre, 1, sim_sb_w, sim_sb_b, 2, c.sim_sb, sim_rb_w, sim_rb_b, 2, c.sim_rb, sim_b_w, sim_b_b);
+    }
+    // the two SongInfoModel recurrences continue from the heads on a branch of their own (two serial kernels of n_bars steps);
+    // their gradient w.r.t. the rhythm goes to a buffer of its own and is added where the rhythm combine needs it
+    float *d_rhythm_sim = w.A(Rbf * 32);
+    L.wait(kBranchSim, 0); L.on(kBranchSim);
+    {
+        float *d_h2 = w.Z(Nb * 8), *d_last1 = w.A(Nb * 9), *d_h1 = w.Z(Nb * T * 9);
+        L.put_last(d_rf, d_h2, N, B, 8);
+        w.lstm_bwd(c.sim_l2, d_h2, 8, 0, 0, c.sim_last1, sim_br_wih, sim_br_whh, sim_br_bih, sim_br_bhh, d_last1, 0);
+        L.put_last(d_last1, d_h1, Nb, T, 9);
+        w.lstm_bwd(c.sim_l1, d_h1, 9, 0, 0, c.rhythm, sim_bl_wih, sim_bl_whh, sim_bl_bih, sim_bl_bhh, d_rhythm_sim, 0);
     }
     L.on(-1);
     // ---------------- PitchedStyleApplier (model.py:624-675)
@@ -328,14 +342,9 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
         w.combine_bwd(c.bars_pair, 2 * Mb, Mb, 2, Mb, c.bars_ss, c.bars_c, d_bars, d_bp, 0);
     }
     L.on(-1);
-    {
-        float *d_h2 = w.Z(Nb * 8), *d_last1 = w.A(Nb * 9), *d_h1 = w.Z(Nb * T * 9);
-        L.put_last(d_rf, d_h2, N, B, 8);
-        w.lstm_bwd(c.sim_l2, d_h2, 8, 0, 0, c.sim_last1, sim_br_wih, sim_br_whh, sim_br_bih, sim_br_bhh, d_last1, 0);
-        L.put_last(d_last1, d_h1, Nb, T, 9);
-        w.lstm_bwd(c.sim_l1, d_h1, 9, 0, 0, c.rhythm, sim_bl_wih, sim_bl_whh, sim_bl_bih, sim_bl_bhh, d_rhythm, 1);
-    }
     // ---------------- combine(pitched, unpitched) of the rhythm (model.py:767)
+    L.wait(-1, kBranchSim);
+    L.axpy(d_rhythm, d_rhythm_sim, Rbf * 32);
     float *d_pre_out, *d_ure_out = nullptr;
     if (U) {
         const long long Mr = (long long)B * T * 320;

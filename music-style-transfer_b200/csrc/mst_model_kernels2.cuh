@@ -342,17 +342,27 @@ k_lstm_bwd_r64(LstmJobs jobs) {
     for (int s = blockIdx.x; s < a.S; s += gridDim.x) {
         if (j < H) { dh_s[j] = 0.f; dc_s[j] = 0.f; }
         __syncthreads();
-        for (int step = a.T - 1; step >= 0; step--) {
+        // the saved tensors of a step (gates, cell, previous cell, upstream gradient) do not depend on the recurrence: they are
+        // loaded one step ahead, during the matrix-vector product, so their L2 latency is off the per-step critical path
+        float n_gi = 0.f, n_gf = 0.f, n_gg = 0.f, n_go = 0.f, n_c = 0.f, n_cprev = 0.f, n_dout = 0.f;
+        auto fetch = [&](int step) {
             const int t = a.reverse ? a.T - 1 - step : step;
             const int t_prev = a.reverse ? t + 1 : t - 1;
+            const long long row = (long long)s * a.T + t;
+            const float *gs = a.gates + row * H4;
+            n_gi = gs[j]; n_gf = gs[H + j]; n_gg = gs[2 * H + j]; n_go = gs[3 * H + j];
+            n_c = a.cells[row * H + j];
+            n_cprev = step > 0 ? a.cells[((long long)s * a.T + t_prev) * H + j] : 0.f;
+            n_dout = a.dout ? a.dout[row * a.out_ld + a.out_off + j] : 0.f;
+        };
+        if (j < H && a.T > 0) fetch(a.T - 1);
+        for (int step = a.T - 1; step >= 0; step--) {
+            const int t = a.reverse ? a.T - 1 - step : step;
             if (j < H) {
                 const long long row = (long long)s * a.T + t;
-                const float *gs = a.gates + row * H4;
-                const float gi = gs[j], gf = gs[H + j], gg = gs[2 * H + j], go = gs[3 * H + j];
-                const float c = a.cells[row * H + j];
-                const float c_prev = step > 0 ? a.cells[((long long)s * a.T + t_prev) * H + j] : 0.f;
+                const float gi = n_gi, gf = n_gf, gg = n_gg, go = n_go, c = n_c, c_prev = n_cprev;
                 const float tc = tanhf(c);
-                const float dh = dh_s[j] + (a.dout ? a.dout[row * a.out_ld + a.out_off + j] : 0.f);
+                const float dh = dh_s[j] + n_dout;
                 const float dc = dc_s[j] + dh * go * (1.f - tc * tc);
                 const float d_i = dc * gg * gi * (1.f - gi);
                 const float d_f = dc * c_prev * gf * (1.f - gf);
@@ -364,6 +374,7 @@ k_lstm_bwd_r64(LstmJobs jobs) {
                 dg_s[j] = d_i; dg_s[H + j] = d_f; dg_s[2 * H + j] = d_g; dg_s[3 * H + j] = d_o;
             }
             __syncthreads();
+            if (j < H && step > 0) fetch(step - 1);
             {   // dh_{step-1}[k] = sum_r W_hh[r][k] dgates[r]: a quarter of the rows per thread, partials through shared memory
                 const float *ds = dg_s + part * H;
                 float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
