@@ -752,10 +752,12 @@ void prep_weights_uce(Launcher &L, Ctx &c) {
     prep_lstm(L, c, c.uce_brf, uce_br_whh, uce_br_bih, uce_br_bhh);
     prep_lstm(L, c, c.uce_brr, uce_br_whh_r, uce_br_bih_r, uce_br_bhh_r);
 }
-void prep_weights_lstm(Launcher &L, Ctx &c) {
+void prep_weights_lstm_first(Launcher &L, Ctx &c) {     // what the pitched chain needs at its first recurrences
     prep_lstm(L, c, c.pce_bl, pce_bl_whh, pce_bl_bih, pce_bl_bhh);
     prep_lstm(L, c, c.pce_brf, pce_br_whh, pce_br_bih, pce_br_bhh);
     prep_lstm(L, c, c.pce_brr, pce_br_whh_r, pce_br_bih_r, pce_br_bhh_r);
+}
+void prep_weights_lstm_late(Launcher &L, Ctx &c) {      // StyleEncoder and SongInfoModel recurrences: hundreds of microseconds later
     prep_lstm(L, c, c.se_l, se_lstm_whh, se_lstm_bih, se_lstm_bhh);
     prep_lstm(L, c, c.sim_l1, sim_bl_whh, sim_bl_bih, sim_bl_bhh);
     prep_lstm(L, c, c.sim_l2, sim_br_whh, sim_br_bih, sim_br_bhh);
@@ -824,20 +826,7 @@ void forward_extract(Launcher &L, Ctx &c) {
     LstmArgs bar_jobs[4];
     int n_bar_jobs = 2;
     L.wait(1, -1); L.on(1);
-    prep_weights_lstm(L, c);
-    {   // linears that read only the instrument features / mode / bpm: off the chains that end in the style vector
-        const float *slw = PRM(c, se_lin_w);
-        L.linear(c.F, 51, PRM(c, se_il_w), 51, PRM(c, se_il_b), c.se_a2, 39, NC, 39, 51, 1);
-        L.linear(c.mode, 2, PRM(c, se_ml_w), 2, PRM(c, se_ml_b), c.se_a3, 13, N, 13, 2, 1);
-        L.linear(c.bpm, 1, PRM(c, se_bp_w), 1, PRM(c, se_bp_b), c.se_a4, 7, N, 7, 1, 1);
-        L.linear(c.se_a2, 39, slw + 192, 251, nullptr, c.se_z[1], 256, NC, 256, 39, 0);
-        L.linear(c.se_a3, 13, slw + 231, 251, nullptr, c.se_z[2], 256, N, 256, 13, 0);
-        L.linear(c.se_a4, 7, slw + 244, 251, nullptr, c.se_z[3], 256, N, 256, 7, 0);
-        if (c.fused) {
-            L.linear(c.F, 51, PRM(c, psa_il_w), 51, PRM(c, psa_il_b), c.psa_i12, 12, NC, 12, 51, 1);
-            L.linear(c.psa_i12, 12, PRM(c, psa_oct_w) + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
-        }
-    }
+    prep_weights_lstm_first(L, c);
     if (c.U) {
         L.wait(0, -1); L.on(0);
         prep_weights_uce(L, c);
@@ -872,7 +861,25 @@ void forward_extract(Launcher &L, Ctx &c) {
         L.linear(c.pce_conv, 456, c.wpcelin_p, 514, nullptr, c.pce_zc, 64, (int)Rb, 64, 456, 0);
     }
     bcast_fwd(L, Dims5{N, C, B, T, 1}, 64, PRM(c, pce_lin_b), c.pce_x, 1, {{c.pce_zc, M_N | M_C | M_B | M_T}, {c.pce_zi, M_N | M_C}});
-    L.wait(-1, 1);                                   // LSTM weights ready
+    L.wait(-1, 1);                                   // LSTM weights of the channel encoder ready
+    // queued on branch 1 only now (host order), so that the wait above does not cover it: the weights of the later recurrences
+    // and the linears that read only instrument features / mode / bpm; the caller's stream takes them in front of the StyleEncoder
+    L.on(1);
+    prep_weights_lstm_late(L, c);
+    {   // linears that read only the instrument features / mode / bpm: off the chains that end in the style vector
+        const float *slw = PRM(c, se_lin_w);
+        L.linear(c.F, 51, PRM(c, se_il_w), 51, PRM(c, se_il_b), c.se_a2, 39, NC, 39, 51, 1);
+        L.linear(c.mode, 2, PRM(c, se_ml_w), 2, PRM(c, se_ml_b), c.se_a3, 13, N, 13, 2, 1);
+        L.linear(c.bpm, 1, PRM(c, se_bp_w), 1, PRM(c, se_bp_b), c.se_a4, 7, N, 7, 1, 1);
+        L.linear(c.se_a2, 39, slw + 192, 251, nullptr, c.se_z[1], 256, NC, 256, 39, 0);
+        L.linear(c.se_a3, 13, slw + 231, 251, nullptr, c.se_z[2], 256, N, 256, 13, 0);
+        L.linear(c.se_a4, 7, slw + 244, 251, nullptr, c.se_z[3], 256, N, 256, 7, 0);
+        if (c.fused) {
+            L.linear(c.F, 51, PRM(c, psa_il_w), 51, PRM(c, psa_il_b), c.psa_i12, 12, NC, 12, 51, 1);
+            L.linear(c.psa_i12, 12, PRM(c, psa_oct_w) + 76, 88, nullptr, c.psa_zi, 450, NC, 450, 12, 0);
+        }
+    }
+    L.on(-1);
     lstm_forward(L, c, c.pce_bl, c.pce_x, pce_bl_wih, c.pce_beats, 64, 0, 0);
     L.take_last(c.pce_beats, c.pce_last, (long long)NC * B, T, 64);
     { CombineArgs a{}; a.x = c.pce_last; a.n_stride = (long long)C * B * 64; a.k_stride = (long long)B * 64; a.N = N; a.K = C; a.M = (long long)B * 64;
@@ -885,6 +892,7 @@ void forward_extract(Launcher &L, Ctx &c) {
     // From here three independent branches: 0 = both rhythm encoders and their combine (then the SongInfoModel recurrences,
     // forward_song_info), 1 = MelodyEncoder, caller's stream = combine of the bars + StyleEncoder (its 192-wide recurrence
     // over the bars is the longest serial kernel of the forward pass).
+    L.wait(-1, 1);                                   // the late weights and static linears (queued long ago)
     L.wait(0, -1); L.wait(1, -1);
     L.on(0);
     // ---------------- PitchedRhythmEncoder (model.py:346-381)

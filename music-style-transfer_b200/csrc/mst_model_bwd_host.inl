@@ -25,6 +25,7 @@ struct Bwd {
     // weight gradients / bias column sums straight into the flat gradient buffer: leaf work, off the dX chain (Launcher::leaf).
     // leaf_dw = false where another kernel of the caller's stream accumulates into the same parameter.
     bool leaf_dw = true;
+    bool in_leaf_term = false;    // inside branch_bwd's leaf re-entry (see there)
     void dw(const float *dY, long long ldy, const float *X, long long ldx, float *gW, long long ldw, int M, int Nout, int K) {
         if (leaf_dw) L.leaf([&] { L.linear_dw(dY, ldy, X, ldx, gW, ldw, M, Nout, K); });
         else L.linear_dw(dY, ldy, X, ldx, gW, ldw, M, Nout, K);
@@ -90,6 +91,14 @@ struct Bwd {
     // dZ (rows x Nout) is the gradient w.r.t. z_s at the source's own row space.
     void branch_bwd(const float *dZ, int rows, int Nout, ParamId W, int col_off, int ldw, const float *a_s, int K,
                     const float *X, long long ldx, int Kin, ParamId w2, ParamId b2, float *dX, long long lddx, int acc_dx) {
+        if (!dX && leaf_dw && !in_leaf_term) {
+            // a term whose input needs no gradient (instrument features, mode, bpm, the grids): nothing downstream reads what
+            // it computes, so all of it is leaf work (Launcher::leaf), off the chain of the caller's branch
+            in_leaf_term = true;
+            L.leaf([&] { branch_bwd(dZ, rows, Nout, W, col_off, ldw, a_s, K, X, ldx, Kin, w2, b2, nullptr, 0, 0); });
+            in_leaf_term = false;
+            return;
+        }
         float *d_a = A((long long)rows * K);
         dw(dZ, Nout, a_s, K, GRD(c, W) + col_off, ldw, rows, Nout, K);
         L.linear_dx(dZ, Nout, PRM(c, W) + col_off, ldw, d_a, K, rows, Nout, K, 0);

@@ -194,3 +194,19 @@ def test_files_read_batch_reads_files_as_they_are(tmp_path):
     with pytest.raises(lib.MstError) as e:
         lib.files_read_batch(paths, np.zeros(64, dtype=np.uint8))
     assert e.value.needed == total
+
+
+@pytest.mark.timeout(120)
+def test_model_workspace_plan_runs_without_a_gpu():
+    """mst_model_workspace_bytes walks the whole forward + backward host code in planning mode (no launches): it must
+    terminate and grow with the batch - this is the cheapest guard against a broken schedule in the host code."""
+    import ctypes
+    from mst_native import model as mm
+    L = mm._L()
+    sizes = {}
+    for n, c, b, u in ((1, 4, 200, 1), (2, 4, 200, 1), (2, 3, 6, 0), (1, 8, 800, 1)):
+        for training in (0, 1):
+            s = mm.ModelShape(n, c, b, 4, u, 0)
+            sizes[(n, c, b, u, training)] = int(L.mst_model_workspace_bytes(ctypes.byref(s), training))
+            assert sizes[(n, c, b, u, training)] > 0
+    assert sizes[(2, 4, 200, 1, 1)] > sizes[(1, 4, 200, 1, 1)] > sizes[(1, 4, 200, 1, 0)]
