@@ -303,7 +303,8 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
             a.dmelody = d_melody; a.dsum = dsum; a.stats = stats; a.dod = dod;
             a.gWc = GRD(c, me_ch_w); a.gbc = GRD(c, me_ch_b); a.gWl = GRD(c, me_lin_w); a.gbl = GRD(c, me_lin_b);
             k_me_bwd_stats2<<<(int)std::min<long long>(((long long)N * B * T + 7) / 8, 148 * 8), 256, 0, L.st>>>(a); L.check();
-            k_me_bwd2<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 4), 256, 0, L.st>>>(a); L.check();
+            // one CTA per SM at most (207 registers: one resident CTA anyway): every warp flushes its 80 register accumulators once
+            k_me_bwd2<<<(int)std::min<long long>((Rb + 7) / 8, 148), 256, 0, L.st>>>(a); L.check();
             k_me_bwd_cells<<<(int)std::min<long long>((Rb + 7) / 8, 148 * 2), 256, 0, L.st>>>(a); L.check();
         }
         const Dims5 d{N, C, B, T, 1};
@@ -364,8 +365,11 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
     } else {
         d_pre_out = d_rhythm;
     }
+    L.wait(-1, 1);                                   // MelodyEncoder's contributions to d_pce_beats / d_pce_bars are in
     if (U) {
-        // ---------------- UnpitchedRhythmEncoder (model.py:418-443)
+        // ---------------- UnpitchedRhythmEncoder (model.py:418-443), on branch 1 (free again) beside the pitched one: it adds
+        // into d_uce_beats / d_uce_bars only, which nothing else touches before the join in front of the bars' unpack below
+        L.wait(1, -1); L.on(1);
         {
             const Dims5 d{N, 1, B, T, 10};
             float *d_x = w.A(Rbf * 32);
@@ -381,8 +385,8 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
             w.branch_bwd(d_x, (int)Rbf, 32, ure_lin_w, 88, 109, c.ure_a3, 16, c.Ug, 94, 94, ure_ch_w, ure_ch_b, nullptr, 0, 0);
             w.branch_bwd(dz3, N, 32, ure_lin_w, 104, 109, c.ure_a4, 5, c.bpm, 1, 1, ure_bp_w, ure_bp_b, nullptr, 0, 0);
         }
+        L.on(-1);
     }
-    L.wait(-1, 1);                                   // MelodyEncoder's contributions to d_pce_beats / d_pce_bars are in
     // ---------------- PitchedRhythmEncoder (model.py:346-381)
     {
         const Dims5 d{N, C, B, T, 10};
@@ -415,6 +419,7 @@ static void backward_impl(Launcher &L, Ctx &c, Arena &ar, Arena &zar, const Trai
     }
     // ---------------- join branch 0: the StyleEncoder's gradient w.r.t. the bars reaches the channel encoders (model.py:766)
     L.wait(-1, 0);
+    if (U) L.wait(-1, 1);                            // the unpitched rhythm encoder's backward
     if (U) {
         if (!L.dry) { k_pair_unpack_add<<<grid_for(Nb * 128), 256, 0, L.st>>>(d_bp, d_pce_bars, d_uce_bars, N, (long long)B * 128); L.check(); }
     } else {
