@@ -195,3 +195,45 @@ def test_raw_bytes_encode_matches_event_encode(torch):
             assert grid_digest(lib, infos[i], arena) == grid_digest(lib, infos_ref[i], arena_ref), i
             n_ok += 1
     assert n_ok >= 15
+
+
+def test_event_pipeline_wire_formats_agree(torch, tmp_path):
+    """The product pipeline (mst_native.pipeline.EventPipeline, behind style.data.iter_inputs) yields the same song infos and
+    bit-identical grids whether the files are parsed on the device (wire='smf', the default) or on the host (wire='events');
+    an unreadable path, an empty file and a truncated file are reported as load failures by both."""
+    from mst_native import abi, lib
+    from mst_native.pipeline import EventPipeline
+    blobs = bundled_blobs()[:6] + golden_event_blobs()[34:44]
+    blobs.insert(2, b'')
+    blobs.insert(5, blobs[0][:1000])
+    paths = []
+    for i, b in enumerate(blobs):
+        p = tmp_path / f'song{i:02d}.mid'
+        p.write_bytes(b)
+        paths.append(str(p))
+    paths.insert(9, str(tmp_path / 'missing.mid'))
+    filt = abi.make_filter(range(128), 0, 0)
+    seen = {}
+    for wire in ('smf', 'events'):
+        pipe = EventPipeline(filt, batch_files=5, slots=3, arena_floats=64 << 20, wire=wire)
+        rows = []
+        for path, r, arena in pipe.run(paths):
+            rec = {'path': path, 'status': int(r['status'])}
+            if rec['status'] == abi.SONG_OK:
+                rec['info'] = {k: np.array(r[k]).copy() for k in abi.SONG_INFO_DTYPE.names if k not in ('pitched_offset', 'unpitched_offset')}
+                rec['digest'] = grid_digest(lib, r, arena)
+            rows.append(rec)
+        pipe.close()
+        seen[wire] = rows
+        assert [r['path'] for r in rows] == paths
+    failed = [r['path'] for r in seen['smf'] if r['status'] == abi.SONG_LOAD_FAILED]
+    assert sorted(os.path.basename(p) for p in failed) == ['missing.mid', 'song02.mid', 'song05.mid']
+    n_ok = 0
+    for a, b in zip(seen['smf'], seen['events']):
+        assert a['status'] == b['status'], (a['path'], a['status'], b['status'])
+        if a['status'] == abi.SONG_OK:
+            for k in a['info']:
+                assert np.array_equal(a['info'][k], b['info'][k]), (a['path'], k)
+            assert a['digest'] == b['digest'], a['path']
+            n_ok += 1
+    assert n_ok >= 10
