@@ -10,9 +10,15 @@ one pass of the whole encode pipeline (libmst_b200.so, mst_encode_batch_device) 
 songs that is larger than L2, and every step rewrites a grid arena that is far larger than L2.
 
 Prints ONE JSON line (see the task contract): value = song-bars/s over all ranks, `roofline` for
-the dominant kernel (k_fill_flat, HBM-write-bound), `e2e` through the host-buffer C-ABI entry point, and
+the dominant kernel (k_fill_flat, HBM-write-bound), `e2e` through the host-buffer C-ABI entry point
+(mst_encode_batch_smf_async: the batch's raw .mid bytes from page-locked memory, parsed on the device;
+`e2e.packed_events` = the same loop on 8-byte event records parsed on the host beforehand), and
 `cpu_baseline` (the C oracle port on the host cores, rank 0, N=1 only).
-`--impl reference` times the CPU implementation (oracle port, all host threads) on the same config.
+Further keys on the same line: `decode`, `files` (files on disk through the product EventPipeline, both wire
+formats), `training` (configs[3], bf16 dense mode) / `training_fp32` / `training_long` / `training_n1` (the
+reference's own batch size, CUDA graph + drop-in call pattern), each with its own `e2e`, and LAST `summary`.
+`--impl reference` times the CPU implementation on the same config: the C oracle port on all host threads for
+the codec, the unmodified reference model from baseline/_ref for the training step.
 """
 import argparse
 import ctypes
