@@ -182,10 +182,10 @@ __device__ __forceinline__ void put(MstEvent *out, uint32_t &count, uint64_t tic
 // returns 0 when the track ends exactly at its chunk end, else a LoadFail code of mst_smf.cpp
 constexpr int kSmfBuf = 256;     // bytes of a track held in shared memory per lane
 
-// `buf`: this lane's first 16-byte chunk of the warp's staging area, chunk k of the lane at buf[k * 32] (lane-interleaved)
+// `buf`: this lane's column of the warp's staging area, 4-byte word j of the lane at buf[j * 32] (lane-interleaved)
 template <int EMIT>
-__device__ int parse_track(const uint8_t *file, uint32_t n, const TrackRec tr, MstEvent *out, uint32_t *n_out, uint4 *buf) {
-    uintptr_t buf_lo = 1;            // absolute address of the buffered bytes (16-byte aligned once filled)
+__device__ int parse_track(const uint8_t *file, uint32_t n, const TrackRec tr, MstEvent *out, uint32_t *n_out, uint32_t *buf) {
+    uint32_t buf_rel = tr.start + 0x40000000u;   // file-relative position of the first buffered byte, modulo 2^32 (nothing buffered yet)
     Rd r{file, n, tr.start, false};
     const uint32_t start = tr.start, size = tr.size, t = tr.index;
     int last_status = -1;
@@ -194,44 +194,46 @@ __device__ int parse_track(const uint8_t *file, uint32_t n, const TrackRec tr, M
     while (r.pos - start != size) {
         if (r.pos - start > size) return 1;                          // ran past the chunk end: the sequential parser reads on to EOF
         // ---- fast path: a channel voice message (99 % of a file) whose delta time takes at most four bytes lies inside one
-        // 8-byte window: two aligned 8-byte loads, then shifts and selects only - no per-byte load latency, and the 32 tracks
+        // 8-byte window: three 4-byte words from shared memory, then funnel shifts and selects only - no per-byte load latency, and the 32 tracks
         // of a warp run the same instructions whatever their message types.  Everything else (meta, sysex, system messages,
         // long delta times, the last 7 bytes of a file, malformed input) takes the byte-wise path below, which starts over at
         // the same position; the two paths emit the same records (the byte-wise one is mst_smf.cpp's loop).
         if (r.pos + 8 <= n) {
-            // the window comes from the lane's 256-byte buffer in shared memory, refilled by sixteen independent 16-byte loads:
-            // one global-memory latency per ~60 messages instead of one per message (next to a zero fill that saturates the
-            // memory system, a dependent global load costs microseconds)
-            const uintptr_t addr = reinterpret_cast<uintptr_t>(file + r.pos);
-            if (addr < buf_lo || addr + 8 > buf_lo + kSmfBuf) {
-                buf_lo = addr & ~(uintptr_t)15;
-                const uint4 *g = reinterpret_cast<const uint4 *>(buf_lo);
+            // the window comes from the lane's 256-byte buffer in shared memory (4-byte words, lane-interleaved: conflict-free),
+            // refilled by sixteen independent 16-byte loads: one global-memory latency per ~60 messages instead of one per
+            // message (next to a zero fill that saturates the memory system, a dependent global load costs microseconds)
+            uint32_t off = r.pos - buf_rel;                          // (wraps to a huge value when pos lies in front of the buffer)
+            if (off > (uint32_t)(kSmfBuf - 8)) {
+                const uintptr_t addr = reinterpret_cast<uintptr_t>(file + r.pos);
+                const uint4 *g = reinterpret_cast<const uint4 *>(addr & ~(uintptr_t)15);
+                off = (uint32_t)(addr & 15);
+                buf_rel = r.pos - off;
                 uint4 v[kSmfBuf / 16];
 #pragma unroll
                 for (int k = 0; k < kSmfBuf / 16; k++) v[k] = g[k];
 #pragma unroll
-                for (int k = 0; k < kSmfBuf / 16; k++) buf[k * 32] = v[k];
+                for (int k = 0; k < kSmfBuf / 16; k++) {
+                    buf[(4 * k + 0) * 32] = v[k].x; buf[(4 * k + 1) * 32] = v[k].y;
+                    buf[(4 * k + 2) * 32] = v[k].z; buf[(4 * k + 3) * 32] = v[k].w;
+                }
             }
-            const uint32_t off = (uint32_t)(addr - buf_lo), wi = off >> 3, sh = (off & 7) * 8;
-            const uint64_t *b64 = reinterpret_cast<const uint64_t *>(buf);
-            const uint64_t wa = b64[(wi >> 1) * 64 + (wi & 1)];
-            const uint64_t wb = sh ? b64[((wi + 1) >> 1) * 64 + ((wi + 1) & 1)] : 0ull;
-            uint64_t w = sh ? (wa >> sh) | (wb << (64 - sh)) : wa;  // byte i of the window = file[pos + i]
-            const uint32_t lo = (uint32_t)w;
+            const uint32_t wj = off >> 2, sh = (off & 3) * 8;
+            const uint32_t w0 = buf[wj * 32], w1 = buf[(wj + 1) * 32], w2 = buf[(wj + 2) * 32];
+            const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);   // bytes 0..3 and 4..7 of the window
             const uint32_t term = ~lo & 0x80808080u;                 // bit 7 of the first delta byte that ends the varint
             if (term != 0) {
                 const uint32_t nd = (uint32_t)__ffs((int)term) >> 3;    // bytes of the delta time: 1..4
                 const uint32_t b0 = lo & 0x7F, b1 = (lo >> 8) & 0x7F, b2 = (lo >> 16) & 0x7F, b3 = (lo >> 24) & 0x7F;
                 const uint32_t v1 = b0, v2 = (v1 << 7) | b1, v3 = (v2 << 7) | b2, v4 = (v3 << 7) | b3;
                 const uint32_t delta = nd == 1 ? v1 : (nd == 2 ? v2 : (nd == 3 ? v3 : v4));
-                w >>= 8 * nd;
-                const uint32_t sb = (uint32_t)w & 0xFF;
+                uint32_t w = nd == 4 ? hi : __funnelshift_r(lo, hi, 8 * nd);     // the four bytes behind the delta time
+                const uint32_t sb = w & 0xFF;
                 const bool running = sb < 0x80;
                 const int status = running ? last_status : (int)sb;
                 if (status >= 0x80 && status < 0xF0) {               // (running status without a status, or >= 0xF0: byte-wise path)
                     if (!running) w >>= 8;
                     const uint32_t need = (status & 0xE0) == 0xC0 ? 1u : 2u;
-                    const uint32_t d0 = (uint32_t)w & 0xFF, d1 = need == 2 ? ((uint32_t)(w >> 8) & 0xFF) : 0u;
+                    const uint32_t d0 = w & 0xFF, d1 = need == 2 ? ((w >> 8) & 0xFF) : 0u;
                     if (d0 > 127 || d1 > 127) return 5;
                     tick = ((uint64_t)delta > (1ull << 62) - tick) ? (1ull << 62) : tick + delta;
                     last_status = status;
@@ -344,7 +346,7 @@ __device__ __forceinline__ uint64_t staging_index(const MstFileIn &fi, const Tra
 
 __global__ void __launch_bounds__(32)
 k_smf_parse(SmfWorkspace ws) {
-    __shared__ uint4 s_buf[kSmfBuf / 16 * 32];
+    __shared__ uint32_t s_buf[(kSmfBuf / 4 + 2) * 32];              // (+2 words: the window reads one word past its last byte)
     const uint32_t n_tracks = min((uint64_t)ws.totals[0], ws.max_tracks);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_tracks; i += gridDim.x * blockDim.x) {
         const TrackRec tr = ws.tracks[i];
