@@ -374,7 +374,7 @@ def run_files(args, torch, lib, abi, synth, filt):
             with open(paths[-1], 'wb') as f:
                 f.write(data)
             n_bytes += len(data)
-        batch = min(64, n_files)
+        batch = min(128, n_files)
         probe = lib.DeviceBatch(*lib.make_songs(per[:batch], [int(t) for t in songs['ticks_per_beat'][:batch]]))
         probe.encode(filt, None)
         arena_floats = int(1.1 * sum(lib.grid_floats(r) for r in probe.infos()))
@@ -766,7 +766,7 @@ def main():
     ap.add_argument('--e2e-slots', type=int, default=3, help='host-path slots (stream + workspace + arena) in rotation')
     ap.add_argument('--long-batch', type=int, default=8, help='long-sequence (C=8, B=800) samples per step per GPU')
     ap.add_argument('--no-long', action='store_true', help='skip the long-sequence training leg')
-    ap.add_argument('--file-songs', type=int, default=256, help='songs written as .mid files for the file-fed encode leg (0: skip)')
+    ap.add_argument('--file-songs', type=int, default=1024, help='songs written as .mid files for the file-fed encode leg (0: skip)')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     args.pool = max(args.pool, args.batch)
