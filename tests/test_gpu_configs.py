@@ -212,3 +212,30 @@ def test_config1_transfer_style_matches_reference(torch, tmp_path, folder_index)
     os.makedirs(OUT, exist_ok=True)
     with open(os.path.join(OUT, f'config1_parity_{folder_index}.txt'), 'w') as f:
         f.write('\n'.join(report) + '\n')
+
+
+def test_config0_through_the_product_training_loop(torch, tmp_path):
+    """The same epoch through mst_native.trainer.train_on_files (files -> EventPipeline with the device-side SMF parser ->
+    ragged batch -> fused train step + Adam): the totals of both iterations and the parameters after the Adam step match the
+    unmodified reference's (configs[0] golden) like the drop-in loop above does."""
+    from mst_native import model as mm, synth, trainer as tr
+    from style import data as d
+    G = np.load(os.path.join(gu.GOLDEN_DIR, 'config0.npz'))
+    files = sorted(write_bundled(tmp_path, 'drums/'))
+    names = [str(n) for n in G['loss_names']]
+    t = tr.Trainer(synth.make_state_dict(108), precision='fp32')
+    seen = []
+
+    def on_step(step, batch, leaves, lr):
+        for i, s in enumerate(batch):
+            seen.append((os.path.basename(s['path']), float(leaves[i][mm.LOSS_LEAVES['total']])))
+    steps = tr.train_on_files(t, files, d.included_instruments, songs_per_step=2, max_steps=1, on_step=on_step)
+    assert steps == 1 and [n for n, _ in seen] == [str(x) for x in G['files']]
+    for it, (_, total) in enumerate(seen):
+        want = float(G['losses'][it, names.index('total')])
+        assert abs(total - want) < 2e-5 * abs(want), (it, total, want)
+    sd = t.state_dict(synth.make_state_dict(108))
+    pn = [str(n) for n in G['param_names']]
+    norms = np.array([float(sd[k].double().norm()) for k in pn])
+    rel = np.abs(norms - G['param_norms']) / np.maximum(G['param_norms'], 1e-9)
+    assert rel.max() < 1e-4, (pn[int(rel.argmax())], rel.max())
