@@ -210,3 +210,32 @@ def test_model_workspace_plan_runs_without_a_gpu():
             sizes[(n, c, b, u, training)] = int(L.mst_model_workspace_bytes(ctypes.byref(s), training))
             assert sizes[(n, c, b, u, training)] > 0
     assert sizes[(2, 4, 200, 1, 1)] > sizes[(1, 4, 200, 1, 1)] > sizes[(1, 4, 200, 1, 0)]
+
+
+def test_raw_bytes_entry_points_fail_loudly_without_gpu(L):
+    """The device-side parser path has no CPU fallback either: without a GPU both entry points return MST_E_NO_DEVICE, and
+    their workspace queries (pure host arithmetic) grow with the byte count."""
+    import ctypes
+    import numpy as np
+    from mst_native import abi, lib
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip('a GPU is present')
+    buf, files = lib.concat_files([b'MThd' + bytes(10), b''])
+    infos = np.zeros(2, dtype=abi.SONG_INFO_DTYPE)
+    filt = abi.make_filter(None, 0, 0).reshape(1)
+    dummy = np.zeros(64, dtype=np.uint8)
+    rc = L.mst_encode_batch_smf_async(buf.ctypes.data, len(buf), files.ctypes.data, 2, filt.ctypes.data, infos.ctypes.data,
+                                      None, 0, dummy.ctypes.data, dummy.size, None)
+    assert rc == -4 and b'no CPU fallback' in L.mst_last_error()
+    events = np.zeros(16, dtype=abi.EVENT_DTYPE)
+    songs = np.zeros(2, dtype=abi.SONG_IN_DTYPE)
+    status = np.zeros(2, dtype=np.int32)
+    total = ctypes.c_uint64(0)
+    rc = L.mst_smf_parse_batch_device(buf.ctypes.data, len(buf), files.ctypes.data, 2, events.ctypes.data, 16, songs.ctypes.data,
+                                      status.ctypes.data, ctypes.byref(total), dummy.ctypes.data, dummy.size, None)
+    assert rc == -4
+    a = L.mst_encode_smf_workspace_bytes(1 << 20, 8, 1 << 20)
+    b = L.mst_encode_smf_workspace_bytes(1 << 24, 8, 1 << 20)
+    assert 0 < a < b
+    assert 0 < L.mst_smf_parse_device_workspace_bytes(1 << 20, 8) < L.mst_smf_parse_device_workspace_bytes(1 << 24, 8)
