@@ -8,8 +8,8 @@
 // Why: the host-buffer path is bound by the host -> device copy once several ranks share one host (8 GPUs: 13.6 - 18.3 GB/s
 // per rank while the kernels run, profiles/r2_h2d_8gpu.txt).  A 16-byte MstEvent is 4 - 5x the bytes the file spends on the
 // event (delta-time varint + running status), so the file itself is the compact wire format, and the parse - which bounded
-// the file-fed path on the host (71 us per file per core) - becomes a few hundred microseconds of latency-bound device work
-// per batch that hides behind the zero fill of another slot.
+// the file-fed path on the host (71 us per file per core) - becomes about a millisecond of latency-bound device work
+// per 512-file batch, most of which overlaps the zero fill of another slot (DESIGN.md section 4 has the measurements).
 //
 // Work decomposition.  A file is a header chunk and n_tracks track chunks; a track chunk can only be parsed sequentially
 // (variable-length delta times, running status), but tracks are independent once their byte ranges are known, and those
@@ -138,7 +138,8 @@ k_smf_tracks(SmfWorkspace ws, uint32_t n_files) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// The track parser (mst_smf.cpp:102-196), one thread per track.  EMIT = 0 counts, EMIT = 1 writes.
+// The track parser (mst_smf.cpp:102-196), one thread per track.  EMIT = 1 writes the records; EMIT = 0 only counts
+// them (not instantiated since records go to a staging area in ONE pass, see k_smf_parse).
 // ------------------------------------------------------------------------------------------------
 struct Rd {
     const uint8_t *p;
